@@ -1,0 +1,295 @@
+"""Freeze tests/golden/*.npz from the reference's own Python -- TEST INFRASTRUCTURE.
+
+Run in the build container (needs /root/reference):
+
+    python -m oracle.make_golden
+
+For every fixture the UNMODIFIED reference code (imported by oracle.ref_import,
+with torch_geometric shimmed and the canonical kNN tie order installed) produces
+the value, the restatement in oracle.restate is asserted to reproduce it, and
+only then is it written.  The reference ships no golden vectors of its own
+(SURVEY.md section 4), so these files are what pins parity.
+
+Fixtures
+  wheat.npz            the one dataset the reference ships (csv-data/WHEAT_combined.csv),
+                       bit-packed markers + float64 phenotypes: the INPUT of every WHEAT case
+  wheat_knn.npz        canonical neighbour lists, k = 32 (shorter k are prefixes), whole file and the
+                       479-row training split; cross-checked against sklearn itself
+  wheat_graph.npz      create_graph(load.py:21-81) edge_index / edge_weight for several settings
+  wheat_partition.npz  split_dataset_graph(util.py:48-73) row indices
+  wheat_model.npz      seeded forward / backward of the GCN factories
+  wheat_train.npz      loss trajectories of train_ensemble2 phase 1 (ensemble2.py:39-124)
+  partition_small.npz  naive_partition(util.py:15-45) on small random neighbour streams
+"""
+import contextlib
+import io
+import os
+import re
+import sys
+import tempfile
+
+import numpy as np
+import pandas as pd
+import torch
+
+from . import ref_import, restate
+
+GOLDEN = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+WHEAT_CSV = os.path.join(ref_import.REFERENCE_ROOT, "csv-data", "WHEAT_combined.csv")
+
+
+def wheat_frame():
+    with open(WHEAT_CSV) as fp:
+        ncol = len(fp.readline().split(","))
+    return pd.read_csv(WHEAT_CSV, names=["value"] + [str(i + 1) for i in range(ncol - 1)])   # load.py:182-187
+
+
+def save(name, **arrays):
+    path = os.path.join(GOLDEN, name)
+    np.savez_compressed(path, **arrays)
+    print(f"wrote {path}  ({os.path.getsize(path) / 1024:.0f} KiB)")
+
+
+def check_against_sklearn(X, k, idx, d2):
+    """Canonical lists vs sklearn proper: distances bit-equal; sets equal where no tie straddles rank k."""
+    from sklearn.neighbors import kneighbors_graph
+    g = kneighbors_graph(X, k, mode="distance", include_self=False).tocsr()
+    n = X.shape[0]
+    sk_d = g.data.reshape(n, k)
+    sk_i = g.indices.reshape(n, k)
+    assert np.array_equal(np.sort(sk_d, axis=1), np.sqrt(d2)), "sorted distance vectors differ from sklearn"
+    kk_idx, kk_d2 = restate.canonical_knn(X, min(k + 1, n - 1))
+    tie_free = kk_d2[:, k - 1] != kk_d2[:, -1] if kk_d2.shape[1] > k else np.ones(n, bool)
+    same = np.array([set(a) == set(b) for a, b in zip(sk_i, idx)])
+    assert np.all(same[tie_free]), "neighbour sets differ from sklearn on tie-free rows"
+    return int(tie_free.sum()), int(same.sum())
+
+
+def main():
+    os.makedirs(GOLDEN, exist_ok=True)
+    ref = ref_import.load(canonical_knn=True)
+    df = wheat_frame()
+    N = len(df)
+    X = df.iloc[:, 1:].values
+    y = df["value"].values
+    assert set(np.unique(X)) <= {0.0, 1.0}
+    save("wheat.npz", x_bits=np.packbits(X.astype(np.uint8), axis=1), n=N, p=X.shape[1], y=y)
+
+    sizes = restate.split_sizes(N, 0.8, True, 0.1)
+    assert sizes == (479, 108, 587)
+
+    # ---- kNN ---------------------------------------------------------------------------------
+    idx_all, d2_all = restate.canonical_knn(X, 32)
+    idx_tr, d2_tr = restate.canonical_knn(X[:479], 32)
+    for k in (1, 3, 5, 8, 10, 32):
+        a, b = restate.canonical_knn(X, k)
+        assert np.array_equal(a, idx_all[:, :k]) and np.array_equal(b, d2_all[:, :k])
+        free, same = check_against_sklearn(X, k, a, b)
+        print(f"k={k}: tie-free rows {free}/{N}, rows with sklearn's neighbour set {same}/{N}")
+    # the partition graph includes the phenotype column (util.py:52-53)
+    idx_full, d2_full = restate.canonical_knn(X, 10, extra=y[:, None])
+    save("wheat_knn.npz", idx_all=idx_all.astype(np.int32), d2_all=d2_all.astype(np.int32),
+         idx_train=idx_tr.astype(np.int32), d2_train=d2_tr.astype(np.int32),
+         idx_with_pheno=idx_full.astype(np.int32), d2_with_pheno=d2_full)
+
+    # ---- create_graph: reference vs restatement ----------------------------------------------
+    graphs = {}
+    for rows, tag in ((slice(0, 479), "train"), (slice(479, 587), "test")):
+        for k in (3, 5, 10):
+            for mode in ("distance", "connectivity"):
+                for smoothing in ("laplacian", "none"):
+                    sub = df.iloc[rows].copy()
+                    d = ref.load.create_graph(sub, n_neighbors=k, smoothing=smoothing, use_weights=True,
+                                              mode=mode, algorithm="euclidean")
+                    mine = restate.create_graph(X[rows], y[rows], n_neighbors=k, smoothing=smoothing,
+                                                use_weights=True, mode=mode)
+                    ei, ew = d.edge_index.numpy(), d.edge_weight.numpy()
+                    assert np.array_equal(ei, mine["edge_index"]), (tag, k, mode, smoothing)
+                    assert np.array_equal(ew, mine["edge_weight"]), (tag, k, mode, smoothing, np.abs(ew - mine["edge_weight"]).max())
+                    assert np.array_equal(d.x.numpy(), mine["x"]) and np.array_equal(d.y.numpy(), mine["y"])
+                    key = f"{tag}_k{k}_{mode}_{smoothing}"
+                    graphs[key + "_ei"] = ei.astype(np.int32)
+                    graphs[key + "_ew"] = ew
+    # duplicates: zero distances are dropped by .nonzero() (load.py:64)
+    Xd = X[:60].copy()
+    Xd[7] = Xd[3]
+    Xd[11] = Xd[3]
+    Xd[40] = Xd[41]
+    yd = y[:60]
+    sub = pd.DataFrame(np.column_stack([yd, Xd]), columns=["value"] + [str(i + 1) for i in range(Xd.shape[1])])
+    d = ref.load.create_graph(sub.copy(), n_neighbors=2, smoothing="laplacian", use_weights=True, mode="distance",
+                              algorithm="euclidean")
+    mine = restate.create_graph(Xd, yd, n_neighbors=2, smoothing="laplacian", use_weights=True, mode="distance")
+    assert np.array_equal(d.edge_index.numpy(), mine["edge_index"])
+    assert np.array_equal(d.edge_weight.numpy(), mine["edge_weight"])
+    graphs["dup_rows"] = np.array([3, 7, 11, 40, 41], dtype=np.int32)
+    graphs["dup_k2_distance_laplacian_ei"] = mine["edge_index"].astype(np.int32)
+    graphs["dup_k2_distance_laplacian_ew"] = mine["edge_weight"]
+    save("wheat_graph.npz", **graphs)
+
+    # ---- partition ---------------------------------------------------------------------------
+    parts = {}
+    for k in (3, 5, 10):
+        for batches in (3, 5, 8, 10, sizes):
+            got = ref.util.split_dataset_graph(df, batches, neighbours=k, metric="euclidean",
+                                               partition=ref.util.naive_partition)
+            want = [list(map(int, g.index.values)) for g in got]
+            mine = restate.split_indices_graph(df, batches, neighbours=k)
+            assert [list(map(int, m)) for m in mine] == want, (k, batches)
+            tag = "split" if isinstance(batches, tuple) else f"b{batches}"
+            for i, w in enumerate(want):
+                parts[f"k{k}_{tag}_{i}"] = np.asarray(w, dtype=np.int32)
+    save("wheat_partition.npz", **parts)
+
+    rng = np.random.default_rng(7)
+    small = {}
+    for case in range(40):
+        n = int(rng.integers(3, 30))
+        k = int(rng.integers(1, min(4, n - 1) + 1))
+        nbr = np.stack([rng.choice(np.delete(np.arange(n), i), size=k, replace=False) for i in range(n)])
+        if case % 4 == 0:      # a few nodes that nobody points to, several pointing at node 0
+            nbr[:, 0] = np.where(np.arange(n) == 0, 1, 0)
+        S = restate.neighbour_stream(nbr)
+        edges = [(i, int(c)) for i in range(n) for c in nbr[i]]
+        szs = [int(s) for s in rng.integers(1, max(2, n // 2) + 1, size=int(rng.integers(1, 5)))]
+        trav, want = set(), []
+        for s in szs:
+            got = [int(v) for v in ref.util.naive_partition(edges, s, bidirectional=False, traversed=set(trav))]
+            trav |= set(got)
+            want.append(got)
+        assert restate.partition_linear(S, n, szs) == want, (case, want, restate.partition_linear(S, n, szs))
+        t2, slow = set(), []
+        for s in szs:
+            got = restate.partition_scan(S, n, s, t2)
+            t2 |= set(got)
+            slow.append(got)
+        assert slow == want, (case, slow, want)
+        small[f"c{case}_nbr"] = nbr.astype(np.int32)
+        small[f"c{case}_sizes"] = np.asarray(szs, dtype=np.int32)
+        small[f"c{case}_flat"] = np.asarray([v for b in want for v in b], dtype=np.int32)
+        small[f"c{case}_lens"] = np.asarray([len(b) for b in want], dtype=np.int32)
+    save("partition_small.npz", **small)
+
+    # ---- model forward / backward ------------------------------------------------------------
+    H = 32
+    train_g = restate.create_graph(X[:479], y[:479], n_neighbors=5, smoothing="laplacian", use_weights=True,
+                                   mode="distance")
+    model_out = {}
+    for name in ("create_network_two_no_conv_dropout", "create_network_no_conv_relu_dropout",
+                 "create_network_two_relu", "create_network_no_conv"):
+        for asl in (True, False):
+            if name != "create_network_two_no_conv_dropout" and not asl:
+                continue
+            torch.manual_seed(0)
+            kw = {"internal_size": H}
+            if "dropout" in name:
+                kw["dropout"] = 0.0
+            if name in ("create_network_two_no_conv_dropout", "create_network_two_relu", "create_network_no_conv"):
+                kw["add_self_loops"] = asl
+            m_ref = getattr(ref.networks, name)(X.shape[1], 1, **kw)
+            torch.manual_seed(0)
+            m_mine = restate.make_model(name, X.shape[1], 1, internal_size=H, dropout=0.0, add_self_loops=asl)
+            sd_ref, sd_mine = m_ref.state_dict(), m_mine.state_dict()
+            assert list(sd_ref.keys()) == list(sd_mine.keys()), (list(sd_ref.keys()), list(sd_mine.keys()))
+            for kk in sd_ref:
+                assert torch.equal(sd_ref[kk], sd_mine[kk]), kk
+            args = restate.as_tensors(train_g)
+            yt = torch.as_tensor(train_g["y"])
+            outs = []
+            for m in (m_ref, m_mine):
+                m.train()
+                m.zero_grad()
+                out = m(*args)
+                loss = torch.nn.MSELoss()(out, yt)
+                loss.backward()
+                outs.append((out.detach(), float(loss), {k: p.grad.clone() for k, p in m.named_parameters()}))
+            assert torch.equal(outs[0][0], outs[1][0]) and outs[0][1] == outs[1][1]
+            for kk in outs[0][2]:   # torch-CPU index_add_/gather backward is not run-to-run bit-stable
+                assert torch.allclose(outs[0][2][kk], outs[1][2][kk], rtol=1e-5, atol=1e-7), kk
+            # the tuple call form must give the same result (sequential.py:100-101)
+            assert torch.equal(m_ref(args), outs[0][0])
+            tag = f"{name}_asl{int(asl)}"
+            for kk, v in sd_ref.items():
+                model_out[f"{tag}__w__{kk}"] = v.numpy()
+            model_out[f"{tag}__out"] = outs[0][0].numpy()
+            model_out[f"{tag}__loss"] = np.float64(outs[0][1])
+            for kk, v in outs[0][2].items():
+                model_out[f"{tag}__g__{kk}"] = v.numpy()
+    save("wheat_model.npz", **model_out)
+
+    # ---- training trajectories through the reference's loader + trainer ------------------------
+    cwd = os.getcwd()
+    traj = {}
+    with tempfile.TemporaryDirectory() as tmp:
+        os.chdir(tmp)
+        try:
+            os.makedirs("output")
+            os.makedirs("model")
+            params = dict(num_neighbours=5, smoothing="laplacian", mode="distance", use_validation=True,
+                          split=0.8, use_weights=True, algorithm="euclidean", batches=3,
+                          split_algorithm=ref.util.split_dataset_graph,
+                          split_algorithm_params={"partition": ref.util.naive_partition})
+            with contextlib.redirect_stdout(io.StringIO()):
+                ds = ref.load.load_data(WHEAT_CSV, **params)
+            data = [g for g in ds]
+            assert len(data) == 4
+            EPOCHS = 6
+
+            def creator():
+                return ref.networks.create_network_two_no_conv_dropout(X.shape[1], 1, internal_size=H, dropout=0.0)
+
+            def opt(model):
+                return torch.optim.Adam(model.parameters(), lr=0.0020594745443455593)
+
+            torch.manual_seed(0)
+            buf = io.StringIO()
+            with contextlib.redirect_stdout(buf):
+                res = ref.ensemble2.train_ensemble2(creator, opt, data, epochs=EPOCHS, aggregate_epochs=2,
+                                                    save_loss=False, print_epochs=True)
+            printed = re.findall(r"Batch: (\d+), Epoch: (\d+), Loss: ([-\d.]+), Test Loss: ([-\d.]+)", buf.getvalue())
+            assert len(printed) == 3 * EPOCHS
+
+            # restatement: same seed, same order of model creation
+            part = restate.split_indices_graph(df, 3, neighbours=5)
+            tr, te, va = restate.split_indices_graph(df, sizes, neighbours=5)
+            g_test = restate.create_graph(X[te], y[te], 5, "laplacian", True, True, "distance")
+            g_valid = restate.create_graph(X[va], y[va], 5, "laplacian", True, True, "distance")
+            assert np.array_equal(data[0].test.edge_index.numpy(), g_test["edge_index"])
+            assert np.array_equal(data[-1].edge_index.numpy(), g_valid["edge_index"])
+            torch.manual_seed(0)
+            for b, rows in enumerate(part):
+                g = restate.create_graph(X[rows], y[rows], 5, "laplacian", True, True, "distance")
+                assert np.array_equal(data[b].edge_index.numpy(), g["edge_index"])
+                assert np.array_equal(data[b].edge_weight.numpy(), g["edge_weight"])
+                assert np.array_equal(data[b].y.numpy(), g["y"])
+                m = restate.make_model("create_network_two_no_conv_dropout", X.shape[1], 1, internal_size=H, dropout=0.0)
+                w0 = {k: v.clone().numpy() for k, v in m.state_dict().items()}
+                o = opt(m)
+                tl, vl = [], []
+                for ep in range(EPOCHS):
+                    a, c, out_test = restate.epoch_step(m, o, g, g_test)
+                    tl.append(a)
+                    vl.append(c)
+                    pa, pc = printed[b * EPOCHS + ep][2:]
+                    assert abs(a - float(pa)) < 2e-5 and abs(c - float(pc)) < 2e-5, (b, ep, a, pa, c, pc)
+                assert abs(min(vl) - res["basics"][f"min_loss_{b}"]) < 1e-6 * abs(min(vl))
+                traj[f"b{b}_rows"] = np.asarray(rows, dtype=np.int32)
+                traj[f"b{b}_train_loss"] = np.asarray(tl)
+                traj[f"b{b}_test_loss"] = np.asarray(vl)
+                traj[f"b{b}_pred_test"] = out_test.numpy()
+                for kk, v in w0.items():
+                    traj[f"b{b}__w0__{kk}"] = v
+                traj[f"b{b}_pred_train"] = m.eval()(*restate.as_tensors(g)).detach().numpy()
+            traj["test_rows"] = np.asarray(te, dtype=np.int32)
+            traj["valid_rows"] = np.asarray(va, dtype=np.int32)
+            traj["lr"] = np.float64(0.0020594745443455593)
+            traj["epochs"] = np.int64(EPOCHS)
+            traj["hidden"] = np.int64(H)
+        finally:
+            os.chdir(cwd)
+    save("wheat_train.npz", **traj)
+    print("golden fixtures regenerated; restatement == reference on every case")
+
+
+if __name__ == "__main__":
+    sys.exit(main())
