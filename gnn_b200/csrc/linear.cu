@@ -1,0 +1,201 @@
+// K5: marker projection H = X . W^T and its gradients -- CUDA-core fp32 tiles (precision 0) and the
+// dispatcher to the tcgen05 kernels (precision 1..3, linear_tc.cu).
+//
+// Replaces GCNConv.lin (PyG Linear(bias=False) -> torch.matmul) and its autograd; call sites
+// gnn/networks/networks.py:271-272 and the other GCN factories.
+//
+// The fp32 path is the exact-arithmetic reference point for the tensor-core path and serves the small
+// inner layers (h x h).  One generic 64x64x16 tile kernel covers the three products through strides:
+//   C(m, n) = sum_k A(m, k) * B(k, n),  A(m, k) = A[m * sam + k * sak],  B(k, n) = B[k * sbk + n * sbn]
+// with the unit-stride dimension of each operand chosen at compile time so that global loads coalesce.
+#include "common.cuh"
+
+namespace gnnb {
+
+constexpr int BM = 64, BN = 64, BK = 16;
+
+template <typename AT> __device__ __forceinline__ float to_f32(AT v) { return (float)v; }
+
+// A_KC: A is contiguous along k (else along m).  B_KC: B is contiguous along k (else along n).
+template <typename AT, bool A_KC, bool B_KC>
+__global__ void __launch_bounds__(256)
+gemm_simt_kernel(const AT* __restrict__ A, int64_t sam, int64_t sak, const float* __restrict__ B, int64_t sbk, int64_t sbn,
+                 float* __restrict__ C, int64_t scm, int64_t scn, int64_t M, int64_t N, int64_t K,
+                 int64_t k_per_split, int64_t split_stride) {
+    __shared__ float As[BK][BM + 4];
+    __shared__ float Bs[BK][BN + 4];
+    const int tid = threadIdx.x;
+    const int tx = tid & 15, ty = tid >> 4;
+    const int64_t m0 = (int64_t)blockIdx.y * BM, n0 = (int64_t)blockIdx.x * BN;
+    const int64_t kb = (int64_t)blockIdx.z * k_per_split;
+    const int64_t ke = (kb + k_per_split < K) ? kb + k_per_split : K;
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+    for (int64_t k0 = kb; k0 < ke; k0 += BK) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            int m, k;
+            if (A_KC) { k = tid & 15; m = (tid >> 4) + 16 * i; }
+            else      { m = tid & 63; k = (tid >> 6) + 4 * i; }
+            int64_t gm = m0 + m, gk = k0 + k;
+            As[k][m] = (gm < M && gk < ke) ? to_f32<AT>(A[gm * sam + gk * sak]) : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            int nn, k;
+            if (B_KC) { k = tid & 15; nn = (tid >> 4) + 16 * i; }
+            else      { nn = tid & 63; k = (tid >> 6) + 4 * i; }
+            int64_t gn = n0 + nn, gk = k0 + k;
+            Bs[k][nn] = (gn < N && gk < ke) ? B[gk * sbk + gn * sbn] : 0.f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < BK; ++k) {
+            float a[4], b[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = As[k][ty + 16 * i];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = Bs[k][tx + 16 * j];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+    float* Cs = C + (int64_t)blockIdx.z * split_stride;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            int64_t gm = m0 + ty + 16 * i, gn = n0 + tx + 16 * j;
+            if (gm < M && gn < N) Cs[gm * scm + gn * scn] = acc[i][j];
+        }
+}
+
+// C(m, n) = sum_s part[s][m][n] in a fixed order; part is dense row-major [M, N] per split
+__global__ void splitk_reduce_kernel(const float* __restrict__ part, int n_splits, int64_t M, int64_t N,
+                                     float* __restrict__ C, int64_t scm, int64_t scn) {
+    int64_t total = M * N;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int sp = 0; sp < n_splits; ++sp) s += part[(int64_t)sp * total + i];
+        C[(i / N) * scm + (i % N) * scn] = s;
+    }
+}
+
+template <typename AT, bool A_KC, bool B_KC>
+static int launch_gemm(const AT* A, int64_t sam, int64_t sak, const float* B, int64_t sbk, int64_t sbn,
+                       float* C, int64_t scm, int64_t scn, int64_t M, int64_t N, int64_t K,
+                       int n_splits, float* partial, cudaStream_t stream) {
+    dim3 grid((unsigned)((N + BN - 1) / BN), (unsigned)((M + BM - 1) / BM), (unsigned)(n_splits > 1 ? n_splits : 1));
+    if (n_splits <= 1) {
+        gemm_simt_kernel<AT, A_KC, B_KC><<<grid, 256, 0, stream>>>(A, sam, sak, B, sbk, sbn, C, scm, scn, M, N, K, K, 0);
+        GNNB_LAUNCH_CHECK();
+        return GNNB_OK;
+    }
+    // split-K: dense row-major [M, N] partials per split, reduced afterwards in a fixed order
+    int64_t kps = ((K + n_splits - 1) / n_splits + BK - 1) / BK * BK;
+    gemm_simt_kernel<AT, A_KC, B_KC><<<grid, 256, 0, stream>>>(A, sam, sak, B, sbk, sbn, partial, N, 1, M, N, K, kps, M * N);
+    GNNB_LAUNCH_CHECK();
+    int64_t blocks = (M * N + 255) / 256;
+    int64_t cap = (int64_t)sm_count() * 16;
+    splitk_reduce_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, stream>>>(partial, n_splits, M, N, C, scm, scn);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+static int pick_splits(int64_t M, int64_t N, int64_t K) {
+    int64_t tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+    int64_t want = (2LL * sm_count() + tiles - 1) / tiles;
+    int64_t maxs = K / 256;               // at least 256 rows of K per split
+    if (want > maxs) want = maxs;
+    if (want > 16) want = 16;
+    if (want < 1) want = 1;
+    return (int)want;
+}
+
+// tensor-core implementations (linear_tc.cu)
+int linear_tc_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* W, int64_t ldw, int64_t h,
+                  float* H, int64_t ldh, int terms, void* ws, size_t ws_bytes, cudaStream_t stream);
+int linear_tc_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
+                    float* dW, int64_t lddw, int terms, void* ws, size_t ws_bytes, cudaStream_t stream);
+size_t linear_tc_workspace(int64_t n, int64_t p, int64_t h, int terms);
+
+}  // namespace gnnb
+
+using namespace gnnb;
+
+extern "C" {
+
+int gnnb_linear_workspace_bytes(int64_t n, int64_t p, int64_t h, int precision, size_t* bytes) {
+    GNNB_REQUIRE(bytes && n >= 0 && p > 0 && h > 0 && precision >= 0 && precision <= 3, GNNB_E_BADARG,
+                 "linear_workspace_bytes: bad argument");
+    size_t out_max = (size_t)h * (size_t)(p > n ? p : n);
+    size_t simt = (size_t)16 * out_max * sizeof(float) + 256;                    // split-K partials (fwd: n*h, bwd_w: h*p)
+    size_t tc = precision > 0 ? linear_tc_workspace(n, p, h, precision) : 0;
+    *bytes = simt > tc ? simt : tc;
+    return GNNB_OK;
+}
+
+int gnnb_linear_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
+                    const float* W, int64_t ldw, int64_t h, float* H, int64_t ldh, int precision,
+                    void* workspace, size_t workspace_bytes, void* stream_) {
+    GNNB_ENTER();
+    cudaStream_t stream = (cudaStream_t)stream_;
+    GNNB_REQUIRE(X && W && H && n >= 0 && p > 0 && h > 0 && ldx >= p && ldw >= p && ldh >= h, GNNB_E_BADARG, "linear_fwd: bad argument");
+    GNNB_REQUIRE(precision >= 0 && precision <= 3, GNNB_E_BADARG, "linear_fwd: precision must be 0..3");
+    if (n == 0) return GNNB_OK;
+    if (precision > 0) return linear_tc_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, precision, workspace, workspace_bytes, stream);
+    int splits = pick_splits(n, h, p);
+    size_t need = splits > 1 ? (size_t)splits * n * h * sizeof(float) : 0;
+    if (need > 0 && (!workspace || workspace_bytes < need)) splits = 1;      // no scratch: single pass over K
+    if (x_is_i8)
+        return launch_gemm<int8_t, true, true>((const int8_t*)X, ldx, 1, W, 1, ldw, H, ldh, 1, n, h, p, splits,
+                                               (float*)workspace, stream);
+    return launch_gemm<float, true, true>((const float*)X, ldx, 1, W, 1, ldw, H, ldh, 1, n, h, p, splits,
+                                          (float*)workspace, stream);
+}
+
+int gnnb_linear_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
+                      const float* dH, int64_t lddh, int64_t h, float* dW, int64_t lddw, int precision,
+                      void* workspace, size_t workspace_bytes, void* stream_) {
+    GNNB_ENTER();
+    cudaStream_t stream = (cudaStream_t)stream_;
+    GNNB_REQUIRE(X && dH && dW && n >= 0 && p > 0 && h > 0 && ldx >= p && lddh >= h && lddw >= p, GNNB_E_BADARG, "linear_bwd_w: bad argument");
+    GNNB_REQUIRE(precision >= 0 && precision <= 3, GNNB_E_BADARG, "linear_bwd_w: precision must be 0..3");
+    if (precision > 0 && n > 0)
+        return linear_tc_bwd_w(X, x_is_i8, ldx, n, p, dH, lddh, h, dW, lddw, precision, workspace, workspace_bytes, stream);
+    // dW[f, j] = sum_i dH[i, f] * X[i, j], run as dW^T so that the typed operand X is A:
+    //   M = p, N = h, K = n, A(m, k) = X[k, m] (contiguous along m), B(k, n) = dH[k, n] (contiguous along n),
+    //   C(m, n) -> dW[n * lddw + m]
+    if (n == 0) {
+        GNNB_CUDA(cudaMemset2DAsync(dW, lddw * sizeof(float), 0, p * sizeof(float), h, stream));
+        return GNNB_OK;
+    }
+    int splits = pick_splits(p, h, n);
+    size_t need = splits > 1 ? (size_t)splits * h * p * sizeof(float) : 0;
+    GNNB_REQUIRE(need == 0 || (workspace && workspace_bytes >= need), GNNB_E_WORKSPACE, "linear_bwd_w: workspace %zu < %zu bytes",
+                 workspace_bytes, need);
+    if (x_is_i8)
+        return launch_gemm<int8_t, false, false>((const int8_t*)X, 1, ldx, dH, lddh, 1, dW, 1, lddw, p, h, n, splits,
+                                                 (float*)workspace, stream);
+    return launch_gemm<float, false, false>((const float*)X, 1, ldx, dH, lddh, 1, dW, 1, lddw, p, h, n, splits,
+                                            (float*)workspace, stream);
+}
+
+int gnnb_linear_bwd_x(const float* dH, int64_t lddh, int64_t n, int64_t h,
+                      const float* W, int64_t ldw, int64_t p, float* dX, int64_t lddx, void* stream_) {
+    GNNB_ENTER();
+    cudaStream_t stream = (cudaStream_t)stream_;
+    GNNB_REQUIRE(dH && W && dX && n >= 0 && p > 0 && h > 0 && lddh >= h && ldw >= p && lddx >= p, GNNB_E_BADARG, "linear_bwd_x: bad argument");
+    if (n == 0) return GNNB_OK;
+    // dX[i, j] = sum_f dH[i, f] * W[f, j]: A = dH (contiguous along k), B = W (contiguous along n)
+    return launch_gemm<float, true, false>(dH, lddh, 1, W, ldw, 1, dX, lddx, 1, n, p, h, 1, nullptr, stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,145 @@
+// K6/K7: neighbourhood aggregation  out[i,:] = sum_e val[e] * H[col[e],:] (+ bias)
+//
+// Replaces MessagePassing.propagate + torch_scatter.scatter(reduce='add') inside PyG's GCNConv (forward)
+// and the autograd of the gather (backward, over the by-source CSR).  Call sites in the reference:
+// gnn/networks/networks.py:271-272 and the other GCN factories.
+//
+// HBM/L2-bound: one warp per output row; a lane owns one float4 of the feature row, so a neighbour row
+// is one coalesced 128-bit-per-lane request; neighbour indices and weights are read 32 at a time with
+// one coalesced load and handed round with shuffles; GATHER_UNROLL independent row gathers are kept in
+// flight per warp.  Summation order is the CSR order (edge order, self loop last) => deterministic.
+#include "common.cuh"
+
+namespace gnnb {
+
+constexpr int GATHER_UNROLL = 8;
+
+__device__ __forceinline__ float4 ld_row4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+
+template <bool HAS_BIAS>
+__global__ void __launch_bounds__(256)
+spmm_vec4_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ val, int64_t n,
+                 const float* __restrict__ H, int64_t ldh, int F, const float* __restrict__ bias,
+                 float* __restrict__ out, int64_t ldo) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t row = warp0; row < n; row += nwarps) {
+        const int start = rowptr[row], end = rowptr[row + 1];
+        for (int fc = 0; fc < F; fc += 128) {
+            const int f = fc + lane * 4;
+            const bool active = f < F;
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int base = start; base < end; base += 32) {
+                const int e = base + lane;
+                int c = 0;
+                float v = 0.f;
+                if (e < end) {
+                    c = __ldg(col + e);
+                    v = __ldg(val + e);
+                }
+                const int cnt = min(32, end - base);
+                int t = 0;
+                for (; t + GATHER_UNROLL <= cnt; t += GATHER_UNROLL) {
+                    float4 h[GATHER_UNROLL];
+                    float w[GATHER_UNROLL];
+#pragma unroll
+                    for (int u = 0; u < GATHER_UNROLL; ++u) {
+                        int cu = __shfl_sync(0xffffffffu, c, t + u);
+                        w[u] = __shfl_sync(0xffffffffu, v, t + u);
+                        h[u] = active ? ld_row4(H + (int64_t)cu * ldh + f) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+#pragma unroll
+                    for (int u = 0; u < GATHER_UNROLL; ++u) {
+                        acc.x = fmaf(w[u], h[u].x, acc.x);
+                        acc.y = fmaf(w[u], h[u].y, acc.y);
+                        acc.z = fmaf(w[u], h[u].z, acc.z);
+                        acc.w = fmaf(w[u], h[u].w, acc.w);
+                    }
+                }
+                for (; t < cnt; ++t) {
+                    int cu = __shfl_sync(0xffffffffu, c, t);
+                    float wu = __shfl_sync(0xffffffffu, v, t);
+                    if (active) {
+                        float4 hu = ld_row4(H + (int64_t)cu * ldh + f);
+                        acc.x = fmaf(wu, hu.x, acc.x);
+                        acc.y = fmaf(wu, hu.y, acc.y);
+                        acc.z = fmaf(wu, hu.z, acc.z);
+                        acc.w = fmaf(wu, hu.w, acc.w);
+                    }
+                }
+            }
+            if (active) {
+                if (HAS_BIAS) {
+                    float4 b = ld_row4(bias + f);
+                    acc.x += b.x; acc.y += b.y; acc.z += b.z; acc.w += b.w;
+                }
+                *reinterpret_cast<float4*>(out + row * ldo + f) = acc;
+            }
+        }
+    }
+}
+
+// any F / any alignment: a lane owns features lane, lane + 32, ...
+template <bool HAS_BIAS>
+__global__ void __launch_bounds__(256)
+spmm_scalar_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ val, int64_t n,
+                   const float* __restrict__ H, int64_t ldh, int F, const float* __restrict__ bias,
+                   float* __restrict__ out, int64_t ldo) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t row = warp0; row < n; row += nwarps) {
+        const int start = rowptr[row], end = rowptr[row + 1];
+        for (int fc = 0; fc < F; fc += 32) {
+            const int f = fc + lane;
+            const bool active = f < F;
+            float acc = 0.f;
+            for (int base = start; base < end; base += 32) {
+                const int e = base + lane;
+                int c = 0;
+                float v = 0.f;
+                if (e < end) {
+                    c = __ldg(col + e);
+                    v = __ldg(val + e);
+                }
+                const int cnt = min(32, end - base);
+                for (int t = 0; t < cnt; ++t) {
+                    int cu = __shfl_sync(0xffffffffu, c, t);
+                    float wu = __shfl_sync(0xffffffffu, v, t);
+                    if (active) acc = fmaf(wu, __ldg(H + (int64_t)cu * ldh + f), acc);
+                }
+            }
+            if (active) out[row * ldo + f] = acc + (HAS_BIAS ? bias[f] : 0.f);
+        }
+    }
+}
+
+}  // namespace gnnb
+
+using namespace gnnb;
+
+extern "C" int gnnb_spmm(const int32_t* rowptr, const int32_t* col, const float* val, int64_t n,
+                         const float* H, int64_t ldh, int64_t F, const float* bias, float* out, int64_t ldo,
+                         void* stream_) {
+    GNNB_ENTER();
+    cudaStream_t stream = (cudaStream_t)stream_;
+    GNNB_REQUIRE(rowptr && col && val && H && out, GNNB_E_BADARG, "spmm: null pointer");
+    GNNB_REQUIRE(n >= 0 && F > 0 && F <= 4096 && ldh >= F && ldo >= F, GNNB_E_BADARG, "spmm: bad shape (F must be 1..4096)");
+    GNNB_REQUIRE(H != out, GNNB_E_BADARG, "spmm: in-place aggregation is not supported");
+    if (n == 0) return GNNB_OK;
+    bool vec = (F % 4 == 0) && (ldh % 4 == 0) && (ldo % 4 == 0) && ((uintptr_t)H % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
+               (!bias || (uintptr_t)bias % 16 == 0);
+    int64_t blocks = (n + 7) / 8;                       // 8 warps (rows) per CTA
+    int64_t cap = (int64_t)sm_count() * 8 * 4;          // grid-stride beyond 32 resident-CTA waves
+    unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
+    if (vec) {
+        if (bias) spmm_vec4_kernel<true><<<grid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
+        else      spmm_vec4_kernel<false><<<grid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
+    } else {
+        if (bias) spmm_scalar_kernel<true><<<grid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
+        else      spmm_scalar_kernel<false><<<grid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
+    }
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}

@@ -1,0 +1,387 @@
+// Errors, device checks, staging kernels, scan and segmented sort.
+#include <stdarg.h>
+
+#include "common.cuh"
+
+namespace gnnb {
+
+static thread_local char g_err[1024] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+static int g_arch_ok[64];      // 0 unknown, 1 ok, -1 not sm_100
+static int g_sms[64];
+
+int require_sm100() {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess)
+        return fail(GNNB_E_CUDA, "no CUDA device: %s (libgnn_b200 has no CPU fallback)", cudaGetErrorString(e));
+    if (dev < 0 || dev >= 64) return fail(GNNB_E_BADARG, "device ordinal %d out of range", dev);
+    if (g_arch_ok[dev] == 0) {
+        int major = 0, minor = 0, sms = 0;
+        cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+        cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        g_sms[dev] = sms;
+        g_arch_ok[dev] = (major == 10 && minor == 0) ? 1 : -1;
+    }
+    if (g_arch_ok[dev] < 0)
+        return fail(GNNB_E_ARCH, "device %d is not sm_100 (B200); this library is built for sm_100a only", dev);
+    return GNNB_OK;
+}
+
+int sm_count() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return (dev >= 0 && dev < 64 && g_sms[dev] > 0) ? g_sms[dev] : 148;
+}
+
+// ------------------------------------------------------------------------------------ scan
+__global__ void scan_reduce_kernel(const int32_t* __restrict__ in, int64_t n, int32_t* __restrict__ block_sums) {
+    __shared__ int32_t warp_sums[8];
+    int64_t base = (int64_t)blockIdx.x * 1024;
+    int32_t s = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        int64_t j = base + threadIdx.x + i * 256;
+        if (j < n) s += in[j];
+    }
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) warp_sums[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int32_t t = 0;
+        for (int w = 0; w < 8; ++w) t += warp_sums[w];
+        block_sums[blockIdx.x] = t;
+    }
+}
+
+// one block: exclusive scan of block_sums in place; total to block_sums[nb]
+__global__ void scan_top_kernel(int32_t* __restrict__ block_sums, int64_t nb, int64_t* __restrict__ total_out) {
+    __shared__ int32_t tile[1024];
+    __shared__ int32_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int64_t base = 0; base < nb; base += 1024) {
+        int64_t j = base + threadIdx.x;
+        int32_t v = (j < nb) ? block_sums[j] : 0;
+        tile[threadIdx.x] = v;
+        __syncthreads();
+        for (int o = 1; o < 1024; o <<= 1) {           // Hillis-Steele inclusive scan
+            int32_t t = (threadIdx.x >= o) ? tile[threadIdx.x - o] : 0;
+            __syncthreads();
+            tile[threadIdx.x] += t;
+            __syncthreads();
+        }
+        int32_t incl = tile[threadIdx.x];
+        int32_t c = carry;
+        if (j < nb) block_sums[j] = c + incl - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = c + incl;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        block_sums[nb] = carry;
+        if (total_out) *total_out = (int64_t)carry;
+    }
+}
+
+__global__ void scan_down_kernel(const int32_t* __restrict__ in, int32_t* __restrict__ out, int64_t n,
+                                 const int32_t* __restrict__ block_sums, int64_t nb) {
+    __shared__ int32_t warp_sums[8];
+    int64_t base = (int64_t)blockIdx.x * 1024 + (int64_t)threadIdx.x * 4;   // 4 consecutive per thread
+    int32_t v[4];
+    int32_t s = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        v[i] = (base + i < n) ? in[base + i] : 0;
+        s += v[i];
+    }
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int32_t incl = s;
+    for (int o = 1; o < 32; o <<= 1) {
+        int32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    int32_t woff = 0;
+    for (int w = 0; w < warp; ++w) woff += warp_sums[w];
+    int32_t run = block_sums[blockIdx.x] + woff + incl - s;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if (base + i < n) out[base + i] = run;
+        run += v[i];
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) out[n] = block_sums[nb];
+}
+
+int scan_exclusive_i32(const int32_t* in, int32_t* out, int64_t n, int32_t* block_sums, int64_t* total_out,
+                       cudaStream_t stream) {
+    int64_t nb = (n + 1023) / 1024;
+    if (nb == 0) nb = 1;
+    scan_reduce_kernel<<<(unsigned)nb, 256, 0, stream>>>(in, n, block_sums);
+    GNNB_LAUNCH_CHECK();
+    scan_top_kernel<<<1, 1024, 0, stream>>>(block_sums, nb, total_out);
+    GNNB_LAUNCH_CHECK();
+    scan_down_kernel<<<(unsigned)nb, 256, 0, stream>>>(in, out, n, block_sums, nb);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+// ------------------------------------------------------------------------------------ segmented sort
+constexpr int SORT_SMALL = 256;        // rows up to this length: one warp, rank sort through shared memory
+
+__global__ void __launch_bounds__(256) segsort_small_kernel(Rec* __restrict__ rec, const int32_t* __restrict__ seg_off,
+                                                            const int32_t* __restrict__ seg_len, int64_t n_seg) {
+    __shared__ Rec stage[8][SORT_SMALL];
+    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int64_t r = (int64_t)blockIdx.x * 8 + warp; r < n_seg; r += (int64_t)gridDim.x * 8) {
+        int len = seg_len[r];
+        if (len <= 1 || len > SORT_SMALL) continue;
+        Rec* seg = rec + seg_off[r];
+        for (int i = lane; i < len; i += 32) stage[warp][i] = seg[i];
+        __syncwarp();
+        for (int i = lane; i < len; i += 32) {
+            unsigned long long key = stage[warp][i].key;
+            int rank = 0;
+            for (int j = 0; j < len; ++j) {
+                unsigned long long kj = stage[warp][j].key;      // broadcast read
+                rank += (kj < key) || (kj == key && j < i);
+            }
+            seg[rank] = stage[warp][i];
+        }
+        __syncwarp();
+    }
+}
+
+// rows longer than SORT_SMALL: one CTA per row, bitonic network with ascending-only exchanges so the
+// virtual +inf padding above `len` never moves; works in place in global memory.
+__global__ void __launch_bounds__(256) segsort_large_kernel(Rec* __restrict__ rec, const int32_t* __restrict__ seg_off,
+                                                            const int32_t* __restrict__ seg_len, int64_t n_seg) {
+    for (int64_t r = blockIdx.x; r < n_seg; r += gridDim.x) {
+        int len = seg_len[r];
+        if (len <= SORT_SMALL) continue;          // uniform across the CTA
+        Rec* seg = rec + seg_off[r];
+        unsigned P = 1;
+        while (P < (unsigned)len) P <<= 1;
+        for (unsigned size = 2; size <= P; size <<= 1) {
+            for (unsigned i = threadIdx.x; i < P; i += blockDim.x) {      // mirror step
+                unsigned j = i ^ (size - 1);
+                if (j > i && j < (unsigned)len) {
+                    Rec a = seg[i], b = seg[j];
+                    if (b.key < a.key) { seg[i] = b; seg[j] = a; }
+                }
+            }
+            __syncthreads();
+            for (unsigned stride = size >> 2; stride > 0; stride >>= 1) {
+                for (unsigned i = threadIdx.x; i < P; i += blockDim.x) {
+                    unsigned j = i ^ stride;
+                    if (j > i && j < (unsigned)len) {
+                        Rec a = seg[i], b = seg[j];
+                        if (b.key < a.key) { seg[i] = b; seg[j] = a; }
+                    }
+                }
+                __syncthreads();
+            }
+        }
+    }
+}
+
+int segment_sort(Rec* rec, const int32_t* seg_off, const int32_t* seg_len, int64_t n_seg, cudaStream_t stream) {
+    if (n_seg <= 0) return GNNB_OK;
+    int sms = sm_count();
+    int64_t want = (n_seg + 7) / 8;
+    unsigned grid_small = (unsigned)(want < (int64_t)sms * 8 ? want : (int64_t)sms * 8);
+    segsort_small_kernel<<<grid_small, 256, 0, stream>>>(rec, seg_off, seg_len, n_seg);
+    GNNB_LAUNCH_CHECK();
+    unsigned grid_large = (unsigned)(n_seg < (int64_t)sms * 4 ? n_seg : (int64_t)sms * 4);
+    segsort_large_kernel<<<grid_large, 256, 0, stream>>>(rec, seg_off, seg_len, n_seg);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+// ------------------------------------------------------------------------------------ staging kernels
+__global__ void synth_kernel(int8_t* __restrict__ X, int64_t n, int64_t p, int64_t ld, int64_t row0, int64_t p_total,
+                             unsigned long long seed, unsigned long long seed_freq) {
+    // one thread per 4 consecutive markers of one row
+    int64_t groups = (p + 3) / 4;
+    int64_t total = n * groups;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        int64_t r = t / groups, j0 = (t % groups) * 4;
+        unsigned long long i = (unsigned long long)(row0 + r);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            int64_t j = j0 + q;
+            if (j >= p) break;
+            unsigned long long hf = splitmix64_dev(seed_freq ^ (unsigned long long)j);
+            unsigned long long thr = 214748365ULL + (((hf >> 32) * 1932735283ULL) >> 32);
+            unsigned long long h = splitmix64_dev(seed ^ (i * (unsigned long long)p_total + (unsigned long long)j));
+            int v = ((h & 0xFFFFFFFFULL) < thr) + ((h >> 32) < thr);
+            X[r * ld + j] = (int8_t)v;
+        }
+    }
+}
+
+__global__ void gather_rows_kernel(const int8_t* __restrict__ X, int64_t ldx, const int64_t* __restrict__ rows,
+                                   int64_t n_rows, int64_t p, int8_t* __restrict__ out, int64_t ldo, int vec16) {
+    // one CTA per output row (grid-stride)
+    for (int64_t r = blockIdx.x; r < n_rows; r += gridDim.x) {
+        const int8_t* src = X + rows[r] * ldx;
+        int8_t* dst = out + r * ldo;
+        if (vec16) {
+            const int4* s4 = reinterpret_cast<const int4*>(src);
+            int4* d4 = reinterpret_cast<int4*>(dst);
+            int64_t nv = p / 16;
+            for (int64_t i = threadIdx.x; i < nv; i += blockDim.x) d4[i] = __ldg(s4 + i);
+            for (int64_t i = nv * 16 + threadIdx.x; i < p; i += blockDim.x) dst[i] = src[i];
+        } else {
+            for (int64_t i = threadIdx.x; i < p; i += blockDim.x) dst[i] = src[i];
+        }
+    }
+}
+
+__global__ void i8_to_f32_kernel(const int8_t* __restrict__ X, int64_t ldx, int64_t n, int64_t p,
+                                 float* __restrict__ out, int64_t ldo) {
+    int64_t total = n * p;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        int64_t r = t / p, j = t % p;
+        out[r * ldo + j] = (float)X[r * ldx + j];
+    }
+}
+
+__global__ void sqnorm_kernel(const int8_t* __restrict__ X, int64_t ldx, int64_t n, int64_t p, int64_t* __restrict__ sq) {
+    // one warp per row
+    int lane = threadIdx.x & 31;
+    int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t r = warp; r < n; r += nwarps) {
+        const int8_t* row = X + r * ldx;
+        long long s = 0;
+        for (int64_t j = lane; j < p; j += 32) {
+            int v = row[j];
+            s += v * v;
+        }
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) sq[r] = s;
+    }
+}
+
+// column sums: out[f] = sum_i A[i, f]; deterministic two-stage (fixed partition of rows, fixed order)
+__global__ void colsum_partial_kernel(const float* __restrict__ A, int64_t lda, int64_t n, int64_t F,
+                                      float* __restrict__ partial, int rows_per_block) {
+    int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+    int64_t r1 = r0 + rows_per_block < n ? r0 + rows_per_block : n;
+    for (int64_t f = threadIdx.x; f < F; f += blockDim.x) {
+        float s = 0.f;
+        for (int64_t r = r0; r < r1; ++r) s += A[r * lda + f];
+        partial[(int64_t)blockIdx.x * F + f] = s;
+    }
+}
+__global__ void colsum_final_kernel(const float* __restrict__ partial, int nblocks, int64_t F, float* __restrict__ out) {
+    for (int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; f < F; f += (int64_t)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int b = 0; b < nblocks; ++b) s += partial[(int64_t)b * F + f];
+        out[f] = s;
+    }
+}
+
+}  // namespace gnnb
+
+using namespace gnnb;
+
+extern "C" {
+
+int gnnb_version(void) { return 100; }                 // 0.1.0
+const char* gnnb_last_error(void) { return g_err; }
+int gnnb_check_device(void) { return require_sm100(); }
+
+int gnnb_synth_genotypes(int8_t* X, int64_t n, int64_t p, int64_t ld, int64_t row0, int64_t p_total,
+                         uint64_t seed, uint64_t seed_freq, void* stream) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(X && n >= 0 && p >= 0 && ld >= p && p_total >= p, GNNB_E_BADARG, "synth_genotypes: bad shape");
+    if (n == 0 || p == 0) return GNNB_OK;
+    int64_t total = n * ((p + 3) / 4);
+    int64_t blocks = (total + 255) / 256;
+    int64_t cap = (int64_t)sm_count() * 32;
+    synth_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(
+        X, n, p, ld, row0, p_total, seed, seed_freq);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+int gnnb_gather_rows_i8(const int8_t* X, int64_t ldx, const int64_t* rows, int64_t n_rows, int64_t p,
+                        int8_t* out, int64_t ldo, void* stream) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(X && rows && out && n_rows >= 0 && p > 0 && ldx >= p && ldo >= p, GNNB_E_BADARG, "gather_rows: bad argument");
+    if (n_rows == 0) return GNNB_OK;
+    int vec16 = (ldx % 16 == 0) && (ldo % 16 == 0) && ((uintptr_t)X % 16 == 0) && ((uintptr_t)out % 16 == 0);
+    int64_t cap = (int64_t)sm_count() * 16;
+    gather_rows_kernel<<<(unsigned)(n_rows < cap ? n_rows : cap), 256, 0, (cudaStream_t)stream>>>(
+        X, ldx, rows, n_rows, p, out, ldo, vec16);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+int gnnb_i8_to_f32(const int8_t* X, int64_t ldx, int64_t n, int64_t p, float* out, int64_t ldo, void* stream) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(X && out && n >= 0 && p > 0 && ldx >= p && ldo >= p, GNNB_E_BADARG, "i8_to_f32: bad argument");
+    if (n == 0) return GNNB_OK;
+    int64_t blocks = (n * p + 255) / 256;
+    int64_t cap = (int64_t)sm_count() * 32;
+    i8_to_f32_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(X, ldx, n, p, out, ldo);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+int gnnb_row_sqnorm_i8(const int8_t* X, int64_t ldx, int64_t n, int64_t p, int64_t* sq, void* stream) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(X && sq && n >= 0 && p > 0 && ldx >= p, GNNB_E_BADARG, "row_sqnorm: bad argument");
+    if (n == 0) return GNNB_OK;
+    int64_t blocks = (n + 7) / 8;
+    int64_t cap = (int64_t)sm_count() * 16;
+    sqnorm_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(X, ldx, n, p, sq);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+int gnnb_colsum_workspace_bytes(int64_t F, size_t* bytes) {
+    GNNB_REQUIRE(bytes && F > 0, GNNB_E_BADARG, "colsum_workspace_bytes: bad argument");
+    *bytes = (size_t)1024 * (size_t)F * sizeof(float);
+    return GNNB_OK;
+}
+
+int gnnb_colsum(const float* A, int64_t lda, int64_t n, int64_t F, float* out,
+                void* workspace, size_t workspace_bytes, void* stream) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(A && out && n >= 0 && F > 0 && lda >= F, GNNB_E_BADARG, "colsum: bad argument");
+    GNNB_REQUIRE(workspace && workspace_bytes >= (size_t)1024 * F * sizeof(float), GNNB_E_WORKSPACE,
+                 "colsum: workspace too small");
+    int64_t nblocks = (n + 63) / 64;
+    if (nblocks > 1024) nblocks = 1024;
+    if (nblocks < 1) nblocks = 1;
+    int rows_per_block = (int)((n + nblocks - 1) / nblocks);
+    if (rows_per_block < 1) rows_per_block = 1;
+    float* partial = static_cast<float*>(workspace);
+    colsum_partial_kernel<<<(unsigned)nblocks, 128, 0, (cudaStream_t)stream>>>(A, lda, n, F, partial, rows_per_block);
+    GNNB_LAUNCH_CHECK();
+    colsum_final_kernel<<<(unsigned)((F + 127) / 128), 128, 0, (cudaStream_t)stream>>>(partial, (int)nblocks, F, out);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+}  // extern "C"

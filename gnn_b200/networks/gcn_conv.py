@@ -1,0 +1,86 @@
+"""GCNConv with the surface of torch_geometric 2.1.0's operator as the reference uses it
+(gnn/networks/networks.py:5, 142-866): ``GCNConv(in_channels, out_channels, add_self_loops=True)``,
+parameters ``lin.weight [out, in]`` (Glorot uniform) and ``bias [out]`` (zeros),
+``forward(x, edge_index, edge_weight=None)``.  Semantics restated in SURVEY.md A.1.
+
+Forward and backward run as CUDA kernels from libgnn_b200.so:
+  gcn_norm + CSR (once per edge list, cached)  -> graph.cu
+  H = x . W^T, dW = dH^T . x, dx = dH . W      -> linear.cu / linear_tc.cu   (x may be int8 genotypes)
+  out = A_hat H + b, dH = A_hat^T dOut         -> spmm.cu
+"""
+import math
+
+import torch
+
+from .. import ops
+
+
+class _GCNConvFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, graph):
+        h = ops.linear_fwd(x, weight)
+        out = ops.spmm(graph.rowptr, graph.col, graph.val, h, bias, n=graph.n)
+        ctx.graph = graph
+        ctx.has_bias = bias is not None
+        ctx.x_needs_grad = x.is_floating_point() and x.requires_grad
+        ctx.save_for_backward(x, weight)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        x, weight = ctx.saved_tensors
+        g = ctx.graph
+        d_out = d_out.contiguous()
+        d_bias = ops.colsum(d_out) if ctx.has_bias else None
+        d_h = ops.spmm(g.rowptr_t, g.col_t, g.val_t, d_out, None, n=g.n)     # transposed CSR
+        d_w = ops.linear_bwd_w(x, d_h)
+        d_x = ops.linear_bwd_x(d_h, weight) if ctx.x_needs_grad else None
+        return d_x, d_w, d_bias, None
+
+
+class _Lin(torch.nn.Module):
+    """Holds ``weight`` so that the parameter is named ``lin.weight`` like PyG's."""
+
+    def __init__(self, in_channels, out_channels):
+        super().__init__()
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.weight = torch.nn.Parameter(torch.empty(out_channels, in_channels))
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        a = math.sqrt(6.0 / (self.in_channels + self.out_channels))
+        with torch.no_grad():
+            self.weight.uniform_(-a, a)
+
+    def forward(self, x):
+        return ops.linear_fwd(x, self.weight)
+
+
+class GCNConv(torch.nn.Module):
+    def __init__(self, in_channels, out_channels, improved=False, cached=False, add_self_loops=True,
+                 normalize=True, bias=True, **_):
+        super().__init__()
+        if improved or not normalize:
+            raise NotImplementedError("only the improved=False, normalize=True GCNConv of the reference is implemented")
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.add_self_loops = add_self_loops
+        self.lin = _Lin(in_channels, out_channels)
+        if bias:
+            self.bias = torch.nn.Parameter(torch.zeros(out_channels))
+        else:
+            self.register_parameter("bias", None)
+
+    def reset_parameters(self):
+        self.lin.reset_parameters()
+        if self.bias is not None:
+            with torch.no_grad():
+                self.bias.zero_()
+
+    def forward(self, x, edge_index, edge_weight=None):
+        if not x.is_cuda:
+            raise RuntimeError("gnn_b200.GCNConv runs on CUDA tensors only (no CPU fallback)")
+        graph = ops.gcn_graph(edge_index, edge_weight, x.shape[0], self.add_self_loops)
+        return _GCNConvFn.apply(x, self.lin.weight, self.bias, graph)
+
+    def __repr__(self):
+        return f"GCNConv({self.in_channels}, {self.out_channels})"

@@ -1,0 +1,78 @@
+"""``Sequential`` with the contract of the reference's gnn/networks/sequential.py (itself PyG's
+Sequential plus optional trailing arguments): a model is declared by its global argument names and a
+list of modules, each optionally followed by a header ``"in1, in2 -> out"``; a trailing ``?`` on a global
+argument makes it optional.  ``nns`` / ``fns`` keep the same meaning, so ``state_dict`` keys
+(``nns.{i}...``) match the reference's checkpoints.
+"""
+import torch
+
+
+def parse_desc(desc):
+    assert "->" in desc
+    left, right = desc.split("->")
+    names = lambda part: [t.strip() for t in part.split(",") if t.strip()]
+    return names(left), names(right)
+
+
+class Sequential(torch.nn.Module):
+    def __init__(self, args, modules):
+        super().__init__()
+        self.args = [t.strip() for t in args.split(",") if t.strip()]
+        assert len(modules) > 0
+        assert isinstance(modules[0], (tuple, list))
+        self.nns, self.fns, self.descs = torch.nn.ModuleList(), [], []
+        for i, entry in enumerate(modules):
+            header = None
+            if isinstance(entry, (tuple, list)):
+                assert len(entry) in (1, 2)
+                header = entry[1] if len(entry) == 2 else None
+                entry = entry[0]
+            if header is not None:
+                ins, outs = parse_desc(header)
+            else:                       # no header: consume and produce what the previous module produced
+                ins = outs = self.descs[i - 1][1]
+            is_module = isinstance(entry, torch.nn.Module)
+            self.nns.append(entry if is_module else None)
+            self.fns.append(None if is_module else entry)
+            self.descs.append((ins, outs))
+
+    def reset_parameters(self):
+        for m in self.nns:
+            if hasattr(m, "reset_parameters"):
+                m.reset_parameters()
+
+    def forward(self, *args):
+        if len(args) == 1 and len(self.args) > 1:      # model((x, edge_index, ...)) call form
+            args = args[0]
+        names = list(self.args)
+        absent = []
+        while len(args) < len(names) and names[-1].endswith("?"):
+            absent.append(names.pop()[:-1])
+        names = [t.strip("?") for t in names]
+        assert len(args) == len(names)
+        state = dict(zip(names, args))
+        state["self"] = self
+        out = None
+        for m, f, (ins, outs) in zip(self.nns, self.fns, self.descs):
+            call = m if f is None else f
+            out = call(*[state[k] for k in ins if k not in absent])
+            out = out if isinstance(out, tuple) else (out,)
+            assert len(out) == len(outs)
+            state.update(zip(outs, out))
+        return out[0] if len(out) == 1 else out
+
+    def __repr__(self):
+        rows = [f"  ({i}): {m if f is None else f.__name__}" for i, (m, f) in enumerate(zip(self.nns, self.fns))]
+        return self.__class__.__name__ + "(\n" + "\n".join(rows) + "\n)"
+
+    def l1_regularize(self, loss, l1_weight=0.1):
+        flat = torch.cat([p.view(-1) for p in self.parameters()])
+        return loss + l1_weight * torch.abs(flat).sum()
+
+    def replace(self, index, module):
+        is_module = isinstance(module, torch.nn.Module)
+        self.nns[index] = module if is_module else None
+        self.fns[index] = None if is_module else module
+
+    def get(self, index):
+        return self.nns[index] if self.nns[index] is not None else self.fns[index]

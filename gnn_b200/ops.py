@@ -1,0 +1,340 @@
+"""Tensor-level wrappers over the C ABI (include/gnnb.h).  torch is plumbing here: device memory,
+streams, autograd bookkeeping.  Every function launches hand-written sm_100a kernels from
+libgnn_b200.so and raises if the library or a B200 is missing -- there is no fallback path.
+"""
+import ctypes
+from collections import OrderedDict
+
+import torch
+
+from . import _lib
+
+# knobs: 0 = CUDA-core reference tiles, 1..3 = tcgen05 with that many bf16 terms, "auto"
+config = {
+    "linear_precision": "auto",
+    "knn_impl": 0,              # 0 = pick, 1 = dp4a tiles, 2 = tcgen05 int8 tiles
+    "knn_query_block": 1 << 18,
+}
+
+_launches = 0                   # C-ABI calls that enqueue kernels (bench.py reports it)
+
+
+def launches():
+    return _launches
+
+
+def _p(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _need_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise _lib.GnnbError("gnn_b200 operators need CUDA tensors (no CPU fallback)")
+
+
+def _ws(nbytes, device):
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+
+
+def _call(name, *args):
+    global _launches
+    _launches += 1
+    return _lib.call(name, *args)
+
+
+# --------------------------------------------------------------------------------------- staging
+def synth_genotypes(n, p, device, row0=0, p_total=None, seed=20240601, seed_freq=20240602, out=None):
+    """int8 [n, p] block of the stateless synthetic genotype matrix."""
+    p_total = p if p_total is None else p_total
+    X = out if out is not None else torch.empty((n, p), dtype=torch.int8, device=device)
+    _need_cuda(X)
+    with torch.cuda.device(X.device):
+        _call("gnnb_synth_genotypes", _p(X), n, p, X.stride(0), row0, p_total, seed, seed_freq, _stream())
+    return X
+
+
+def gather_rows(X, rows, ld_align=16):
+    """X[rows] for int8 genotypes (df.iloc[batch_nodes], util.py:68); row stride padded to 16 bytes."""
+    _need_cuda(X, rows)
+    rows = rows.to(torch.int64).contiguous()
+    p = X.shape[1]
+    ld = (p + ld_align - 1) // ld_align * ld_align
+    buf = torch.zeros((rows.numel(), ld), dtype=torch.int8, device=X.device)
+    with torch.cuda.device(X.device):
+        _call("gnnb_gather_rows_i8", _p(X), X.stride(0), _p(rows), rows.numel(), p, _p(buf), ld, _stream())
+    return buf[:, :p]
+
+
+def i8_to_f32(X):
+    _need_cuda(X)
+    out = torch.empty(X.shape, dtype=torch.float32, device=X.device)
+    with torch.cuda.device(X.device):
+        _call("gnnb_i8_to_f32", _p(X), X.stride(0), X.shape[0], X.shape[1], _p(out), out.stride(0), _stream())
+    return out
+
+
+def row_sqnorm(X):
+    _need_cuda(X)
+    sq = torch.empty(X.shape[0], dtype=torch.int64, device=X.device)
+    with torch.cuda.device(X.device):
+        _call("gnnb_row_sqnorm_i8", _p(X), X.stride(0), X.shape[0], X.shape[1], _p(sq), _stream())
+    return sq
+
+
+def _rows_ok(X):
+    if X.dtype != torch.int8 or X.dim() != 2 or X.stride(1) != 1:
+        raise _lib.GnnbError("genotypes must be a 2-D int8 tensor with unit column stride")
+
+
+# --------------------------------------------------------------------------------------- K1
+def knn_block(Q, sq_q, q_off, K, sq_k, k_off, k, best_d2, best_idx, merge, extra_q=None, extra_k=None, impl=None):
+    """Fold the key block K (global rows k_off..) into the running lists of the query block Q."""
+    _rows_ok(Q)
+    _rows_ok(K)
+    _need_cuda(Q, K, best_d2, best_idx)
+    impl = config["knn_impl"] if impl is None else impl
+    n_extra = 0 if extra_q is None else extra_q.shape[1]
+    with torch.cuda.device(Q.device):
+        nbytes = _lib.workspace_bytes("gnnb_knn_workspace_bytes", Q.shape[0], K.shape[0], Q.shape[1], k, impl)
+        ws = _ws(nbytes, Q.device)
+        _call("gnnb_knn_i8", _p(Q), Q.stride(0), _p(sq_q), Q.shape[0], q_off,
+              _p(K), K.stride(0), _p(sq_k), K.shape[0], k_off, Q.shape[1],
+              _p(extra_q), _p(extra_k), n_extra, k, _p(best_d2), _p(best_idx), int(merge), impl,
+              _p(ws), ws.numel(), _stream())
+
+
+def knn(X, k, extra=None, impl=None):
+    """Canonical k nearest neighbours of every row of int8 X (sklearn call at load.py:52-59, util.py:52-57).
+
+    extra: optional float64 [n, m] side columns (the phenotype column the partition graph keeps).
+    Returns (idx int32 [n, k], d2 float64 [n, k]) in ascending (d2, index) order.
+    """
+    _rows_ok(X)
+    n = X.shape[0]
+    if not 0 < k < n:
+        raise ValueError(f"Expected n_neighbors <= n_samples_fit, but n_neighbors = {k + 1}, n_samples_fit = {n}")
+    if extra is not None:
+        extra = extra.to(device=X.device, dtype=torch.float64).reshape(n, -1).contiguous()
+    sq = row_sqnorm(X)
+    best_d2 = torch.empty((n, k), dtype=torch.float64, device=X.device)
+    best_idx = torch.empty((n, k), dtype=torch.int32, device=X.device)
+    qb = config["knn_query_block"]
+    for q0 in range(0, n, qb):
+        q1 = min(n, q0 + qb)
+        knn_block(X[q0:q1], sq[q0:q1], q0, X, sq, 0, k, best_d2[q0:q1], best_idx[q0:q1], 0,
+                  None if extra is None else extra[q0:q1], extra, impl)
+    return best_idx, best_d2
+
+
+# --------------------------------------------------------------------------------------- K2 / K3
+def build_edges(idx, d2, mode="connectivity", smoothing="laplacian", use_weights=False):
+    """Edge list of load.py:61-80 from canonical neighbour lists.
+    Returns (edge_index int64 [2, E], edge_weight float64 [E] or None)."""
+    _need_cuda(idx, d2)
+    idx = idx.contiguous()
+    d2 = d2.contiguous()
+    n, k = idx.shape
+    m = 1 if mode == "distance" else 0
+    dev = idx.device
+    with torch.cuda.device(dev):
+        if smoothing == "laplacian":
+            ws = _ws(_lib.workspace_bytes("gnnb_graph_workspace_bytes", n, k), dev)
+            n_edges = torch.zeros(1, dtype=torch.int64, device=dev)
+            _call("gnnb_graph_count", _p(idx), _p(d2), n, k, m, _p(n_edges), _p(ws), ws.numel(), _stream())
+            E = int(n_edges.item())                       # the one host sync of the graph build
+            ei = torch.empty((2, E), dtype=torch.int64, device=dev)
+            ew = torch.empty(E, dtype=torch.float64, device=dev)
+            _call("gnnb_graph_fill", n, k, int(bool(use_weights)), E, _p(ei), _p(ew), _p(ws), ws.numel(), _stream())
+        else:
+            E = n * k
+            ws = _ws(256, dev)
+            ei = torch.empty((2, E), dtype=torch.int64, device=dev)
+            ew = torch.empty(E, dtype=torch.float64, device=dev)
+            _call("gnnb_graph_knn_edges", _p(idx), _p(d2), n, k, m, int(bool(use_weights)), _p(ei), _p(ew),
+                  _p(ws), ws.numel(), _stream())
+    return ei, (ew if use_weights else None)
+
+
+# --------------------------------------------------------------------------------------- K4
+class GcnGraph:
+    """GCN-normalised adjacency in CSR, by target (forward) and by source (backward)."""
+    __slots__ = ("n", "nnz", "rowptr", "col", "val", "rowptr_t", "col_t", "val_t", "_keep")
+
+    def agg_bytes(self, F, s=4):
+        """Algorithmic bytes of one aggregation launch."""
+        return self.nnz * (F * s + 8) + self.n * F * s + (self.n + 1) * 4 + self.n * 4 + F * 4
+
+
+_graph_cache = OrderedDict()
+_GRAPH_CACHE_MAX = 512
+
+
+def gcn_graph(edge_index, edge_weight, n, add_self_loops=True):
+    """gcn_norm + CSR of PyG's GCNConv, built once per (edge list, weights) and cached:
+    the reference recomputes it on every forward (cached=False); the result is identical."""
+    _need_cuda(edge_index, edge_weight)
+    if edge_index.dtype != torch.int64 or edge_index.dim() != 2 or edge_index.shape[0] != 2:
+        raise _lib.GnnbError("edge_index must be int64 [2, E]")
+    key = (edge_index.data_ptr(), edge_index._version, edge_index.shape[1],
+           None if edge_weight is None else (edge_weight.data_ptr(), edge_weight._version, edge_weight.dtype),
+           int(n), bool(add_self_loops))
+    hit = _graph_cache.get(key)
+    if hit is not None:
+        _graph_cache.move_to_end(key)
+        return hit
+    ei = edge_index.contiguous()
+    ew = None if edge_weight is None else edge_weight.to(torch.float32).contiguous()
+    E = ei.shape[1]
+    dev = ei.device
+    g = GcnGraph()
+    with torch.cuda.device(dev):
+        ws = _ws(_lib.workspace_bytes("gnnb_csr_workspace_bytes", n, E), dev)
+        nnz_t = torch.zeros(1, dtype=torch.int64, device=dev)
+        _call("gnnb_csr_count", _p(ei), E, n, int(add_self_loops), _p(nnz_t), _p(ws), ws.numel(), _stream())
+        nnz = int(nnz_t.item())
+        g.n, g.nnz = int(n), nnz
+        g.rowptr = torch.empty(n + 1, dtype=torch.int32, device=dev)
+        g.rowptr_t = torch.empty(n + 1, dtype=torch.int32, device=dev)
+        g.col = torch.empty(max(nnz, 1), dtype=torch.int32, device=dev)
+        g.col_t = torch.empty(max(nnz, 1), dtype=torch.int32, device=dev)
+        g.val = torch.empty(max(nnz, 1), dtype=torch.float32, device=dev)
+        g.val_t = torch.empty(max(nnz, 1), dtype=torch.float32, device=dev)
+        _call("gnnb_csr_build", _p(ei), _p(ew), E, n, int(add_self_loops), nnz,
+              _p(g.rowptr), _p(g.col), _p(g.val), _p(g.rowptr_t), _p(g.col_t), _p(g.val_t),
+              _p(ws), ws.numel(), _stream())
+    g._keep = (edge_index, edge_weight)     # keeps the keyed storage alive so its address cannot be reused
+    _graph_cache[key] = g
+    while len(_graph_cache) > _GRAPH_CACHE_MAX:
+        _graph_cache.popitem(last=False)
+    return g
+
+
+def clear_graph_cache():
+    _graph_cache.clear()
+
+
+# --------------------------------------------------------------------------------------- K6 / K7
+def spmm(rowptr, col, val, H, bias=None, n=None):
+    """out[i] = sum_e val[e] * H[col[e]] (+ bias) over CSR row i."""
+    _need_cuda(rowptr, H)
+    if H.dtype != torch.float32 or H.stride(1) != 1:
+        H = H.to(torch.float32).contiguous()
+    n = rowptr.numel() - 1 if n is None else n
+    out = torch.empty((n, H.shape[1]), dtype=torch.float32, device=H.device)
+    with torch.cuda.device(H.device):
+        _call("gnnb_spmm", _p(rowptr), _p(col), _p(val), n, _p(H), H.stride(0), H.shape[1],
+              _p(bias), _p(out), out.stride(0), _stream())
+    return out
+
+
+# --------------------------------------------------------------------------------------- K5
+def _precision(n, p, h, x_is_i8):
+    prec = config["linear_precision"]
+    if prec == "auto":
+        return 0
+    return int(prec)
+
+
+def linear_fwd(X, W, precision=None):
+    """H = X . W^T with X int8 genotype codes or float32, W float32 [h, p]."""
+    _need_cuda(X, W)
+    x_is_i8 = X.dtype == torch.int8
+    if not x_is_i8 and X.dtype != torch.float32:
+        X = X.to(torch.float32)
+    if X.stride(1) != 1:
+        X = X.contiguous()
+    W = W.contiguous()
+    n, p = X.shape
+    h = W.shape[0]
+    prec = _precision(n, p, h, x_is_i8) if precision is None else precision
+    H = torch.empty((n, h), dtype=torch.float32, device=X.device)
+    with torch.cuda.device(X.device):
+        ws = _ws(_lib.workspace_bytes("gnnb_linear_workspace_bytes", n, p, h, prec), X.device)
+        _call("gnnb_linear_fwd", _p(X), int(x_is_i8), X.stride(0), n, p, _p(W), W.stride(0), h,
+              _p(H), H.stride(0), prec, _p(ws), ws.numel(), _stream())
+    return H
+
+
+def linear_bwd_w(X, dH, precision=None):
+    """dW [h, p] = dH^T . X"""
+    _need_cuda(X, dH)
+    x_is_i8 = X.dtype == torch.int8
+    if not x_is_i8 and X.dtype != torch.float32:
+        X = X.to(torch.float32)
+    if X.stride(1) != 1:
+        X = X.contiguous()
+    dH = dH.contiguous()
+    n, p = X.shape
+    h = dH.shape[1]
+    prec = _precision(n, p, h, x_is_i8) if precision is None else precision
+    dW = torch.empty((h, p), dtype=torch.float32, device=X.device)
+    with torch.cuda.device(X.device):
+        ws = _ws(_lib.workspace_bytes("gnnb_linear_workspace_bytes", n, p, h, prec), X.device)
+        _call("gnnb_linear_bwd_w", _p(X), int(x_is_i8), X.stride(0), n, p, _p(dH), dH.stride(0), h,
+              _p(dW), dW.stride(0), prec, _p(ws), ws.numel(), _stream())
+    return dW
+
+
+def linear_bwd_x(dH, W):
+    """dX [n, p] = dH . W"""
+    _need_cuda(dH, W)
+    dH = dH.contiguous()
+    W = W.contiguous()
+    n, h = dH.shape
+    p = W.shape[1]
+    dX = torch.empty((n, p), dtype=torch.float32, device=dH.device)
+    with torch.cuda.device(dH.device):
+        _call("gnnb_linear_bwd_x", _p(dH), dH.stride(0), n, h, _p(W), W.stride(0), p, _p(dX), dX.stride(0), _stream())
+    return dX
+
+
+def colsum(A):
+    _need_cuda(A)
+    A = A.contiguous()
+    n, F = A.shape
+    out = torch.empty(F, dtype=torch.float32, device=A.device)
+    with torch.cuda.device(A.device):
+        ws = _ws(_lib.workspace_bytes("gnnb_colsum_workspace_bytes", F), A.device)
+        _call("gnnb_colsum", _p(A), A.stride(0), n, F, _p(out), _p(ws), ws.numel(), _stream())
+    return out
+
+
+# --------------------------------------------------------------------------------------- subsampling
+def first_occurrence(idx):
+    """first_pos[v] = first position of node v in the flattened neighbour lists."""
+    _need_cuda(idx)
+    S = idx.contiguous().view(-1)
+    n = idx.shape[0]
+    fp = torch.empty(n, dtype=torch.int64, device=idx.device)
+    with torch.cuda.device(idx.device):
+        _call("gnnb_first_occurrence", _p(S), S.numel(), n, _p(fp), _stream())
+    return fp
+
+
+def partition_walk(order, n_nodes, sizes, taken=None):
+    """Host cursor walk of naive_partition over all batches (util.py:15-45, 63-68).
+    ``taken``: optional uint8 [n_nodes] numpy array, the `traversed` set, updated in place."""
+    import numpy as np
+    order = np.ascontiguousarray(order, dtype=np.int64)
+    sizes = np.ascontiguousarray(sizes, dtype=np.int64)
+    out = np.empty(n_nodes + 1, dtype=np.int64)
+    lens = np.zeros(len(sizes), dtype=np.int64)
+    if taken is not None:
+        assert taken.dtype == np.uint8 and taken.size == n_nodes and taken.flags["C_CONTIGUOUS"]
+    rc = _lib.lib().gnnb_partition_walk_host(
+        order.ctypes.data_as(ctypes.c_void_p), order.size, n_nodes,
+        sizes.ctypes.data_as(ctypes.c_void_p), sizes.size,
+        None if taken is None else taken.ctypes.data_as(ctypes.c_void_p),
+        out.ctypes.data_as(ctypes.c_void_p), lens.ctypes.data_as(ctypes.c_void_p))
+    if rc < 0:
+        _lib.check(int(rc), "gnnb_partition_walk_host")
+    res, pos = [], 0
+    for ln in lens:
+        res.append(out[pos:pos + int(ln)].copy())
+        pos += int(ln)
+    return res

@@ -1,0 +1,171 @@
+/*
+ * gnnb.h -- C ABI of libgnn_b200.so, the sm_100a implementation of the message-passing
+ * hot path of ragsGo/GNN (kNN graph from a genotype matrix -> GCN forward/backward ->
+ * subsampled-subgraph training).
+ *
+ * The reference is pure Python and has no FFI of its own: every entry point below
+ * replaces a call the reference makes into an un-vendored Python library, cited as
+ * file:line into /root/reference.  INTEGRATION.md shows the ctypes stub a maintainer of
+ * the reference would add for each of them.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer into caller-owned memory unless the name ends in
+ *     _host; the library never allocates, frees or keeps a pointer past the call;
+ *   - matrices are row-major; `ld` arguments are row strides in ELEMENTS;
+ *   - `stream` is a cudaStream_t passed as void*; functions only enqueue work on it and
+ *     return without synchronising unless their comment says otherwise;
+ *   - return value 0 = ok, negative = GNNB_E_*; gnnb_last_error() gives the text
+ *     (thread-local).  There is no CPU fallback: on a device that is not sm_100 every
+ *     compute entry point fails with GNNB_E_ARCH.
+ */
+#ifndef GNNB_H_
+#define GNNB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GNNB_OK            0
+#define GNNB_E_BADARG     -1
+#define GNNB_E_UNSUPPORTED -2
+#define GNNB_E_ARCH       -3
+#define GNNB_E_WORKSPACE  -4
+#define GNNB_E_CUDA       -5
+
+#define GNNB_KNN_MAX_K    64      /* neighbours per row the selection kernels hold on chip */
+
+/* ---- library / errors ------------------------------------------------------------------ */
+int         gnnb_version(void);                 /* 10000*major + 100*minor + patch */
+const char* gnnb_last_error(void);              /* text of the last failure on this thread */
+int         gnnb_check_device(void);            /* 0 iff the current device is sm_100; no launch */
+
+/* ---- synthetic inputs (measurement only; no reference counterpart, the
+ *      reference reads csv-data/<file>.csv at gnn/loaders/load.py:182-187) ---------------------- */
+int gnnb_synth_genotypes(int8_t* X, int64_t n, int64_t p, int64_t ld, int64_t row0, int64_t p_total,
+                         uint64_t seed, uint64_t seed_freq, void* stream);
+
+/* ---- genotype staging ------------------------------------------------------------------ */
+/* out[r, :] = X[rows[r], :]  -- replaces df.iloc[batch_nodes] at gnn/loaders/util.py:68 */
+int gnnb_gather_rows_i8(const int8_t* X, int64_t ldx, const int64_t* rows, int64_t n_rows, int64_t p,
+                        int8_t* out, int64_t ldo, void* stream);
+/* x_f32 = float(X) -- replaces torch.tensor(df_x.values.tolist(), dtype=float) at load.py:50 */
+int gnnb_i8_to_f32(const int8_t* X, int64_t ldx, int64_t n, int64_t p, float* out, int64_t ldo, void* stream);
+/* sq[i] = sum_j X[i,j]^2 (int64) -- the ||x||^2 term of sklearn's Euclidean kNN (load.py:52-59) */
+int gnnb_row_sqnorm_i8(const int8_t* X, int64_t ldx, int64_t n, int64_t p, int64_t* sq, void* stream);
+
+/* ---- K1: k nearest neighbours ---------------------------------------------------------- */
+/* Replaces sklearn.neighbors.kneighbors_graph(X, k, mode, metric='euclidean', include_self=False)
+ * at gnn/loaders/load.py:52-59 and gnn/loaders/util.py:52-57.
+ *
+ * For every query row (global index q_off + r) keeps the k smallest pairs (d2, j) over the key rows
+ * (global index k_off + c), j != i, in lexicographic order -- the canonical tie rule of SURVEY.md A.2.
+ *   d2 = ||q||^2 + ||k||^2 - 2 q.k   exactly (integer-coded int8 markers), plus, when n_extra > 0,
+ *        sum_c (eq[r,c] - ek[c',c])^2 accumulated left to right in float64 (the phenotype column that
+ *        gnn/loaders/util.py:52-53 leaves in the frame).
+ * best_d2 [n_q, k] float64 and best_idx [n_q, k] int32 hold the running result in ascending order;
+ * merge = 0 starts from empty lists, merge = 1 folds the new key block into the lists already there
+ * (streaming over key blocks / ring passes between GPUs).  Unfilled slots hold (+inf, -1).
+ * impl: 0 = pick, 1 = CUDA-core dp4a tiles, 2 = tcgen05 int8 tensor-core tiles.
+ */
+int gnnb_knn_workspace_bytes(int64_t n_q, int64_t n_k, int64_t p, int k, int impl, size_t* bytes);
+int gnnb_knn_i8(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q, int64_t q_off,
+                const int8_t* K, int64_t ldk, const int64_t* sq_k, int64_t n_k, int64_t k_off,
+                int64_t p,
+                const double* extra_q, const double* extra_k, int n_extra,
+                int k, double* best_d2, int32_t* best_idx, int merge, int impl,
+                void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- K2/K3: similarity graph -> Laplacian edge list ------------------------------------- */
+/* Replaces gnn/loaders/load.py:61-80 (scipy CSR arithmetic, csgraph.laplacian,
+ * from_scipy_sparse_matrix, the 1 - |L| / max(L) weight map).
+ * Phase 1 (gnnb_graph_count) sizes the output: n_edges_out[0] = nnz(W) + n on the device.
+ * Phase 2 (gnnb_graph_fill) writes edge_index int64 [2, E] (off-diagonal block sorted by (row, col),
+ * then the n diagonal entries) and edge_weight float64 [E]
+ * (use_weights: 1 - |L| / float32(max L); otherwise the Laplacian entries themselves).
+ * mode: 0 = connectivity, 1 = distance.  The same workspace must be passed to both phases.
+ */
+int gnnb_graph_workspace_bytes(int64_t n, int k, size_t* bytes);
+int gnnb_graph_count(const int32_t* idx, const double* d2, int64_t n, int k, int mode,
+                     int64_t* n_edges_out, void* workspace, size_t workspace_bytes, void* stream);
+int gnnb_graph_fill(int64_t n, int k, int use_weights, int64_t n_edges,
+                    int64_t* edge_index, double* edge_weight,
+                    void* workspace, size_t workspace_bytes, void* stream);
+/* smoothing != "laplacian" (load.py:76-80): the directed kNN CSR in row-major order */
+int gnnb_graph_knn_edges(const int32_t* idx, const double* d2, int64_t n, int k, int mode, int use_weights,
+                         int64_t* edge_index, double* edge_weight, void* workspace, size_t workspace_bytes,
+                         void* stream);
+
+/* ---- K4: GCN normalisation + CSR ---------------------------------------------------------- */
+/* Replaces torch_geometric 2.1.0 gcn_norm / add_remaining_self_loops / scatter_add inside
+ * GCNConv.forward (call sites gnn/networks/networks.py:271-272 and the other factories).
+ * From an arbitrary edge list (src = edge_index[0], dst = edge_index[1], optional float32 weights)
+ * builds, deterministically,
+ *   by-target CSR  rowptr [n+1], col [nnz] (= source), val [nnz] = dis[src] * w * dis[dst]
+ *   by-source CSR  rowptr_t [n+1], col_t [nnz] (= target), val_t [nnz]        (for the backward pass)
+ * with entries of a row in edge order and the self loop last; nnz = #(src != dst) + n when
+ * add_self_loops, else E.  nnz must be computed by the caller with gnnb_csr_count.
+ */
+int gnnb_csr_workspace_bytes(int64_t n, int64_t n_edges, size_t* bytes);
+int gnnb_csr_count(const int64_t* edge_index, int64_t n_edges, int64_t n, int add_self_loops,
+                   int64_t* nnz_out, void* workspace, size_t workspace_bytes, void* stream);
+int gnnb_csr_build(const int64_t* edge_index, const float* edge_weight, int64_t n_edges, int64_t n,
+                   int add_self_loops, int64_t nnz,
+                   int32_t* rowptr, int32_t* col, float* val,
+                   int32_t* rowptr_t, int32_t* col_t, float* val_t,
+                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- K6/K7: neighbourhood aggregation ------------------------------------------------------ */
+/* out[i, :] = sum_{e in row i} val[e] * H[col[e], :] (+ bias)  -- replaces MessagePassing.propagate +
+ * torch_scatter.scatter(reduce='add') of GCNConv (forward), and, over the by-source CSR, its autograd
+ * (backward: dH[j] = sum_{e: src = j} val_e * dOut[dst_e]).  float32, F <= 4096.  bias may be NULL.
+ */
+int gnnb_spmm(const int32_t* rowptr, const int32_t* col, const float* val, int64_t n,
+              const float* H, int64_t ldh, int64_t F, const float* bias, float* out, int64_t ldo,
+              void* stream);
+
+/* ---- K5: marker projection ------------------------------------------------------------------ */
+/* Replaces GCNConv.lin (PyG Linear(bias=False) -> torch.matmul) and its autograd.
+ *   fwd   : H [n, h]  = X [n, p] . W [h, p]^T
+ *   bwd_w : dW [h, p] = dH [n, h]^T . X [n, p]
+ *   bwd_x : dX [n, p] = dH [n, h] . W [h, p]                      (inner layers only)
+ * X is either int8 genotype codes in [0, 127] (x_is_i8 = 1) or float32.
+ * precision: 0 = fp32 CUDA-core tiles (exact reference arithmetic),
+ *            1 / 2 / 3 = tcgen05 bf16 tensor-core tiles with the fp32 operand split into that many
+ *            bf16 terms (3 ~ fp32-exact for integer-coded X; 1 = plain bf16 projection), fp32 accumulate.
+ */
+int gnnb_linear_workspace_bytes(int64_t n, int64_t p, int64_t h, int precision, size_t* bytes);
+int gnnb_linear_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
+                    const float* W, int64_t ldw, int64_t h, float* H, int64_t ldh, int precision,
+                    void* workspace, size_t workspace_bytes, void* stream);
+int gnnb_linear_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
+                      const float* dH, int64_t lddh, int64_t h, float* dW, int64_t lddw, int precision,
+                      void* workspace, size_t workspace_bytes, void* stream);
+int gnnb_linear_bwd_x(const float* dH, int64_t lddh, int64_t n, int64_t h,
+                      const float* W, int64_t ldw, int64_t p, float* dX, int64_t lddx, void* stream);
+/* db[f] = sum_i dOut[i, f]  -- the bias gradient of GCNConv; fixed summation order.
+ * workspace: gnnb_colsum_workspace_bytes(F) bytes. */
+int gnnb_colsum_workspace_bytes(int64_t F, size_t* bytes);
+int gnnb_colsum(const float* A, int64_t lda, int64_t n, int64_t F, float* out,
+                void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- subsampling -------------------------------------------------------------------------- */
+/* first_pos[v] = min{ e : S[e] == v } (INT64_MAX when v never occurs), S = the neighbour column of
+ * the kNN edge list in row-major order, i.e. idx flattened -- the parallel half of
+ * gnn/loaders/util.py:15-45. */
+int gnnb_first_occurrence(const int32_t* S, int64_t len, int64_t n, int64_t* first_pos, void* stream);
+/* HOST function (no device work): the cursor walk of naive_partition / split_dataset_graph
+ * (gnn/loaders/util.py:15-45, 63-68).  order_host = node ids sorted by first_pos (only those that occur),
+ * sizes_host = requested batch sizes; taken_io_host (nullable, uint8 [n_nodes]) is the `traversed` set on
+ * entry and on return; writes the concatenated batches to out_host (capacity n_nodes) and the length of
+ * each batch to out_len_host.  Returns the number of nodes written, or a negative error. */
+int64_t gnnb_partition_walk_host(const int64_t* order_host, int64_t n_order, int64_t n_nodes,
+                                 const int64_t* sizes_host, int64_t n_sizes, uint8_t* taken_io_host,
+                                 int64_t* out_host, int64_t* out_len_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GNNB_H_ */

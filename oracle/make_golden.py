@@ -280,6 +280,11 @@ def main():
                 for kk, v in w0.items():
                     traj[f"b{b}__w0__{kk}"] = v
                 traj[f"b{b}_pred_train"] = m.eval()(*restate.as_tensors(g)).detach().numpy()
+            for key, val in res["basics"].items():          # final metrics of ensemble2.py:214-256
+                if isinstance(val, (int, float, np.floating, np.integer)):
+                    traj[f"ens_{key}"] = np.float64(val)
+            traj["ens_cors"] = np.asarray(res["basics"]["cors"], dtype=np.float64)
+            traj["ens_losses"] = np.asarray(res["basics"]["losses"], dtype=np.float64)
             traj["test_rows"] = np.asarray(te, dtype=np.int32)
             traj["valid_rows"] = np.asarray(va, dtype=np.int32)
             traj["lr"] = np.float64(0.0020594745443455593)

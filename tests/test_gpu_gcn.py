@@ -1,0 +1,222 @@
+"""K4-K7 on the B200: GCN normalisation + CSR, aggregation, projection and their gradients against the
+oracle's torch-CPU restatement of PyG's GCNConv.  Tolerance 1e-4 relative (north_star)."""
+import numpy as np
+import pytest
+import torch
+
+from gnn_b200 import ops
+from gnn_b200.networks import networks as nets
+from gnn_b200.networks.gcn_conv import GCNConv
+from oracle import pyg_shim, restate, synth
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def rel_err(a, b):
+    a = a.detach().cpu().double()
+    b = b.detach().cpu().double()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def random_graph(n, e, seed, loops=True, weights=True):
+    rng = np.random.default_rng(seed)
+    ei = rng.integers(0, n, size=(2, e))
+    if loops:
+        ei[:, : max(1, e // 20)] = rng.integers(0, n, size=max(1, e // 20))      # some explicit self loops (+ duplicates)
+    ew = rng.random(e).astype(np.float32) if weights else None
+    return torch.from_numpy(ei), (None if ew is None else torch.from_numpy(ew))
+
+
+def dense_from_csr(rowptr, col, val, n):
+    A = torch.zeros(n, n, dtype=torch.float64)
+    rp = rowptr.cpu().numpy()
+    c = col.cpu().numpy()
+    v = val.cpu().double()
+    for i in range(n):
+        for q in range(rp[i], rp[i + 1]):
+            A[i, c[q]] += v[q]
+    return A
+
+
+@pytest.mark.parametrize("asl", [True, False])
+@pytest.mark.parametrize("weights", [True, False])
+def test_csr_build_matches_gcn_norm(asl, weights):
+    n, e = 97, 900
+    ei, ew = random_graph(n, e, 1, weights=weights)
+    g = ops.gcn_graph(ei.to(DEV), None if ew is None else ew.to(DEV), n, asl)
+    torch.cuda.synchronize()
+    ei2, w2 = pyg_shim.gcn_norm(ei, ew, n, asl)
+    A_ref = torch.zeros(n, n, dtype=torch.float64)
+    A_ref.index_put_((ei2[1], ei2[0]), w2.double(), accumulate=True)              # [target, source]
+    A = dense_from_csr(g.rowptr, g.col, g.val, n)
+    At = dense_from_csr(g.rowptr_t, g.col_t, g.val_t, n)
+    assert g.nnz == ei2.shape[1] == int(g.rowptr[-1])
+    torch.testing.assert_close(A, A_ref, rtol=1e-6, atol=1e-7)
+    torch.testing.assert_close(At, A_ref.t(), rtol=1e-6, atol=1e-7)
+    # order inside a row = edge order, self loop last
+    rp, col = g.rowptr.cpu().numpy(), g.col.cpu().numpy()
+    src, dst = ei2[0].numpy(), ei2[1].numpy()
+    for i in (0, 13, n - 1):
+        assert list(col[rp[i]:rp[i + 1]]) == list(src[dst == i])
+    assert ops.gcn_graph(ei.to(DEV), None, n, asl) is not None
+
+
+def test_graph_cache_hits_same_tensors():
+    ei, ew = random_graph(50, 300, 2)
+    ei, ew = ei.to(DEV), ew.to(DEV)
+    a = ops.gcn_graph(ei, ew, 50, True)
+    assert ops.gcn_graph(ei, ew, 50, True) is a
+    assert ops.gcn_graph(ei, ew, 50, False) is not a
+    ew.mul_(2.0)                                              # in-place change bumps the version counter
+    assert ops.gcn_graph(ei, ew, 50, True) is not a
+
+
+@pytest.mark.parametrize("F", [1, 3, 32, 100, 128, 132, 260])
+def test_spmm_against_dense(F):
+    n = 300
+    ei, ew = random_graph(n, 4000, 3)
+    g = ops.gcn_graph(ei.to(DEV), ew.to(DEV), n, True)
+    H = torch.randn(n, F, device=DEV)
+    b = torch.randn(F, device=DEV)
+    A = dense_from_csr(g.rowptr, g.col, g.val, n).to(DEV)
+    out = ops.spmm(g.rowptr, g.col, g.val, H, b)
+    ref = (A @ H.double() + b.double()).float()
+    assert rel_err(out, ref) < 1e-5
+    out_t = ops.spmm(g.rowptr_t, g.col_t, g.val_t, H, None)
+    assert rel_err(out_t, (A.t() @ H.double()).float()) < 1e-5
+    # linearity (size-independent property)
+    H2 = torch.randn(n, F, device=DEV)
+    lhs = ops.spmm(g.rowptr, g.col, g.val, H + 2 * H2, None)
+    rhs = ops.spmm(g.rowptr, g.col, g.val, H, None) + 2 * ops.spmm(g.rowptr, g.col, g.val, H2, None)
+    assert rel_err(lhs, rhs) < 1e-5
+
+
+@pytest.mark.parametrize("n,p,h", [(70, 33, 5), (479, 1279, 100), (300, 2048, 32), (1000, 100, 100), (5, 7, 3)])
+@pytest.mark.parametrize("int8_x", [True, False])
+def test_linear_fp32_path(n, p, h, int8_x):
+    X = synth.genotypes(n, p, seed=n)
+    Xd = torch.from_numpy(X).to(DEV)
+    if not int8_x:
+        Xd = Xd.float() + 0.25 * torch.randn(n, p, device=DEV)
+    W = torch.randn(h, p, device=DEV) * 0.05
+    dH = torch.randn(n, h, device=DEV)
+    Xf = Xd.double()
+    assert rel_err(ops.linear_fwd(Xd, W, precision=0), Xf @ W.double().t()) < 1e-5
+    assert rel_err(ops.linear_bwd_w(Xd, dH, precision=0), dH.double().t() @ Xf) < 1e-5
+    assert rel_err(ops.linear_bwd_x(dH, W), dH.double() @ W.double()) < 1e-5
+
+
+def oracle_and_mine(name, inp, hidden, asl=True, seed=0):
+    torch.manual_seed(seed)
+    ref = restate.make_model(name, inp, 1, internal_size=hidden, dropout=0.0, add_self_loops=asl)
+    kw = {"internal_size": hidden}
+    if "dropout" in name:
+        kw["dropout"] = 0.0
+    if name in ("create_network_two_no_conv_dropout", "create_network_two_relu", "create_network_no_conv",
+                "create_network_two_no_conv", "create_network_no_conv_dropout", "create_network_two_no_conv_relu",
+                "create_network_two_no_conv_relu_dropout"):
+        kw["add_self_loops"] = asl
+    mine = getattr(nets, name)(inp, 1, **kw)
+    mine.load_state_dict(ref.state_dict())                    # weights always come from the oracle model
+    return ref, mine.to(DEV)
+
+
+def to_dev(g):
+    x = torch.from_numpy(np.ascontiguousarray(g["x"]).astype(np.int8)).to(DEV)
+    ei = torch.from_numpy(g["edge_index"]).to(DEV)
+    ew = None if g["edge_weight"] is None else torch.from_numpy(g["edge_weight"]).to(DEV)
+    return x, ei, ew, torch.from_numpy(g["y"]).to(DEV)
+
+
+@pytest.mark.parametrize("name,asl", [("create_network_two_no_conv_dropout", True), ("create_network_two_no_conv_dropout", False),
+                                      ("create_network_no_conv_relu_dropout", True), ("create_network_two_relu", True),
+                                      ("create_network_no_conv", True)])
+def test_model_forward_backward_golden(wheat, golden, name, asl):
+    """Seeded forward/backward of the reference factories on the WHEAT training graph (golden from the
+    reference's own run): activations, loss and every gradient within 1e-4 relative."""
+    X, y = wheat
+    gold = golden("wheat_model.npz")
+    tag = f"{name}_asl{int(asl)}"
+    graph = restate.create_graph(X[:479], y[:479], 5, "laplacian", True, True, "distance")
+    x, ei, ew, yt = to_dev(graph)
+    _, mine = oracle_and_mine(name, 1279, 32, asl)
+    mine.load_state_dict({k.split("__w__")[1]: torch.from_numpy(gold[k]) for k in gold.files if k.startswith(tag + "__w__")})
+    mine.train()
+    out = mine(x, ei, ew.float())
+    loss = torch.nn.MSELoss()(out, yt)
+    loss.backward()
+    assert rel_err(out, torch.from_numpy(gold[tag + "__out"])) < 1e-4
+    assert abs(float(loss) - float(gold[tag + "__loss"])) < 1e-4 * float(gold[tag + "__loss"])
+    for kk, prm in mine.named_parameters():
+        assert rel_err(prm.grad, torch.from_numpy(gold[f"{tag}__g__{kk}"])) < 1e-4, kk
+    # call forms of sequential.py:100-101 and the no-weights form of batches.py:37
+    assert torch.equal(mine((x, ei, ew.float())), mine(x, ei, ew.float()))
+    assert mine((x, ei)).shape == out.shape
+    # float32 x (the reference's own dtype) gives the same activations as the int8 codes
+    assert rel_err(mine(x.float(), ei, ew.float()), out) < 1e-5
+
+
+def test_inner_layer_input_gradient_and_raw_knn_graph():
+    """dx through an inner GCNConv, and a non-symmetric edge list (smoothing='none', load.py:76-80) where the
+    backward needs the transposed CSR."""
+    n, p, k = 400, 64, 6
+    X = synth.genotypes(n, p, seed=9)
+    y = synth.phenotypes(n, p)[:, 0]
+    g = restate.create_graph(X, y, k, "none", True, True, "distance")
+    x, ei, ew, yt = to_dev(g)
+    torch.manual_seed(1)
+    ref = pyg_shim.GCNConv(p, 16)
+    mine = GCNConv(p, 16).to(DEV)
+    mine.load_state_dict(ref.state_dict())
+    xr = torch.from_numpy(g["x"]).clone().requires_grad_(True)
+    xm = x.float().clone().requires_grad_(True)
+    o_ref = ref(xr, torch.from_numpy(g["edge_index"]), torch.from_numpy(g["edge_weight"]).float())
+    o_mine = mine(xm, ei, ew.float())
+    wgt = torch.randn(n, 16)
+    (o_ref * wgt).sum().backward()
+    (o_mine * wgt.to(DEV)).sum().backward()
+    assert rel_err(o_mine, o_ref) < 1e-4
+    assert rel_err(xm.grad, xr.grad) < 1e-4
+    assert rel_err(mine.lin.weight.grad, ref.lin.weight.grad) < 1e-4
+    assert rel_err(mine.bias.grad, ref.bias.grad) < 1e-4
+
+
+def test_training_trajectory_golden(wheat, golden):
+    """Six epochs of train_ensemble2's epoch body (ensemble2.py:51-88) per subgraph: losses within 1e-4
+    relative of the reference's trajectory, predictions with Pearson r >= 0.9999."""
+    from gnn_b200.data import GenotypeTable
+    from gnn_b200.loaders.load import create_graph
+    from gnn_b200.trainers.util import get_args_tuple
+    X, y = wheat
+    g = golden("wheat_train.npz")
+    H, E, lr = int(g["hidden"]), int(g["epochs"]), float(g["lr"])
+    te = g["test_rows"]
+    test = create_graph(GenotypeTable.from_numpy(X[te], y[te]), 5, "laplacian", True, mode="distance")
+    for b in range(3):
+        rows = g[f"b{b}_rows"]
+        batch = create_graph(GenotypeTable.from_numpy(X[rows], y[rows]), 5, "laplacian", True, mode="distance")
+        model = nets.create_network_two_no_conv_dropout(1279, 1, internal_size=H, dropout=0.0)
+        model.load_state_dict({k.split("__w0__")[1]: torch.from_numpy(g[k]) for k in g.files if k.startswith(f"b{b}__w0__")})
+        model.to(DEV)
+        opt = torch.optim.Adam(model.parameters(), lr=lr)
+        lf = torch.nn.MSELoss()
+        tl, vl = [], []
+        for _ in range(E):
+            model.train()
+            opt.zero_grad()
+            out = model(*get_args_tuple(batch))
+            model.eval()
+            out_test = model(*get_args_tuple(batch.test if hasattr(batch, "test") else test))
+            loss = lf(out, batch.y)
+            loss.backward()
+            opt.step()
+            tl.append(float(loss))
+            vl.append(float(lf(out_test, test.y)))
+        np.testing.assert_allclose(tl, g[f"b{b}_train_loss"], rtol=1e-4)
+        np.testing.assert_allclose(vl, g[f"b{b}_test_loss"], rtol=1e-4)
+        assert restate.pearson(out_test.detach().cpu().numpy(), g[f"b{b}_pred_test"]) >= 0.9999
+        model.eval()
+        pred_train = model(*get_args_tuple(batch)).detach().cpu().numpy()
+        assert restate.pearson(pred_train, g[f"b{b}_pred_train"]) >= 0.9999
+        assert rel_err(torch.from_numpy(pred_train), torch.from_numpy(g[f"b{b}_pred_train"])) < 1e-3

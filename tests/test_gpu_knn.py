@@ -1,0 +1,142 @@
+"""K1 on the B200 through the C ABI: canonical kNN lists must be bit-exact against the oracle."""
+import numpy as np
+import pytest
+import torch
+
+from gnn_b200 import ops
+from oracle import restate, synth
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def dev_i8(X, pad=True):
+    X = np.ascontiguousarray(X, dtype=np.int8)
+    n, p = X.shape
+    ld = (p + 15) // 16 * 16 if pad else p
+    buf = torch.zeros((n, ld), dtype=torch.int8, device=DEV)
+    buf[:, :p] = torch.from_numpy(X).to(DEV)
+    return buf[:, :p]
+
+
+def run_knn(X, k, extra=None, impl=None, pad=True):
+    idx, d2 = ops.knn(dev_i8(X, pad), k, extra=None if extra is None else torch.from_numpy(extra), impl=impl)
+    torch.cuda.synchronize()
+    return idx.cpu().numpy().astype(np.int64), d2.cpu().numpy()
+
+
+def check(X, k, extra=None, impl=None, pad=True):
+    idx, d2 = run_knn(X, k, extra, impl, pad)
+    ridx, rd2 = restate.canonical_knn(X, k, extra=extra)
+    bad = np.nonzero((idx != ridx).any(axis=1) | (d2 != rd2).any(axis=1))[0]
+    assert bad.size == 0, f"{bad.size} rows differ, first {bad[:5]}: got {idx[bad[0]]} {d2[bad[0]]} want {ridx[bad[0]]} {rd2[bad[0]]}"
+
+
+@pytest.mark.parametrize("impl", [1, 0])
+def test_wheat_golden(wheat, golden, impl):
+    X, y = wheat
+    g = golden("wheat_knn.npz")
+    idx, d2 = run_knn(X, 32, impl=impl)
+    assert np.array_equal(idx, g["idx_all"]) and np.array_equal(d2, g["d2_all"].astype(np.float64))
+    idx, d2 = run_knn(X[:479], 32, impl=impl)
+    assert np.array_equal(idx, g["idx_train"]) and np.array_equal(d2, g["d2_train"].astype(np.float64))
+    for k in (1, 5, 10):                                   # shorter lists are prefixes of the k = 32 list
+        a, b = run_knn(X, k, impl=impl)
+        assert np.array_equal(a, g["idx_all"][:, :k]) and np.array_equal(b, g["d2_all"][:, :k].astype(np.float64))
+
+
+@pytest.mark.parametrize("impl", [1, 0])
+def test_wheat_with_phenotype_column(wheat, golden, impl):
+    """The partition graph keeps the float phenotype column (util.py:52-53): float64 epilogue, bit-exact."""
+    X, y = wheat
+    g = golden("wheat_knn.npz")
+    idx, d2 = run_knn(X, 10, extra=y[:, None], impl=impl)
+    assert np.array_equal(idx, g["idx_with_pheno"])
+    assert np.array_equal(d2, g["d2_with_pheno"])
+
+
+@pytest.mark.parametrize("n,p,k", [(130, 64, 1), (257, 100, 5), (1000, 777, 32), (64, 13, 63), (65, 1279, 64), (2, 5, 1),
+                                   (3000, 256, 10)])
+@pytest.mark.parametrize("impl", [1, 0])
+def test_synthetic_shapes(n, p, k, impl):
+    check(synth.genotypes(n, p, seed=11 + n), k, impl=impl)
+
+
+def test_unpadded_rows_and_general_int8_codes():
+    rng = np.random.default_rng(5)
+    X = rng.integers(0, 128, size=(300, 203)).astype(np.int8)
+    check(X, 7, impl=1, pad=False)                          # ld = 203: byte-wise loads
+    check(X, 7, impl=0, pad=True)
+
+
+def test_duplicates_and_heavy_ties():
+    X = synth.genotypes(200, 40, seed=3)
+    X[10] = X[4]; X[11] = X[4]; X[150:160] = X[0]
+    check(X, 12, impl=1)
+    check(X, 12, impl=0)
+    check(np.zeros((90, 33), dtype=np.int8), 20, impl=0)    # every distance equal: order is by index alone
+
+
+def test_two_float_columns():
+    X = synth.genotypes(400, 90, seed=8)
+    extra = np.random.default_rng(1).standard_normal((400, 2))
+    check(X, 9, extra=extra, impl=0)
+
+
+def test_streaming_key_blocks_equal_one_pass():
+    """merge=1 folds key blocks into the running lists: the result must not depend on the blocking."""
+    X = synth.genotypes(700, 300, seed=21)
+    Xd = dev_i8(X)
+    sq = ops.row_sqnorm(Xd)
+    k = 16
+    one_i, one_d = ops.knn(Xd, k)
+    best_d = torch.empty((700, k), dtype=torch.float64, device=DEV)
+    best_i = torch.empty((700, k), dtype=torch.int32, device=DEV)
+    bounds = [0, 130, 131, 500, 700]
+    order = [2, 0, 3, 1]                                     # any order of key blocks
+    for t, b in enumerate(order):
+        lo, hi = bounds[b], bounds[b + 1]
+        ops.knn_block(Xd, sq, 0, Xd[lo:hi], sq[lo:hi], lo, k, best_d, best_i, merge=int(t > 0))
+    torch.cuda.synchronize()
+    assert torch.equal(best_i, one_i) and torch.equal(best_d, one_d)
+    # query blocks with an offset (what a rank owning rows [q0, q1) does)
+    q0, q1 = 200, 333
+    bd = torch.empty((q1 - q0, k), dtype=torch.float64, device=DEV)
+    bi = torch.empty((q1 - q0, k), dtype=torch.int32, device=DEV)
+    ops.knn_block(Xd[q0:q1], sq[q0:q1], q0, Xd, sq, 0, k, bd, bi, merge=0)
+    assert torch.equal(bi, one_i[q0:q1]) and torch.equal(bd, one_d[q0:q1])
+
+
+def test_unfilled_slots_and_errors():
+    X = dev_i8(synth.genotypes(5, 20))
+    sq = ops.row_sqnorm(X)
+    bd = torch.empty((5, 4), dtype=torch.float64, device=DEV)
+    bi = torch.empty((5, 4), dtype=torch.int32, device=DEV)
+    ops.knn_block(X, sq, 0, X[:2], sq[:2], 0, 4, bd, bi, merge=0)     # only 2 keys: rows 0/1 see one, others two
+    torch.cuda.synchronize()
+    assert torch.isinf(bd[:, 2:]).all() and (bi[:, 2:] == -1).all()
+    assert torch.isinf(bd[0, 1]) and bi[0, 0] == 1
+    with pytest.raises(ValueError):
+        ops.knn(X, 5)
+    from gnn_b200._lib import GnnbError
+    with pytest.raises(GnnbError, match="outside 1.."):
+        ops.knn_block(X, sq, 0, X, sq, 0, 65, bd, bi, merge=0)
+
+
+def test_large_property_checks():
+    """20k x 2k: sortedness, self exclusion, and a random sample of rows against brute force."""
+    n, p, k = 20000, 2048, 32
+    X = ops.synth_genotypes(n, p, DEV)
+    idx, d2 = ops.knn(X, k)
+    torch.cuda.synchronize()
+    assert (d2[:, 1:] >= d2[:, :-1]).all()
+    ties = d2[:, 1:] == d2[:, :-1]
+    assert (idx[:, 1:][ties] > idx[:, :-1][ties]).all()
+    assert not (idx == torch.arange(n, device=DEV, dtype=torch.int32)[:, None]).any()
+    Xh = X.cpu().numpy().astype(np.float64)
+    rows = np.random.default_rng(0).choice(n, 48, replace=False)
+    d = ((Xh[rows] ** 2).sum(1)[:, None] + (Xh ** 2).sum(1)[None, :] - 2.0 * Xh[rows] @ Xh.T)
+    d[np.arange(48), rows] = np.inf
+    order = np.argsort(d, axis=1, kind="stable")[:, :k]
+    assert np.array_equal(order, idx.cpu().numpy()[rows])
+    assert np.array_equal(np.take_along_axis(d, order, 1), d2.cpu().numpy()[rows])

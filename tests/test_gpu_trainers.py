@@ -1,0 +1,88 @@
+"""The trainer drop-ins on the B200 against the reference's own run (golden): loader -> partition ->
+per-batch graphs -> train_ensemble2 phase 1 + 2 -> final metrics; plus train / train_batches smoke parity."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from gnn_b200.loaders.load import load_data
+from gnn_b200.loaders.util import naive_partition, split_dataset_graph
+from gnn_b200.networks import networks as nets
+from gnn_b200.trainers.batches import train_batches
+from gnn_b200.trainers.ensemble2 import train_ensemble2
+from gnn_b200.trainers.plain import train
+
+pytestmark = pytest.mark.gpu
+LR = 0.0020594745443455593
+
+
+@pytest.fixture(scope="module")
+def wheat_csv(tmp_path_factory, wheat):
+    X, y = wheat
+    path = tmp_path_factory.mktemp("csv") / "WHEAT_combined.csv"
+    with open(path, "w") as fp:
+        for yi, row in zip(y, X):
+            fp.write(repr(float(yi)) + "," + ",".join("1.0" if v else "0.0" for v in row) + "\n")
+    return str(path)
+
+
+@pytest.fixture(scope="module")
+def wheat_batches(wheat_csv):
+    ds = load_data(wheat_csv, num_neighbours=5, smoothing="laplacian", mode="distance", use_validation=True, split=0.8,
+                   use_weights=True, algorithm="euclidean", batches=3, split_algorithm=split_dataset_graph,
+                   split_algorithm_params={"partition": naive_partition})
+    return ds
+
+
+def test_loader_structure(wheat_batches, golden):
+    g = golden("wheat_train.npz")
+    ds = wheat_batches
+    assert len(ds) == 4 and ds.num_features == 1279                      # 3 batches + the validation graph
+    data = [d for d in ds]
+    for b in range(3):
+        assert data[b].x.shape == (199, 1279) and data[b].test.x.shape == (108, 1279)
+    assert data[-1].x.shape == (12, 1279) and data[-1].test is not None
+    assert data[0].edge_weight.dtype == torch.float64 and data[0].edge_index.dtype == torch.int64
+
+
+def test_train_ensemble2_against_reference(wheat_batches, golden):
+    g = golden("wheat_train.npz")
+    data = [d for d in wheat_batches]
+    H, E = int(g["hidden"]), int(g["epochs"])
+    torch.manual_seed(0)                                                  # same draw order as the reference run
+    res = train_ensemble2(lambda: nets.create_network_two_no_conv_dropout(1279, 1, internal_size=H, dropout=0.0),
+                          lambda m: torch.optim.Adam(m.parameters(), lr=LR), data, epochs=E, aggregate_epochs=2,
+                          save_loss=False, print_epochs=False)["basics"]
+    for b in range(3):
+        assert abs(res[f"min_loss_{b}"] - float(g[f"ens_min_loss_{b}"])) <= 1e-4 * float(g[f"ens_min_loss_{b}"])
+        assert res[f"min_epoch_{b}"] == int(g[f"ens_min_epoch_{b}"])
+    np.testing.assert_allclose(res["losses"], g["ens_losses"], rtol=1e-4)
+    for key in ("best_loss", "aggr_loss", "min_loss_validation"):
+        assert abs(res[key] - float(g[f"ens_{key}"])) <= 2e-4 * abs(float(g[f"ens_{key}"])), key
+    for key in ("cor_best", "cor_valid"):
+        assert abs(res[key] - float(g[f"ens_{key}"])) < 1e-3, key
+    np.testing.assert_allclose(res["cors"], g["ens_cors"], atol=1e-3)
+    assert abs(res["heritability"]) < 1e-5
+    assert res["epoch"] == E and isinstance(res["aggr_model"], nets.Ensemble)
+    assert [k for k, _ in res["aggr_model"].named_parameters()] == ["aggregator.weight", "aggregator.bias"]
+
+
+def test_train_and_train_batches_run_and_learn(wheat_csv):
+    ds = load_data(wheat_csv, num_neighbours=5, smoothing="laplacian", mode="distance", use_validation=False, split=0.8,
+                   use_weights=True, algorithm="euclidean")
+    assert len(ds) == 1
+    data = ds[0]
+    torch.manual_seed(1)
+    out = train(lambda: nets.create_network_no_conv_relu_dropout(1279, 1, internal_size=16, dropout=0.0),
+                lambda m: torch.optim.Adam(m.parameters(), lr=0.01), data, epochs=12, save_loss=False)["basics"]
+    assert len(out["losses"]) == 12 and len(out["cors"]) == 12 and len(out["dcors"]) == 12
+    assert all(np.isfinite(out["losses"])) and 0 <= out["dcors"][-1] <= 1
+    ds = load_data(wheat_csv, num_neighbours=3, use_validation=False, split=0.8, algorithm="euclidean", batches=4,
+                   split_algorithm=split_dataset_graph, split_algorithm_params={"partition": naive_partition})
+    assert len(ds) == 4
+    torch.manual_seed(2)
+    model = nets.create_network_two_no_conv_relu(1279, 1, internal_size=16)
+    opt = torch.optim.Adam(model.parameters(), lr=0.003)
+    losses, epoch = train_batches(model, opt, [d for d in ds], epochs=5, save_loss=False, print_steps=False)
+    assert epoch == 4 and len(losses) == 5 and all(np.isfinite(losses))
