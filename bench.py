@@ -1,0 +1,390 @@
+#!/usr/bin/env python
+"""bench.py -- train epochs/sec of the GCN hot path on synthetic genotypes (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            (N > 1: launched by torchrun, one rank per GPU)
+    python bench.py --impl reference ...                      (the CPU path, oracle port, on the host cores)
+
+Workload (config.workload): the C5 configuration of BASELINE.json -- synthetic 1M individuals x 50k SNPs
+(stateless generator), k = 32 kNN graphs with Laplacian smoothing, `split_dataset` into 64
+subgraph batches of 15,625 individuals, network create_network_two_no_conv_dropout (hidden 100, dropout
+0.4012, Adam lr 2.0595e-3: the shipped hyper-parameters, gnn/main.py:497-547).
+
+A "step" is one EPOCH: every training subgraph visited once (forward, backward, gradient
+all-reduce over the ranks, Adam step) plus one eval-mode forward on the test graph.  With N GPUs the 64
+subgraphs are sharded round-robin over the ranks (strong scaling: the work of an epoch is fixed).
+
+value  = epochs/s with every input resident in HBM when the timed region starts.
+e2e    = epochs/s with every subgraph's inputs (int8 genotypes, edge list, weights, phenotypes) copied
+         from pinned host memory inside the timed region and each step's loss read back to the host.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+LR, DROPOUT, HIDDEN = 0.0020594745443455593, 0.4011713125675628, 100
+SEED_DATA, SEED_FREQ, SEED_PHENO = 20240601, 20240602, 20240603
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--individuals", type=int, default=1_000_000)
+    ap.add_argument("--markers", type=int, default=50_000)
+    ap.add_argument("--neighbours", type=int, default=32)
+    ap.add_argument("--batches", type=int, default=64)
+    ap.add_argument("--hidden", type=int, default=HIDDEN)
+    ap.add_argument("--precision", default="auto")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample", type=int, default=2048, help="individuals in the CPU-baseline sample subgraph")
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------------------- synthetic phenotypes
+def _splitmix64(z):
+    z = np.asarray(z, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        z = z + np.uint64(0x9E3779B97F4A7C15)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        return z ^ (z >> np.uint64(31))
+
+
+def phenotypes(rows, p, n_causal=100, h2=0.5):
+    """y = X beta + eps on 100 causal SNPs for the given individual ids (host, numpy; same model as oracle/synth.py)."""
+    rng = np.random.default_rng(SEED_PHENO)
+    causal = np.sort(rng.choice(p, size=min(n_causal, p), replace=False)).astype(np.uint64)
+    beta = rng.standard_normal(causal.size)
+    hf = _splitmix64(np.uint64(SEED_FREQ) ^ causal)
+    thr = np.uint64(214748365) + (((hf >> np.uint64(32)) * np.uint64(1932735283)) >> np.uint64(32))
+    rows = np.asarray(rows, dtype=np.uint64)
+    g = np.empty(rows.size)
+    with np.errstate(over="ignore"):
+        for r0 in range(0, rows.size, 1 << 16):
+            i = rows[r0:r0 + (1 << 16), None]
+            h = _splitmix64(np.uint64(SEED_DATA) ^ (i * np.uint64(p) + causal[None, :]))
+            x = ((h & np.uint64(0xFFFFFFFF)) < thr).astype(np.float64) + ((h >> np.uint64(32)) < thr).astype(np.float64)
+            g[r0:r0 + x.shape[0]] = x @ beta
+    noise = np.random.default_rng(SEED_PHENO + 1 + int(rows[0]) if rows.size else 0).standard_normal(rows.size)
+    return g + noise * np.sqrt(max(g.var(), 1e-12) * (1.0 - h2) / h2)
+
+
+# ----------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------- our arm
+def run_ours(a):
+    import torch.distributed as dist
+    from gnn_b200 import ops, parallel
+    from gnn_b200.data import GenotypeTable
+    from gnn_b200.loaders.load import create_graph
+    from gnn_b200.networks import networks as nets
+    from gnn_b200.trainers.util import get_args_tuple
+
+    rank, world, local_rank = parallel.init_distributed()
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if a.precision != "auto":
+        ops.config["linear_precision"] = int(a.precision)
+    N, p, k, B = a.individuals, a.markers, a.neighbours, a.batches
+    per = N // B                                                     # util.py:77-78
+    split = int(N * 0.8)                                             # load.py:193-201, use_validation=True
+    valid = int(0.1 * (N - split))
+    test_lo, test_hi = split, N - valid
+    mine = parallel.owned(B, rank, world)
+
+    t_setup = time.time()
+
+    def make_graph(lo, hi):
+        X = ops.synth_genotypes(hi - lo, p, dev, row0=lo, p_total=p, seed=SEED_DATA, seed_freq=SEED_FREQ)
+        table = GenotypeTable(X, phenotypes(np.arange(lo, hi), p))
+        return create_graph(table, n_neighbors=k, smoothing="laplacian", use_weights=True, mode="distance",
+                            algorithm="euclidean")
+
+    batches = [make_graph(b * per, (b + 1) * per) for b in mine]
+    test = make_graph(test_lo, test_hi)
+    torch.manual_seed(0)
+    model = nets.create_network_two_no_conv_dropout(p, 1, internal_size=a.hidden, dropout=DROPOUT).to(dev)
+    parallel.broadcast_parameters(model)
+    flat = parallel.FlatGrads(model.parameters())
+    opt = torch.optim.Adam(model.parameters(), lr=LR)
+    loss_func = torch.nn.MSELoss()
+    for g in batches + [test]:                                       # gcn_norm + CSR once per graph (cached)
+        ew = g.edge_weight.float()
+        g.edge_weight = ew                                           # float32 once, as get_args_tuple would per call
+        ops.gcn_graph(g.edge_index, g.edge_weight, g.x.shape[0], True)
+    torch.cuda.synchronize()
+    setup_s = time.time() - t_setup
+
+    def epoch(graphs):
+        losses = []
+        for g in graphs:
+            losses.append(parallel.dp_step(model, flat, opt, g, world, loss_func, get_args_tuple))
+        out_test = parallel.sharded_eval(model, test, rank, world, get_args_tuple)
+        test_loss = loss_func(out_test, test.y)
+        return torch.stack(losses + [test_loss])
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        last = None
+        for _ in range(steps):
+            last = fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms) / steps, last
+
+    # ---- resident-in-HBM epochs
+    for _ in range(a.warmup):
+        epoch(batches)
+    launches0 = ops.launches()
+    ops.profiler = ops.Profiler()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    ms_per_epoch, last = timed(lambda: epoch(batches), a.steps)
+    clock_info = clocks.stop() if rank == 0 else None
+    prof = ops.profiler.summary()
+    ops.profiler = None
+    launches = ops.launches() - launches0
+    losses_host = last.cpu().numpy()
+
+    # ---- end to end: host buffers -> device every step, loss back to the host every step
+    e2e = None
+    if not a.no_e2e:
+        host = []
+        for g in batches:
+            hx = torch.empty(g.x.shape, dtype=torch.int8).pin_memory()
+            hx.copy_(g.x)
+            host.append((hx, g.edge_index.cpu().pin_memory(), g.edge_weight.cpu().pin_memory(), g.y.cpu().pin_memory()))
+        h2d = sum(t.numel() * t.element_size() for t in host[0]) if host else 0
+        copy_stream = torch.cuda.Stream()
+        from gnn_b200.data import Data
+
+        def stage(i):
+            with torch.cuda.stream(copy_stream):
+                hx, hei, hew, hy = host[i]
+                d = Data(x=hx.to(dev, non_blocking=True), edge_index=hei.to(dev, non_blocking=True),
+                         y=hy.to(dev, non_blocking=True))
+                d.edge_weight = hew.to(dev, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(copy_stream)
+            return d, ev
+
+        def epoch_e2e():
+            out = []
+            nxt = stage(0) if host else None
+            for i in range(len(host)):
+                d, ev = nxt
+                nxt = stage(i + 1) if i + 1 < len(host) else None        # prefetch the next subgraph while this one trains
+                torch.cuda.current_stream().wait_event(ev)
+                loss = parallel.dp_step(model, flat, opt, d, world, loss_func, get_args_tuple)
+                out.append(float(loss))                                   # D2H read of the step's result
+            out_test = parallel.sharded_eval(model, test, rank, world, get_args_tuple)
+            out.append(float(loss_func(out_test, test.y)))
+            return out
+
+        ops.clear_graph_cache()
+        for _ in range(max(1, min(a.warmup, 1))):
+            epoch_e2e()
+        ms_e2e, _ = timed(epoch_e2e, max(1, min(a.steps, 2)))
+        e2e = {"value": 1000.0 / ms_e2e, "unit": "epochs/s", "h2d_bytes_per_step": int(h2d * len(host)),
+               "d2h_bytes_per_step": 4 * (len(host) + 1),
+               "note": "per epoch: every owned subgraph's int8 genotypes + edge list + weights + phenotypes H2D from pinned "
+                       "memory (prefetched one subgraph ahead on a copy stream), gcn_norm/CSR rebuilt per step, loss D2H per step"}
+
+    if rank != 0:
+        return None
+    # ---- roofline of the dominant kernel (CUDA events inside the timed region)
+    dom = max(prof.items(), key=lambda kv: kv[1]["ms"]) if prof else (None, None)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    roofline = None
+    if dom[0] is not None:
+        name, st = dom
+        avg_ms = st["ms"] / st["calls"]
+        if name in ("gnnb_spmm",):
+            peak = peaks.get("hbm_gbs", 6650.0)
+            ach = st["bytes"] / st["calls"] / (avg_ms * 1e-3) / 1e9
+            roofline = {"kernel": name, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                        "traffic": None}
+        else:
+            peak = peaks.get("bf16_tflops_sustained", 1400.0)
+            ach = st["flops"] / st["calls"] / (avg_ms * 1e-3) / 1e12
+            roofline = {"kernel": name, "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                        "traffic": None}
+        roofline["peak_source"] = "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)"
+        roofline["avg_launch_ms"] = avg_ms
+        roofline["share_of_step"] = st["ms"] / (ms_per_epoch * a.steps)
+        roofline["by_kernel_ms_per_epoch"] = {k2: v["ms"] / a.steps for k2, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}
+        agg = prof.get("gnnb_spmm")
+        if agg:
+            roofline["aggregation_gbs"] = agg["bytes"] / (agg["ms"] * 1e-3) / 1e9
+            roofline["aggregation_frac_of_hbm"] = roofline["aggregation_gbs"] / peaks.get("hbm_gbs", 6650.0)
+    line = {
+        "metric": "train epochs/sec", "value": 1000.0 / ms_per_epoch, "unit": "epochs/s", "n_gpus": world, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": ms_per_epoch, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32 (int8 genotypes; bf16-split tensor-core projection when precision > 0)", "data": "synthetic",
+        "config": {"workload": f"C5: synthetic {N} individuals x {p} SNPs, k={k} kNN Laplacian graphs, {B} subgraph batches of "
+                               f"{per} (split_dataset), test graph {test_hi - test_lo} nodes, create_network_two_no_conv_dropout "
+                               f"hidden {a.hidden} dropout {DROPOUT:.4f}, Adam",
+                   "parallelism": f"dp{world} (subgraphs sharded, flat-gradient all-reduce)",
+                   "linear_precision": ops.config["linear_precision"],
+                   "l2": "inputs per epoch far exceed L2 (genotypes >= 0.78 GB per subgraph); no flush needed",
+                   "setup_s": round(setup_s, 1), "final_train_loss": float(losses_host[-2]),
+                   "final_test_loss": float(losses_host[-1])},
+        "clocks": clock_info, "gpu_launches": int(launches), "roofline": roofline, "e2e": e2e,
+    }
+    return line
+
+
+# ----------------------------------------------------------------------------------------- CPU arm (oracle port)
+def cpu_epoch_rate(a, sample_n):
+    """Times the oracle port (reference algorithm, torch-CPU + numpy) on a bounded sample and scales to one epoch
+    of the full workload.  Returns (epochs_per_s, description, cores)."""
+    from oracle import restate, synth
+    p, k = a.markers, min(a.neighbours, sample_n - 1)
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    X = synth.genotypes(sample_n, p)
+    y = synth.phenotypes(sample_n, p)[:, 0]
+    t0 = time.time()
+    g = restate.create_graph(X, y, k, "laplacian", True, True, "distance")
+    t_graph = time.time() - t0
+    torch.manual_seed(0)
+    m = restate.make_model("create_network_two_no_conv_dropout", p, 1, internal_size=a.hidden, dropout=DROPOUT)
+    opt = torch.optim.Adam(m.parameters(), lr=LR)
+    args, yt, lf = restate.as_tensors(g), torch.as_tensor(g["y"]), torch.nn.MSELoss()
+
+    def train_part():                                              # ensemble2.py:52-57, 82-88
+        m.train()
+        opt.zero_grad()
+        loss = lf(m(*args), yt)
+        loss.backward()
+        opt.step()
+
+    def eval_part():                                               # ensemble2.py:59-64
+        m.eval()
+        with torch.no_grad():
+            m(*args)
+
+    train_part()
+    eval_part()                                                    # warm-up
+    reps = 2
+    t0 = time.time()
+    for _ in range(reps):
+        train_part()
+    t_train = (time.time() - t0) / reps
+    t0 = time.time()
+    for _ in range(reps):
+        eval_part()
+    t_eval = (time.time() - t0) / reps
+    # one full epoch = B train steps of `per` nodes + one eval forward of the test graph: scale linearly in node count
+    N, B = a.individuals, a.batches
+    per = N // B
+    test_n = (N - int(0.1 * (N - int(N * 0.8)))) - int(N * 0.8)
+    t_epoch = B * per * (t_train / sample_n) + test_n * (t_eval / sample_n)
+    t_step = t_train + t_eval
+    desc = (f"oracle port (torch-CPU restatement of the reference epoch body, ensemble2.py:51-88) on one synthetic subgraph of "
+            f"{sample_n} x {p}, k={k}: graph build {t_graph:.1f}s (not in the rate), train step {t_train:.2f}s + eval forward {t_eval:.2f}s; scaled linearly in nodes to "
+            f"{B} x {per} train + {test_n} test nodes")
+    return 1.0 / t_epoch, desc, cores
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return None
+    rates = []
+    desc, cores = "", 1
+    for _ in range(max(1, a.steps)):
+        r, desc, cores = cpu_epoch_rate(a, a.cpu_sample)
+        rates.append(r)
+    value = float(np.mean(rates))
+    N, p, k, B = a.individuals, a.markers, a.neighbours, a.batches
+    return {
+        "impl": "reference", "metric": "train epochs/sec", "value": value, "unit": "epochs/s", "n_gpus": a.gpus,
+        "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1000.0 / value, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"C5: synthetic {N} individuals x {p} SNPs, k={k}, {B} subgraph batches (CPU: bounded sample, scaled)"},
+        "cpu_baseline": {"value": value, "unit": "epochs/s", "cores": cores, "kind": "port", "sample": desc},
+        "e2e": {"value": value, "unit": "epochs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        line = run_reference(a)
+    else:
+        line = run_ours(a)
+        if line is not None and not a.no_cpu_baseline and line["n_gpus"] == 1:
+            v, desc, cores = cpu_epoch_rate(a, a.cpu_sample)
+            line["cpu_baseline"] = {"value": v, "unit": "epochs/s", "cores": cores, "kind": "port", "sample": desc}
+    if line is not None:
+        print(json.dumps(line), flush=True)
+    try:
+        import torch.distributed as dist
+        if dist.is_initialized():
+            dist.destroy_process_group()
+    except Exception:
+        pass
+
+
+if __name__ == "__main__":
+    main()

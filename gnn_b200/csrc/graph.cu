@@ -191,8 +191,9 @@ static size_t csr_ws_layout(void* ws, size_t bytes, int64_t n, int64_t n_edges, 
     c.block_sums = cv.take<int32_t>(scan_blocks(n));
     c.totals = cv.take<int64_t>(2);
     c.dis = cv.take<float>(n);
-    c.rec_in = cv.take<Rec>((size_t)n_edges + 1);
-    c.rec_out = cv.take<Rec>((size_t)n_edges + 1);
+    // segments are laid out by the final rowptr, which reserves one slot per row for the self loop
+    c.rec_in = cv.take<Rec>((size_t)n_edges + (size_t)n + 1);
+    c.rec_out = cv.take<Rec>((size_t)n_edges + (size_t)n + 1);
     if (out) *out = c;
     return cv.off;
 }

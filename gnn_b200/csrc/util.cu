@@ -327,8 +327,9 @@ int gnnb_synth_genotypes(int8_t* X, int64_t n, int64_t p, int64_t ld, int64_t ro
 int gnnb_gather_rows_i8(const int8_t* X, int64_t ldx, const int64_t* rows, int64_t n_rows, int64_t p,
                         int8_t* out, int64_t ldo, void* stream) {
     GNNB_ENTER();
-    GNNB_REQUIRE(X && rows && out && n_rows >= 0 && p > 0 && ldx >= p && ldo >= p, GNNB_E_BADARG, "gather_rows: bad argument");
+    GNNB_REQUIRE(n_rows >= 0 && p > 0 && ldx >= p && ldo >= p, GNNB_E_BADARG, "gather_rows: bad shape");
     if (n_rows == 0) return GNNB_OK;
+    GNNB_REQUIRE(X && rows && out, GNNB_E_BADARG, "gather_rows: null pointer");
     int vec16 = (ldx % 16 == 0) && (ldo % 16 == 0) && ((uintptr_t)X % 16 == 0) && ((uintptr_t)out % 16 == 0);
     int64_t cap = (int64_t)sm_count() * 16;
     gather_rows_kernel<<<(unsigned)(n_rows < cap ? n_rows : cap), 256, 0, (cudaStream_t)stream>>>(

@@ -188,6 +188,10 @@ class _ILoc:
         if isinstance(key, tuple):          # df.iloc[start:stop, :]
             key = key[0]
         n = len(self.t)
+        if isinstance(key, slice) and key.step in (None, 1):
+            a, b, _ = key.indices(n)                       # contiguous rows: a view, no copy (util.py:82)
+            b = max(a, b)
+            return GenotypeTable(self.t.markers[a:b], self.t.value[a:b], self.t.index[a:b])
         if isinstance(key, slice):
             rows = np.arange(n)[key]
         else:

@@ -56,7 +56,7 @@ def split_indices_graph(table, batches, neighbours=5):
     cache = table.__dict__.setdefault("_partition_order", {})
     order = cache.get(neighbours)
     if order is None:       # the reference rebuilds this graph for every split of the same frame (load.py:203, :238)
-        extra = torch.from_numpy(table.value.reshape(-1, 1))
+        extra = torch.from_numpy(np.array(table.value, dtype=np.float64).reshape(-1, 1))
         idx, _ = ops.knn(table.markers, neighbours, extra=extra)
         first_pos = ops.first_occurrence(idx).cpu().numpy()      # device scatter-min, then one D2H of n int64
         seen = np.nonzero(first_pos != np.iinfo(np.int64).max)[0]
@@ -75,7 +75,7 @@ def split_dataset_graph(df, batches, neighbours=5, metric='euclidian', partition
         parts = split_indices_graph(table, batches, neighbours)
     else:
         # any other partitioner gets what the reference gives it: the (row, col) edge list (util.py:59-68)
-        extra = torch.from_numpy(table.value.reshape(-1, 1))
+        extra = torch.from_numpy(np.array(table.value, dtype=np.float64).reshape(-1, 1))
         idx, _ = ops.knn(table.markers, neighbours, extra=extra)
         nbr = idx.cpu().numpy()
         edges = [(i, int(c)) for i in range(nbr.shape[0]) for c in nbr[i]]

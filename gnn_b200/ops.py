@@ -41,10 +41,48 @@ def _ws(nbytes, device):
     return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
 
 
+class Profiler:
+    """CUDA-event timing of every C-ABI call on the launching stream, with the algorithmic work each call
+    declares (bench.py derives the roofline numbers from this; events cost ~1 us per call)."""
+
+    def __init__(self):
+        self.records = []            # (name, work_dict, start_event, end_event)
+
+    def summary(self):
+        torch.cuda.synchronize()
+        out = {}
+        for name, work, e0, e1 in self.records:
+            slot = out.setdefault(name, {"calls": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
+            slot["calls"] += 1
+            slot["ms"] += e0.elapsed_time(e1)
+            slot["flops"] += work.get("flops", 0.0)
+            slot["bytes"] += work.get("bytes", 0.0)
+        return out
+
+
+profiler = None                 # set to a Profiler() to time calls
+_work = {}                      # algorithmic work of the next call (set by the wrappers below)
+
+
 def _call(name, *args):
-    global _launches
+    global _launches, _work
     _launches += 1
-    return _lib.call(name, *args)
+    if profiler is None:
+        _work = {}
+        return _lib.call(name, *args)
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    rc = _lib.call(name, *args)
+    e1.record()
+    profiler.records.append((name, _work, e0, e1))
+    _work = {}
+    return rc
+
+
+def _declare(**work):
+    global _work
+    _work = work
 
 
 # --------------------------------------------------------------------------------------- staging
@@ -102,6 +140,7 @@ def knn_block(Q, sq_q, q_off, K, sq_k, k_off, k, best_d2, best_idx, merge, extra
     with torch.cuda.device(Q.device):
         nbytes = _lib.workspace_bytes("gnnb_knn_workspace_bytes", Q.shape[0], K.shape[0], Q.shape[1], k, impl)
         ws = _ws(nbytes, Q.device)
+        _declare(flops=2.0 * Q.shape[0] * K.shape[0] * Q.shape[1])
         _call("gnnb_knn_i8", _p(Q), Q.stride(0), _p(sq_q), Q.shape[0], q_off,
               _p(K), K.stride(0), _p(sq_k), K.shape[0], k_off, Q.shape[1],
               _p(extra_q), _p(extra_k), n_extra, k, _p(best_d2), _p(best_idx), int(merge), impl,
@@ -226,6 +265,9 @@ def spmm(rowptr, col, val, H, bias=None, n=None):
         H = H.to(torch.float32).contiguous()
     n = rowptr.numel() - 1 if n is None else n
     out = torch.empty((n, H.shape[1]), dtype=torch.float32, device=H.device)
+    nnz = int(col.numel())
+    F = int(H.shape[1])
+    _declare(bytes=float(nnz * (F * 4 + 8) + n * F * 4 + (n + 1) * 4 + n * 4 + F * 4))    # AGG_BYTES, SURVEY.md 8d
     with torch.cuda.device(H.device):
         _call("gnnb_spmm", _p(rowptr), _p(col), _p(val), n, _p(H), H.stride(0), H.shape[1],
               _p(bias), _p(out), out.stride(0), _stream())
@@ -255,6 +297,7 @@ def linear_fwd(X, W, precision=None):
     H = torch.empty((n, h), dtype=torch.float32, device=X.device)
     with torch.cuda.device(X.device):
         ws = _ws(_lib.workspace_bytes("gnnb_linear_workspace_bytes", n, p, h, prec), X.device)
+        _declare(flops=2.0 * n * p * h, bytes=float(n * p * X.element_size() + h * p * 4 + n * h * 4))
         _call("gnnb_linear_fwd", _p(X), int(x_is_i8), X.stride(0), n, p, _p(W), W.stride(0), h,
               _p(H), H.stride(0), prec, _p(ws), ws.numel(), _stream())
     return H
@@ -275,6 +318,7 @@ def linear_bwd_w(X, dH, precision=None):
     dW = torch.empty((h, p), dtype=torch.float32, device=X.device)
     with torch.cuda.device(X.device):
         ws = _ws(_lib.workspace_bytes("gnnb_linear_workspace_bytes", n, p, h, prec), X.device)
+        _declare(flops=2.0 * n * p * h, bytes=float(n * p * X.element_size() + h * p * 4 + n * h * 4))
         _call("gnnb_linear_bwd_w", _p(X), int(x_is_i8), X.stride(0), n, p, _p(dH), dH.stride(0), h,
               _p(dW), dW.stride(0), prec, _p(ws), ws.numel(), _stream())
     return dW
@@ -288,6 +332,7 @@ def linear_bwd_x(dH, W):
     n, h = dH.shape
     p = W.shape[1]
     dX = torch.empty((n, p), dtype=torch.float32, device=dH.device)
+    _declare(flops=2.0 * n * p * h)
     with torch.cuda.device(dH.device):
         _call("gnnb_linear_bwd_x", _p(dH), dH.stride(0), n, h, _p(W), W.stride(0), p, _p(dX), dX.stride(0), _stream())
     return dX

@@ -1,0 +1,125 @@
+"""Data-parallel training over subsampled subgraphs: one process per GPU, NCCL over NVLink.
+
+The reference has no distributed code; its closest analogue is ``train_batches``
+(gnn/trainers/batches.py:31-68), one optimiser step per subgraph.  Here subgraphs are independent units:
+rank r owns batches r, r + G, r + 2G, ...; one step = every rank runs forward/backward on its next
+subgraph, the flat fp32 gradient buffer is summed with ONE all-reduce and divided by G, and every rank
+applies the same Adam step.  The per-epoch evaluation on the test graph shards the expensive marker
+projection by rows and all-gathers the [n, h] result; the cheap remainder is replicated.
+
+Nothing here needs a GPU to be tested: the host logic runs under gloo in tests/test_dp_gloo.py.
+"""
+import os
+
+import torch
+import torch.distributed as dist
+
+
+def init_distributed(backend=None):
+    """(rank, world, local_rank) from the torchrun environment; initialises the process group if world > 1."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if backend == "nccl":
+            torch.cuda.set_device(local_rank)
+        dist.init_process_group(backend=backend, rank=rank, world_size=world)
+    return rank, world, local_rank
+
+
+def owned(n_items, rank, world):
+    """Indices of the units (subgraph batches) rank owns: round robin."""
+    return list(range(rank, n_items, world))
+
+
+def row_shard(n_rows, rank, world, align=128):
+    """[lo, hi) of the rows rank projects in the sharded evaluation; shard sizes are multiples of `align`."""
+    per = (n_rows + world - 1) // world
+    per = (per + align - 1) // align * align
+    lo = min(n_rows, rank * per)
+    return lo, min(n_rows, lo + per)
+
+
+class FlatGrads:
+    """All gradients of a model as views into one contiguous fp32 buffer -> a single all-reduce per step."""
+
+    def __init__(self, params):
+        self.params = [p for p in params if p.requires_grad]
+        total = sum(p.numel() for p in self.params)
+        dev = self.params[0].device
+        self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
+        off = 0
+        for p in self.params:
+            p.grad = self.flat[off:off + p.numel()].view_as(p)
+            off += p.numel()
+
+    def zero(self):
+        self.flat.zero_()
+
+    def allreduce_mean(self, world, group=None):
+        if world > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
+            self.flat.div_(world)
+
+
+def broadcast_parameters(model, src=0):
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        for p in model.parameters():
+            dist.broadcast(p.data, src=src)
+        for b in model.buffers():
+            dist.broadcast(b.data, src=src)
+
+
+def allgather_rows(local, n_rows, rank, world, align=128):
+    """Concatenate row shards [lo_r, hi_r) of an [n_rows, F] matrix held one per rank."""
+    if world == 1:
+        return local
+    per = row_shard(n_rows, 0, world, align)[1]
+    pad = torch.zeros((per, local.shape[1]), dtype=local.dtype, device=local.device)
+    pad[:local.shape[0]] = local
+    out = torch.empty((world * per, local.shape[1]), dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(out, pad)
+    return out[:n_rows]
+
+
+def dp_step(model, flat, optimizer, batch, world, loss_func, args_of):
+    """One data-parallel optimiser step on this rank's subgraph; returns the local loss (0-d tensor)."""
+    model.train()
+    flat.zero()
+    out = model(*args_of(batch))
+    loss = loss_func(out, batch.y)
+    loss.backward()
+    flat.allreduce_mean(world)
+    optimizer.step()
+    return loss.detach()
+
+
+@torch.no_grad()
+def sharded_eval(model, data, rank, world, args_of):
+    """Eval-mode forward on the test graph with the first layer's projection sharded by rows."""
+    from . import ops
+    from .networks.gcn_conv import GCNConv
+    model.eval()
+    args = args_of(data)
+    first = model.nns[0]
+    if world == 1 or not isinstance(first, GCNConv):
+        return model(*args)
+    x, edge_index = args[0], args[1]
+    edge_weight = args[2] if len(args) > 2 else None
+    n = x.shape[0]
+    lo, hi = row_shard(n, rank, world)
+    h_local = ops.linear_fwd(x[lo:hi], first.lin.weight)
+    h = allgather_rows(h_local, n, rank, world)
+    g = ops.gcn_graph(edge_index, edge_weight, n, first.add_self_loops)
+    out = ops.spmm(g.rowptr, g.col, g.val, h, first.bias, n=n)
+    for m, f, (ins, _) in list(zip(model.nns, model.fns, model.descs))[1:]:
+        call = m if f is None else f
+        if isinstance(m, GCNConv):
+            out = call(out, edge_index, edge_weight) if edge_weight is not None else call(out, edge_index)
+        else:
+            out = call(out)
+    return out

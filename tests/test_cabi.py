@@ -35,7 +35,7 @@ def test_version_and_error_string():
 
 def test_workspace_queries_need_no_gpu():
     assert _lib.workspace_bytes("gnnb_graph_workspace_bytes", 1000, 8) > 2 * 1000 * 8 * 16
-    assert _lib.workspace_bytes("gnnb_csr_workspace_bytes", 1000, 9000) > 2 * 9000 * 16
+    assert _lib.workspace_bytes("gnnb_csr_workspace_bytes", 1000, 9000) > 2 * (9000 + 1000) * 16
     assert _lib.workspace_bytes("gnnb_knn_workspace_bytes", 1000, 1000, 128, 32, 0) > 1000 * 32 * 12
     assert _lib.workspace_bytes("gnnb_colsum_workspace_bytes", 100) == 1024 * 100 * 4
     with pytest.raises(_lib.GnnbError):

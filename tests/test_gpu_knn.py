@@ -119,7 +119,7 @@ def test_unfilled_slots_and_errors():
     with pytest.raises(ValueError):
         ops.knn(X, 5)
     from gnn_b200._lib import GnnbError
-    with pytest.raises(GnnbError, match="outside 1.."):
+    with pytest.raises(GnnbError, match="1..64"):
         ops.knn_block(X, sq, 0, X, sq, 0, 65, bd, bi, merge=0)
 
 
