@@ -48,7 +48,8 @@ def distance_correlation(a, b, max_n=16384):
     A, B = centred(a), centred(b)
     dcov2 = (A * B).mean()
     dvar = torch.sqrt((A * A).mean() * (B * B).mean())
-    return torch.sqrt(torch.clamp(dcov2, min=0.0) / dvar)
+    r2 = torch.where(dvar > 0, torch.clamp(dcov2, min=0.0) / dvar.clamp_min(1e-300), torch.zeros_like(dvar))
+    return torch.sqrt(r2)                                       # 0 for a constant vector, as dcor returns
 
 
 def to_host(*scalars):
