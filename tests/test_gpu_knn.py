@@ -32,7 +32,7 @@ def check(X, k, extra=None, impl=None, pad=True):
     assert bad.size == 0, f"{bad.size} rows differ, first {bad[:5]}: got {idx[bad[0]]} {d2[bad[0]]} want {ridx[bad[0]]} {rd2[bad[0]]}"
 
 
-@pytest.mark.parametrize("impl", [1, 0])
+@pytest.mark.parametrize("impl", [1, 2, 0])
 def test_wheat_golden(wheat, golden, impl):
     X, y = wheat
     g = golden("wheat_knn.npz")
@@ -45,7 +45,7 @@ def test_wheat_golden(wheat, golden, impl):
         assert np.array_equal(a, g["idx_all"][:, :k]) and np.array_equal(b, g["d2_all"][:, :k].astype(np.float64))
 
 
-@pytest.mark.parametrize("impl", [1, 0])
+@pytest.mark.parametrize("impl", [1, 2, 0])
 def test_wheat_with_phenotype_column(wheat, golden, impl):
     """The partition graph keeps the float phenotype column (util.py:52-53): float64 epilogue, bit-exact."""
     X, y = wheat
@@ -57,9 +57,19 @@ def test_wheat_with_phenotype_column(wheat, golden, impl):
 
 @pytest.mark.parametrize("n,p,k", [(130, 64, 1), (257, 100, 5), (1000, 777, 32), (64, 13, 63), (65, 1279, 64), (2, 5, 1),
                                    (3000, 256, 10)])
-@pytest.mark.parametrize("impl", [1, 0])
+@pytest.mark.parametrize("impl", [1, 2, 0])
 def test_synthetic_shapes(n, p, k, impl):
     check(synth.genotypes(n, p, seed=11 + n), k, impl=impl)
+
+
+@pytest.mark.parametrize("n,p,k", [(128, 128, 3), (129, 257, 32), (1000, 4096, 33), (2500, 130, 64), (5000, 1279, 16)])
+def test_tensor_core_path_equals_cuda_core_path(n, p, k):
+    """impl=2 (tcgen05 int8 tiles) and impl=1 (dp4a tiles) must produce the same bits."""
+    X = dev_i8(synth.genotypes(n, p, seed=n + p))
+    a_i, a_d = ops.knn(X, k, impl=1)
+    b_i, b_d = ops.knn(X, k, impl=2)
+    torch.cuda.synchronize()
+    assert torch.equal(a_i, b_i) and torch.equal(a_d, b_d)
 
 
 def test_unpadded_rows_and_general_int8_codes():
@@ -73,14 +83,16 @@ def test_duplicates_and_heavy_ties():
     X = synth.genotypes(200, 40, seed=3)
     X[10] = X[4]; X[11] = X[4]; X[150:160] = X[0]
     check(X, 12, impl=1)
-    check(X, 12, impl=0)
-    check(np.zeros((90, 33), dtype=np.int8), 20, impl=0)    # every distance equal: order is by index alone
+    check(X, 12, impl=2)
+    check(np.zeros((90, 33), dtype=np.int8), 20, impl=0)
+    check(np.zeros((300, 64), dtype=np.int8), 20, impl=2)    # every distance equal: order is by index alone
 
 
 def test_two_float_columns():
     X = synth.genotypes(400, 90, seed=8)
     extra = np.random.default_rng(1).standard_normal((400, 2))
-    check(X, 9, extra=extra, impl=0)
+    check(X, 9, extra=extra, impl=1)
+    check(X, 9, extra=extra, impl=2)
 
 
 def test_streaming_key_blocks_equal_one_pass():
