@@ -126,6 +126,33 @@ int linear_tc_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t 
                     float* dW, int64_t lddw, int terms, void* ws, size_t ws_bytes, cudaStream_t stream);
 size_t linear_tc_workspace(int64_t n, int64_t p, int64_t h, int terms);
 
+int linear_simt_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* W, int64_t ldw, int64_t h,
+                    float* H, int64_t ldh, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+    int splits = pick_splits(n, h, p);
+    size_t need = splits > 1 ? (size_t)splits * n * h * sizeof(float) : 0;
+    if (need > 0 && (!workspace || workspace_bytes < need)) splits = 1;      // no scratch: single pass over K
+    if (x_is_i8)
+        return launch_gemm<int8_t, true, true>((const int8_t*)X, ldx, 1, W, 1, ldw, H, ldh, 1, n, h, p, splits,
+                                               (float*)workspace, stream);
+    return launch_gemm<float, true, true>((const float*)X, ldx, 1, W, 1, ldw, H, ldh, 1, n, h, p, splits,
+                                          (float*)workspace, stream);
+}
+
+int linear_simt_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
+                      float* dW, int64_t lddw, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+    // dW[f, j] = sum_i dH[i, f] * X[i, j], run as dW^T so that the typed operand X is A:
+    //   M = p, N = h, K = n, A(m, k) = X[k, m] (contiguous along m), B(k, n) = dH[k, n] (contiguous along n),
+    //   C(m, n) -> dW[n * lddw + m]
+    int splits = pick_splits(p, h, n);
+    size_t need = splits > 1 ? (size_t)splits * h * p * sizeof(float) : 0;
+    if (need > 0 && (!workspace || workspace_bytes < need)) splits = 1;
+    if (x_is_i8)
+        return launch_gemm<int8_t, false, false>((const int8_t*)X, 1, ldx, dH, lddh, 1, dW, 1, lddw, p, h, n, splits,
+                                                 (float*)workspace, stream);
+    return launch_gemm<float, false, false>((const float*)X, 1, ldx, dH, lddh, 1, dW, 1, lddw, p, h, n, splits,
+                                            (float*)workspace, stream);
+}
+
 }  // namespace gnnb
 
 using namespace gnnb;
@@ -151,14 +178,7 @@ int gnnb_linear_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t 
     GNNB_REQUIRE(precision >= 0 && precision <= 3, GNNB_E_BADARG, "linear_fwd: precision must be 0..3");
     if (n == 0) return GNNB_OK;
     if (precision > 0) return linear_tc_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, precision, workspace, workspace_bytes, stream);
-    int splits = pick_splits(n, h, p);
-    size_t need = splits > 1 ? (size_t)splits * n * h * sizeof(float) : 0;
-    if (need > 0 && (!workspace || workspace_bytes < need)) splits = 1;      // no scratch: single pass over K
-    if (x_is_i8)
-        return launch_gemm<int8_t, true, true>((const int8_t*)X, ldx, 1, W, 1, ldw, H, ldh, 1, n, h, p, splits,
-                                               (float*)workspace, stream);
-    return launch_gemm<float, true, true>((const float*)X, ldx, 1, W, 1, ldw, H, ldh, 1, n, h, p, splits,
-                                          (float*)workspace, stream);
+    return linear_simt_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, workspace, workspace_bytes, stream);
 }
 
 int gnnb_linear_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
@@ -168,24 +188,13 @@ int gnnb_linear_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_
     cudaStream_t stream = (cudaStream_t)stream_;
     GNNB_REQUIRE(X && dH && dW && n >= 0 && p > 0 && h > 0 && ldx >= p && lddh >= h && lddw >= p, GNNB_E_BADARG, "linear_bwd_w: bad argument");
     GNNB_REQUIRE(precision >= 0 && precision <= 3, GNNB_E_BADARG, "linear_bwd_w: precision must be 0..3");
-    if (precision > 0 && n > 0)
-        return linear_tc_bwd_w(X, x_is_i8, ldx, n, p, dH, lddh, h, dW, lddw, precision, workspace, workspace_bytes, stream);
-    // dW[f, j] = sum_i dH[i, f] * X[i, j], run as dW^T so that the typed operand X is A:
-    //   M = p, N = h, K = n, A(m, k) = X[k, m] (contiguous along m), B(k, n) = dH[k, n] (contiguous along n),
-    //   C(m, n) -> dW[n * lddw + m]
     if (n == 0) {
         GNNB_CUDA(cudaMemset2DAsync(dW, lddw * sizeof(float), 0, p * sizeof(float), h, stream));
         return GNNB_OK;
     }
-    int splits = pick_splits(p, h, n);
-    size_t need = splits > 1 ? (size_t)splits * h * p * sizeof(float) : 0;
-    GNNB_REQUIRE(need == 0 || (workspace && workspace_bytes >= need), GNNB_E_WORKSPACE, "linear_bwd_w: workspace %zu < %zu bytes",
-                 workspace_bytes, need);
-    if (x_is_i8)
-        return launch_gemm<int8_t, false, false>((const int8_t*)X, 1, ldx, dH, lddh, 1, dW, 1, lddw, p, h, n, splits,
-                                                 (float*)workspace, stream);
-    return launch_gemm<float, false, false>((const float*)X, 1, ldx, dH, lddh, 1, dW, 1, lddw, p, h, n, splits,
-                                            (float*)workspace, stream);
+    if (precision > 0)
+        return linear_tc_bwd_w(X, x_is_i8, ldx, n, p, dH, lddh, h, dW, lddw, precision, workspace, workspace_bytes, stream);
+    return linear_simt_bwd_w(X, x_is_i8, ldx, n, p, dH, lddh, h, dW, lddw, workspace, workspace_bytes, stream);
 }
 
 int gnnb_linear_bwd_x(const float* dH, int64_t lddh, int64_t n, int64_t h,

@@ -1,13 +1,334 @@
-// K5 on tcgen05 tensor cores -- placeholder until the TMA/TMEM kernels land.
-#include "common.cuh"
+// K5 on the 5th-generation tensor cores: the marker projection H = X . W^T and its weight gradient
+// dW = dH^T . X for int8 genotype codes X, fp32 W / dH, fp32 accumulation in TMEM.
+//
+// Replaces GCNConv.lin (PyG Linear(bias=False) -> torch.matmul, and its autograd) for the first layer, where
+// p = #markers is large; call sites gnn/networks/networks.py:271-272 and the other GCN factories.
+//
+// Precision: the genotype codes (0..127) are exact in bf16.  The fp32 operand (W, or dH) is split into T bf16
+// terms (hi, mid, lo) whose products with X are accumulated in the same fp32 TMEM accumulator:
+// T = 1 is a plain bf16 projection, T = 2 carries ~16 mantissa bits (rel. error ~1e-5), T = 3 is fp32-faithful.
+//
+// X stays int8 in HBM (1 byte per element, the only large stream).  Per k-block a TMA load brings the raw int8
+// tile into a staging ring; four converter warps expand it to bf16 directly into the 128-byte-swizzled UMMA
+// operand layout (prmt + one packed bf16 subtract per pair); the fp32 operand's bf16 terms arrive by TMA from
+// an L2-resident workspace that a small prep kernel fills once per call.
+//
+//   forward  : CTA = 128 rows of X.     A = X tile (K-major),     B = W terms  [h_pad x 64]  (K-major),  D[128 x h_pad]
+//   backward : CTA = 128 columns of X.  A = X^T tile (MN-major),  B = dH terms [64 x 128]    (MN-major), D[128 x 128]
+//
+// warps: 0 = TMA producer (X), 3 = TMA producer (terms), 1 = MMA issuer, 2 = TMEM allocator,
+//        4-7 = converter, then epilogue (TMEM -> registers -> global).
+#include <cuda_bf16.h>
+
+#include "tc_common.cuh"
+
 namespace gnnb {
-int linear_tc_fwd(const void*, int, int64_t, int64_t, int64_t, const float*, int64_t, int64_t, float*, int64_t, int, void*, size_t,
-                  cudaStream_t) {
-    return fail(GNNB_E_UNSUPPORTED, "linear_fwd: tensor-core precision modes are not built into this library");
+
+using namespace tc;
+
+namespace {
+constexpr int BM = 128;                 // rows (fwd) / columns (bwd) of X per CTA == UMMA M
+constexpr int BK = 64;                  // k elements per block
+constexpr int CW = 4;                   // converter warps; warp c owns k-blocks c, c + CW, ... (whole tiles, so that
+                                        // four conversions are in flight and their latencies overlap)
+constexpr int NX = 8, NA = 4, NB_MAX = 4;   // ring depths; NX and NA are multiples of CW so that a ring slot is only
+                                            // ever touched by one converter warp (no phase aliasing between warps)
+static_assert(NX % CW == 0 && NA % CW == 0, "ring slots must map to a single converter warp");
+constexpr int X_STAGE_BYTES = BM * BK;              // int8: fwd 128 rows x 64 B, bwd 64 rows x 128 B
+constexpr int A_BYTES = BM * BK * 2;                // bf16 operand tile
+constexpr int MAX_TERMS = 3;
+
+struct Bars {
+    uint64_t x_full[NX], x_empty[NX], a_full[NA], a_empty[NA], b_full[NB_MAX], b_empty[NB_MAX], acc_full;
+    uint32_t tmem_ptr;
+};
+
+constexpr size_t SMEM_LIMIT = 232448;       // 227 KB of dynamic shared memory per CTA
+__host__ __device__ inline size_t tc_smem_fixed() { return 1024 + (size_t)NX * X_STAGE_BYTES + (size_t)NA * A_BYTES + sizeof(Bars) + 64; }
+// stages of the bf16-term ring that fit next to the int8 staging ring and the operand ring
+__host__ __device__ inline int nb_stages(int terms, int b_tile_bytes) {
+    size_t per = (size_t)terms * b_tile_bytes;
+    int nb = (int)((SMEM_LIMIT - tc_smem_fixed()) / per);
+    return nb > NB_MAX ? NB_MAX : nb;
 }
-int linear_tc_bwd_w(const void*, int, int64_t, int64_t, int64_t, const float*, int64_t, int64_t, float*, int64_t, int, void*, size_t,
-                    cudaStream_t) {
-    return fail(GNNB_E_UNSUPPORTED, "linear_bwd_w: tensor-core precision modes are not built into this library");
+__host__ __device__ inline size_t tc_smem_bytes(int terms, int b_tile_bytes) {
+    return tc_smem_fixed() + (size_t)nb_stages(terms, b_tile_bytes) * terms * b_tile_bytes;
 }
-size_t linear_tc_workspace(int64_t, int64_t, int64_t, int) { return 0; }
+
+// fp32 -> up to three bf16 terms: x ~ hi + mid + lo
+__device__ __forceinline__ void split3(float x, __nv_bfloat16& hi, __nv_bfloat16& mid, __nv_bfloat16& lo) {
+    hi = __float2bfloat16_rn(x);
+    float r = x - __bfloat162float(hi);
+    mid = __float2bfloat16_rn(r);
+    lo = __float2bfloat16_rn(r - __bfloat162float(mid));
+}
+
+// out[t][r][c] (t < terms, r < rows_out, c < cols_out, row stride ld_out) = term t of in[r][c], zero outside [rows, cols]
+__global__ void split_terms_kernel(const float* __restrict__ in, int64_t ld_in, int64_t rows, int64_t cols,
+                                   __nv_bfloat16* __restrict__ out, int64_t rows_out, int64_t cols_out, int64_t ld_out, int terms) {
+    int64_t total = rows_out * cols_out;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t r = i / cols_out, c = i % cols_out;
+        float x = (r < rows && c < cols) ? in[r * ld_in + c] : 0.f;
+        __nv_bfloat16 t0, t1, t2;
+        split3(x, t0, t1, t2);
+        out[r * ld_out + c] = t0;
+        if (terms > 1) out[rows_out * ld_out + r * ld_out + c] = t1;
+        if (terms > 2) out[2 * rows_out * ld_out + r * ld_out + c] = t2;
+    }
+}
+
+// 16 int8 codes in [0, 127] -> 16 bf16, exactly: bytes are spliced under the exponent of 128.0 (0x4300 | b = 128 + b)
+// and 128.0 is subtracted with one packed bf16 op per pair.
+__device__ __forceinline__ void cvt16(const uint4& in, uint4& lo, uint4& hi) {
+    const __nv_bfloat162 k128 = __halves2bfloat162(__ushort_as_bfloat16((unsigned short)0x4300), __ushort_as_bfloat16((unsigned short)0x4300));
+    const uint32_t w[4] = {in.x, in.y, in.z, in.w};
+    uint32_t o[8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        uint32_t p0 = __byte_perm(w[i], 0x43434343u, 0x4140);      // {b0, 0x43, b1, 0x43}
+        uint32_t p1 = __byte_perm(w[i], 0x43434343u, 0x4342);      // {b2, 0x43, b3, 0x43}
+        __nv_bfloat162 q0 = __hsub2(*reinterpret_cast<__nv_bfloat162*>(&p0), k128);
+        __nv_bfloat162 q1 = __hsub2(*reinterpret_cast<__nv_bfloat162*>(&p1), k128);
+        o[2 * i] = *reinterpret_cast<uint32_t*>(&q0);
+        o[2 * i + 1] = *reinterpret_cast<uint32_t*>(&q1);
+    }
+    lo = make_uint4(o[0], o[1], o[2], o[3]);
+    hi = make_uint4(o[4], o[5], o[6], o[7]);
+}
+}  // namespace
+
+// BWD = false: D[m = row of X, n = feature]   += sum_k X[m, k] * W_t[n, k]
+// BWD = true : D[m = column of X, n = feature] += sum_k X[k, m] * dH_t[k, n]
+template <bool BWD>
+__global__ void __launch_bounds__(256, 1)
+linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
+                 int64_t k_total, int terms, int n_pad, int64_t b_term_rows,
+                 float* __restrict__ out, int64_t ld_out, int64_t m_total, int n_valid) {
+    extern __shared__ uint8_t smem_raw[];
+    const int warp = threadIdx.x >> 5;
+    uint8_t* base = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);
+    const int b_tile_bytes = BWD ? (BK * 128 * 2) : (n_pad * BK * 2);     // one term: bwd 2 groups x 64 k x 128 B; fwd n_pad x 128 B
+    const int NB = nb_stages(terms, b_tile_bytes);
+    uint8_t* x_stage = base;
+    uint8_t* a_tiles = x_stage + NX * X_STAGE_BYTES;
+    uint8_t* b_tiles = a_tiles + NA * A_BYTES;
+    Bars* bars = reinterpret_cast<Bars*>(b_tiles + (size_t)NB * terms * b_tile_bytes);
+    const int n_kb = (int)((k_total + BK - 1) / BK);
+    const int64_t m0 = (int64_t)blockIdx.x * BM;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NX; ++s) { mbar_init(&bars->x_full[s], 1); mbar_init(&bars->x_empty[s], 1); }
+        for (int s = 0; s < NA; ++s) { mbar_init(&bars->a_full[s], 1); mbar_init(&bars->a_empty[s], 1); }
+        for (int s = 0; s < NB; ++s) { mbar_init(&bars->b_full[s], 1); mbar_init(&bars->b_empty[s], 1); }
+        mbar_init(&bars->acc_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc<128>(&bars->tmem_ptr);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = bars->tmem_ptr;
+
+    if (warp == 0) {
+        // ===================================================== TMA producer: raw int8 tiles of X
+        if (elect_one()) {
+            prefetch_tensormap(&map_x);
+            for (int kb = 0; kb < n_kb; ++kb) {
+                const int s = kb % NX;
+                mbar_wait(&bars->x_empty[s], ((kb / NX) & 1) ^ 1);
+                mbar_arrive_expect_tx(&bars->x_full[s], X_STAGE_BYTES);
+                if (BWD) tma_load_2d(x_stage + s * X_STAGE_BYTES, &map_x, &bars->x_full[s], (int32_t)m0, kb * BK);   // [64 k-rows x 128 cols]
+                else     tma_load_2d(x_stage + s * X_STAGE_BYTES, &map_x, &bars->x_full[s], kb * BK, (int32_t)m0);   // [128 rows x 64 k]
+            }
+        }
+    } else if (warp == 3) {
+        // ===================================================== TMA producer: bf16 terms of the fp32 operand
+        if (elect_one()) {
+            prefetch_tensormap(&map_b);
+            for (int kb = 0; kb < n_kb; ++kb) {
+                const int s = kb % NB;
+                mbar_wait(&bars->b_empty[s], ((kb / NB) & 1) ^ 1);
+                mbar_arrive_expect_tx(&bars->b_full[s], (uint32_t)(terms * b_tile_bytes));
+                uint8_t* dst = b_tiles + (size_t)s * terms * b_tile_bytes;
+                for (int t = 0; t < terms; ++t) {
+                    if (BWD) {   // two 64-feature groups of [64 k-rows x 128 B]
+                        tma_load_2d(dst + t * b_tile_bytes, &map_b, &bars->b_full[s], 0, (int32_t)(t * b_term_rows + kb * BK));
+                        tma_load_2d(dst + t * b_tile_bytes + BK * 128, &map_b, &bars->b_full[s], 64, (int32_t)(t * b_term_rows + kb * BK));
+                    } else {     // [n_pad rows x 64 k]
+                        tma_load_2d(dst + t * b_tile_bytes, &map_b, &bars->b_full[s], kb * BK, (int32_t)(t * b_term_rows));
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================================================== MMA issuer (one thread)
+        if (elect_one()) {
+            const uint32_t idesc = make_idesc(/*F32*/ 1, /*BF16*/ 1, BWD ? 1 : 0, BWD ? 1 : 0, BM, (uint32_t)n_pad);
+            for (int kb = 0; kb < n_kb; ++kb) {
+                const int sa = kb % NA, sb = kb % NB;
+                mbar_wait(&bars->a_full[sa], (kb / NA) & 1);
+                mbar_wait(&bars->b_full[sb], (kb / NB) & 1);
+                tc_fence_after_sync();
+                const uint32_t a_addr = smem_u32(a_tiles + sa * A_BYTES);
+                const uint32_t b_addr0 = smem_u32(b_tiles + (size_t)sb * terms * b_tile_bytes);
+                for (int t = 0; t < terms; ++t) {
+                    const uint32_t b_addr = b_addr0 + t * b_tile_bytes;
+#pragma unroll
+                    for (int k16 = 0; k16 < BK / 16; ++k16) {
+                        uint64_t da, db;
+                        if (BWD) {   // MN-major: 16 k = two 8-row atoms (2048 B); 64-element groups BK * 128 B apart
+                            da = make_smem_desc(a_addr + k16 * 2048, BK * 128, 1024);
+                            db = make_smem_desc(b_addr + k16 * 2048, BK * 128, 1024);
+                        } else {     // K-major: 16 k = 32 B inside the 128-byte row
+                            da = make_smem_desc(a_addr + k16 * 32, 16, 1024);
+                            db = make_smem_desc(b_addr + k16 * 32, 16, 1024);
+                        }
+                        mma_bf16_ss(tmem_base, da, db, idesc, (kb > 0 || t > 0 || k16 > 0) ? 1u : 0u);
+                    }
+                }
+                tc_commit(&bars->a_empty[sa]);
+                tc_commit(&bars->b_empty[sb]);
+            }
+            tc_commit(&bars->acc_full);
+        }
+    } else if (warp >= 4) {
+        // ===================================================== converter: int8 staging -> bf16 UMMA operand
+        const int t = threadIdx.x - 128;
+        const int lane = threadIdx.x & 31, cw = warp - 4;
+        for (int kb = cw; kb < n_kb; kb += CW) {
+            const int sx = kb % NX, sa = kb % NA;
+            mbar_wait(&bars->x_full[sx], (kb / NX) & 1);
+            mbar_wait(&bars->a_empty[sa], ((kb / NA) & 1) ^ 1);
+            const uint8_t* src = x_stage + sx * X_STAGE_BYTES;
+            uint8_t* dst = a_tiles + sa * A_BYTES;
+#pragma unroll 4
+            for (int i = 0; i < 16; ++i) {
+                const int task = i * 32 + lane;                  // 512 16-byte chunks per tile
+                uint4 in, lo, hi;
+                if (BWD) {
+                    // staging [64 k-rows][128 B]: chunk c of row r
+                    const int c = task & 7, r = task >> 3;
+                    in = *reinterpret_cast<const uint4*>(src + r * 128 + c * 16);
+                    cvt16(in, lo, hi);
+                    // MN-major operand: group g = 64 columns, k-row r: 128 B = 8 chunks, chunk j stored at j ^ (r % 8)
+                    const int g = c >> 2, j0 = 2 * (c & 3);
+                    uint8_t* row = dst + g * (BK * 128) + (r >> 3) * 1024 + (r & 7) * 128;
+                    *reinterpret_cast<uint4*>(row + ((j0 ^ (r & 7)) << 4)) = lo;
+                    *reinterpret_cast<uint4*>(row + (((j0 + 1) ^ (r & 7)) << 4)) = hi;
+                } else {
+                    // staging [128 rows][64 B]: chunk c of row r
+                    const int c = task & 3, r = task >> 2;
+                    in = *reinterpret_cast<const uint4*>(src + r * 64 + c * 16);
+                    cvt16(in, lo, hi);
+                    // K-major operand: row r holds 64 k = 128 B = 8 chunks, chunk j stored at j ^ (r % 8)
+                    const int j0 = 2 * c;
+                    uint8_t* row = dst + (r >> 3) * 1024 + (r & 7) * 128;
+                    *reinterpret_cast<uint4*>(row + ((j0 ^ (r & 7)) << 4)) = lo;
+                    *reinterpret_cast<uint4*>(row + (((j0 + 1) ^ (r & 7)) << 4)) = hi;
+                }
+            }
+            fence_proxy_async();                       // generic-proxy stores -> visible to the tensor-core (async) proxy
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(&bars->a_full[sa]);
+                mbar_arrive(&bars->x_empty[sx]);
+            }
+        }
+        // ===================================================== epilogue
+        mbar_wait(&bars->acc_full, 0);
+        tc_fence_after_sync();
+        const int wq = warp & 3;
+        const int64_t m = m0 + t;                      // fwd: row of X; bwd: column of X (marker)
+#pragma unroll 1
+        for (int chunk = 0; chunk * 32 < n_pad; ++chunk) {
+            uint32_t v[32];
+            tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(32 * wq) << 16) + chunk * 32, v);
+            tmem_ld_wait();
+            if (m < m_total) {
+#pragma unroll
+                for (int c = 0; c < 32; ++c) {
+                    const int f = chunk * 32 + c;
+                    if (f < n_valid) {
+                        if (BWD) out[(int64_t)f * ld_out + m] = __uint_as_float(v[c]);     // dW[f, marker]: a warp writes 32 consecutive markers
+                        else     out[m * ld_out + f] = __uint_as_float(v[c]);              // H[row, f]
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc<128>(tmem_base);
+}
+
+static bool tc_shape_ok(const void* X, int64_t ldx, int64_t h) {
+    return (uintptr_t)X % 16 == 0 && ldx % 16 == 0 && h >= 1 && h <= 128;
+}
+
+size_t linear_tc_workspace(int64_t n, int64_t p, int64_t h, int terms) {
+    if (h > 128 || terms < 1 || terms > MAX_TERMS) return 0;
+    size_t p_ld = align_up((size_t)p, 8), h_pad = align_up((size_t)h, 16);
+    size_t fwd = (size_t)terms * h_pad * p_ld * 2;             // W terms   [T][h_pad][p_ld]
+    size_t bwd = (size_t)terms * (size_t)n * 128 * 2;          // dH terms  [T][n][128]
+    return (fwd > bwd ? fwd : bwd) + 1024;
+}
+
+// simt fallbacks live in linear.cu
+int linear_simt_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* W, int64_t ldw, int64_t h,
+                    float* H, int64_t ldh, void* ws, size_t ws_bytes, cudaStream_t stream);
+int linear_simt_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
+                      float* dW, int64_t lddw, void* ws, size_t ws_bytes, cudaStream_t stream);
+
+int linear_tc_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* W, int64_t ldw, int64_t h,
+                  float* H, int64_t ldh, int terms, void* ws, size_t ws_bytes, cudaStream_t stream) {
+    if (!x_is_i8 || !tc_shape_ok(X, ldx, h) || p < 64 || n < 1)
+        return linear_simt_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, ws, ws_bytes, stream);    // small / float inputs: exact fp32 tiles
+    const int64_t p_ld = (int64_t)align_up((size_t)p, 8), h_pad = (int64_t)align_up((size_t)h, 16);
+    const size_t need = (size_t)terms * h_pad * p_ld * 2;
+    GNNB_REQUIRE(ws && ws_bytes >= need + 1024, GNNB_E_WORKSPACE, "linear_fwd: workspace %zu < %zu bytes", ws_bytes, need + 1024);
+    __nv_bfloat16* Wt = reinterpret_cast<__nv_bfloat16*>(align_up((size_t)(uintptr_t)ws, 1024));
+    {
+        int64_t total = h_pad * p_ld, blocks = (total + 255) / 256, cap = (int64_t)sm_count() * 16;
+        split_terms_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, stream>>>(W, ldw, h, p, Wt, h_pad, p_ld, p_ld, terms);
+        GNNB_LAUNCH_CHECK();
+    }
+    CUtensorMap map_x, map_b;
+    int rc = make_tensor_map_2d(&map_x, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, BK, BM, /*swizzle*/ false);
+    if (rc != GNNB_OK) return rc;
+    rc = make_tensor_map_2d(&map_b, Wt, 2, (uint64_t)p_ld, (uint64_t)(terms * h_pad), (uint64_t)p_ld * 2, BK, (uint32_t)h_pad, true);
+    if (rc != GNNB_OK) return rc;
+    const size_t smem = tc_smem_bytes(terms, (int)(h_pad * BK * 2));
+    GNNB_CUDA(cudaFuncSetAttribute(linear_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned grid = (unsigned)((n + BM - 1) / BM);
+    linear_tc_kernel<false><<<grid, 256, smem, stream>>>(map_x, map_b, p, terms, (int)h_pad, h_pad, H, ldh, n, (int)h);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+int linear_tc_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
+                    float* dW, int64_t lddw, int terms, void* ws, size_t ws_bytes, cudaStream_t stream) {
+    if (!x_is_i8 || !tc_shape_ok(X, ldx, h) || p < 128 || n < 64)
+        return linear_simt_bwd_w(X, x_is_i8, ldx, n, p, dH, lddh, h, dW, lddw, ws, ws_bytes, stream);
+    const size_t need = (size_t)terms * (size_t)n * 128 * 2;
+    GNNB_REQUIRE(ws && ws_bytes >= need + 1024, GNNB_E_WORKSPACE, "linear_bwd_w: workspace %zu < %zu bytes", ws_bytes, need + 1024);
+    __nv_bfloat16* Dt = reinterpret_cast<__nv_bfloat16*>(align_up((size_t)(uintptr_t)ws, 1024));
+    {
+        int64_t total = n * 128, blocks = (total + 255) / 256, cap = (int64_t)sm_count() * 16;
+        split_terms_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, stream>>>(dH, lddh, n, h, Dt, n, 128, 128, terms);
+        GNNB_LAUNCH_CHECK();
+    }
+    CUtensorMap map_x, map_b;
+    int rc = make_tensor_map_2d(&map_x, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, 128, BK, /*swizzle*/ false);
+    if (rc != GNNB_OK) return rc;
+    rc = make_tensor_map_2d(&map_b, Dt, 2, 128, (uint64_t)(terms * n), 256, 64, BK, true);
+    if (rc != GNNB_OK) return rc;
+    const size_t smem = tc_smem_bytes(terms, BK * 128 * 2);
+    GNNB_CUDA(cudaFuncSetAttribute(linear_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned grid = (unsigned)((p + BM - 1) / BM);
+    linear_tc_kernel<true><<<grid, 256, smem, stream>>>(map_x, map_b, n, terms, 128, n, dW, lddw, p, (int)h);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
 }  // namespace gnnb

@@ -163,9 +163,9 @@ __host__ __device__ constexpr uint32_t make_idesc(uint32_t c_format, uint32_t ab
 
 // ------------------------------------------------------------------------------------------ host: tensor maps
 // 2-D row-major matrix [rows, cols] of `elem_bytes`-byte elements with row stride `ld_bytes`; box = {box_cols, box_rows};
-// 128-byte swizzle, out-of-bounds elements read as zero.
+// 128-byte swizzle (or none), out-of-bounds elements read as zero.
 int make_tensor_map_2d(CUtensorMap* map, const void* base, int elem_bytes, uint64_t cols, uint64_t rows, uint64_t ld_bytes,
-                       uint32_t box_cols, uint32_t box_rows);
+                       uint32_t box_cols, uint32_t box_rows, bool swizzle128 = true);
 
 }  // namespace tc
 }  // namespace gnnb

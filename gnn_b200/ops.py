@@ -277,8 +277,8 @@ def spmm(rowptr, col, val, H, bias=None, n=None):
 # --------------------------------------------------------------------------------------- K5
 def _precision(n, p, h, x_is_i8):
     prec = config["linear_precision"]
-    if prec == "auto":
-        return 0
+    if prec == "auto":          # int8 genotypes: tcgen05 with a 2-term bf16 split (rel. error ~1e-5); float x: fp32 tiles
+        return 2 if x_is_i8 else 0
     return int(prec)
 
 

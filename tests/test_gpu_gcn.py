@@ -107,6 +107,30 @@ def test_linear_fp32_path(n, p, h, int8_x):
     assert rel_err(ops.linear_bwd_x(dH, W), dH.double() @ W.double()) < 1e-5
 
 
+@pytest.mark.parametrize("n,p,h", [(128, 64, 16), (479, 1279, 100), (1000, 4096, 100), (300, 2050, 128), (130, 200, 7), (4000, 512, 32)])
+@pytest.mark.parametrize("terms,tol", [(3, 1e-5), (2, 5e-5), (1, 8e-3)])
+def test_linear_tensor_core_path(n, p, h, terms, tol):
+    """tcgen05 projection with the fp32 operand split into `terms` bf16 terms, against float64."""
+    X = synth.genotypes(n, p, seed=n + p)
+    buf = torch.zeros((n, (p + 15) // 16 * 16), dtype=torch.int8, device=DEV)
+    buf[:, :p] = torch.from_numpy(X).to(DEV)
+    Xd = buf[:, :p]
+    g = torch.Generator(device="cpu").manual_seed(n)
+    W = (torch.randn(h, p, generator=g) * 0.05).to(DEV)
+    dH = torch.randn(n, h, generator=g).to(DEV)
+    Xf = Xd.double()
+    fwd = ops.linear_fwd(Xd, W, precision=terms)
+    bwd = ops.linear_bwd_w(Xd, dH, precision=terms)
+    torch.cuda.synchronize()
+    assert rel_err(fwd, Xf @ W.double().t()) < tol
+    assert rel_err(bwd, dH.double().t() @ Xf) < tol
+    # general codes up to 127 are exact in bf16 as well
+    Xg = torch.randint(0, 128, (n, p), dtype=torch.int8, device=DEV)
+    buf[:, :p] = Xg
+    assert rel_err(ops.linear_fwd(buf[:, :p], W, precision=3), Xg.double() @ W.double().t()) < 3e-5
+    assert rel_err(ops.linear_bwd_w(buf[:, :p], dH, precision=3), dH.double().t() @ Xg.double()) < 3e-5
+
+
 def oracle_and_mine(name, inp, hidden, asl=True, seed=0):
     torch.manual_seed(seed)
     ref = restate.make_model(name, inp, 1, internal_size=hidden, dropout=0.0, add_self_loops=asl)
