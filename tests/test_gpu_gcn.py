@@ -108,7 +108,7 @@ def test_linear_fp32_path(n, p, h, int8_x):
 
 
 @pytest.mark.parametrize("n,p,h", [(128, 64, 16), (479, 1279, 100), (1000, 4096, 100), (300, 2050, 128), (130, 200, 7), (4000, 512, 32)])
-@pytest.mark.parametrize("terms,tol", [(3, 1e-5), (2, 5e-5), (1, 8e-3)])
+@pytest.mark.parametrize("terms,tol", [(3, 3e-5), (2, 6e-5), (1, 8e-3)])
 def test_linear_tensor_core_path(n, p, h, terms, tol):
     """tcgen05 projection with the fp32 operand split into `terms` bf16 terms, against float64."""
     X = synth.genotypes(n, p, seed=n + p)
