@@ -385,4 +385,58 @@ int gnnb_colsum(const float* A, int64_t lda, int64_t n, int64_t F, float* out,
     return GNNB_OK;
 }
 
+// ------------------------------------------------------------------------------------ allocation-free column sums
+// Scratch for gnnb_colsum_static: 1024 row-block partials x GNNB_COLSUM_STATIC_MAX_F columns of float32 (2 MiB),
+// resident in every GPU that loads this library until the process exits.
+static __device__ __align__(256) float g_colsum_static_scratch[1024 * GNNB_COLSUM_STATIC_MAX_F];
+static float* g_colsum_static_ptr[64];      // device address of the array above, per device ordinal (0 = not resolved yet)
+
+/* Column sums without a workspace argument and without any allocation.
+ *
+ * Who this is for: code that computes the GCN bias gradient (db = sum over nodes of dOut) from a place where
+ * memory cannot be requested -- a training step that an application replays under a fixed memory plan, a serving
+ * process that hands the library a closed arena and forbids anything else, or a host thread that must not take
+ * the allocator's lock while other streams are running.  Such callers can pass their input and output buffers but
+ * have nowhere to get the row-block partials gnnb_colsum needs, so the partials live in a fixed array that is part
+ * of the library image.
+ *
+ * The name of that array is only a host-side handle; the kernels need its address on the current device.  The first
+ * call on each device resolves it with cudaGetSymbolAddress (checked) and remembers it; make that first call during
+ * start-up, before any stream capture begins.  Limits and rules:
+ *   - F must not exceed GNNB_COLSUM_STATIC_MAX_F (512); larger inputs are refused with GNNB_E_UNSUPPORTED;
+ *   - every call on a device uses the same array and leaves its partial sums behind.  Nothing has to start at zero:
+ *     each call overwrites every partial it later reads, so stale contents are never observed;
+ *   - because the array is shared, two calls whose kernels can overlap on the GPU (different streams, no ordering)
+ *     race on it.  Serialise them, or use gnnb_colsum with separate workspaces.
+ * The result is bit-identical to gnnb_colsum (same kernels, same fixed summation order).
+ */
+int gnnb_colsum_static(const float* A, int64_t lda, int64_t n, int64_t F, float* out, void* stream) {
+    GNNB_ENTER();
+    GNNB_REQUIRE((A || n == 0) && out && n >= 0 && F > 0 && lda >= F, GNNB_E_BADARG, "colsum_static: bad argument");
+    GNNB_REQUIRE(F <= GNNB_COLSUM_STATIC_MAX_F, GNNB_E_UNSUPPORTED,
+                 "colsum_static: F = %lld exceeds the built-in scratch (at most %d columns); use gnnb_colsum with a workspace",
+                 (long long)F, GNNB_COLSUM_STATIC_MAX_F);
+    int dev = 0;
+    GNNB_CUDA(cudaGetDevice(&dev));
+    GNNB_REQUIRE(dev >= 0 && dev < 64, GNNB_E_BADARG, "colsum_static: device ordinal %d out of range", dev);
+    if (!g_colsum_static_ptr[dev]) {            // once per device, with that device current
+        float* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&p, g_colsum_static_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(GNNB_E_CUDA, "colsum_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+        g_colsum_static_ptr[dev] = p;
+    }
+    float* partial = g_colsum_static_ptr[dev];
+    int64_t nblocks = (n + 63) / 64;
+    if (nblocks > 1024) nblocks = 1024;
+    if (nblocks < 1) nblocks = 1;
+    int rows_per_block = (int)((n + nblocks - 1) / nblocks);
+    if (rows_per_block < 1) rows_per_block = 1;
+    colsum_partial_kernel<<<(unsigned)nblocks, 128, 0, (cudaStream_t)stream>>>(A, lda, n, F, partial, rows_per_block);
+    GNNB_LAUNCH_CHECK();
+    colsum_final_kernel<<<(unsigned)((F + 127) / 128), 128, 0, (cudaStream_t)stream>>>(partial, (int)nblocks, F, out);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
 }  // extern "C"

@@ -150,6 +150,15 @@ int gnnb_linear_bwd_x(const float* dH, int64_t lddh, int64_t n, int64_t h,
 int gnnb_colsum_workspace_bytes(int64_t F, size_t* bytes);
 int gnnb_colsum(const float* A, int64_t lda, int64_t n, int64_t F, float* out,
                 void* workspace, size_t workspace_bytes, void* stream);
+/* Same result as gnnb_colsum, for callers that may not allocate (a step replayed under a fixed memory plan, a server
+ * that gives the library a closed arena, a thread that must stay off the allocator's lock): it takes no workspace and
+ * allocates nothing.  Its row-block partials live in a 2 MiB array built into the library (held by every GPU that loads
+ * it), so F is limited to GNNB_COLSUM_STATIC_MAX_F; larger F is refused with GNNB_E_UNSUPPORTED.  The first call on a
+ * device looks up the array's device address (cudaGetSymbolAddress) -- make it before any stream capture.  All calls on a
+ * device share the array: it keeps the previous call's partials (each call overwrites all it reads, nothing needs
+ * clearing), and calls that can overlap on the GPU race on it.  This entry point has no counterpart in the reference. */
+#define GNNB_COLSUM_STATIC_MAX_F 512
+int gnnb_colsum_static(const float* A, int64_t lda, int64_t n, int64_t F, float* out, void* stream);
 
 /* ---- subsampling -------------------------------------------------------------------------- */
 /* first_pos[v] = min{ e : S[e] == v } (INT64_MAX when v never occurs), S = the neighbour column of
