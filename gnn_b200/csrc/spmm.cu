@@ -13,6 +13,7 @@
 namespace gnnb {
 
 constexpr int GATHER_UNROLL = 8;
+constexpr int LONG_ROW = 256;       // rows with more entries than this (hubs of the kNN graph) get a whole CTA
 
 __device__ __forceinline__ float4 ld_row4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 
@@ -26,6 +27,7 @@ spmm_vec4_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t row = warp0; row < n; row += nwarps) {
         const int start = rowptr[row], end = rowptr[row + 1];
+        if (end - start > LONG_ROW) continue;                   // spmm_long_rows_kernel owns this row
         for (int fc = 0; fc < F; fc += 128) {
             const int f = fc + lane * 4;
             const bool active = f < F;
@@ -91,6 +93,7 @@ spmm_scalar_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t row = warp0; row < n; row += nwarps) {
         const int start = rowptr[row], end = rowptr[row + 1];
+        if (end - start > LONG_ROW) continue;
         for (int fc = 0; fc < F; fc += 32) {
             const int f = fc + lane;
             const bool active = f < F;
@@ -112,6 +115,106 @@ spmm_scalar_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict
             }
             if (active) out[row * ldo + f] = acc + (HAS_BIAS ? bias[f] : 0.f);
         }
+    }
+}
+
+// Hub rows: the kNN graphs are heavy-tailed (median degree 35, maximum in the thousands), so one warp per row leaves
+// the whole GPU waiting for a handful of warps.  Rows longer than LONG_ROW are handled here by a whole CTA: the 8 warps
+// take the row's 32-entry chunks round-robin, and the 8 partial sums are added in warp order (fixed => deterministic).
+// CTAs scan blocks of 64 rows for candidates, so no list of long rows has to be kept with the graph (the order in
+// which a CTA visits its candidates does not matter: rows are independent).
+template <bool HAS_BIAS, bool VEC>
+__global__ void __launch_bounds__(256)
+spmm_long_rows_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ val, int64_t n,
+                      const float* __restrict__ H, int64_t ldh, int F, const float* __restrict__ bias,
+                      float* __restrict__ out, int64_t ldo) {
+    constexpr int SCAN = 64;
+    __shared__ int s_rows[SCAN];
+    __shared__ int s_count;
+    __shared__ float4 s_part[8][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t base_row = (int64_t)blockIdx.x * SCAN; base_row < n; base_row += (int64_t)gridDim.x * SCAN) {
+        if (threadIdx.x == 0) s_count = 0;
+        __syncthreads();
+        const int64_t r = base_row + threadIdx.x;
+        if (threadIdx.x < SCAN && r < n && rowptr[r + 1] - rowptr[r] > LONG_ROW) s_rows[atomicAdd(&s_count, 1)] = (int)threadIdx.x;
+        __syncthreads();
+        const int count = s_count;
+        for (int q = 0; q < count; ++q) {
+            const int64_t row = base_row + s_rows[q];
+            const int start = rowptr[row], end = rowptr[row + 1];
+            for (int fc = 0; fc < F; fc += (VEC ? 128 : 32)) {
+                const int f = fc + (VEC ? lane * 4 : lane);
+                const bool active = f < F;
+                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int base = start + warp * 32; base < end; base += 8 * 32) {
+                    const int e = base + lane;
+                    int c = 0;
+                    float v = 0.f;
+                    if (e < end) {
+                        c = __ldg(col + e);
+                        v = __ldg(val + e);
+                    }
+                    const int cnt = min(32, end - base);
+                    int t = 0;
+                    if (VEC) {
+                        for (; t + GATHER_UNROLL <= cnt; t += GATHER_UNROLL) {
+                            float4 h[GATHER_UNROLL];
+                            float w[GATHER_UNROLL];
+#pragma unroll
+                            for (int u = 0; u < GATHER_UNROLL; ++u) {
+                                int cu = __shfl_sync(0xffffffffu, c, t + u);
+                                w[u] = __shfl_sync(0xffffffffu, v, t + u);
+                                h[u] = active ? ld_row4(H + (int64_t)cu * ldh + f) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            }
+#pragma unroll
+                            for (int u = 0; u < GATHER_UNROLL; ++u) {
+                                acc.x = fmaf(w[u], h[u].x, acc.x);
+                                acc.y = fmaf(w[u], h[u].y, acc.y);
+                                acc.z = fmaf(w[u], h[u].z, acc.z);
+                                acc.w = fmaf(w[u], h[u].w, acc.w);
+                            }
+                        }
+                    }
+                    for (; t < cnt; ++t) {
+                        int cu = __shfl_sync(0xffffffffu, c, t);
+                        float wu = __shfl_sync(0xffffffffu, v, t);
+                        if (active) {
+                            if (VEC) {
+                                float4 hu = ld_row4(H + (int64_t)cu * ldh + f);
+                                acc.x = fmaf(wu, hu.x, acc.x);
+                                acc.y = fmaf(wu, hu.y, acc.y);
+                                acc.z = fmaf(wu, hu.z, acc.z);
+                                acc.w = fmaf(wu, hu.w, acc.w);
+                            } else {
+                                acc.x = fmaf(wu, __ldg(H + (int64_t)cu * ldh + f), acc.x);
+                            }
+                        }
+                    }
+                }
+                s_part[warp][lane] = acc;
+                __syncthreads();
+                if (warp == 0 && active) {
+                    float4 tot = s_part[0][lane];
+#pragma unroll
+                    for (int w2 = 1; w2 < 8; ++w2) {
+                        tot.x += s_part[w2][lane].x; tot.y += s_part[w2][lane].y;
+                        tot.z += s_part[w2][lane].z; tot.w += s_part[w2][lane].w;
+                    }
+                    if (VEC) {
+                        if (HAS_BIAS) {
+                            float4 b = ld_row4(bias + f);
+                            tot.x += b.x; tot.y += b.y; tot.z += b.z; tot.w += b.w;
+                        }
+                        *reinterpret_cast<float4*>(out + row * ldo + f) = tot;
+                    } else {
+                        out[row * ldo + f] = tot.x + (HAS_BIAS ? bias[f] : 0.f);
+                    }
+                }
+                __syncthreads();
+            }
+        }
+        __syncthreads();
     }
 }
 
@@ -141,5 +244,18 @@ extern "C" int gnnb_spmm(const int32_t* rowptr, const int32_t* col, const float*
         else      spmm_scalar_kernel<false><<<grid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
     }
     GNNB_LAUNCH_CHECK();
+    {   // hub rows (skipped above)
+        int64_t lblocks = (n + 63) / 64;
+        int64_t lcap = (int64_t)sm_count() * 8;
+        unsigned lgrid = (unsigned)(lblocks < lcap ? lblocks : lcap);
+        if (vec) {
+            if (bias) spmm_long_rows_kernel<true, true><<<lgrid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
+            else      spmm_long_rows_kernel<false, true><<<lgrid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
+        } else {
+            if (bias) spmm_long_rows_kernel<true, false><<<lgrid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
+            else      spmm_long_rows_kernel<false, false><<<lgrid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
+        }
+        GNNB_LAUNCH_CHECK();
+    }
     return GNNB_OK;
 }
