@@ -150,7 +150,7 @@ def run_ours(a):
     model = nets.create_network_two_no_conv_dropout(p, 1, internal_size=a.hidden, dropout=DROPOUT).to(dev)
     parallel.broadcast_parameters(model)
     flat = parallel.FlatGrads(model.parameters())
-    opt = torch.optim.Adam(model.parameters(), lr=LR)
+    opt = torch.optim.Adam(model.parameters(), lr=LR, fused=True)      # same update rule as main.py:318, one kernel
     loss_func = torch.nn.MSELoss()
     for g in batches + [test]:                                       # gcn_norm + CSR once per graph (cached)
         ew = g.edge_weight.float()
@@ -194,7 +194,9 @@ def run_ours(a):
     clocks = ClockSampler(local_rank)
     if rank == 0:
         clocks.start()
+    torch.cuda.profiler.start()                              # ncu --profile-from-start off isolates the timed region
     ms_per_epoch, last = timed(lambda: epoch(batches), a.steps)
+    torch.cuda.profiler.stop()
     clock_info = clocks.stop() if rank == 0 else None
     prof = ops.profiler.summary()
     ops.profiler = None
