@@ -19,6 +19,7 @@
 // warps: 0 = TMA producer (X), 3 = TMA producer (terms), 1 = MMA issuer, 2 = TMEM allocator,
 //        4-7 = converter, then epilogue (TMEM -> registers -> global).
 #include <cuda_bf16.h>
+#include <stdlib.h>
 
 #include "tc_common.cuh"
 
@@ -104,7 +105,7 @@ template <bool BWD>
 __global__ void __launch_bounds__(256, 1)
 linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
                  int64_t k_total, int terms, int n_pad, int64_t b_term_rows,
-                 float* __restrict__ out, int64_t ld_out, int64_t m_total, int n_valid) {
+                 float* __restrict__ out, int64_t ld_out, int64_t m_total, int n_valid, int csize) {
     extern __shared__ uint8_t smem_raw[];
     const int warp = threadIdx.x >> 5;
     uint8_t* base = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);
@@ -116,17 +117,22 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     Bars* bars = reinterpret_cast<Bars*>(b_tiles + (size_t)NB * terms * b_tile_bytes);
     const int n_kb = (int)((k_total + BK - 1) / BK);
     const int64_t m0 = (int64_t)blockIdx.x * BM;
+    // Cluster of `csize` CTAs (neighbouring X tiles): the bf16 term tiles are identical for all of them, so each CTA
+    // fetches 1/csize of every tile and multicasts it -- L2 -> SM traffic for the terms drops by csize.
+    const uint32_t crank = csize > 1 ? cluster_ctarank() : 0;
+    const uint16_t cmask = (uint16_t)((1u << csize) - 1);
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < NX; ++s) { mbar_init(&bars->x_full[s], 1); mbar_init(&bars->x_empty[s], 1); }
         for (int s = 0; s < NA; ++s) { mbar_init(&bars->a_full[s], 1); mbar_init(&bars->a_empty[s], 1); }
-        for (int s = 0; s < NB; ++s) { mbar_init(&bars->b_full[s], 1); mbar_init(&bars->b_empty[s], 1); }
+        for (int s = 0; s < NB; ++s) { mbar_init(&bars->b_full[s], 1); mbar_init(&bars->b_empty[s], (uint32_t)csize); }
         mbar_init(&bars->acc_full, 1);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc<128>(&bars->tmem_ptr);
     tc_fence_before_sync();
     __syncthreads();
+    if (csize > 1) cluster_sync_all();                 // every peer's barriers exist before anyone multicasts into them
     tc_fence_after_sync();
     const uint32_t tmem_base = bars->tmem_ptr;
 
@@ -152,11 +158,23 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 mbar_arrive_expect_tx(&bars->b_full[s], (uint32_t)(terms * b_tile_bytes));
                 uint8_t* dst = b_tiles + (size_t)s * terms * b_tile_bytes;
                 for (int t = 0; t < terms; ++t) {
-                    if (BWD) {   // two 64-feature groups of [64 k-rows x 128 B]
-                        tma_load_2d(dst + t * b_tile_bytes, &map_b, &bars->b_full[s], 0, (int32_t)(t * b_term_rows + kb * BK));
-                        tma_load_2d(dst + t * b_tile_bytes + BK * 128, &map_b, &bars->b_full[s], 64, (int32_t)(t * b_term_rows + kb * BK));
-                    } else {     // [n_pad rows x 64 k]
-                        tma_load_2d(dst + t * b_tile_bytes, &map_b, &bars->b_full[s], kb * BK, (int32_t)(t * b_term_rows));
+                    uint8_t* tile = dst + t * b_tile_bytes;
+                    if (BWD) {   // two 64-feature groups of [64 k-rows x 128 B]; a CTA fetches BK / csize k-rows of each
+                        const int rows = BK / csize, r0 = (int)crank * rows;
+                        const int32_t grow = (int32_t)(t * b_term_rows + kb * BK + r0);
+                        if (csize > 1) {
+                            tma_load_2d_multicast(tile + r0 * 128, &map_b, &bars->b_full[s], 0, grow, cmask);
+                            tma_load_2d_multicast(tile + BK * 128 + r0 * 128, &map_b, &bars->b_full[s], 64, grow, cmask);
+                        } else {
+                            tma_load_2d(tile, &map_b, &bars->b_full[s], 0, grow);
+                            tma_load_2d(tile + BK * 128, &map_b, &bars->b_full[s], 64, grow);
+                        }
+                    } else {     // [n_pad rows x 64 k]; a CTA fetches n_pad / csize rows
+                        const int rows = n_pad / csize, r0 = (int)crank * rows;
+                        if (csize > 1)
+                            tma_load_2d_multicast(tile + r0 * 128, &map_b, &bars->b_full[s], kb * BK, (int32_t)(t * b_term_rows + r0), cmask);
+                        else
+                            tma_load_2d(tile, &map_b, &bars->b_full[s], kb * BK, (int32_t)(t * b_term_rows));
                     }
                 }
             }
@@ -188,7 +206,8 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     }
                 }
                 tc_commit(&bars->a_empty[sa]);
-                tc_commit(&bars->b_empty[sb]);
+                if (csize > 1) tc_commit_multicast(&bars->b_empty[sb], cmask);     // every producer of the cluster may refill this slot
+                else           tc_commit(&bars->b_empty[sb]);
             }
             tc_commit(&bars->acc_full);
         }
@@ -202,30 +221,43 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             mbar_wait(&bars->a_empty[sa], ((kb / NA) & 1) ^ 1);
             const uint8_t* src = x_stage + sx * X_STAGE_BYTES;
             uint8_t* dst = a_tiles + sa * A_BYTES;
-#pragma unroll 4
-            for (int i = 0; i < 16; ++i) {
-                const int task = i * 32 + lane;                  // 512 16-byte chunks per tile
-                uint4 in, lo, hi;
-                if (BWD) {
-                    // staging [64 k-rows][128 B]: chunk c of row r
-                    const int c = task & 7, r = task >> 3;
-                    in = *reinterpret_cast<const uint4*>(src + r * 128 + c * 16);
-                    cvt16(in, lo, hi);
-                    // MN-major operand: group g = 64 columns, k-row r: 128 B = 8 chunks, chunk j stored at j ^ (r % 8)
-                    const int g = c >> 2, j0 = 2 * (c & 3);
-                    uint8_t* row = dst + g * (BK * 128) + (r >> 3) * 1024 + (r & 7) * 128;
-                    *reinterpret_cast<uint4*>(row + ((j0 ^ (r & 7)) << 4)) = lo;
-                    *reinterpret_cast<uint4*>(row + (((j0 + 1) ^ (r & 7)) << 4)) = hi;
-                } else {
-                    // staging [128 rows][64 B]: chunk c of row r
-                    const int c = task & 3, r = task >> 2;
-                    in = *reinterpret_cast<const uint4*>(src + r * 64 + c * 16);
-                    cvt16(in, lo, hi);
-                    // K-major operand: row r holds 64 k = 128 B = 8 chunks, chunk j stored at j ^ (r % 8)
-                    const int j0 = 2 * c;
-                    uint8_t* row = dst + (r >> 3) * 1024 + (r & 7) * 128;
-                    *reinterpret_cast<uint4*>(row + ((j0 ^ (r & 7)) << 4)) = lo;
-                    *reinterpret_cast<uint4*>(row + (((j0 + 1) ^ (r & 7)) << 4)) = hi;
+            // 512 16-byte chunks per tile, 16 per lane, in batches of 8: all loads of a batch are issued before any
+            // conversion or store so that their shared-memory latencies overlap (explicit ld/st.shared: no alias stalls)
+            const uint32_t src_s = smem_u32(src), dst_s = smem_u32(dst);
+#pragma unroll 1
+            for (int b0 = 0; b0 < 16; b0 += 8) {
+                uint4 in[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int task = (b0 + u) * 32 + lane;
+                    // fwd staging [128 rows][64 B]: chunk c = task & 3 of row task >> 2  -> byte offset task * 16
+                    // bwd staging [64 k-rows][128 B]: chunk c = task & 7 of row task >> 3 -> byte offset task * 16
+                    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                                 : "=r"(in[u].x), "=r"(in[u].y), "=r"(in[u].z), "=r"(in[u].w) : "r"(src_s + task * 16));
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int task = (b0 + u) * 32 + lane;
+                    uint4 lo, hi;
+                    cvt16(in[u], lo, hi);
+                    uint32_t row_off, j0, sw;
+                    if (BWD) {
+                        // MN-major operand: group g = 64 columns, k-row r: 128 B = 8 chunks, chunk j stored at j ^ (r % 8)
+                        const int c = task & 7, r = task >> 3;
+                        row_off = (uint32_t)((c >> 2) * (BK * 128) + (r >> 3) * 1024 + (r & 7) * 128);
+                        j0 = 2 * (c & 3);
+                        sw = r & 7;
+                    } else {
+                        // K-major operand: row r holds 64 k = 128 B = 8 chunks, chunk j stored at j ^ (r % 8)
+                        const int c = task & 3, r = task >> 2;
+                        row_off = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128);
+                        j0 = 2 * c;
+                        sw = r & 7;
+                    }
+                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};"
+                                 :: "r"(dst_s + row_off + ((j0 ^ sw) << 4)), "r"(lo.x), "r"(lo.y), "r"(lo.z), "r"(lo.w) : "memory");
+                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};"
+                                 :: "r"(dst_s + row_off + (((j0 + 1) ^ sw) << 4)), "r"(hi.x), "r"(hi.y), "r"(hi.z), "r"(hi.w) : "memory");
                 }
             }
             fence_proxy_async();                       // generic-proxy stores -> visible to the tensor-core (async) proxy
@@ -259,7 +291,43 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     }
     tc_fence_before_sync();
     __syncthreads();
+    if (csize > 1) cluster_sync_all();                 // no CTA leaves while a peer can still write into its shared memory
     if (warp == 2) tmem_dealloc<128>(tmem_base);
+}
+
+// cluster size for the multicast of the term tiles: GNNB_LINEAR_CLUSTER (1, 2, 4 or 8) overrides the default of 4
+static int cluster_size(int64_t tiles) {
+    static int forced = -1;
+    if (forced < 0) {
+        const char* e = getenv("GNNB_LINEAR_CLUSTER");
+        int v = e ? atoi(e) : 0;
+        forced = (v == 1 || v == 2 || v == 4 || v == 8) ? v : 0;
+    }
+    int c = forced ? forced : 4;
+    while (c > 1 && tiles < 2 * c) c >>= 1;
+    return c;
+}
+
+template <bool BWD>
+static int launch_tc(const CUtensorMap& map_x, const CUtensorMap& map_b, int64_t k_total, int terms, int n_pad, int64_t b_term_rows,
+                     float* out, int64_t ld_out, int64_t m_total, int n_valid, int csize, int64_t tiles, size_t smem,
+                     cudaStream_t stream) {
+    GNNB_CUDA(cudaFuncSetAttribute(linear_tc_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)((tiles + csize - 1) / csize * csize));
+    cfg.blockDim = dim3(256);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)csize;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_tc_kernel<BWD>, map_x, map_b, k_total, terms, n_pad, b_term_rows, out, ld_out, m_total,
+                                 n_valid, csize));
+    return GNNB_OK;
 }
 
 static bool tc_shape_ok(const void* X, int64_t ldx, int64_t h) {
@@ -268,7 +336,7 @@ static bool tc_shape_ok(const void* X, int64_t ldx, int64_t h) {
 
 size_t linear_tc_workspace(int64_t n, int64_t p, int64_t h, int terms) {
     if (h > 128 || terms < 1 || terms > MAX_TERMS) return 0;
-    size_t p_ld = align_up((size_t)p, 8), h_pad = align_up((size_t)h, 16);
+    size_t p_ld = align_up((size_t)p, 8), h_pad = align_up((size_t)h, 32);
     size_t fwd = (size_t)terms * h_pad * p_ld * 2;             // W terms   [T][h_pad][p_ld]
     size_t bwd = (size_t)terms * (size_t)n * 128 * 2;          // dH terms  [T][n][128]
     return (fwd > bwd ? fwd : bwd) + 1024;
@@ -284,7 +352,8 @@ int linear_tc_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
                   float* H, int64_t ldh, int terms, void* ws, size_t ws_bytes, cudaStream_t stream) {
     if (!x_is_i8 || !tc_shape_ok(X, ldx, h) || p < 64 || n < 1)
         return linear_simt_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, ws, ws_bytes, stream);    // small / float inputs: exact fp32 tiles
-    const int64_t p_ld = (int64_t)align_up((size_t)p, 8), h_pad = (int64_t)align_up((size_t)h, 16);
+    // h is padded to a multiple of 32 so that a quarter of the term tile (the multicast slice) is whole 8-row swizzle atoms
+    const int64_t p_ld = (int64_t)align_up((size_t)p, 8), h_pad = (int64_t)align_up((size_t)h, 32);
     const size_t need = (size_t)terms * h_pad * p_ld * 2;
     GNNB_REQUIRE(ws && ws_bytes >= need + 1024, GNNB_E_WORKSPACE, "linear_fwd: workspace %zu < %zu bytes", ws_bytes, need + 1024);
     __nv_bfloat16* Wt = reinterpret_cast<__nv_bfloat16*>(align_up((size_t)(uintptr_t)ws, 1024));
@@ -296,14 +365,12 @@ int linear_tc_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
     CUtensorMap map_x, map_b;
     int rc = make_tensor_map_2d(&map_x, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, BK, BM, /*swizzle*/ false);
     if (rc != GNNB_OK) return rc;
-    rc = make_tensor_map_2d(&map_b, Wt, 2, (uint64_t)p_ld, (uint64_t)(terms * h_pad), (uint64_t)p_ld * 2, BK, (uint32_t)h_pad, true);
+    const int64_t tiles = (n + BM - 1) / BM;
+    const int csize = cluster_size(tiles);
+    rc = make_tensor_map_2d(&map_b, Wt, 2, (uint64_t)p_ld, (uint64_t)(terms * h_pad), (uint64_t)p_ld * 2, BK, (uint32_t)(h_pad / csize), true);
     if (rc != GNNB_OK) return rc;
     const size_t smem = tc_smem_bytes(terms, (int)(h_pad * BK * 2));
-    GNNB_CUDA(cudaFuncSetAttribute(linear_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const unsigned grid = (unsigned)((n + BM - 1) / BM);
-    linear_tc_kernel<false><<<grid, 256, smem, stream>>>(map_x, map_b, p, terms, (int)h_pad, h_pad, H, ldh, n, (int)h);
-    GNNB_LAUNCH_CHECK();
-    return GNNB_OK;
+    return launch_tc<false>(map_x, map_b, p, terms, (int)h_pad, h_pad, H, ldh, n, (int)h, csize, tiles, smem, stream);
 }
 
 int linear_tc_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
@@ -321,14 +388,12 @@ int linear_tc_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t 
     CUtensorMap map_x, map_b;
     int rc = make_tensor_map_2d(&map_x, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, 128, BK, /*swizzle*/ false);
     if (rc != GNNB_OK) return rc;
-    rc = make_tensor_map_2d(&map_b, Dt, 2, 128, (uint64_t)(terms * n), 256, 64, BK, true);
+    const int64_t tiles = (p + BM - 1) / BM;
+    const int csize = cluster_size(tiles);
+    rc = make_tensor_map_2d(&map_b, Dt, 2, 128, (uint64_t)(terms * n), 256, 64, (uint32_t)(BK / csize), true);
     if (rc != GNNB_OK) return rc;
     const size_t smem = tc_smem_bytes(terms, BK * 128 * 2);
-    GNNB_CUDA(cudaFuncSetAttribute(linear_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const unsigned grid = (unsigned)((p + BM - 1) / BM);
-    linear_tc_kernel<true><<<grid, 256, smem, stream>>>(map_x, map_b, n, terms, 128, n, dW, lddw, p, (int)h);
-    GNNB_LAUNCH_CHECK();
-    return GNNB_OK;
+    return launch_tc<true>(map_x, map_b, n, terms, 128, n, dW, lddw, p, (int)h, csize, tiles, smem, stream);
 }
 
 }  // namespace gnnb
