@@ -38,6 +38,7 @@ static_assert(NX % CW == 0 && NA % CW == 0, "ring slots must map to a single con
 constexpr int X_STAGE_BYTES = BM * BK;              // int8: fwd 128 rows x 64 B, bwd 64 rows x 128 B
 constexpr int A_BYTES = BM * BK * 2;                // bf16 operand tile
 constexpr int MAX_TERMS = 3;
+constexpr int MAX_SPLITS = 8;
 
 struct Bars {
     uint64_t x_full[NX], x_empty[NX], a_full[NA], a_empty[NA], b_full[NB_MAX], b_empty[NB_MAX], acc_full;
@@ -101,11 +102,16 @@ __device__ __forceinline__ void cvt16(const uint4& in, uint4& lo, uint4& hi) {
 
 // BWD = false: D[m = row of X, n = feature]   += sum_k X[m, k] * W_t[n, k]
 // BWD = true : D[m = column of X, n = feature] += sum_k X[k, m] * dH_t[k, n]
+//
+// A CTA owns `rt` (1, 2 or 4) adjacent 128-wide X tiles -- one TMEM accumulator each -- and a range of k-blocks
+// (split-K over blockIdx.y).  Every term tile fetched from L2 is re-used by all `rt` X tiles: an SM takes in about
+// 32 B/clk, and with one X tile per CTA the term tiles (32 KB per k-block at 2 terms) are 80 % of that traffic.
+// The X and A rings run over "units" u = local k-block * rt + tile; the term ring runs over k-blocks.
 template <bool BWD>
 __global__ void __launch_bounds__(256, 1)
 linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
                  int64_t k_total, int terms, int n_pad, int64_t b_term_rows,
-                 float* __restrict__ out, int64_t ld_out, int64_t m_total, int n_valid, int csize) {
+                 float* __restrict__ out, int64_t ld_out, int64_t split_stride, int64_t m_total, int n_valid, int csize, int rt) {
     extern __shared__ uint8_t smem_raw[];
     const int warp = threadIdx.x >> 5;
     uint8_t* base = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);
@@ -115,10 +121,12 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     uint8_t* a_tiles = x_stage + NX * X_STAGE_BYTES;
     uint8_t* b_tiles = a_tiles + NA * A_BYTES;
     Bars* bars = reinterpret_cast<Bars*>(b_tiles + (size_t)NB * terms * b_tile_bytes);
-    const int n_kb = (int)((k_total + BK - 1) / BK);
-    const int64_t m0 = (int64_t)blockIdx.x * BM;
-    // Cluster of `csize` CTAs (neighbouring X tiles): the bf16 term tiles are identical for all of them, so each CTA
-    // fetches 1/csize of every tile and multicasts it -- L2 -> SM traffic for the terms drops by csize.
+    const int n_kb_all = (int)((k_total + BK - 1) / BK);
+    const int kb0 = (int)((int64_t)n_kb_all * blockIdx.y / gridDim.y);
+    const int n_kb = (int)((int64_t)n_kb_all * (blockIdx.y + 1) / gridDim.y) - kb0;      // k-blocks of this split
+    const int n_units = n_kb * rt;
+    const int64_t m0 = (int64_t)blockIdx.x * BM * rt;
+    // Optional cluster of `csize` CTAs (neighbouring X tiles) that multicast the term tiles to each other.
     const uint32_t crank = csize > 1 ? cluster_ctarank() : 0;
     const uint16_t cmask = (uint16_t)((1u << csize) - 1);
 
@@ -129,7 +137,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         mbar_init(&bars->acc_full, 1);
         fence_barrier_init();
     }
-    if (warp == 2) tmem_alloc<128>(&bars->tmem_ptr);
+    if (warp == 2) tmem_alloc<512>(&bars->tmem_ptr);
     tc_fence_before_sync();
     __syncthreads();
     if (csize > 1) cluster_sync_all();                 // every peer's barriers exist before anyone multicasts into them
@@ -140,21 +148,22 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         // ===================================================== TMA producer: raw int8 tiles of X
         if (elect_one()) {
             prefetch_tensormap(&map_x);
-            for (int kb = 0; kb < n_kb; ++kb) {
-                const int s = kb % NX;
-                mbar_wait(&bars->x_empty[s], ((kb / NX) & 1) ^ 1);
+            for (int u = 0; u < n_units; ++u) {
+                const int s = u % NX, kb = kb0 + u / rt, j = u % rt;
+                mbar_wait(&bars->x_empty[s], ((u / NX) & 1) ^ 1);
                 mbar_arrive_expect_tx(&bars->x_full[s], X_STAGE_BYTES);
-                if (BWD) tma_load_2d(x_stage + s * X_STAGE_BYTES, &map_x, &bars->x_full[s], (int32_t)m0, kb * BK);   // [64 k-rows x 128 cols]
-                else     tma_load_2d(x_stage + s * X_STAGE_BYTES, &map_x, &bars->x_full[s], kb * BK, (int32_t)m0);   // [128 rows x 64 k]
+                const int32_t mj = (int32_t)(m0 + (int64_t)j * BM);
+                if (BWD) tma_load_2d(x_stage + s * X_STAGE_BYTES, &map_x, &bars->x_full[s], mj, kb * BK);   // [64 k-rows x 128 cols]
+                else     tma_load_2d(x_stage + s * X_STAGE_BYTES, &map_x, &bars->x_full[s], kb * BK, mj);   // [128 rows x 64 k]
             }
         }
     } else if (warp == 3) {
         // ===================================================== TMA producer: bf16 terms of the fp32 operand
         if (elect_one()) {
             prefetch_tensormap(&map_b);
-            for (int kb = 0; kb < n_kb; ++kb) {
-                const int s = kb % NB;
-                mbar_wait(&bars->b_empty[s], ((kb / NB) & 1) ^ 1);
+            for (int i = 0; i < n_kb; ++i) {
+                const int s = i % NB, kb = kb0 + i;
+                mbar_wait(&bars->b_empty[s], ((i / NB) & 1) ^ 1);
                 mbar_arrive_expect_tx(&bars->b_full[s], (uint32_t)(terms * b_tile_bytes));
                 uint8_t* dst = b_tiles + (size_t)s * terms * b_tile_bytes;
                 for (int t = 0; t < terms; ++t) {
@@ -183,13 +192,15 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         // ===================================================== MMA issuer (one thread)
         if (elect_one()) {
             const uint32_t idesc = make_idesc(/*F32*/ 1, /*BF16*/ 1, BWD ? 1 : 0, BWD ? 1 : 0, BM, (uint32_t)n_pad);
-            for (int kb = 0; kb < n_kb; ++kb) {
-                const int sa = kb % NA, sb = kb % NB;
-                mbar_wait(&bars->a_full[sa], (kb / NA) & 1);
-                mbar_wait(&bars->b_full[sb], (kb / NB) & 1);
+            for (int u = 0; u < n_units; ++u) {
+                const int i = u / rt, j = u % rt;
+                const int sa = u % NA, sb = i % NB;
+                mbar_wait(&bars->a_full[sa], (u / NA) & 1);
+                if (j == 0) mbar_wait(&bars->b_full[sb], (i / NB) & 1);
                 tc_fence_after_sync();
                 const uint32_t a_addr = smem_u32(a_tiles + sa * A_BYTES);
                 const uint32_t b_addr0 = smem_u32(b_tiles + (size_t)sb * terms * b_tile_bytes);
+                const uint32_t d_tmem = tmem_base + (uint32_t)j * 128;
                 for (int t = 0; t < terms; ++t) {
                     const uint32_t b_addr = b_addr0 + t * b_tile_bytes;
 #pragma unroll
@@ -202,12 +213,14 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                             da = make_smem_desc(a_addr + k16 * 32, 16, 1024);
                             db = make_smem_desc(b_addr + k16 * 32, 16, 1024);
                         }
-                        mma_bf16_ss(tmem_base, da, db, idesc, (kb > 0 || t > 0 || k16 > 0) ? 1u : 0u);
+                        mma_bf16_ss(d_tmem, da, db, idesc, (i > 0 || t > 0 || k16 > 0) ? 1u : 0u);
                     }
                 }
                 tc_commit(&bars->a_empty[sa]);
-                if (csize > 1) tc_commit_multicast(&bars->b_empty[sb], cmask);     // every producer of the cluster may refill this slot
-                else           tc_commit(&bars->b_empty[sb]);
+                if (j == rt - 1) {
+                    if (csize > 1) tc_commit_multicast(&bars->b_empty[sb], cmask);     // every producer of the cluster may refill this slot
+                    else           tc_commit(&bars->b_empty[sb]);
+                }
             }
             tc_commit(&bars->acc_full);
         }
@@ -215,10 +228,10 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         // ===================================================== converter: int8 staging -> bf16 UMMA operand
         const int t = threadIdx.x - 128;
         const int lane = threadIdx.x & 31, cw = warp - 4;
-        for (int kb = cw; kb < n_kb; kb += CW) {
-            const int sx = kb % NX, sa = kb % NA;
-            mbar_wait(&bars->x_full[sx], (kb / NX) & 1);
-            mbar_wait(&bars->a_empty[sa], ((kb / NA) & 1) ^ 1);
+        for (int u = cw; u < n_units; u += CW) {
+            const int sx = u % NX, sa = u % NA;
+            mbar_wait(&bars->x_full[sx], (u / NX) & 1);
+            mbar_wait(&bars->a_empty[sa], ((u / NA) & 1) ^ 1);
             const uint8_t* src = x_stage + sx * X_STAGE_BYTES;
             uint8_t* dst = a_tiles + sa * A_BYTES;
             // 512 16-byte chunks per tile, 16 per lane, in batches of 8: all loads of a batch are issued before any
@@ -228,18 +241,18 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             for (int b0 = 0; b0 < 16; b0 += 8) {
                 uint4 in[8];
 #pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    const int task = (b0 + u) * 32 + lane;
+                for (int q = 0; q < 8; ++q) {
+                    const int task = (b0 + q) * 32 + lane;
                     // fwd staging [128 rows][64 B]: chunk c = task & 3 of row task >> 2  -> byte offset task * 16
                     // bwd staging [64 k-rows][128 B]: chunk c = task & 7 of row task >> 3 -> byte offset task * 16
                     asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                                 : "=r"(in[u].x), "=r"(in[u].y), "=r"(in[u].z), "=r"(in[u].w) : "r"(src_s + task * 16));
+                                 : "=r"(in[q].x), "=r"(in[q].y), "=r"(in[q].z), "=r"(in[q].w) : "r"(src_s + task * 16));
                 }
 #pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    const int task = (b0 + u) * 32 + lane;
+                for (int q = 0; q < 8; ++q) {
+                    const int task = (b0 + q) * 32 + lane;
                     uint4 lo, hi;
-                    cvt16(in[u], lo, hi);
+                    cvt16(in[q], lo, hi);
                     uint32_t row_off, j0, sw;
                     if (BWD) {
                         // MN-major operand: group g = 64 columns, k-row r: 128 B = 8 chunks, chunk j stored at j ^ (r % 8)
@@ -267,23 +280,26 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 mbar_arrive(&bars->x_empty[sx]);
             }
         }
-        // ===================================================== epilogue
+        // ===================================================== epilogue: accumulators -> (partial) output
         mbar_wait(&bars->acc_full, 0);
         tc_fence_after_sync();
         const int wq = warp & 3;
-        const int64_t m = m0 + t;                      // fwd: row of X; bwd: column of X (marker)
+        float* dst_out = out + (int64_t)blockIdx.y * split_stride;
+        for (int j = 0; j < rt; ++j) {
+            const int64_t m = m0 + (int64_t)j * BM + t;        // fwd: row of X; bwd: column of X (marker)
 #pragma unroll 1
-        for (int chunk = 0; chunk * 32 < n_pad; ++chunk) {
-            uint32_t v[32];
-            tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(32 * wq) << 16) + chunk * 32, v);
-            tmem_ld_wait();
-            if (m < m_total) {
+            for (int chunk = 0; chunk * 32 < n_pad; ++chunk) {
+                uint32_t v[32];
+                tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(32 * wq) << 16) + (uint32_t)j * 128 + chunk * 32, v);
+                tmem_ld_wait();
+                if (m < m_total && n_kb > 0) {
 #pragma unroll
-                for (int c = 0; c < 32; ++c) {
-                    const int f = chunk * 32 + c;
-                    if (f < n_valid) {
-                        if (BWD) out[(int64_t)f * ld_out + m] = __uint_as_float(v[c]);     // dW[f, marker]: a warp writes 32 consecutive markers
-                        else     out[m * ld_out + f] = __uint_as_float(v[c]);              // H[row, f]
+                    for (int c = 0; c < 32; ++c) {
+                        const int f = chunk * 32 + c;
+                        if (f < n_valid) {
+                            if (BWD) dst_out[(int64_t)f * ld_out + m] = __uint_as_float(v[c]);    // dW[f, marker]: a warp writes 32 consecutive markers
+                            else     dst_out[m * ld_out + f] = __uint_as_float(v[c]);             // H[row, f]
+                        }
                     }
                 }
             }
@@ -292,29 +308,66 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     tc_fence_before_sync();
     __syncthreads();
     if (csize > 1) cluster_sync_all();                 // no CTA leaves while a peer can still write into its shared memory
-    if (warp == 2) tmem_dealloc<128>(tmem_base);
+    if (warp == 2) tmem_dealloc<512>(tmem_base);
 }
 
-// cluster size for the multicast of the term tiles: GNNB_LINEAR_CLUSTER (1, 2, 4 or 8) overrides the default of 4
-static int cluster_size(int64_t tiles) {
+// out[i] = sum_s part[s * stride + i] in a fixed order (split-K partials -> result)
+__global__ void splitk_sum_kernel(const float* __restrict__ part, int n_splits, int64_t stride, int64_t rows, int64_t cols,
+                                  int64_t ld_part, float* __restrict__ out, int64_t ld_out) {
+    const int64_t total = rows * cols;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / cols, c = i % cols;
+        float s = 0.f;
+        for (int sp = 0; sp < n_splits; ++sp) s += part[(int64_t)sp * stride + r * ld_part + c];
+        out[r * ld_out + c] = s;
+    }
+}
+
+// cluster size for the multicast of the term tiles: GNNB_LINEAR_CLUSTER (1, 2, 4 or 8); default 1 -- measured no gain,
+// because what limits the kernel is the bytes an SM can take in per clock, and a multicast still delivers every byte.
+static int cluster_size(int64_t supertiles) {
     static int forced = -1;
     if (forced < 0) {
         const char* e = getenv("GNNB_LINEAR_CLUSTER");
         int v = e ? atoi(e) : 0;
-        forced = (v == 1 || v == 2 || v == 4 || v == 8) ? v : 0;
+        forced = (v == 1 || v == 2 || v == 4 || v == 8) ? v : 1;
     }
-    int c = forced ? forced : 4;
-    while (c > 1 && tiles < 2 * c) c >>= 1;
+    int c = forced;
+    while (c > 1 && supertiles < 2 * c) c >>= 1;
     return c;
+}
+
+// X tiles per CTA (GNNB_LINEAR_RT overrides) and k-splits so that the grid still fills the GPU
+static void plan_tiles(int64_t tiles, int64_t n_kb, int* rt_out, int* splits_out) {
+    static int forced = -1;
+    if (forced < 0) {
+        const char* e = getenv("GNNB_LINEAR_RT");
+        int v = e ? atoi(e) : 0;
+        forced = (v == 1 || v == 2 || v == 4) ? v : 0;
+    }
+    // default 1: measured on B200, sharing a term tile between 2 or 4 X tiles does not pay -- the kernel is bound by
+    // shared-memory bandwidth (UMMA operand reads + TMA writes + the converter), not by L2 -> SM traffic
+    int rt = forced ? forced : 1;
+    int64_t supertiles = (tiles + rt - 1) / rt;
+    int64_t s = sm_count() / supertiles;
+    if (s > n_kb / 16) s = n_kb / 16;
+    if (s > MAX_SPLITS) s = MAX_SPLITS;
+    if (s < 1) s = 1;
+    *rt_out = rt;
+    *splits_out = (int)s;
 }
 
 template <bool BWD>
 static int launch_tc(const CUtensorMap& map_x, const CUtensorMap& map_b, int64_t k_total, int terms, int n_pad, int64_t b_term_rows,
-                     float* out, int64_t ld_out, int64_t m_total, int n_valid, int csize, int64_t tiles, size_t smem,
-                     cudaStream_t stream) {
+                     float* out, int64_t ld_out, int64_t out_rows, int64_t out_cols, float* partial, int64_t m_total, int n_valid,
+                     int64_t tiles, size_t smem, cudaStream_t stream) {
+    int rt, splits;
+    plan_tiles(tiles, (k_total + BK - 1) / BK, &rt, &splits);
+    const int64_t supertiles = (tiles + rt - 1) / rt;
+    const int csize = cluster_size(supertiles);
     GNNB_CUDA(cudaFuncSetAttribute(linear_tc_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)((tiles + csize - 1) / csize * csize));
+    cfg.gridDim = dim3((unsigned)((supertiles + csize - 1) / csize * csize), (unsigned)splits);
     cfg.blockDim = dim3(256);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
@@ -325,8 +378,17 @@ static int launch_tc(const CUtensorMap& map_x, const CUtensorMap& map_b, int64_t
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_tc_kernel<BWD>, map_x, map_b, k_total, terms, n_pad, b_term_rows, out, ld_out, m_total,
-                                 n_valid, csize));
+    float* dst = splits > 1 ? partial : out;
+    const int64_t ld_dst = splits > 1 ? out_cols : ld_out;
+    const int64_t stride = splits > 1 ? out_rows * out_cols : 0;
+    GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_tc_kernel<BWD>, map_x, map_b, k_total, terms, n_pad, b_term_rows, dst, ld_dst, stride,
+                                 m_total, n_valid, csize, rt));
+    if (splits > 1) {
+        int64_t total = out_rows * out_cols, blocks = (total + 255) / 256, cap = (int64_t)sm_count() * 16;
+        splitk_sum_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, stream>>>(partial, splits, stride, out_rows, out_cols,
+                                                                                     out_cols, out, ld_out);
+        GNNB_LAUNCH_CHECK();
+    }
     return GNNB_OK;
 }
 
@@ -334,12 +396,16 @@ static bool tc_shape_ok(const void* X, int64_t ldx, int64_t h) {
     return (uintptr_t)X % 16 == 0 && ldx % 16 == 0 && h >= 1 && h <= 128;
 }
 
+static size_t terms_bytes_fwd(int64_t p, int64_t h, int terms) {
+    return align_up((size_t)terms * align_up((size_t)h, 32) * align_up((size_t)p, 8) * 2, 1024);
+}
+static size_t terms_bytes_bwd(int64_t n, int terms) { return align_up((size_t)terms * (size_t)n * 128 * 2, 1024); }
+
 size_t linear_tc_workspace(int64_t n, int64_t p, int64_t h, int terms) {
     if (h > 128 || terms < 1 || terms > MAX_TERMS) return 0;
-    size_t p_ld = align_up((size_t)p, 8), h_pad = align_up((size_t)h, 32);
-    size_t fwd = (size_t)terms * h_pad * p_ld * 2;             // W terms   [T][h_pad][p_ld]
-    size_t bwd = (size_t)terms * (size_t)n * 128 * 2;          // dH terms  [T][n][128]
-    return (fwd > bwd ? fwd : bwd) + 1024;
+    size_t fwd = terms_bytes_fwd(p, h, terms) + (size_t)MAX_SPLITS * n * h * sizeof(float);     // W terms + split-K partials of H
+    size_t bwd = terms_bytes_bwd(n, terms) + (size_t)MAX_SPLITS * h * p * sizeof(float);        // dH terms + partials of dW
+    return (fwd > bwd ? fwd : bwd) + 2048;
 }
 
 // simt fallbacks live in linear.cu
@@ -352,48 +418,56 @@ int linear_tc_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
                   float* H, int64_t ldh, int terms, void* ws, size_t ws_bytes, cudaStream_t stream) {
     if (!x_is_i8 || !tc_shape_ok(X, ldx, h) || p < 64 || n < 1)
         return linear_simt_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, ws, ws_bytes, stream);    // small / float inputs: exact fp32 tiles
-    // h is padded to a multiple of 32 so that a quarter of the term tile (the multicast slice) is whole 8-row swizzle atoms
+    // h is padded to a multiple of 32 so that a quarter of the term tile (a multicast slice) is whole 8-row swizzle atoms
     const int64_t p_ld = (int64_t)align_up((size_t)p, 8), h_pad = (int64_t)align_up((size_t)h, 32);
-    const size_t need = (size_t)terms * h_pad * p_ld * 2;
-    GNNB_REQUIRE(ws && ws_bytes >= need + 1024, GNNB_E_WORKSPACE, "linear_fwd: workspace %zu < %zu bytes", ws_bytes, need + 1024);
-    __nv_bfloat16* Wt = reinterpret_cast<__nv_bfloat16*>(align_up((size_t)(uintptr_t)ws, 1024));
+    const size_t need = linear_tc_workspace(n, p, h, terms);
+    GNNB_REQUIRE(ws && ws_bytes >= need, GNNB_E_WORKSPACE, "linear_fwd: workspace %zu < %zu bytes", ws_bytes, need);
+    uint8_t* wsb = reinterpret_cast<uint8_t*>(align_up((size_t)(uintptr_t)ws, 1024));
+    __nv_bfloat16* Wt = reinterpret_cast<__nv_bfloat16*>(wsb);
+    float* partial = reinterpret_cast<float*>(wsb + terms_bytes_fwd(p, h, terms));
     {
         int64_t total = h_pad * p_ld, blocks = (total + 255) / 256, cap = (int64_t)sm_count() * 16;
         split_terms_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, stream>>>(W, ldw, h, p, Wt, h_pad, p_ld, p_ld, terms);
         GNNB_LAUNCH_CHECK();
     }
+    const int64_t tiles = (n + BM - 1) / BM;
+    int rt, splits;
+    plan_tiles(tiles, (p + BK - 1) / BK, &rt, &splits);
+    const int csize = cluster_size((tiles + rt - 1) / rt);
     CUtensorMap map_x, map_b;
     int rc = make_tensor_map_2d(&map_x, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, BK, BM, /*swizzle*/ false);
     if (rc != GNNB_OK) return rc;
-    const int64_t tiles = (n + BM - 1) / BM;
-    const int csize = cluster_size(tiles);
     rc = make_tensor_map_2d(&map_b, Wt, 2, (uint64_t)p_ld, (uint64_t)(terms * h_pad), (uint64_t)p_ld * 2, BK, (uint32_t)(h_pad / csize), true);
     if (rc != GNNB_OK) return rc;
     const size_t smem = tc_smem_bytes(terms, (int)(h_pad * BK * 2));
-    return launch_tc<false>(map_x, map_b, p, terms, (int)h_pad, h_pad, H, ldh, n, (int)h, csize, tiles, smem, stream);
+    return launch_tc<false>(map_x, map_b, p, terms, (int)h_pad, h_pad, H, ldh, n, h, partial, n, (int)h, tiles, smem, stream);
 }
 
 int linear_tc_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
                     float* dW, int64_t lddw, int terms, void* ws, size_t ws_bytes, cudaStream_t stream) {
     if (!x_is_i8 || !tc_shape_ok(X, ldx, h) || p < 128 || n < 64)
         return linear_simt_bwd_w(X, x_is_i8, ldx, n, p, dH, lddh, h, dW, lddw, ws, ws_bytes, stream);
-    const size_t need = (size_t)terms * (size_t)n * 128 * 2;
-    GNNB_REQUIRE(ws && ws_bytes >= need + 1024, GNNB_E_WORKSPACE, "linear_bwd_w: workspace %zu < %zu bytes", ws_bytes, need + 1024);
-    __nv_bfloat16* Dt = reinterpret_cast<__nv_bfloat16*>(align_up((size_t)(uintptr_t)ws, 1024));
+    const size_t need = linear_tc_workspace(n, p, h, terms);
+    GNNB_REQUIRE(ws && ws_bytes >= need, GNNB_E_WORKSPACE, "linear_bwd_w: workspace %zu < %zu bytes", ws_bytes, need);
+    uint8_t* wsb = reinterpret_cast<uint8_t*>(align_up((size_t)(uintptr_t)ws, 1024));
+    __nv_bfloat16* Dt = reinterpret_cast<__nv_bfloat16*>(wsb);
+    float* partial = reinterpret_cast<float*>(wsb + terms_bytes_bwd(n, terms));
     {
         int64_t total = n * 128, blocks = (total + 255) / 256, cap = (int64_t)sm_count() * 16;
         split_terms_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, stream>>>(dH, lddh, n, h, Dt, n, 128, 128, terms);
         GNNB_LAUNCH_CHECK();
     }
+    const int64_t tiles = (p + BM - 1) / BM;
+    int rt, splits;
+    plan_tiles(tiles, (n + BK - 1) / BK, &rt, &splits);
+    const int csize = cluster_size((tiles + rt - 1) / rt);
     CUtensorMap map_x, map_b;
     int rc = make_tensor_map_2d(&map_x, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, 128, BK, /*swizzle*/ false);
     if (rc != GNNB_OK) return rc;
-    const int64_t tiles = (p + BM - 1) / BM;
-    const int csize = cluster_size(tiles);
     rc = make_tensor_map_2d(&map_b, Dt, 2, 128, (uint64_t)(terms * n), 256, 64, (uint32_t)(BK / csize), true);
     if (rc != GNNB_OK) return rc;
     const size_t smem = tc_smem_bytes(terms, BK * 128 * 2);
-    return launch_tc<true>(map_x, map_b, n, terms, 128, n, dW, lddw, p, (int)h, csize, tiles, smem, stream);
+    return launch_tc<true>(map_x, map_b, n, terms, 128, n, dW, lddw, h, p, partial, p, (int)h, tiles, smem, stream);
 }
 
 }  // namespace gnnb
