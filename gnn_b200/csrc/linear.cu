@@ -114,7 +114,7 @@ static int pick_splits(int64_t M, int64_t N, int64_t K) {
     int64_t want = (2LL * sm_count() + tiles - 1) / tiles;
     int64_t maxs = K / 256;               // at least 256 rows of K per split
     if (want > maxs) want = maxs;
-    if (want > 16) want = 16;
+    if (want > 64) want = 64;
     if (want < 1) want = 1;
     return (int)want;
 }
@@ -163,7 +163,12 @@ int gnnb_linear_workspace_bytes(int64_t n, int64_t p, int64_t h, int precision, 
     GNNB_REQUIRE(bytes && n >= 0 && p > 0 && h > 0 && precision >= 0 && precision <= 3, GNNB_E_BADARG,
                  "linear_workspace_bytes: bad argument");
     size_t out_max = (size_t)h * (size_t)(p > n ? p : n);
-    size_t simt = (size_t)16 * out_max * sizeof(float) + 256;                    // split-K partials (fwd: n*h, bwd_w: h*p)
+    // split-K partials (fwd: n*h, bwd_w: h*p): at most 64 splits, and never more than ~2 waves of 64x64 tiles
+    size_t tiles_min = (out_max + 4095) / 4096;
+    size_t max_splits = (2 * 148 + tiles_min - 1) / tiles_min;
+    if (max_splits > 64) max_splits = 64;
+    if (max_splits < 1) max_splits = 1;
+    size_t simt = max_splits * out_max * sizeof(float) + 256;
     size_t tc = precision > 0 ? linear_tc_workspace(n, p, h, precision) : 0;
     *bytes = simt > tc ? simt : tc;
     return GNNB_OK;

@@ -39,6 +39,7 @@ constexpr int X_STAGE_BYTES = BM * BK;              // int8: fwd 128 rows x 64 B
 constexpr int A_BYTES = BM * BK * 2;                // bf16 operand tile
 constexpr int MAX_TERMS = 3;
 constexpr int MAX_SPLITS = 8;
+constexpr int ACC_COLS = 256;            // TMEM columns per X tile: [0, n_pad) hi (+ third term), [n_pad, 2 n_pad) lo
 
 struct Bars {
     uint64_t x_full[NX], x_empty[NX], a_full[NA], a_empty[NA], b_full[NB_MAX], b_empty[NB_MAX], acc_full;
@@ -192,6 +193,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         // ===================================================== MMA issuer (one thread)
         if (elect_one()) {
             const uint32_t idesc = make_idesc(/*F32*/ 1, /*BF16*/ 1, BWD ? 1 : 0, BWD ? 1 : 0, BM, (uint32_t)n_pad);
+            const uint32_t idesc2 = make_idesc(1, 1, BWD ? 1 : 0, BWD ? 1 : 0, BM, (uint32_t)(2 * n_pad));
             for (int u = 0; u < n_units; ++u) {
                 const int i = u / rt, j = u % rt;
                 const int sa = u % NA, sb = i % NB;
@@ -200,9 +202,16 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 tc_fence_after_sync();
                 const uint32_t a_addr = smem_u32(a_tiles + sa * A_BYTES);
                 const uint32_t b_addr0 = smem_u32(b_tiles + (size_t)sb * terms * b_tile_bytes);
-                const uint32_t d_tmem = tmem_base + (uint32_t)j * 128;
-                for (int t = 0; t < terms; ++t) {
+                const uint32_t d_tmem = tmem_base + (uint32_t)j * ACC_COLS;
+                // Terms are stacked along N in shared memory, so two of them form ONE operand of N = 2 * n_pad: the
+                // hi and lo products land in adjacent accumulator column blocks (summed in the epilogue) and the A tile
+                // is read from shared memory once per k16 instead of once per term (UMMA operand reads are what
+                // saturates the 128 B/clk of shared memory here).
+                for (int t = 0; t < terms; t += 2) {
+                    const bool pair = (t + 1 < terms) && (2 * n_pad <= 256);
                     const uint32_t b_addr = b_addr0 + t * b_tile_bytes;
+                    const uint32_t idesc_t = pair ? idesc2 : idesc;
+                    const uint32_t d_col = d_tmem;
 #pragma unroll
                     for (int k16 = 0; k16 < BK / 16; ++k16) {
                         uint64_t da, db;
@@ -213,7 +222,23 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                             da = make_smem_desc(a_addr + k16 * 32, 16, 1024);
                             db = make_smem_desc(b_addr + k16 * 32, 16, 1024);
                         }
-                        mma_bf16_ss(d_tmem, da, db, idesc, (i > 0 || t > 0 || k16 > 0) ? 1u : 0u);
+                        // a paired MMA writes columns [0, 2 n_pad); a single one (third term) accumulates into [0, n_pad)
+                        mma_bf16_ss(d_col, da, db, idesc_t, (i > 0 || t > 0 || k16 > 0) ? 1u : 0u);
+                    }
+                    if (!pair && t + 1 < terms) {      // n_pad too wide to pair: fall back to one MMA per term
+                        const uint32_t b_addr1 = b_addr + b_tile_bytes;
+#pragma unroll
+                        for (int k16 = 0; k16 < BK / 16; ++k16) {
+                            uint64_t da, db;
+                            if (BWD) {
+                                da = make_smem_desc(a_addr + k16 * 2048, BK * 128, 1024);
+                                db = make_smem_desc(b_addr1 + k16 * 2048, BK * 128, 1024);
+                            } else {
+                                da = make_smem_desc(a_addr + k16 * 32, 16, 1024);
+                                db = make_smem_desc(b_addr1 + k16 * 32, 16, 1024);
+                            }
+                            mma_bf16_ss(d_col, da, db, idesc, 1u);
+                        }
                     }
                 }
                 tc_commit(&bars->a_empty[sa]);
@@ -285,20 +310,24 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         tc_fence_after_sync();
         const int wq = warp & 3;
         float* dst_out = out + (int64_t)blockIdx.y * split_stride;
+        const bool paired = terms >= 2 && 2 * n_pad <= 256;
         for (int j = 0; j < rt; ++j) {
             const int64_t m = m0 + (int64_t)j * BM + t;        // fwd: row of X; bwd: column of X (marker)
 #pragma unroll 1
             for (int chunk = 0; chunk * 32 < n_pad; ++chunk) {
-                uint32_t v[32];
-                tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(32 * wq) << 16) + (uint32_t)j * 128 + chunk * 32, v);
+                uint32_t v[32], w[32];
+                const uint32_t taddr = tmem_base + ((uint32_t)(32 * wq) << 16) + (uint32_t)j * ACC_COLS + chunk * 32;
+                tmem_ld_32x32b_x32(taddr, v);
+                if (paired) tmem_ld_32x32b_x32(taddr + (uint32_t)n_pad, w);      // the lo-term products
                 tmem_ld_wait();
                 if (m < m_total && n_kb > 0) {
 #pragma unroll
                     for (int c = 0; c < 32; ++c) {
                         const int f = chunk * 32 + c;
                         if (f < n_valid) {
-                            if (BWD) dst_out[(int64_t)f * ld_out + m] = __uint_as_float(v[c]);    // dW[f, marker]: a warp writes 32 consecutive markers
-                            else     dst_out[m * ld_out + f] = __uint_as_float(v[c]);             // H[row, f]
+                            const float r = paired ? __uint_as_float(v[c]) + __uint_as_float(w[c]) : __uint_as_float(v[c]);
+                            if (BWD) dst_out[(int64_t)f * ld_out + m] = r;    // dW[f, marker]: a warp writes 32 consecutive markers
+                            else     dst_out[m * ld_out + f] = r;             // H[row, f]
                         }
                     }
                 }
@@ -308,6 +337,163 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     tc_fence_before_sync();
     __syncthreads();
     if (csize > 1) cluster_sync_all();                 // no CTA leaves while a peer can still write into its shared memory
+    if (warp == 2) tmem_dealloc<512>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Forward projection with the A operand in TENSOR MEMORY.
+// The converter warps write the bf16 X tile straight into TMEM (tcgen05.st), not into shared memory: the tile never
+// costs shared-memory bandwidth again (UMMA reads only the term tiles from shared memory), eight A slots fit beside
+// the accumulator (8 x 32 columns), and the shared memory that the bf16 A ring used goes to deeper TMA rings.
+//   TMEM columns [0, 256): accumulator (hi | lo halves), [256, 512): 8 A slots of 32 columns (64 bf16 per row)
+// Thread = row of the tile = TMEM lane, so all four converter warps work on every k-block (a warp can only touch its
+// own 32 lanes).  The int8 staging tile uses the 64-byte TMA swizzle so that 32 rows can be read without bank conflicts.
+namespace {
+constexpr int TA_NX = 12, TA_NA = 8, TA_NB_MAX = 4;
+// One "full" and one "empty" barrier per k-block slot (ring of TA_NA): `full` collects the four converter warps AND the
+// TMA bytes of the term tiles, `empty` is one tcgen05.commit that both the converters and the term producer watch.
+// The MMA-issuing thread therefore pays one wait and one commit per k-block (a hop over an mbarrier costs ~230 cycles).
+struct TaBars {
+    uint64_t x_full[TA_NX], x_empty[TA_NX], full[TA_NA], empty[TA_NA], acc_full;
+    uint32_t tmem_ptr;
+};
+__host__ __device__ inline size_t ta_fixed() { return 1024 + (size_t)TA_NX * X_STAGE_BYTES + sizeof(TaBars) + 64; }
+__host__ __device__ inline int ta_nb(int terms, int b_tile_bytes) {
+    int nb = (int)((SMEM_LIMIT - ta_fixed()) / ((size_t)terms * b_tile_bytes));
+    return nb > TA_NB_MAX ? TA_NB_MAX : nb;
+}
+}  // namespace
+
+__global__ void __launch_bounds__(256, 1)
+linear_fwd_ta_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
+                     int64_t k_total, int terms, int n_pad, float* __restrict__ out, int64_t ld_out, int64_t m_total, int n_valid) {
+    extern __shared__ uint8_t smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint8_t* base = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);
+    const int b_tile_bytes = n_pad * BK * 2;
+    const int NB = ta_nb(terms, b_tile_bytes);
+    uint8_t* x_stage = base;
+    uint8_t* b_tiles = x_stage + TA_NX * X_STAGE_BYTES;
+    TaBars* bars = reinterpret_cast<TaBars*>(b_tiles + (size_t)NB * terms * b_tile_bytes);
+    const int n_kb = (int)((k_total + BK - 1) / BK);
+    const int64_t m0 = (int64_t)blockIdx.x * BM;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < TA_NX; ++s) { mbar_init(&bars->x_full[s], 1); mbar_init(&bars->x_empty[s], 4); }
+        for (int s = 0; s < TA_NA; ++s) { mbar_init(&bars->full[s], 5); mbar_init(&bars->empty[s], 1); }
+        mbar_init(&bars->acc_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc<512>(&bars->tmem_ptr);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = bars->tmem_ptr;
+    const bool paired = terms >= 2;
+
+    if (warp == 0) {
+        if (elect_one()) {                                     // TMA: raw int8 tiles of X, [128 rows x 64 B], 64-byte swizzle
+            prefetch_tensormap(&map_x);
+            for (int u = 0; u < n_kb; ++u) {
+                const int s = u % TA_NX;
+                mbar_wait(&bars->x_empty[s], ((u / TA_NX) & 1) ^ 1);
+                mbar_arrive_expect_tx(&bars->x_full[s], X_STAGE_BYTES);
+                tma_load_2d(x_stage + s * X_STAGE_BYTES, &map_x, &bars->x_full[s], u * BK, (int32_t)m0);
+            }
+        }
+    } else if (warp == 3) {
+        if (elect_one()) {                                     // TMA: bf16 terms of W, [n_pad rows x 64 k] each
+            prefetch_tensormap(&map_b);
+            for (int u = 0; u < n_kb; ++u) {
+                const int s = u % NB, f = u % TA_NA;
+                if (u >= NB) {                                 // term slot s was last read by k-block u - NB
+                    const int v = u - NB;
+                    mbar_wait(&bars->empty[v % TA_NA], (v / TA_NA) & 1);
+                }
+                mbar_arrive_expect_tx(&bars->full[f], (uint32_t)(terms * b_tile_bytes));
+                uint8_t* dst = b_tiles + (size_t)s * terms * b_tile_bytes;
+                for (int t = 0; t < terms; ++t)
+                    tma_load_2d(dst + t * b_tile_bytes, &map_b, &bars->full[f], u * BK, t * n_pad);
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {                                     // MMA issue: A from TMEM, B from shared memory
+            const uint32_t idesc1 = make_idesc(1, 1, 0, 0, BM, (uint32_t)n_pad);
+            const uint32_t idesc2 = make_idesc(1, 1, 0, 0, BM, (uint32_t)(2 * n_pad));
+            for (int u = 0; u < n_kb; ++u) {
+                const int sa = u % TA_NA, sb = u % NB;
+                mbar_wait(&bars->full[sa], (u / TA_NA) & 1);
+                tc_fence_after_sync();
+                const uint32_t a_tmem = tmem_base + 256 + (uint32_t)sa * 32;
+                const uint64_t db0 = make_smem_desc(smem_u32(b_tiles + (size_t)sb * terms * b_tile_bytes), 16, 1024);
+                const uint64_t term_step = (uint64_t)(b_tile_bytes >> 4);
+#pragma unroll
+                for (int k16 = 0; k16 < BK / 16; ++k16)        // hi (+ lo) terms as one operand of N = n_pad or 2 n_pad
+                    mma_bf16_ts(tmem_base, a_tmem + k16 * 8, db0 + (uint64_t)(k16 * 2), paired ? idesc2 : idesc1, (u > 0 || k16 > 0) ? 1u : 0u);
+                if (terms == 3) {
+#pragma unroll
+                    for (int k16 = 0; k16 < BK / 16; ++k16)
+                        mma_bf16_ts(tmem_base, a_tmem + k16 * 8, db0 + 2 * term_step + (uint64_t)(k16 * 2), idesc1, 1u);
+                }
+                tc_commit(&bars->empty[sa]);
+            }
+            tc_commit(&bars->acc_full);
+        }
+    } else if (warp >= 4) {
+        // ===================================================== converter: int8 staging (smem) -> bf16 A slot (TMEM)
+        const int wq = warp & 3;
+        const int r = 32 * wq + lane;                          // row of the tile == TMEM lane
+        const uint32_t sw = (uint32_t)((r >> 1) & 3);          // 64-byte swizzle: 16-byte chunk index ^= (row / 2) % 4
+        for (int u = 0; u < n_kb; ++u) {
+            const int sx = u % TA_NX, sa = u % TA_NA;
+            mbar_wait(&bars->x_full[sx], (u / TA_NX) & 1);
+            mbar_wait(&bars->empty[sa], ((u / TA_NA) & 1) ^ 1);
+            tc_fence_after_sync();
+            const uint32_t row_s = smem_u32(x_stage + sx * X_STAGE_BYTES) + (uint32_t)r * 64;
+            uint4 in[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                             : "=r"(in[c].x), "=r"(in[c].y), "=r"(in[c].z), "=r"(in[c].w) : "r"(row_s + (((uint32_t)c ^ sw) << 4)));
+            uint32_t v[32];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                uint4 lo, hi;
+                cvt16(in[c], lo, hi);
+                v[8 * c + 0] = lo.x; v[8 * c + 1] = lo.y; v[8 * c + 2] = lo.z; v[8 * c + 3] = lo.w;
+                v[8 * c + 4] = hi.x; v[8 * c + 5] = hi.y; v[8 * c + 6] = hi.z; v[8 * c + 7] = hi.w;
+            }
+            tmem_st_32x32b_x32(tmem_base + ((uint32_t)(32 * wq) << 16) + 256 + (uint32_t)sa * 32, v);
+            tmem_st_wait();
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(&bars->full[sa]);
+                mbar_arrive(&bars->x_empty[sx]);
+            }
+        }
+        // ===================================================== epilogue
+        mbar_wait(&bars->acc_full, 0);
+        tc_fence_after_sync();
+        const int64_t m = m0 + r;
+#pragma unroll 1
+        for (int chunk = 0; chunk * 32 < n_pad; ++chunk) {
+            uint32_t a[32], b[32];
+            const uint32_t taddr = tmem_base + ((uint32_t)(32 * wq) << 16) + chunk * 32;
+            tmem_ld_32x32b_x32(taddr, a);
+            if (paired) tmem_ld_32x32b_x32(taddr + (uint32_t)n_pad, b);
+            tmem_ld_wait();
+            if (m < m_total) {
+#pragma unroll
+                for (int c = 0; c < 32; ++c) {
+                    const int f = chunk * 32 + c;
+                    if (f < n_valid) out[m * ld_out + f] = paired ? __uint_as_float(a[c]) + __uint_as_float(b[c]) : __uint_as_float(a[c]);
+                }
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
     if (warp == 2) tmem_dealloc<512>(tmem_base);
 }
 
@@ -348,6 +534,7 @@ static void plan_tiles(int64_t tiles, int64_t n_kb, int* rt_out, int* splits_out
     // default 1: measured on B200, sharing a term tile between 2 or 4 X tiles does not pay -- the kernel is bound by
     // shared-memory bandwidth (UMMA operand reads + TMA writes + the converter), not by L2 -> SM traffic
     int rt = forced ? forced : 1;
+    if (rt > 512 / ACC_COLS) rt = 512 / ACC_COLS;          // TMEM holds 512 columns
     int64_t supertiles = (tiles + rt - 1) / rt;
     int64_t s = sm_count() / supertiles;
     if (s > n_kb / 16) s = n_kb / 16;
@@ -431,6 +618,22 @@ int linear_tc_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
         GNNB_LAUNCH_CHECK();
     }
     const int64_t tiles = (n + BM - 1) / BM;
+    static int use_ta = -1;
+    if (use_ta < 0) { const char* e = getenv("GNNB_LINEAR_TA"); use_ta = e ? atoi(e) : 1; }
+    if (use_ta && h_pad <= 128) {
+        // A operand in tensor memory (see linear_fwd_ta_kernel)
+        CUtensorMap mx, mb;
+        int rc2 = make_tensor_map_2d(&mx, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, BK, BM, false, /*swizzle64*/ true);
+        if (rc2 != GNNB_OK) return rc2;
+        rc2 = make_tensor_map_2d(&mb, Wt, 2, (uint64_t)p_ld, (uint64_t)(terms * h_pad), (uint64_t)p_ld * 2, BK, (uint32_t)h_pad, true);
+        if (rc2 != GNNB_OK) return rc2;
+        const int btile = (int)(h_pad * BK * 2);
+        const size_t smem_ta = ta_fixed() + (size_t)ta_nb(terms, btile) * terms * btile;
+        GNNB_CUDA(cudaFuncSetAttribute(linear_fwd_ta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ta));
+        linear_fwd_ta_kernel<<<(unsigned)tiles, 256, smem_ta, stream>>>(mx, mb, p, terms, (int)h_pad, H, ldh, n, (int)h);
+        GNNB_LAUNCH_CHECK();
+        return GNNB_OK;
+    }
     int rt, splits;
     plan_tiles(tiles, (p + BK - 1) / BK, &rt, &splits);
     const int csize = cluster_size((tiles + rt - 1) / rt);

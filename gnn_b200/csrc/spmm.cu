@@ -17,14 +17,15 @@ constexpr int LONG_ROW = 256;       // rows with more entries than this (hubs of
 
 __device__ __forceinline__ float4 ld_row4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 
+// warp-per-row part (rows of at most LONG_ROW entries); `block` / `nblocks` index the CTAs that play this role
 template <bool HAS_BIAS>
-__global__ void __launch_bounds__(256)
-spmm_vec4_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ val, int64_t n,
-                 const float* __restrict__ H, int64_t ldh, int F, const float* __restrict__ bias,
-                 float* __restrict__ out, int64_t ldo) {
+__device__ __forceinline__ void spmm_rows_vec4(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                                               const float* __restrict__ val, int64_t n, const float* __restrict__ H, int64_t ldh, int F,
+                                               const float* __restrict__ bias, float* __restrict__ out, int64_t ldo,
+                                               int64_t block, int64_t nblocks) {
     const int lane = threadIdx.x & 31;
-    const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t warp0 = (block * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = (nblocks * blockDim.x) >> 5;
     for (int64_t row = warp0; row < n; row += nwarps) {
         const int start = rowptr[row], end = rowptr[row + 1];
         if (end - start > LONG_ROW) continue;                   // spmm_long_rows_kernel owns this row
@@ -123,17 +124,17 @@ spmm_scalar_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict
 // take the row's 32-entry chunks round-robin, and the 8 partial sums are added in warp order (fixed => deterministic).
 // CTAs scan blocks of 64 rows for candidates, so no list of long rows has to be kept with the graph (the order in
 // which a CTA visits its candidates does not matter: rows are independent).
-template <bool HAS_BIAS, bool VEC>
-__global__ void __launch_bounds__(256)
-spmm_long_rows_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ val, int64_t n,
-                      const float* __restrict__ H, int64_t ldh, int F, const float* __restrict__ bias,
-                      float* __restrict__ out, int64_t ldo) {
+template <bool HAS_BIAS, bool VEC, int NW>
+__device__ __forceinline__ void spmm_long_rows(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                                               const float* __restrict__ val, int64_t n, const float* __restrict__ H, int64_t ldh, int F,
+                                               const float* __restrict__ bias, float* __restrict__ out, int64_t ldo,
+                                               int64_t block, int64_t nblocks) {
     constexpr int SCAN = 64;
     __shared__ int s_rows[SCAN];
     __shared__ int s_count;
-    __shared__ float4 s_part[8][32];
+    __shared__ float4 s_part[NW][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int64_t base_row = (int64_t)blockIdx.x * SCAN; base_row < n; base_row += (int64_t)gridDim.x * SCAN) {
+    for (int64_t base_row = block * SCAN; base_row < n; base_row += nblocks * SCAN) {
         if (threadIdx.x == 0) s_count = 0;
         __syncthreads();
         const int64_t r = base_row + threadIdx.x;
@@ -147,7 +148,7 @@ spmm_long_rows_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restr
                 const int f = fc + (VEC ? lane * 4 : lane);
                 const bool active = f < F;
                 float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int base = start + warp * 32; base < end; base += 8 * 32) {
+                for (int base = start + warp * 32; base < end; base += NW * 32) {
                     const int e = base + lane;
                     int c = 0;
                     float v = 0.f;
@@ -197,7 +198,7 @@ spmm_long_rows_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restr
                 if (warp == 0 && active) {
                     float4 tot = s_part[0][lane];
 #pragma unroll
-                    for (int w2 = 1; w2 < 8; ++w2) {
+                    for (int w2 = 1; w2 < NW; ++w2) {
                         tot.x += s_part[w2][lane].x; tot.y += s_part[w2][lane].y;
                         tot.z += s_part[w2][lane].z; tot.w += s_part[w2][lane].w;
                     }
@@ -218,6 +219,28 @@ spmm_long_rows_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restr
     }
 }
 
+// One launch for both roles: the first `long_blocks` CTAs scan for hub rows (they start first, which is what the tail
+// wants), the rest run one warp per ordinary row.
+template <bool HAS_BIAS>
+__global__ void __launch_bounds__(512)
+spmm_fused_vec4_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ val, int64_t n,
+                       const float* __restrict__ H, int64_t ldh, int F, const float* __restrict__ bias,
+                       float* __restrict__ out, int64_t ldo, int long_blocks) {
+    if ((int)blockIdx.x < long_blocks)
+        spmm_long_rows<HAS_BIAS, true, 16>(rowptr, col, val, n, H, ldh, F, bias, out, ldo, blockIdx.x, long_blocks);
+    else
+        spmm_rows_vec4<HAS_BIAS>(rowptr, col, val, n, H, ldh, F, bias, out, ldo, (int64_t)blockIdx.x - long_blocks,
+                                 (int64_t)gridDim.x - long_blocks);
+}
+
+template <bool HAS_BIAS>
+__global__ void __launch_bounds__(256)
+spmm_long_rows_scalar_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ val, int64_t n,
+                             const float* __restrict__ H, int64_t ldh, int F, const float* __restrict__ bias,
+                             float* __restrict__ out, int64_t ldo) {
+    spmm_long_rows<HAS_BIAS, false, 8>(rowptr, col, val, n, H, ldh, F, bias, out, ldo, blockIdx.x, gridDim.x);
+}
+
 }  // namespace gnnb
 
 using namespace gnnb;
@@ -233,27 +256,28 @@ extern "C" int gnnb_spmm(const int32_t* rowptr, const int32_t* col, const float*
     if (n == 0) return GNNB_OK;
     bool vec = (F % 4 == 0) && (ldh % 4 == 0) && (ldo % 4 == 0) && ((uintptr_t)H % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
                (!bias || (uintptr_t)bias % 16 == 0);
-    int64_t blocks = (n + 7) / 8;                       // 8 warps (rows) per CTA
-    int64_t cap = (int64_t)sm_count() * 8 * 4;          // grid-stride beyond 32 resident-CTA waves
-    unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
+    const int64_t sms = sm_count();
     if (vec) {
-        if (bias) spmm_vec4_kernel<true><<<grid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
-        else      spmm_vec4_kernel<false><<<grid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
+        int64_t long_blocks = (n + 63) / 64;                // hub-row role: 64 rows scanned per CTA iteration
+        if (long_blocks > sms * 8) long_blocks = sms * 8;
+        int64_t main_blocks = (n + 15) / 16;                // 16 warps (rows) per CTA
+        if (main_blocks > sms * 4 * 8) main_blocks = sms * 4 * 8;
+        unsigned grid = (unsigned)(long_blocks + main_blocks);
+        if (bias) spmm_fused_vec4_kernel<true><<<grid, 512, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo, (int)long_blocks);
+        else      spmm_fused_vec4_kernel<false><<<grid, 512, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo, (int)long_blocks);
+        GNNB_LAUNCH_CHECK();
     } else {
-        if (bias) spmm_scalar_kernel<true><<<grid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
-        else      spmm_scalar_kernel<false><<<grid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
-    }
-    GNNB_LAUNCH_CHECK();
-    {   // hub rows (skipped above)
+        int64_t blocks = (n + 7) / 8;
+        int64_t cap = sms * 8 * 4;
+        unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
         int64_t lblocks = (n + 63) / 64;
-        int64_t lcap = (int64_t)sm_count() * 8;
-        unsigned lgrid = (unsigned)(lblocks < lcap ? lblocks : lcap);
-        if (vec) {
-            if (bias) spmm_long_rows_kernel<true, true><<<lgrid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
-            else      spmm_long_rows_kernel<false, true><<<lgrid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
+        unsigned lgrid = (unsigned)(lblocks < sms * 8 ? lblocks : sms * 8);
+        if (bias) {
+            spmm_scalar_kernel<true><<<grid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
+            spmm_long_rows_scalar_kernel<true><<<lgrid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
         } else {
-            if (bias) spmm_long_rows_kernel<true, false><<<lgrid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
-            else      spmm_long_rows_kernel<false, false><<<lgrid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
+            spmm_scalar_kernel<false><<<grid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
+            spmm_long_rows_scalar_kernel<false><<<lgrid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo);
         }
         GNNB_LAUNCH_CHECK();
     }

@@ -22,7 +22,7 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 int make_tensor_map_2d(CUtensorMap* map, const void* base, int elem_bytes, uint64_t cols, uint64_t rows, uint64_t ld_bytes,
-                       uint32_t box_cols, uint32_t box_rows, bool swizzle128) {
+                       uint32_t box_cols, uint32_t box_rows, bool swizzle128, bool swizzle64) {
     EncodeTiledFn fn = get_encode_fn();
     if (!fn) return fail(GNNB_E_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
     if ((uintptr_t)base % 16 != 0 || ld_bytes % 16 != 0)
@@ -36,7 +36,7 @@ int make_tensor_map_2d(CUtensorMap* map, const void* base, int elem_bytes, uint6
     cuuint32_t box[2] = {box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = fn(map, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                    swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                    swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : (swizzle64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE), CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(GNNB_E_CUDA, "cuTensorMapEncodeTiled failed with code %d", (int)r);
     return GNNB_OK;
 }

@@ -281,23 +281,39 @@ __global__ void sqnorm_kernel(const int8_t* __restrict__ X, int64_t ldx, int64_t
     }
 }
 
-// column sums: out[f] = sum_i A[i, f]; deterministic two-stage (fixed partition of rows, fixed order)
-__global__ void colsum_partial_kernel(const float* __restrict__ A, int64_t lda, int64_t n, int64_t F,
-                                      float* __restrict__ partial, int rows_per_block) {
-    int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
-    int64_t r1 = r0 + rows_per_block < n ? r0 + rows_per_block : n;
-    for (int64_t f = threadIdx.x; f < F; f += blockDim.x) {
+// column sums: out[f] = sum_i A[i, f]; deterministic two-stage (fixed partition of rows, fixed order inside a block)
+// stage 1: block b owns rows [b * rows_per_block, ...): 8 row-lanes x 32 columns per pass, lanes combined in lane order
+__global__ void __launch_bounds__(256) colsum_partial_kernel(const float* __restrict__ A, int64_t lda, int64_t n, int64_t F,
+                                                             float* __restrict__ partial, int rows_per_block) {
+    __shared__ float red[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+    const int64_t r1 = r0 + rows_per_block < n ? r0 + rows_per_block : n;
+    for (int64_t f0 = 0; f0 < F; f0 += 32) {
+        const int64_t f = f0 + tx;
         float s = 0.f;
-        for (int64_t r = r0; r < r1; ++r) s += A[r * lda + f];
-        partial[(int64_t)blockIdx.x * F + f] = s;
+        if (f < F)
+            for (int64_t r = r0 + ty; r < r1; r += 8) s += A[r * lda + f];
+        red[ty][tx] = s;
+        __syncthreads();
+        if (ty == 0 && f < F) {
+            float t = red[0][tx];
+#pragma unroll
+            for (int q = 1; q < 8; ++q) t += red[q][tx];
+            partial[(int64_t)blockIdx.x * F + f] = t;
+        }
+        __syncthreads();
     }
 }
-__global__ void colsum_final_kernel(const float* __restrict__ partial, int nblocks, int64_t F, float* __restrict__ out) {
-    for (int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; f < F; f += (int64_t)gridDim.x * blockDim.x) {
-        float s = 0.f;
-        for (int b = 0; b < nblocks; ++b) s += partial[(int64_t)b * F + f];
-        out[f] = s;
-    }
+// stage 2: one warp per column, lanes stride over the blocks, fixed butterfly order
+__global__ void __launch_bounds__(256) colsum_final_kernel(const float* __restrict__ partial, int nblocks, int64_t F, float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t f = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (f >= F) return;
+    float s = 0.f;
+    for (int b = lane; b < nblocks; b += 32) s += partial[(int64_t)b * F + f];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) out[f] = s;
 }
 
 }  // namespace gnnb
@@ -378,9 +394,9 @@ int gnnb_colsum(const float* A, int64_t lda, int64_t n, int64_t F, float* out,
     int rows_per_block = (int)((n + nblocks - 1) / nblocks);
     if (rows_per_block < 1) rows_per_block = 1;
     float* partial = static_cast<float*>(workspace);
-    colsum_partial_kernel<<<(unsigned)nblocks, 128, 0, (cudaStream_t)stream>>>(A, lda, n, F, partial, rows_per_block);
+    colsum_partial_kernel<<<(unsigned)nblocks, 256, 0, (cudaStream_t)stream>>>(A, lda, n, F, partial, rows_per_block);
     GNNB_LAUNCH_CHECK();
-    colsum_final_kernel<<<(unsigned)((F + 127) / 128), 128, 0, (cudaStream_t)stream>>>(partial, (int)nblocks, F, out);
+    colsum_final_kernel<<<(unsigned)((F * 32 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(partial, (int)nblocks, F, out);
     GNNB_LAUNCH_CHECK();
     return GNNB_OK;
 }
@@ -432,9 +448,9 @@ int gnnb_colsum_static(const float* A, int64_t lda, int64_t n, int64_t F, float*
     if (nblocks < 1) nblocks = 1;
     int rows_per_block = (int)((n + nblocks - 1) / nblocks);
     if (rows_per_block < 1) rows_per_block = 1;
-    colsum_partial_kernel<<<(unsigned)nblocks, 128, 0, (cudaStream_t)stream>>>(A, lda, n, F, partial, rows_per_block);
+    colsum_partial_kernel<<<(unsigned)nblocks, 256, 0, (cudaStream_t)stream>>>(A, lda, n, F, partial, rows_per_block);
     GNNB_LAUNCH_CHECK();
-    colsum_final_kernel<<<(unsigned)((F + 127) / 128), 128, 0, (cudaStream_t)stream>>>(partial, (int)nblocks, F, out);
+    colsum_final_kernel<<<(unsigned)((F * 32 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(partial, (int)nblocks, F, out);
     GNNB_LAUNCH_CHECK();
     return GNNB_OK;
 }
