@@ -341,7 +341,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// Forward projection with the A operand in TENSOR MEMORY.
+// Projection kernels with the A operand (the X tile) in TENSOR MEMORY.
 // The converter warps write the bf16 X tile straight into TMEM (tcgen05.st), not into shared memory: the tile never
 // costs shared-memory bandwidth again (UMMA reads only the term tiles from shared memory), eight A slots fit beside
 // the accumulator (8 x 32 columns), and the shared memory that the bf16 A ring used goes to deeper TMA rings.
@@ -364,13 +364,15 @@ __host__ __device__ inline int ta_nb(int terms, int b_tile_bytes) {
 }
 }  // namespace
 
+template <bool BWD>
 __global__ void __launch_bounds__(256, 1)
-linear_fwd_ta_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
-                     int64_t k_total, int terms, int n_pad, float* __restrict__ out, int64_t ld_out, int64_t m_total, int n_valid) {
+linear_ta_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
+                 int64_t k_total, int terms, int n_pad, int64_t b_term_rows,
+                 float* __restrict__ out, int64_t ld_out, int64_t m_total, int n_valid) {
     extern __shared__ uint8_t smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint8_t* base = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);
-    const int b_tile_bytes = n_pad * BK * 2;
+    const int b_tile_bytes = BWD ? (BK * 128 * 2) : (n_pad * BK * 2);
     const int NB = ta_nb(terms, b_tile_bytes);
     uint8_t* x_stage = base;
     uint8_t* b_tiles = x_stage + TA_NX * X_STAGE_BYTES;
@@ -398,7 +400,8 @@ linear_fwd_ta_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
                 const int s = u % TA_NX;
                 mbar_wait(&bars->x_empty[s], ((u / TA_NX) & 1) ^ 1);
                 mbar_arrive_expect_tx(&bars->x_full[s], X_STAGE_BYTES);
-                tma_load_2d(x_stage + s * X_STAGE_BYTES, &map_x, &bars->x_full[s], u * BK, (int32_t)m0);
+                if (BWD) tma_load_2d(x_stage + s * X_STAGE_BYTES, &map_x, &bars->x_full[s], (int32_t)m0, u * BK);   // [64 k-rows x 128 markers]
+                else     tma_load_2d(x_stage + s * X_STAGE_BYTES, &map_x, &bars->x_full[s], u * BK, (int32_t)m0);   // [128 rows x 64 k]
             }
         }
     } else if (warp == 3) {
@@ -412,28 +415,38 @@ linear_fwd_ta_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
                 }
                 mbar_arrive_expect_tx(&bars->full[f], (uint32_t)(terms * b_tile_bytes));
                 uint8_t* dst = b_tiles + (size_t)s * terms * b_tile_bytes;
-                for (int t = 0; t < terms; ++t)
-                    tma_load_2d(dst + t * b_tile_bytes, &map_b, &bars->full[f], u * BK, t * n_pad);
+                for (int t = 0; t < terms; ++t) {
+                    if (BWD) {   // dH terms: two 64-feature groups of [64 k-rows x 128 B]
+                        const int32_t grow = (int32_t)(t * b_term_rows + (int64_t)u * BK);
+                        tma_load_2d(dst + t * b_tile_bytes, &map_b, &bars->full[f], 0, grow);
+                        tma_load_2d(dst + t * b_tile_bytes + BK * 128, &map_b, &bars->full[f], 64, grow);
+                    } else {
+                        tma_load_2d(dst + t * b_tile_bytes, &map_b, &bars->full[f], u * BK, t * n_pad);
+                    }
+                }
             }
         }
     } else if (warp == 1) {
         if (elect_one()) {                                     // MMA issue: A from TMEM, B from shared memory
-            const uint32_t idesc1 = make_idesc(1, 1, 0, 0, BM, (uint32_t)n_pad);
-            const uint32_t idesc2 = make_idesc(1, 1, 0, 0, BM, (uint32_t)(2 * n_pad));
+            // A comes from TMEM (rows = lanes, k along columns); B is K-major (forward) or MN-major (backward) in shared memory
+            const uint32_t idesc1 = make_idesc(1, 1, 0, BWD ? 1 : 0, BM, (uint32_t)n_pad);
+            const uint32_t idesc2 = make_idesc(1, 1, 0, BWD ? 1 : 0, BM, (uint32_t)(2 * n_pad));
             for (int u = 0; u < n_kb; ++u) {
                 const int sa = u % TA_NA, sb = u % NB;
                 mbar_wait(&bars->full[sa], (u / TA_NA) & 1);
                 tc_fence_after_sync();
                 const uint32_t a_tmem = tmem_base + 256 + (uint32_t)sa * 32;
-                const uint64_t db0 = make_smem_desc(smem_u32(b_tiles + (size_t)sb * terms * b_tile_bytes), 16, 1024);
+                const uint32_t b_addr = smem_u32(b_tiles + (size_t)sb * terms * b_tile_bytes);
+                const uint64_t db0 = BWD ? make_smem_desc(b_addr, BK * 128, 1024) : make_smem_desc(b_addr, 16, 1024);
                 const uint64_t term_step = (uint64_t)(b_tile_bytes >> 4);
+                const uint64_t k_step = BWD ? (2048 >> 4) : (32 >> 4);      // 16 k: two 8-row atoms (MN-major) / 32 bytes (K-major)
 #pragma unroll
                 for (int k16 = 0; k16 < BK / 16; ++k16)        // hi (+ lo) terms as one operand of N = n_pad or 2 n_pad
-                    mma_bf16_ts(tmem_base, a_tmem + k16 * 8, db0 + (uint64_t)(k16 * 2), paired ? idesc2 : idesc1, (u > 0 || k16 > 0) ? 1u : 0u);
+                    mma_bf16_ts(tmem_base, a_tmem + k16 * 8, db0 + k16 * k_step, paired ? idesc2 : idesc1, (u > 0 || k16 > 0) ? 1u : 0u);
                 if (terms == 3) {
 #pragma unroll
                     for (int k16 = 0; k16 < BK / 16; ++k16)
-                        mma_bf16_ts(tmem_base, a_tmem + k16 * 8, db0 + 2 * term_step + (uint64_t)(k16 * 2), idesc1, 1u);
+                        mma_bf16_ts(tmem_base, a_tmem + k16 * 8, db0 + 2 * term_step + k16 * k_step, idesc1, 1u);
                 }
                 tc_commit(&bars->empty[sa]);
             }
@@ -449,19 +462,36 @@ linear_fwd_ta_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
             mbar_wait(&bars->x_full[sx], (u / TA_NX) & 1);
             mbar_wait(&bars->empty[sa], ((u / TA_NA) & 1) ^ 1);
             tc_fence_after_sync();
-            const uint32_t row_s = smem_u32(x_stage + sx * X_STAGE_BYTES) + (uint32_t)r * 64;
-            uint4 in[4];
-#pragma unroll
-            for (int c = 0; c < 4; ++c)
-                asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                             : "=r"(in[c].x), "=r"(in[c].y), "=r"(in[c].z), "=r"(in[c].w) : "r"(row_s + (((uint32_t)c ^ sw) << 4)));
             uint32_t v[32];
+            if (BWD) {
+                // staging [64 k-rows][128 markers]: this thread owns marker column r, i.e. one byte of every row (a warp reads
+                // 32 consecutive bytes per row: one wavefront, no conflicts); pairs of k become one bf16x2 column of the A slot
+                const uint32_t col_s = smem_u32(x_stage + sx * X_STAGE_BYTES) + (uint32_t)r;
+                const __nv_bfloat162 k128 = __halves2bfloat162(__ushort_as_bfloat16((unsigned short)0x4300), __ushort_as_bfloat16((unsigned short)0x4300));
+                uint32_t bytes[64];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                uint4 lo, hi;
-                cvt16(in[c], lo, hi);
-                v[8 * c + 0] = lo.x; v[8 * c + 1] = lo.y; v[8 * c + 2] = lo.z; v[8 * c + 3] = lo.w;
-                v[8 * c + 4] = hi.x; v[8 * c + 5] = hi.y; v[8 * c + 6] = hi.z; v[8 * c + 7] = hi.w;
+                for (int kk = 0; kk < 64; ++kk)
+                    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(bytes[kk]) : "r"(col_s + kk * 128));
+#pragma unroll
+                for (int q = 0; q < 32; ++q) {
+                    uint32_t w = __byte_perm(bytes[2 * q], bytes[2 * q + 1], 0x5410) | 0x43004300u;     // {b_k, 0x43, b_k+1, 0x43}
+                    __nv_bfloat162 h2 = __hsub2(*reinterpret_cast<__nv_bfloat162*>(&w), k128);
+                    v[q] = *reinterpret_cast<uint32_t*>(&h2);
+                }
+            } else {
+                const uint32_t row_s = smem_u32(x_stage + sx * X_STAGE_BYTES) + (uint32_t)r * 64;
+                uint4 in[4];
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                                 : "=r"(in[c].x), "=r"(in[c].y), "=r"(in[c].z), "=r"(in[c].w) : "r"(row_s + (((uint32_t)c ^ sw) << 4)));
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint4 lo, hi;
+                    cvt16(in[c], lo, hi);
+                    v[8 * c + 0] = lo.x; v[8 * c + 1] = lo.y; v[8 * c + 2] = lo.z; v[8 * c + 3] = lo.w;
+                    v[8 * c + 4] = hi.x; v[8 * c + 5] = hi.y; v[8 * c + 6] = hi.z; v[8 * c + 7] = hi.w;
+                }
             }
             tmem_st_32x32b_x32(tmem_base + ((uint32_t)(32 * wq) << 16) + 256 + (uint32_t)sa * 32, v);
             tmem_st_wait();
@@ -487,7 +517,11 @@ linear_fwd_ta_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
 #pragma unroll
                 for (int c = 0; c < 32; ++c) {
                     const int f = chunk * 32 + c;
-                    if (f < n_valid) out[m * ld_out + f] = paired ? __uint_as_float(a[c]) + __uint_as_float(b[c]) : __uint_as_float(a[c]);
+                    if (f < n_valid) {
+                        const float rr = paired ? __uint_as_float(a[c]) + __uint_as_float(b[c]) : __uint_as_float(a[c]);
+                        if (BWD) out[(int64_t)f * ld_out + m] = rr;      // dW[f, marker]: a warp writes 32 consecutive markers
+                        else     out[m * ld_out + f] = rr;               // H[row, f]
+                    }
                 }
             }
         }
@@ -629,8 +663,8 @@ int linear_tc_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
         if (rc2 != GNNB_OK) return rc2;
         const int btile = (int)(h_pad * BK * 2);
         const size_t smem_ta = ta_fixed() + (size_t)ta_nb(terms, btile) * terms * btile;
-        GNNB_CUDA(cudaFuncSetAttribute(linear_fwd_ta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ta));
-        linear_fwd_ta_kernel<<<(unsigned)tiles, 256, smem_ta, stream>>>(mx, mb, p, terms, (int)h_pad, H, ldh, n, (int)h);
+        GNNB_CUDA(cudaFuncSetAttribute(linear_ta_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ta));
+        linear_ta_kernel<false><<<(unsigned)tiles, 256, smem_ta, stream>>>(mx, mb, p, terms, (int)h_pad, h_pad, H, ldh, n, (int)h);
         GNNB_LAUNCH_CHECK();
         return GNNB_OK;
     }
@@ -661,6 +695,21 @@ int linear_tc_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t 
         GNNB_LAUNCH_CHECK();
     }
     const int64_t tiles = (p + BM - 1) / BM;
+    static int use_ta = -1;
+    if (use_ta < 0) { const char* e = getenv("GNNB_LINEAR_TA"); use_ta = e ? atoi(e) : 1; }
+    if (use_ta) {
+        CUtensorMap mx, mb;
+        int rc2 = make_tensor_map_2d(&mx, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, 128, BK, /*swizzle*/ false);
+        if (rc2 != GNNB_OK) return rc2;
+        rc2 = make_tensor_map_2d(&mb, Dt, 2, 128, (uint64_t)(terms * n), 256, 64, BK, true);
+        if (rc2 != GNNB_OK) return rc2;
+        const int btile = BK * 128 * 2;
+        const size_t smem_ta = ta_fixed() + (size_t)ta_nb(terms, btile) * terms * btile;
+        GNNB_CUDA(cudaFuncSetAttribute(linear_ta_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ta));
+        linear_ta_kernel<true><<<(unsigned)tiles, 256, smem_ta, stream>>>(mx, mb, n, terms, 128, n, dW, lddw, p, (int)h);
+        GNNB_LAUNCH_CHECK();
+        return GNNB_OK;
+    }
     int rt, splits;
     plan_tiles(tiles, (n + BK - 1) / BK, &rt, &splits);
     const int csize = cluster_size((tiles + rt - 1) / rt);
