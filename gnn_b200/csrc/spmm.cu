@@ -12,7 +12,7 @@
 
 namespace gnnb {
 
-constexpr int GATHER_UNROLL = 8;
+constexpr int GATHER_UNROLL = 4;
 constexpr int LONG_ROW = 256;       // rows with more entries than this (hubs of the kNN graph) get a whole CTA
 
 __device__ __forceinline__ float4 ld_row4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
@@ -222,12 +222,12 @@ __device__ __forceinline__ void spmm_long_rows(const int32_t* __restrict__ rowpt
 // One launch for both roles: the first `long_blocks` CTAs scan for hub rows (they start first, which is what the tail
 // wants), the rest run one warp per ordinary row.
 template <bool HAS_BIAS>
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(256, 4)        // <= 64 registers: 32 resident warps per SM for the gather latency
 spmm_fused_vec4_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ val, int64_t n,
                        const float* __restrict__ H, int64_t ldh, int F, const float* __restrict__ bias,
                        float* __restrict__ out, int64_t ldo, int long_blocks) {
     if ((int)blockIdx.x < long_blocks)
-        spmm_long_rows<HAS_BIAS, true, 16>(rowptr, col, val, n, H, ldh, F, bias, out, ldo, blockIdx.x, long_blocks);
+        spmm_long_rows<HAS_BIAS, true, 8>(rowptr, col, val, n, H, ldh, F, bias, out, ldo, blockIdx.x, long_blocks);
     else
         spmm_rows_vec4<HAS_BIAS>(rowptr, col, val, n, H, ldh, F, bias, out, ldo, (int64_t)blockIdx.x - long_blocks,
                                  (int64_t)gridDim.x - long_blocks);
@@ -260,11 +260,11 @@ extern "C" int gnnb_spmm(const int32_t* rowptr, const int32_t* col, const float*
     if (vec) {
         int64_t long_blocks = (n + 63) / 64;                // hub-row role: 64 rows scanned per CTA iteration
         if (long_blocks > sms * 8) long_blocks = sms * 8;
-        int64_t main_blocks = (n + 15) / 16;                // 16 warps (rows) per CTA
-        if (main_blocks > sms * 4 * 8) main_blocks = sms * 4 * 8;
+        int64_t main_blocks = (n + 7) / 8;                  // 8 warps (rows) per CTA
+        if (main_blocks > sms * 4 * 16) main_blocks = sms * 4 * 16;
         unsigned grid = (unsigned)(long_blocks + main_blocks);
-        if (bias) spmm_fused_vec4_kernel<true><<<grid, 512, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo, (int)long_blocks);
-        else      spmm_fused_vec4_kernel<false><<<grid, 512, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo, (int)long_blocks);
+        if (bias) spmm_fused_vec4_kernel<true><<<grid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo, (int)long_blocks);
+        else      spmm_fused_vec4_kernel<false><<<grid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo, (int)long_blocks);
         GNNB_LAUNCH_CHECK();
     } else {
         int64_t blocks = (n + 7) / 8;
