@@ -35,7 +35,9 @@ PROTOTYPES = {
     "gnnb_csr_workspace_bytes": (_i32, [_i64, _i64, _psz]),
     "gnnb_csr_count": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp, _sz, _vp]),
     "gnnb_csr_build": (_i32, [_vp, _vp, _i64, _i64, _i32, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
-    "gnnb_spmm": (_i32, [_vp, _vp, _vp, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _vp]),
+    "gnnb_spmm": (_i32, [_vp, _vp, _vp, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _vp]),
+    "gnnb_spmm_long_row": (_i32, []),
+    "gnnb_spmm_workspace_bytes": (_i32, [_i64, _i64, _psz]),
     "gnnb_linear_workspace_bytes": (_i32, [_i64, _i64, _i64, _i32, _psz]),
     "gnnb_linear_fwd": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _i64, _i32, _vp, _sz, _vp]),
     "gnnb_linear_bwd_w": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _i64, _i32, _vp, _sz, _vp]),

@@ -219,6 +219,112 @@ __device__ __forceinline__ void spmm_long_rows(const int32_t* __restrict__ rowpt
     }
 }
 
+// Hub rows split into tasks of LONG_ROW entries (the plan is made once per graph by the caller): one warp per task
+// writes its partial sum to scratch; the warp that completes a row last adds the partials in task order, so the result
+// does not depend on which warp that is.
+template <bool HAS_BIAS>
+__device__ __forceinline__ void spmm_hub_tasks(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                                               const float* __restrict__ val, const float* __restrict__ H, int64_t ldh, int F,
+                                               const float* __restrict__ bias, float* __restrict__ out, int64_t ldo,
+                                               const int32_t* __restrict__ task_row, const int32_t* __restrict__ task_chunk,
+                                               const int32_t* __restrict__ task_first, const int32_t* __restrict__ task_count,
+                                               int64_t n_tasks, float* __restrict__ partial, int* __restrict__ counters,
+                                               int64_t block, int64_t nblocks) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = (block * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = (nblocks * blockDim.x) >> 5;
+    for (int64_t t = warp0; t < n_tasks; t += nwarps) {
+        const int row = task_row[t];
+        const int start = rowptr[row] + task_chunk[t] * LONG_ROW;
+        const int end = min(start + LONG_ROW, rowptr[row + 1]);
+        for (int fc = 0; fc < F; fc += 128) {
+            const int f = fc + lane * 4;
+            const bool active = f < F;
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int base = start; base < end; base += 32) {
+                const int e = base + lane;
+                int c = 0;
+                float v = 0.f;
+                if (e < end) {
+                    c = __ldg(col + e);
+                    v = __ldg(val + e);
+                }
+                const int cnt = min(32, end - base);
+                int q = 0;
+                for (; q + GATHER_UNROLL <= cnt; q += GATHER_UNROLL) {
+                    float4 h[GATHER_UNROLL];
+                    float w[GATHER_UNROLL];
+#pragma unroll
+                    for (int u = 0; u < GATHER_UNROLL; ++u) {
+                        int cu = __shfl_sync(0xffffffffu, c, q + u);
+                        w[u] = __shfl_sync(0xffffffffu, v, q + u);
+                        h[u] = active ? ld_row4(H + (int64_t)cu * ldh + f) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+#pragma unroll
+                    for (int u = 0; u < GATHER_UNROLL; ++u) {
+                        acc.x = fmaf(w[u], h[u].x, acc.x);
+                        acc.y = fmaf(w[u], h[u].y, acc.y);
+                        acc.z = fmaf(w[u], h[u].z, acc.z);
+                        acc.w = fmaf(w[u], h[u].w, acc.w);
+                    }
+                }
+                for (; q < cnt; ++q) {
+                    int cu = __shfl_sync(0xffffffffu, c, q);
+                    float wu = __shfl_sync(0xffffffffu, v, q);
+                    if (active) {
+                        float4 hu = ld_row4(H + (int64_t)cu * ldh + f);
+                        acc.x = fmaf(wu, hu.x, acc.x);
+                        acc.y = fmaf(wu, hu.y, acc.y);
+                        acc.z = fmaf(wu, hu.z, acc.z);
+                        acc.w = fmaf(wu, hu.w, acc.w);
+                    }
+                }
+            }
+            if (active) *reinterpret_cast<float4*>(partial + t * F + f) = acc;
+        }
+        __threadfence();
+        __syncwarp();
+        const int first = task_first[t], count = task_count[t];
+        int prev = 0;
+        if (lane == 0) prev = atomicAdd(&counters[first], 1);
+        prev = __shfl_sync(0xffffffffu, prev, 0);
+        if (prev == count - 1) {                   // this warp completed the row: add the partials in task order
+            __threadfence();
+            for (int fc = 0; fc < F; fc += 128) {
+                const int f = fc + lane * 4;
+                if (f < F) {
+                    float4 tot = __ldcg(reinterpret_cast<const float4*>(partial + (int64_t)first * F + f));
+                    for (int q = 1; q < count; ++q) {
+                        float4 pq = __ldcg(reinterpret_cast<const float4*>(partial + (int64_t)(first + q) * F + f));
+                        tot.x += pq.x; tot.y += pq.y; tot.z += pq.z; tot.w += pq.w;
+                    }
+                    if (HAS_BIAS) {
+                        float4 b = ld_row4(bias + f);
+                        tot.x += b.x; tot.y += b.y; tot.z += b.z; tot.w += b.w;
+                    }
+                    *reinterpret_cast<float4*>(out + (int64_t)row * ldo + f) = tot;
+                }
+            }
+        }
+    }
+}
+
+template <bool HAS_BIAS>
+__global__ void __launch_bounds__(256, 4)
+spmm_planned_vec4_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, const float* __restrict__ val, int64_t n,
+                         const float* __restrict__ H, int64_t ldh, int F, const float* __restrict__ bias,
+                         float* __restrict__ out, int64_t ldo, int hub_blocks,
+                         const int32_t* __restrict__ task_row, const int32_t* __restrict__ task_chunk,
+                         const int32_t* __restrict__ task_first, const int32_t* __restrict__ task_count, int64_t n_tasks,
+                         float* __restrict__ partial, int* __restrict__ counters) {
+    if ((int)blockIdx.x < hub_blocks)
+        spmm_hub_tasks<HAS_BIAS>(rowptr, col, val, H, ldh, F, bias, out, ldo, task_row, task_chunk, task_first, task_count, n_tasks,
+                                 partial, counters, blockIdx.x, hub_blocks);
+    else
+        spmm_rows_vec4<HAS_BIAS>(rowptr, col, val, n, H, ldh, F, bias, out, ldo, (int64_t)blockIdx.x - hub_blocks,
+                                 (int64_t)gridDim.x - hub_blocks);
+}
+
 // One launch for both roles: the first `long_blocks` CTAs scan for hub rows (they start first, which is what the tail
 // wants), the rest run one warp per ordinary row.
 template <bool HAS_BIAS>
@@ -245,8 +351,18 @@ spmm_long_rows_scalar_kernel(const int32_t* __restrict__ rowptr, const int32_t* 
 
 using namespace gnnb;
 
+extern "C" int gnnb_spmm_long_row(void) { return LONG_ROW; }
+
+extern "C" int gnnb_spmm_workspace_bytes(int64_t n_hub_tasks, int64_t F, size_t* bytes) {
+    GNNB_REQUIRE(bytes && n_hub_tasks >= 0 && F > 0, GNNB_E_BADARG, "spmm_workspace_bytes: bad argument");
+    *bytes = align_up((size_t)n_hub_tasks * sizeof(int), 256) + (size_t)n_hub_tasks * (size_t)F * sizeof(float) + 256;
+    return GNNB_OK;
+}
+
 extern "C" int gnnb_spmm(const int32_t* rowptr, const int32_t* col, const float* val, int64_t n,
                          const float* H, int64_t ldh, int64_t F, const float* bias, float* out, int64_t ldo,
+                         const int32_t* hub_task_row, const int32_t* hub_task_chunk, const int32_t* hub_task_first,
+                         const int32_t* hub_task_count, int64_t n_hub_tasks, void* workspace, size_t workspace_bytes,
                          void* stream_) {
     GNNB_ENTER();
     cudaStream_t stream = (cudaStream_t)stream_;
@@ -257,6 +373,31 @@ extern "C" int gnnb_spmm(const int32_t* rowptr, const int32_t* col, const float*
     bool vec = (F % 4 == 0) && (ldh % 4 == 0) && (ldo % 4 == 0) && ((uintptr_t)H % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
                (!bias || (uintptr_t)bias % 16 == 0);
     const int64_t sms = sm_count();
+    if (vec && n_hub_tasks > 0 && hub_task_row) {
+        // planned path: hub rows are split into tasks shared by many warps
+        GNNB_REQUIRE(hub_task_chunk && hub_task_first && hub_task_count, GNNB_E_BADARG, "spmm: incomplete hub plan");
+        size_t need = 0;
+        gnnb_spmm_workspace_bytes(n_hub_tasks, F, &need);
+        GNNB_REQUIRE(workspace && workspace_bytes >= need, GNNB_E_WORKSPACE, "spmm: workspace %zu < %zu bytes", workspace_bytes, need);
+        int* counters = static_cast<int*>(workspace);
+        float* partial = reinterpret_cast<float*>(static_cast<char*>(workspace) + align_up((size_t)n_hub_tasks * sizeof(int), 256));
+        GNNB_CUDA(cudaMemsetAsync(counters, 0, (size_t)n_hub_tasks * sizeof(int), stream));
+        int64_t hub_blocks = (n_hub_tasks + 7) / 8;
+        if (hub_blocks > sms * 8) hub_blocks = sms * 8;
+        int64_t main_blocks = (n + 7) / 8;
+        if (main_blocks > sms * 4 * 16) main_blocks = sms * 4 * 16;
+        unsigned grid = (unsigned)(hub_blocks + main_blocks);
+        if (bias)
+            spmm_planned_vec4_kernel<true><<<grid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo, (int)hub_blocks,
+                                                                     hub_task_row, hub_task_chunk, hub_task_first, hub_task_count,
+                                                                     n_hub_tasks, partial, counters);
+        else
+            spmm_planned_vec4_kernel<false><<<grid, 256, 0, stream>>>(rowptr, col, val, n, H, ldh, (int)F, bias, out, ldo, (int)hub_blocks,
+                                                                      hub_task_row, hub_task_chunk, hub_task_first, hub_task_count,
+                                                                      n_hub_tasks, partial, counters);
+        GNNB_LAUNCH_CHECK();
+        return GNNB_OK;
+    }
     if (vec) {
         int64_t long_blocks = (n + 63) / 64;                // hub-row role: 64 rows scanned per CTA iteration
         if (long_blocks > sms * 8) long_blocks = sms * 8;

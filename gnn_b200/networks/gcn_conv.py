@@ -19,7 +19,7 @@ class _GCNConvFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, graph):
         h = ops.linear_fwd(x, weight)
-        out = ops.spmm(graph.rowptr, graph.col, graph.val, h, bias, n=graph.n)
+        out = ops.spmm(graph.rowptr, graph.col, graph.val, h, bias, n=graph.n, hub=graph.hub)
         ctx.graph = graph
         ctx.has_bias = bias is not None
         ctx.x_needs_grad = x.is_floating_point() and x.requires_grad
@@ -32,7 +32,7 @@ class _GCNConvFn(torch.autograd.Function):
         g = ctx.graph
         d_out = d_out.contiguous()
         d_bias = ops.colsum(d_out) if ctx.has_bias else None
-        d_h = ops.spmm(g.rowptr_t, g.col_t, g.val_t, d_out, None, n=g.n)     # transposed CSR
+        d_h = ops.spmm(g.rowptr_t, g.col_t, g.val_t, d_out, None, n=g.n, hub=g.hub_t)     # transposed CSR
         d_w = ops.linear_bwd_w(x, d_h)
         d_x = ops.linear_bwd_x(d_h, weight) if ctx.x_needs_grad else None
         return d_x, d_w, d_bias, None

@@ -202,7 +202,7 @@ def build_edges(idx, d2, mode="connectivity", smoothing="laplacian", use_weights
 # --------------------------------------------------------------------------------------- K4
 class GcnGraph:
     """GCN-normalised adjacency in CSR, by target (forward) and by source (backward)."""
-    __slots__ = ("n", "nnz", "rowptr", "col", "val", "rowptr_t", "col_t", "val_t", "_keep")
+    __slots__ = ("n", "nnz", "rowptr", "col", "val", "rowptr_t", "col_t", "val_t", "hub", "hub_t", "_keep")
 
     def agg_bytes(self, F, s=4):
         """Algorithmic bytes of one aggregation launch."""
@@ -246,6 +246,8 @@ def gcn_graph(edge_index, edge_weight, n, add_self_loops=True):
         _call("gnnb_csr_build", _p(ei), _p(ew), E, n, int(add_self_loops), nnz,
               _p(g.rowptr), _p(g.col), _p(g.val), _p(g.rowptr_t), _p(g.col_t), _p(g.val_t),
               _p(ws), ws.numel(), _stream())
+    g.hub = hub_plan(g.rowptr)              # hub rows cut into tasks (forward CSR and its transpose)
+    g.hub_t = hub_plan(g.rowptr_t)
     g._keep = (edge_index, edge_weight)     # keeps the keyed storage alive so its address cannot be reused
     _graph_cache[key] = g
     while len(_graph_cache) > _GRAPH_CACHE_MAX:
@@ -253,13 +255,30 @@ def gcn_graph(edge_index, edge_weight, n, add_self_loops=True):
     return g
 
 
+def hub_plan(rowptr):
+    """Task list for rows longer than gnnb_spmm_long_row() (see include/gnnb.h): (task_row, task_chunk, task_first,
+    task_count) as int32 tensors, or None when the graph has no such row.  Index bookkeeping only -- done once per graph."""
+    chunk = int(_lib.lib().gnnb_spmm_long_row())
+    deg = (rowptr[1:] - rowptr[:-1]).to(torch.int64)
+    long_rows = torch.nonzero(deg > chunk).flatten()
+    if long_rows.numel() == 0:
+        return None
+    nch = (deg[long_rows] + chunk - 1) // chunk
+    first = torch.cumsum(nch, 0) - nch
+    task_row = torch.repeat_interleave(long_rows, nch)
+    task_first = torch.repeat_interleave(first, nch)
+    task_count = torch.repeat_interleave(nch, nch)
+    task_chunk = torch.arange(task_row.numel(), device=rowptr.device) - task_first
+    return tuple(t.to(torch.int32).contiguous() for t in (task_row, task_chunk, task_first, task_count))
+
+
 def clear_graph_cache():
     _graph_cache.clear()
 
 
 # --------------------------------------------------------------------------------------- K6 / K7
-def spmm(rowptr, col, val, H, bias=None, n=None):
-    """out[i] = sum_e val[e] * H[col[e]] (+ bias) over CSR row i."""
+def spmm(rowptr, col, val, H, bias=None, n=None, hub=None):
+    """out[i] = sum_e val[e] * H[col[e]] (+ bias) over CSR row i.  ``hub``: optional task plan from ``hub_plan``."""
     _need_cuda(rowptr, H)
     if H.dtype != torch.float32 or H.stride(1) != 1:
         H = H.to(torch.float32).contiguous()
@@ -269,8 +288,14 @@ def spmm(rowptr, col, val, H, bias=None, n=None):
     F = int(H.shape[1])
     _declare(bytes=float(nnz * (F * 4 + 8) + n * F * 4 + (n + 1) * 4 + n * 4 + F * 4))    # AGG_BYTES, SURVEY.md 8d
     with torch.cuda.device(H.device):
-        _call("gnnb_spmm", _p(rowptr), _p(col), _p(val), n, _p(H), H.stride(0), H.shape[1],
-              _p(bias), _p(out), out.stride(0), _stream())
+        if hub is not None:
+            nt = hub[0].numel()
+            ws = _ws(_lib.workspace_bytes("gnnb_spmm_workspace_bytes", nt, F), H.device)
+            _call("gnnb_spmm", _p(rowptr), _p(col), _p(val), n, _p(H), H.stride(0), F, _p(bias), _p(out), out.stride(0),
+                  _p(hub[0]), _p(hub[1]), _p(hub[2]), _p(hub[3]), nt, _p(ws), ws.numel(), _stream())
+        else:
+            _call("gnnb_spmm", _p(rowptr), _p(col), _p(val), n, _p(H), H.stride(0), F, _p(bias), _p(out), out.stride(0),
+                  None, None, None, None, 0, None, 0, _stream())
     return out
 
 

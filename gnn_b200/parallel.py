@@ -115,7 +115,7 @@ def sharded_eval(model, data, rank, world, args_of):
     h_local = ops.linear_fwd(x[lo:hi], first.lin.weight)
     h = allgather_rows(h_local, n, rank, world)
     g = ops.gcn_graph(edge_index, edge_weight, n, first.add_self_loops)
-    out = ops.spmm(g.rowptr, g.col, g.val, h, first.bias, n=n)
+    out = ops.spmm(g.rowptr, g.col, g.val, h, first.bias, n=n, hub=g.hub)
     for m, f, (ins, _) in list(zip(model.nns, model.fns, model.descs))[1:]:
         call = m if f is None else f
         if isinstance(m, GCNConv):

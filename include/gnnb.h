@@ -124,7 +124,18 @@ int gnnb_csr_build(const int64_t* edge_index, const float* edge_weight, int64_t 
  */
 int gnnb_spmm(const int32_t* rowptr, const int32_t* col, const float* val, int64_t n,
               const float* H, int64_t ldh, int64_t F, const float* bias, float* out, int64_t ldo,
+              const int32_t* hub_task_row, const int32_t* hub_task_chunk, const int32_t* hub_task_first,
+              const int32_t* hub_task_count, int64_t n_hub_tasks, void* workspace, size_t workspace_bytes,
               void* stream);
+/* Optional plan for heavy-tailed graphs (the kNN graphs have hubs with thousands of neighbours): every row with more than
+ * gnnb_spmm_long_row() entries is cut into tasks of that many entries; task t covers chunk hub_task_chunk[t] of row
+ * hub_task_row[t], hub_task_first[t] is the index of the row's first task and hub_task_count[t] its number of tasks
+ * (tasks of a row are consecutive).  Partial sums go to the workspace and are added in task order by whichever warp
+ * finishes the row last, so the result is deterministic.  Pass n_hub_tasks = 0 and NULLs to let one CTA handle each
+ * long row instead (no workspace needed). */
+int gnnb_spmm_long_row(void);
+int gnnb_spmm_workspace_bytes(int64_t n_hub_tasks, int64_t F, size_t* bytes);
+
 
 /* ---- K5: marker projection ------------------------------------------------------------------ */
 /* Replaces GCNConv.lin (PyG Linear(bias=False) -> torch.matmul) and its autograd.

@@ -15,8 +15,9 @@ for n, p, k in ((15625, 50000, 32), (180000, 4096, 32)):
     ei, ew = ops.build_edges(idx, d2, mode="distance", smoothing="laplacian", use_weights=True)
     g = ops.gcn_graph(ei, ew.float(), n, True)
     H = torch.randn(n, 100, device="cuda"); b = torch.randn(100, device="cuda")
-    ms = timeit(lambda: ops.spmm(g.rowptr, g.col, g.val, H, b))
+    ms0 = timeit(lambda: ops.spmm(g.rowptr, g.col, g.val, H, b))
+    ms = timeit(lambda: ops.spmm(g.rowptr, g.col, g.val, H, b, hub=g.hub))
     ref = torch.sparse_csr_tensor(g.rowptr.long(), g.col.long(), g.val, (n, n)).to_dense() @ H + b if n < 20000 else None
-    out = ops.spmm(g.rowptr, g.col, g.val, H, b)
+    out = ops.spmm(g.rowptr, g.col, g.val, H, b, hub=g.hub)
     err = float((out - ref).abs().max() / ref.abs().max()) if ref is not None else -1
-    print(f"n={n} nnz={g.nnz} maxdeg={int((g.rowptr[1:]-g.rowptr[:-1]).max())}: {ms*1000:.1f} us  {g.agg_bytes(100)/ms/1e6:.0f} GB/s alg  err {err:.1e}", flush=True)
+    print(f"n={n} nnz={g.nnz} maxdeg={int((g.rowptr[1:]-g.rowptr[:-1]).max())}: planned {ms*1000:.1f} us ({g.agg_bytes(100)/ms/1e6:.0f} GB/s alg), unplanned {ms0*1000:.1f} us, tasks {0 if g.hub is None else g.hub[0].numel()}  err {err:.1e}", flush=True)

@@ -25,7 +25,7 @@ if which in ("all", "spmm"):
     H = torch.randn(n, h, device="cuda")
     b = torch.randn(h, device="cuda")
     for _ in range(reps):
-        out = ops.spmm(g.rowptr, g.col, g.val, H, b)
+        out = ops.spmm(g.rowptr, g.col, g.val, H, b, hub=g.hub)
     print("nnz", g.nnz, "agg bytes", g.agg_bytes(h))
 torch.cuda.synchronize()
 print("done", which)

@@ -83,6 +83,7 @@ def test_spmm_against_dense(F):
     out = ops.spmm(g.rowptr, g.col, g.val, H, b)
     ref = (A @ H.double() + b.double()).float()
     assert rel_err(out, ref) < 1e-5
+    assert rel_err(ops.spmm(g.rowptr, g.col, g.val, H, b, hub=g.hub), ref) < 1e-5
     out_t = ops.spmm(g.rowptr_t, g.col_t, g.val_t, H, None)
     assert rel_err(out_t, (A.t() @ H.double()).float()) < 1e-5
     # linearity (size-independent property)
@@ -129,6 +130,35 @@ def test_linear_tensor_core_path(n, p, h, terms, tol):
     buf[:, :p] = Xg
     assert rel_err(ops.linear_fwd(buf[:, :p], W, precision=3), Xg.double() @ W.double().t()) < 3e-5
     assert rel_err(ops.linear_bwd_w(buf[:, :p], dH, precision=3), dH.double().t() @ Xg.double()) < 3e-5
+
+
+@pytest.mark.parametrize("F", [4, 100, 256])
+def test_spmm_hub_rows_planned_and_unplanned(F):
+    """A graph with hubs (rows of 300 .. 5000 entries): the planned path (tasks + last-arriver reduction) and the
+    CTA-per-row path both match a dense product, and repeated calls are bit-identical (deterministic)."""
+    n = 6000
+    rng = np.random.default_rng(0)
+    src = [rng.integers(0, n, size=40 * n)]
+    dst = [rng.integers(0, n, size=40 * n)]
+    for hub, deg in ((5, 300), (17, 1000), (4000, 5000), (n - 1, 257)):
+        src.append(rng.integers(0, n, size=deg))
+        dst.append(np.full(deg, hub))
+    ei = torch.from_numpy(np.stack([np.concatenate(src), np.concatenate(dst)])).to(DEV)
+    ew = torch.rand(ei.shape[1], device=DEV)
+    g = ops.gcn_graph(ei, ew, n, True)
+    assert g.hub is not None and int(g.hub[0].numel()) >= 2 + 4 + 20 + 2
+    H = torch.randn(n, F, device=DEV)
+    b = torch.randn(F, device=DEV)
+    ref = torch.zeros(n, F, dtype=torch.float64, device=DEV)
+    rp = g.rowptr.long()
+    rows = torch.repeat_interleave(torch.arange(n, device=DEV), rp[1:] - rp[:-1])
+    ref.index_add_(0, rows, g.val[: g.nnz].double()[:, None] * H.double()[g.col[: g.nnz].long()])
+    ref += b.double()
+    a1 = ops.spmm(g.rowptr, g.col, g.val, H, b, hub=g.hub)
+    a2 = ops.spmm(g.rowptr, g.col, g.val, H, b, hub=None)
+    assert rel_err(a1, ref) < 1e-5 and rel_err(a2, ref) < 1e-5
+    for _ in range(3):
+        assert torch.equal(ops.spmm(g.rowptr, g.col, g.val, H, b, hub=g.hub), a1)
 
 
 def oracle_and_mine(name, inp, hidden, asl=True, seed=0):
