@@ -267,11 +267,11 @@ int gnnb_knn_i8(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q, 
             size_t smem = dp4a_smem_bytes(k);
             dim3 grid((unsigned)((n_q + TQ - 1) / TQ), (unsigned)n_splits);
             if (n_extra > 0) {
-                GNNB_CUDA(cudaFuncSetAttribute(knn_dp4a_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                { static size_t hw_ = 0; if ((size_t)(smem) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_dp4a_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem))); hw_ = (size_t)(smem); } }
                 knn_dp4a_kernel<true><<<grid, 256, smem, stream>>>(Q, ldq, sq_q, n_q, q_off, K, ldk, sq_k, n_k, k_off, p,
                                                                    extra_q, extra_k, n_extra, k, n_splits, part_d2, part_idx, aligned4);
             } else {
-                GNNB_CUDA(cudaFuncSetAttribute(knn_dp4a_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                { static size_t hw_ = 0; if ((size_t)(smem) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_dp4a_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem))); hw_ = (size_t)(smem); } }
                 knn_dp4a_kernel<false><<<grid, 256, smem, stream>>>(Q, ldq, sq_q, n_q, q_off, K, ldk, sq_k, n_k, k_off, p,
                                                                     extra_q, extra_k, n_extra, k, n_splits, part_d2, part_idx, aligned4);
             }

@@ -261,11 +261,11 @@ int knn_tc_launch(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q
     const int groups = (q_tiles + QG - 1) / QG;
     const unsigned grid = (unsigned)(groups * QG * n_splits);
     if (extra) {
-        GNNB_CUDA(cudaFuncSetAttribute(knn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        { static size_t hw_ = 0; if ((size_t)(smem) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem))); hw_ = (size_t)(smem); } }
         knn_tc_kernel<true><<<grid, 256, smem, stream>>>(map_q, map_k, sq_q, n_q, q_off, sq_k, n_k, k_off, p, extra_q, extra_k,
                                                          n_extra, k, n_splits, q_tiles, stages, part_d2, part_idx);
     } else {
-        GNNB_CUDA(cudaFuncSetAttribute(knn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        { static size_t hw_ = 0; if ((size_t)(smem) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem))); hw_ = (size_t)(smem); } }
         knn_tc_kernel<false><<<grid, 256, smem, stream>>>(map_q, map_k, sq_q, n_q, q_off, sq_k, n_k, k_off, p, extra_q, extra_k,
                                                           n_extra, k, n_splits, q_tiles, stages, part_d2, part_idx);
     }

@@ -586,7 +586,7 @@ static int launch_tc(const CUtensorMap& map_x, const CUtensorMap& map_b, int64_t
     plan_tiles(tiles, (k_total + BK - 1) / BK, &rt, &splits);
     const int64_t supertiles = (tiles + rt - 1) / rt;
     const int csize = cluster_size(supertiles);
-    GNNB_CUDA(cudaFuncSetAttribute(linear_tc_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    { static size_t hw_ = 0; if ((size_t)(smem) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(linear_tc_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem))); hw_ = (size_t)(smem); } }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((supertiles + csize - 1) / csize * csize), (unsigned)splits);
     cfg.blockDim = dim3(256);
@@ -663,7 +663,7 @@ int linear_tc_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
         if (rc2 != GNNB_OK) return rc2;
         const int btile = (int)(h_pad * BK * 2);
         const size_t smem_ta = ta_fixed() + (size_t)ta_nb(terms, btile) * terms * btile;
-        GNNB_CUDA(cudaFuncSetAttribute(linear_ta_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ta));
+        { static size_t hw_ = 0; if ((size_t)(smem_ta) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(linear_ta_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem_ta))); hw_ = (size_t)(smem_ta); } }
         linear_ta_kernel<false><<<(unsigned)tiles, 256, smem_ta, stream>>>(mx, mb, p, terms, (int)h_pad, h_pad, H, ldh, n, (int)h);
         GNNB_LAUNCH_CHECK();
         return GNNB_OK;
@@ -705,7 +705,7 @@ int linear_tc_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t 
         if (rc2 != GNNB_OK) return rc2;
         const int btile = BK * 128 * 2;
         const size_t smem_ta = ta_fixed() + (size_t)ta_nb(terms, btile) * terms * btile;
-        GNNB_CUDA(cudaFuncSetAttribute(linear_ta_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ta));
+        { static size_t hw_ = 0; if ((size_t)(smem_ta) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(linear_ta_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem_ta))); hw_ = (size_t)(smem_ta); } }
         linear_ta_kernel<true><<<(unsigned)tiles, 256, smem_ta, stream>>>(mx, mb, n, terms, 128, n, dW, lddw, p, (int)h);
         GNNB_LAUNCH_CHECK();
         return GNNB_OK;

@@ -37,8 +37,31 @@ def _need_cuda(*tensors):
             raise _lib.GnnbError("gnn_b200 operators need CUDA tensors (no CPU fallback)")
 
 
+_ws_cache = {}
+
+
 def _ws(nbytes, device):
-    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+    """Scratch for one C-ABI call.  One grow-only buffer per (device, stream): calls on a stream are ordered, so the
+    next call may reuse it; this keeps the allocator (and its lock) off the per-step path."""
+    nbytes = max(int(nbytes), 256)
+    key = (device.index if device.index is not None else torch.cuda.current_device(), torch.cuda.current_stream(device).cuda_stream)
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < nbytes or torch.cuda.is_current_stream_capturing():
+        buf = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        if not torch.cuda.is_current_stream_capturing():
+            _ws_cache[key] = buf
+    return buf
+
+
+_wsb_cache = {}
+
+
+def _ws_bytes(name, *args):
+    key = (name,) + args
+    v = _wsb_cache.get(key)
+    if v is None:
+        v = _wsb_cache[key] = _lib.workspace_bytes(name, *args)
+    return v
 
 
 class Profiler:
@@ -138,7 +161,7 @@ def knn_block(Q, sq_q, q_off, K, sq_k, k_off, k, best_d2, best_idx, merge, extra
     impl = config["knn_impl"] if impl is None else impl
     n_extra = 0 if extra_q is None else extra_q.shape[1]
     with torch.cuda.device(Q.device):
-        nbytes = _lib.workspace_bytes("gnnb_knn_workspace_bytes", Q.shape[0], K.shape[0], Q.shape[1], k, impl)
+        nbytes = _ws_bytes("gnnb_knn_workspace_bytes", Q.shape[0], K.shape[0], Q.shape[1], k, impl)
         ws = _ws(nbytes, Q.device)
         _declare(flops=2.0 * Q.shape[0] * K.shape[0] * Q.shape[1])
         _call("gnnb_knn_i8", _p(Q), Q.stride(0), _p(sq_q), Q.shape[0], q_off,
@@ -182,7 +205,7 @@ def build_edges(idx, d2, mode="connectivity", smoothing="laplacian", use_weights
     dev = idx.device
     with torch.cuda.device(dev):
         if smoothing == "laplacian":
-            ws = _ws(_lib.workspace_bytes("gnnb_graph_workspace_bytes", n, k), dev)
+            ws = _ws(_ws_bytes("gnnb_graph_workspace_bytes", n, k), dev)
             n_edges = torch.zeros(1, dtype=torch.int64, device=dev)
             _call("gnnb_graph_count", _p(idx), _p(d2), n, k, m, _p(n_edges), _p(ws), ws.numel(), _stream())
             E = int(n_edges.item())                       # the one host sync of the graph build
@@ -232,7 +255,7 @@ def gcn_graph(edge_index, edge_weight, n, add_self_loops=True):
     dev = ei.device
     g = GcnGraph()
     with torch.cuda.device(dev):
-        ws = _ws(_lib.workspace_bytes("gnnb_csr_workspace_bytes", n, E), dev)
+        ws = _ws(_ws_bytes("gnnb_csr_workspace_bytes", n, E), dev)
         nnz_t = torch.zeros(1, dtype=torch.int64, device=dev)
         _call("gnnb_csr_count", _p(ei), E, n, int(add_self_loops), _p(nnz_t), _p(ws), ws.numel(), _stream())
         nnz = int(nnz_t.item())
@@ -290,7 +313,7 @@ def spmm(rowptr, col, val, H, bias=None, n=None, hub=None):
     with torch.cuda.device(H.device):
         if hub is not None:
             nt = hub[0].numel()
-            ws = _ws(_lib.workspace_bytes("gnnb_spmm_workspace_bytes", nt, F), H.device)
+            ws = _ws(_ws_bytes("gnnb_spmm_workspace_bytes", nt, F), H.device)
             _call("gnnb_spmm", _p(rowptr), _p(col), _p(val), n, _p(H), H.stride(0), F, _p(bias), _p(out), out.stride(0),
                   _p(hub[0]), _p(hub[1]), _p(hub[2]), _p(hub[3]), nt, _p(ws), ws.numel(), _stream())
         else:
@@ -321,7 +344,7 @@ def linear_fwd(X, W, precision=None):
     prec = _precision(n, p, h, x_is_i8) if precision is None else precision
     H = torch.empty((n, h), dtype=torch.float32, device=X.device)
     with torch.cuda.device(X.device):
-        ws = _ws(_lib.workspace_bytes("gnnb_linear_workspace_bytes", n, p, h, prec), X.device)
+        ws = _ws(_ws_bytes("gnnb_linear_workspace_bytes", n, p, h, prec), X.device)
         _declare(flops=2.0 * n * p * h, bytes=float(n * p * X.element_size() + h * p * 4 + n * h * 4))
         _call("gnnb_linear_fwd", _p(X), int(x_is_i8), X.stride(0), n, p, _p(W), W.stride(0), h,
               _p(H), H.stride(0), prec, _p(ws), ws.numel(), _stream())
@@ -342,7 +365,7 @@ def linear_bwd_w(X, dH, precision=None):
     prec = _precision(n, p, h, x_is_i8) if precision is None else precision
     dW = torch.empty((h, p), dtype=torch.float32, device=X.device)
     with torch.cuda.device(X.device):
-        ws = _ws(_lib.workspace_bytes("gnnb_linear_workspace_bytes", n, p, h, prec), X.device)
+        ws = _ws(_ws_bytes("gnnb_linear_workspace_bytes", n, p, h, prec), X.device)
         _declare(flops=2.0 * n * p * h, bytes=float(n * p * X.element_size() + h * p * 4 + n * h * 4))
         _call("gnnb_linear_bwd_w", _p(X), int(x_is_i8), X.stride(0), n, p, _p(dH), dH.stride(0), h,
               _p(dW), dW.stride(0), prec, _p(ws), ws.numel(), _stream())
@@ -369,7 +392,7 @@ def colsum(A):
     n, F = A.shape
     out = torch.empty(F, dtype=torch.float32, device=A.device)
     with torch.cuda.device(A.device):
-        ws = _ws(_lib.workspace_bytes("gnnb_colsum_workspace_bytes", F), A.device)
+        ws = _ws(_ws_bytes("gnnb_colsum_workspace_bytes", F), A.device)
         _call("gnnb_colsum", _p(A), A.stride(0), n, F, _p(out), _p(ws), ws.numel(), _stream())
     return out
 
