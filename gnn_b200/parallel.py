@@ -123,3 +123,44 @@ def sharded_eval(model, data, rank, world, args_of):
         else:
             out = call(out)
     return out
+
+
+def knn_sharded(X_local, row0, n_total, k, rank, world, extra_local=None):
+    """Row-sharded kNN graph build: rank r owns query rows [row0, row0 + n_local) of the n_total
+    individuals.  Key blocks are passed round by NCCL broadcast, one owner at a time, and folded into the
+    owner-local running lists with gnnb_knn_i8(merge=1); no neighbour list is ever reduced across ranks.
+    Returns (idx int32 [n_local, k] of GLOBAL row ids, d2 float64 [n_local, k]) -- bit-identical to ops.knn on the
+    whole matrix, whatever the number of ranks."""
+    from . import ops
+    dev = X_local.device
+    n_local, p = X_local.shape
+    sq_local = ops.row_sqnorm(X_local)
+    best_d2 = torch.empty((n_local, k), dtype=torch.float64, device=dev)
+    best_idx = torch.empty((n_local, k), dtype=torch.int32, device=dev)
+    if world == 1:
+        ops.knn_block(X_local, sq_local, row0, X_local, sq_local, row0, k, best_d2, best_idx, 0, extra_local, extra_local)
+        return best_idx, best_d2
+    sizes = torch.zeros(world, dtype=torch.int64, device=dev)
+    sizes[rank] = n_local
+    dist.all_reduce(sizes)
+    offs = torch.cumsum(sizes, 0) - sizes
+    sizes, offs = sizes.tolist(), offs.tolist()
+    ld = X_local.stride(0)
+    n_extra = 0 if extra_local is None else extra_local.shape[1]
+    for step, owner in enumerate(range(world)):
+        nk = int(sizes[owner])
+        if owner == rank:
+            keys, sqk, ek = X_local, sq_local, extra_local
+        else:
+            buf = torch.empty((nk, ld), dtype=torch.int8, device=dev)
+            keys, sqk = buf[:, :p], torch.empty(nk, dtype=torch.int64, device=dev)
+            ek = torch.empty((nk, n_extra), dtype=torch.float64, device=dev) if n_extra else None
+        # broadcast the padded storage so that the receiver keeps the 16-byte row stride TMA needs
+        store = X_local.as_strided((n_local, ld), (ld, 1)) if owner == rank else buf
+        dist.broadcast(store, src=owner)
+        dist.broadcast(sqk, src=owner)
+        if n_extra:
+            dist.broadcast(ek, src=owner)
+        ops.knn_block(X_local, sq_local, row0, keys, sqk, int(offs[owner]), k, best_d2, best_idx, int(step > 0),
+                      extra_local, ek)
+    return best_idx, best_d2

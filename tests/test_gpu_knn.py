@@ -152,3 +152,13 @@ def test_large_property_checks():
     order = np.argsort(d, axis=1, kind="stable")[:, :k]
     assert np.array_equal(order, idx.cpu().numpy()[rows])
     assert np.array_equal(np.take_along_axis(d, order, 1), d2.cpu().numpy()[rows])
+
+
+def test_row_sharded_entry_point_single_rank():
+    """parallel.knn_sharded with one rank equals ops.knn; the 2-rank NCCL run is scripts/check_knn_sharded.py
+    (bit-identical on 2 B200s, recorded in profiles/README.md)."""
+    from gnn_b200 import parallel
+    X = dev_i8(synth.genotypes(900, 300, seed=4))
+    a_i, a_d = parallel.knn_sharded(X, 0, 900, 12, 0, 1)
+    b_i, b_d = ops.knn(X, 12)
+    assert torch.equal(a_i, b_i) and torch.equal(a_d, b_d)
