@@ -94,7 +94,7 @@ __global__ void graph_unique_kernel(const Rec* __restrict__ rec, const int32_t* 
         unsigned long long prev = ~0ULL;
         for (int i = 0; i < len; ++i) {
             unsigned long long c = seg[i].key >> 1;
-            cnt += (c != prev);
+            cnt += (c != prev) && (c != (unsigned long long)r);      // a self entry (include_self) is not an edge of L
             prev = c;
         }
         ucnt[r] = cnt;
@@ -112,7 +112,7 @@ __global__ void graph_emit_offdiag_kernel(const Rec* __restrict__ rec, const int
         const Rec* seg = rec + seg_off[r];
         int len = cap[r];
         int64_t e = rowptr[r];
-        double dsum = 0.0;
+        double dsum = 0.0, diag = 0.0;
         int i = 0;
         while (i < len) {
             unsigned long long c = seg[i].key >> 1;
@@ -122,6 +122,12 @@ __global__ void graph_emit_offdiag_kernel(const Rec* __restrict__ rec, const int
                 ++i;
             }
             double w = 0.5 * v;                                  // load.py:68
+            if (c == (unsigned long long)r) {                    // include_self: W[r,r] is summed, then removed again
+                diag = w;                                        // (csgraph.laplacian: m.sum(axis) - m.diagonal())
+                dsum = __dadd_rn(dsum, w);
+                ++i;
+                continue;
+            }
             edge_index[e] = r;
             edge_index[n_edges + e] = (int64_t)c;
             edge_weight[e] = -w;                                 // csgraph.laplacian: L = D - W (load.py:69)
@@ -129,6 +135,7 @@ __global__ void graph_emit_offdiag_kernel(const Rec* __restrict__ rec, const int
             ++e;
             ++i;
         }
+        dsum = __dsub_rn(dsum, diag);
         deg[r] = dsum;
         atomicMax(lmax_bits, d2u(dsum));
     }

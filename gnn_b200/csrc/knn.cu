@@ -140,6 +140,105 @@ knn_dp4a_kernel(const int8_t* __restrict__ Q, int64_t ldq, const int64_t* __rest
     }
 }
 
+// Float features (scaled / transformed markers, load.py:45-48): d2 = sum_c fl(fl(q_c - k_c)^2), accumulated left to right
+// in float64 with un-fused operations -- the same arithmetic, in the same order, as the oracle, so the lists are
+// bit-identical.  CUDA-core tiles (64 x 64 pairs, 16 columns per stage); the tensor-core route for this case is future work.
+constexpr int FQ = 64, FK = 64, FC = 16;
+__global__ void __launch_bounds__(256)
+knn_f64_kernel(const double* __restrict__ Q, int64_t ldq, int64_t n_q, int64_t q_off,
+               const double* __restrict__ K, int64_t ldk, int64_t n_k, int64_t k_off, int64_t p,
+               int k, int n_splits, double* __restrict__ part_d2, int32_t* __restrict__ part_idx) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double* Qs = reinterpret_cast<double*>(smem_raw);            // [FQ][FC + 1]
+    double* Ks = Qs + FQ * (FC + 1);                             // [FK][FC + 1]
+    double* D = Ks + FK * (FC + 1);                              // [FQ][FK + 1]
+    double* list_d = D + FQ * (FK + 1);                          // [k][FQ]
+    int* list_i = reinterpret_cast<int*>(list_d + (size_t)k * FQ);
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int64_t q0 = (int64_t)blockIdx.x * FQ;
+    const int split = blockIdx.y;
+    const int64_t n_ktiles = (n_k + FK - 1) / FK;
+    const int64_t kt_begin = n_ktiles * split / n_splits, kt_end = n_ktiles * (split + 1) / n_splits;
+    RowSelector sel;
+    if (tid < FQ) sel.init(list_d, list_i, FQ, tid, k);
+    for (int64_t kt = kt_begin; kt < kt_end; ++kt) {
+        const int64_t k0 = kt * FK;
+        double acc[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+        for (int64_t c0 = 0; c0 < p; c0 += FC) {
+            const int c = tid & 15;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int r = (tid >> 4) + 16 * i;
+                const int64_t gq = q0 + r, gk = k0 + r, gc = c0 + c;
+                Qs[r * (FC + 1) + c] = (gq < n_q && gc < p) ? Q[gq * ldq + gc] : 0.0;
+                Ks[r * (FC + 1) + c] = (gk < n_k && gc < p) ? K[gk * ldk + gc] : 0.0;
+            }
+            __syncthreads();
+            const int cmax = (int)((p - c0) < FC ? (p - c0) : FC);
+            for (int cc = 0; cc < cmax; ++cc) {
+                double qv[4], kv[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) qv[i] = Qs[(ty + 16 * i) * (FC + 1) + cc];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) kv[j] = Ks[(tx + 16 * j) * (FC + 1) + cc];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const double diff = __dsub_rn(qv[i], kv[j]);
+                        acc[i][j] = __dadd_rn(acc[i][j], __dmul_rn(diff, diff));
+                    }
+            }
+            __syncthreads();
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) D[(ty + 16 * i) * (FK + 1) + tx + 16 * j] = acc[i][j];
+        __syncthreads();
+        if (tid < FQ && q0 + tid < n_q) {
+            const int64_t gi = q_off + q0 + tid;
+            const int ncols = (int)((n_k - k0) < FK ? (n_k - k0) : FK);
+            for (int c = 0; c < ncols; ++c) {
+                const int64_t gj = k_off + k0 + c;
+                if (gj != gi) sel.offer(D[tid * (FK + 1) + c], (int)gj);
+            }
+        }
+        __syncthreads();
+    }
+    if (tid < FQ && q0 + tid < n_q) {
+        double* od = part_d2 + ((int64_t)split * n_q + q0 + tid) * k;
+        int32_t* oi = part_idx + ((int64_t)split * n_q + q0 + tid) * k;
+        for (int t = 0; t < k; ++t) {
+            od[t] = sel.d(t);
+            oi[t] = sel.i(t);
+        }
+    }
+}
+
+// include_self=True (load.py:28,57): the k smallest (d2, j) over ALL j are the first k of the self-excluded list with
+// (0, i) inserted at its lexicographic place.
+__global__ void knn_insert_self_kernel(double* __restrict__ best_d2, int32_t* __restrict__ best_idx, int64_t n, int k, int64_t q_off) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    double* d = best_d2 + r * k;
+    int32_t* ix = best_idx + r * k;
+    const int me = (int)(q_off + r);
+    int pos = 0;
+    while (pos < k && d[pos] == 0.0 && ix[pos] >= 0 && ix[pos] < me) ++pos;
+    if (pos == k) return;
+    for (int t = k - 1; t > pos; --t) {
+        d[t] = d[t - 1];
+        ix[t] = ix[t - 1];
+    }
+    d[pos] = 0.0;
+    ix[pos] = me;
+}
+
 // one thread per query row: merge n_lists sorted partial lists (and the running result when merge != 0)
 __global__ void knn_merge_kernel(const double* __restrict__ part_d2, const int32_t* __restrict__ part_idx, int n_lists,
                                  int64_t n_q, int k, double* __restrict__ best_d2, int32_t* __restrict__ best_idx,
@@ -280,6 +379,50 @@ int gnnb_knn_i8(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q, 
     }
     knn_merge_kernel<<<(unsigned)((n_q + 127) / 128), 128, 0, stream>>>(part_d2, part_idx, n_splits, n_q, k, best_d2, best_idx,
                                                                         merge, tmp_d2, tmp_idx);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+int gnnb_knn_f64(const double* Q, int64_t ldq, int64_t n_q, int64_t q_off,
+                 const double* K, int64_t ldk, int64_t n_k, int64_t k_off, int64_t p,
+                 int k, double* best_d2, int32_t* best_idx, int merge,
+                 void* workspace, size_t workspace_bytes, void* stream_) {
+    GNNB_ENTER();
+    cudaStream_t stream = (cudaStream_t)stream_;
+    GNNB_REQUIRE(Q && K && best_d2 && best_idx, GNNB_E_BADARG, "knn_f64: null pointer");
+    GNNB_REQUIRE(n_q >= 0 && n_k >= 0 && p > 0 && ldq >= p && ldk >= p, GNNB_E_BADARG, "knn_f64: bad shape");
+    GNNB_REQUIRE(k > 0 && k <= GNNB_KNN_MAX_K, GNNB_E_UNSUPPORTED, "knn_f64: k = %d outside 1..%d", k, GNNB_KNN_MAX_K);
+    GNNB_REQUIRE(q_off + n_q < 2147483647LL && k_off + n_k < 2147483647LL, GNNB_E_UNSUPPORTED, "knn_f64: indices exceed int32");
+    if (n_q == 0) return GNNB_OK;
+    size_t need = 0;
+    gnnb_knn_workspace_bytes(n_q, n_k, p, k, 1, &need);
+    GNNB_REQUIRE(workspace && workspace_bytes >= need, GNNB_E_WORKSPACE, "knn_f64: workspace %zu < %zu bytes", workspace_bytes, need);
+    int n_splits = n_k == 0 ? 0 : knn_pick_splits(n_q, n_k, FQ, FK);
+    Carver cv(workspace, workspace_bytes);
+    size_t per = (size_t)n_q * k;
+    double* part_d2 = cv.take<double>(per * (n_splits > 0 ? n_splits : 1));
+    int32_t* part_idx = cv.take<int32_t>(per * (n_splits > 0 ? n_splits : 1));
+    double* tmp_d2 = cv.take<double>(per);
+    int32_t* tmp_idx = cv.take<int32_t>(per);
+    GNNB_REQUIRE(cv.ok(), GNNB_E_WORKSPACE, "knn_f64: workspace carve overflow");
+    if (n_splits > 0) {
+        size_t smem = (size_t)(2 * FQ * (FC + 1) + FQ * (FK + 1)) * sizeof(double) + (size_t)k * FQ * (sizeof(double) + sizeof(int));
+        { static size_t hw_ = 0; if (smem > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); hw_ = smem; } }
+        dim3 grid((unsigned)((n_q + FQ - 1) / FQ), (unsigned)n_splits);
+        knn_f64_kernel<<<grid, 256, smem, stream>>>(Q, ldq, n_q, q_off, K, ldk, n_k, k_off, p, k, n_splits, part_d2, part_idx);
+        GNNB_LAUNCH_CHECK();
+    }
+    knn_merge_kernel<<<(unsigned)((n_q + 127) / 128), 128, 0, stream>>>(part_d2, part_idx, n_splits, n_q, k, best_d2, best_idx,
+                                                                        merge, tmp_d2, tmp_idx);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+int gnnb_knn_insert_self(double* best_d2, int32_t* best_idx, int64_t n_q, int k, int64_t q_off, void* stream) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(best_d2 && best_idx && n_q >= 0 && k > 0 && k <= GNNB_KNN_MAX_K && q_off >= 0, GNNB_E_BADARG, "knn_insert_self: bad argument");
+    if (n_q == 0) return GNNB_OK;
+    knn_insert_self_kernel<<<(unsigned)((n_q + 127) / 128), 128, 0, (cudaStream_t)stream>>>(best_d2, best_idx, n_q, k, q_off);
     GNNB_LAUNCH_CHECK();
     return GNNB_OK;
 }

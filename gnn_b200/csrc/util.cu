@@ -264,6 +264,84 @@ __global__ void i8_to_f32_kernel(const int8_t* __restrict__ X, int64_t ldx, int6
     }
 }
 
+// Sum of val(0..n-1) in the order numpy's pairwise summation uses for a contiguous float64 reduction (blocks of <= 128
+// elements with 8 running partial sums, halves split at a multiple of 8) -- the order behind pandas' DataFrame.std().
+template <class F>
+__device__ double np_pairwise_sum(int64_t n, F val) {
+    int64_t lo[40], len[40];
+    double acc[40];
+    int st[40];
+    int sp = 0;
+    lo[0] = 0; len[0] = n; st[0] = 0; sp = 1;
+    double ret = 0.0;
+    while (sp > 0) {
+        const int t = sp - 1;
+        if (st[t] == 0) {
+            const int64_t a = lo[t], m = len[t];
+            if (m < 8) {
+                double res = 0.0;
+                for (int64_t i = 0; i < m; ++i) res = __dadd_rn(res, val(a + i));
+                ret = res;
+                --sp;
+            } else if (m <= 128) {
+                double r[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) r[j] = val(a + j);
+                int64_t i = 8;
+                for (; i < m - (m % 8); i += 8) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) r[j] = __dadd_rn(r[j], val(a + i + j));
+                }
+                double res = __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])),
+                                       __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7])));
+                for (; i < m; ++i) res = __dadd_rn(res, val(a + i));
+                ret = res;
+                --sp;
+            } else {
+                int64_t n2 = m / 2;
+                n2 -= n2 % 8;
+                st[t] = 1;
+                lo[sp] = a; len[sp] = n2; st[sp] = 0; ++sp;
+            }
+        } else if (st[t] == 1) {
+            acc[t] = ret;
+            st[t] = 2;
+            int64_t n2 = len[t] / 2;
+            n2 -= n2 % 8;
+            lo[sp] = lo[t] + n2; len[sp] = len[t] - n2; st[sp] = 0; ++sp;
+        } else {
+            ret = __dadd_rn(acc[t], ret);
+            --sp;
+        }
+    }
+    return ret;
+}
+
+// `scaled` features (load.py:45-48): x -= mean; x /= std (ddof 1); NaN -> 0, column by column, with pandas' arithmetic:
+// mean = exact integer sum / n; std = sqrt(pairwise_sum((avg - d)^2) / (n - 1)) where d = x - mean and avg = pairwise_sum(d) / n.
+// One thread per column; neighbouring threads read neighbouring bytes of a row.
+__global__ void scale_columns_kernel(const int8_t* __restrict__ X, int64_t ldx, int64_t n, int64_t p,
+                                     double* __restrict__ out64, int64_t ld64, float* __restrict__ out32, int64_t ld32) {
+    int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= p) return;
+    const int8_t* col = X + c;
+    long long s = 0;
+    for (int64_t r = 0; r < n; ++r) s += col[r * ldx];
+    const double mean = (double)s / (double)n;
+    auto centred = [&](int64_t r) { return __dsub_rn((double)col[r * ldx], mean); };
+    const double cnt = n > 1 ? (double)n : nan("");              // pandas: count <= ddof -> NaN
+    const double avg = np_pairwise_sum(n, centred) / cnt;
+    auto sqdev = [&](int64_t r) { double t = __dsub_rn(avg, centred(r)); return __dmul_rn(t, t); };
+    const double var = np_pairwise_sum(n, sqdev) / (n > 1 ? (double)(n - 1) : nan(""));
+    const double sd = sqrt(var);
+    for (int64_t r = 0; r < n; ++r) {
+        double v = centred(r) / sd;
+        if (v != v) v = 0.0;                                       // fillna(0)
+        if (out64) out64[r * ld64 + c] = v;
+        if (out32) out32[r * ld32 + c] = (float)v;
+    }
+}
+
 __global__ void sqnorm_kernel(const int8_t* __restrict__ X, int64_t ldx, int64_t n, int64_t p, int64_t* __restrict__ sq) {
     // one warp per row
     int lane = threadIdx.x & 31;
@@ -361,6 +439,17 @@ int gnnb_i8_to_f32(const int8_t* X, int64_t ldx, int64_t n, int64_t p, float* ou
     int64_t blocks = (n * p + 255) / 256;
     int64_t cap = (int64_t)sm_count() * 32;
     i8_to_f32_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(X, ldx, n, p, out, ldo);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+int gnnb_scale_columns_i8(const int8_t* X, int64_t ldx, int64_t n, int64_t p, double* out64, int64_t ld64,
+                          float* out32, int64_t ld32, void* stream) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(X && (out64 || out32) && n >= 0 && p > 0 && ldx >= p, GNNB_E_BADARG, "scale_columns: bad argument");
+    GNNB_REQUIRE((!out64 || ld64 >= p) && (!out32 || ld32 >= p), GNNB_E_BADARG, "scale_columns: output stride < p");
+    if (n == 0) return GNNB_OK;
+    scale_columns_kernel<<<(unsigned)((p + 127) / 128), 128, 0, (cudaStream_t)stream>>>(X, ldx, n, p, out64, ld64, out32, ld32);
     GNNB_LAUNCH_CHECK();
     return GNNB_OK;
 }

@@ -119,10 +119,11 @@ class GenotypeTable:
     float feature transforms of load.py:38-48 are not part of this path yet.
     """
 
-    def __init__(self, markers, value, index=None):
+    def __init__(self, markers, value, index=None, int_labels=False):
         import numpy as np
         assert markers.dtype == torch.int8 and markers.dim() == 2 and markers.is_cuda
         self.markers = markers
+        self.int_labels = int_labels        # marker columns labelled 1..P as integers (load.py:189-191), else '1'..'p'
         self.value = np.asarray(value, dtype=np.float64).reshape(-1)
         self.index = np.arange(len(self.value)) if index is None else np.asarray(index)
         assert self.markers.shape[0] == self.value.shape[0]
@@ -149,8 +150,11 @@ class GenotypeTable:
 
     @staticmethod
     def from_frame(df, device="cuda"):
+        import numpy as np
         vals = df.values
-        return GenotypeTable.from_numpy(vals[:, 1:], vals[:, 0], device=device)._with_index(df.index.values)
+        t = GenotypeTable.from_numpy(vals[:, 1:], vals[:, 0], device=device)._with_index(df.index.values)
+        t.int_labels = list(df.columns[1:]) == list(range(1, df.shape[1])) and all(isinstance(c, (int, np.integer)) for c in df.columns[1:])
+        return t
 
     def _with_index(self, index):
         import numpy as np
@@ -176,7 +180,7 @@ class GenotypeTable:
         if rows.size and (rows.min() < 0 or rows.max() >= len(self)):
             raise IndexError("positional indexers are out-of-bounds")
         r = torch.from_numpy(rows).to(self.markers.device)
-        return GenotypeTable(ops.gather_rows(self.markers, r), self.value[rows], self.index[rows])
+        return GenotypeTable(ops.gather_rows(self.markers, r), self.value[rows], self.index[rows], self.int_labels)
 
 
 class _ILoc:
@@ -191,7 +195,7 @@ class _ILoc:
         if isinstance(key, slice) and key.step in (None, 1):
             a, b, _ = key.indices(n)                       # contiguous rows: a view, no copy (util.py:82)
             b = max(a, b)
-            return GenotypeTable(self.t.markers[a:b], self.t.value[a:b], self.t.index[a:b])
+            return GenotypeTable(self.t.markers[a:b], self.t.value[a:b], self.t.index[a:b], self.t.int_labels)
         if isinstance(key, slice):
             rows = np.arange(n)[key]
         else:

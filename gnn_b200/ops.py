@@ -193,6 +193,65 @@ def knn(X, k, extra=None, impl=None):
     return best_idx, best_d2
 
 
+def insert_self(best_idx, best_d2, q_off=0):
+    """include_self=True (load.py:28,57): fold (0, i) into self-excluded lists, in place."""
+    _need_cuda(best_idx, best_d2)
+    n, k = best_idx.shape
+    assert best_idx.is_contiguous() and best_d2.is_contiguous()
+    with torch.cuda.device(best_idx.device):
+        _call("gnnb_knn_insert_self", _p(best_d2), _p(best_idx), n, k, q_off, _stream())
+    return best_idx, best_d2
+
+
+def knn_including_self(search, n, k):
+    """k smallest (d2, j) over all j, self included, from a self-excluding search ``search(kk) -> (idx, d2)``."""
+    if not 0 < k <= n:
+        raise ValueError(f"Expected n_neighbors <= n_samples_fit, but n_neighbors = {k}, n_samples_fit = {n}")
+    kk = min(k, n - 1)
+    if kk == 0:                                                  # one row: its only neighbour is itself
+        dev = torch.device("cuda", torch.cuda.current_device())
+        idx = torch.full((n, k), -1, dtype=torch.int32, device=dev)
+        d2 = torch.full((n, k), float("inf"), dtype=torch.float64, device=dev)
+        return insert_self(idx, d2)
+    idx, d2 = search(kk)
+    if kk < k:
+        idx = torch.cat([idx, torch.full((n, k - kk), -1, dtype=torch.int32, device=idx.device)], dim=1).contiguous()
+        d2 = torch.cat([d2, torch.full((n, k - kk), float("inf"), dtype=torch.float64, device=d2.device)], dim=1).contiguous()
+    return insert_self(idx, d2)
+
+
+def scale_columns(X, want64=True, want32=True):
+    """``scaled=True`` of load.py:45-48 on int8 codes: (x - mean) / std per column with pandas' arithmetic, NaN -> 0.
+    Returns (float64 [n, p] or None, float32 [n, p] or None)."""
+    _rows_ok(X)
+    n, p = X.shape
+    o64 = torch.empty((n, p), dtype=torch.float64, device=X.device) if want64 else None
+    ld32 = (p + 3) // 4 * 4
+    o32 = torch.empty((n, ld32), dtype=torch.float32, device=X.device)[:, :p] if want32 else None
+    with torch.cuda.device(X.device):
+        _declare(bytes=3.0 * n * p + (8.0 if want64 else 0) * n * p + (4.0 if want32 else 0) * n * p)
+        _call("gnnb_scale_columns_i8", _p(X), X.stride(0), n, p, _p(o64) if want64 else None, p,
+              _p(o32) if want32 else None, ld32, _stream())
+    return o64, o32
+
+
+def knn_float(X, k):
+    """Canonical kNN for float64 features [n, p] (scaled / transformed markers).  Same output contract as ``knn``."""
+    _need_cuda(X)
+    X = X.to(torch.float64).contiguous()
+    n, p = X.shape
+    if not 0 < k < n:
+        raise ValueError(f"Expected n_neighbors <= n_samples_fit, but n_neighbors = {k + 1}, n_samples_fit = {n}")
+    best_d2 = torch.empty((n, k), dtype=torch.float64, device=X.device)
+    best_idx = torch.empty((n, k), dtype=torch.int32, device=X.device)
+    with torch.cuda.device(X.device):
+        ws = _ws(_ws_bytes("gnnb_knn_workspace_bytes", n, n, p, k, 1), X.device)
+        _declare(flops=3.0 * n * n * p)
+        _call("gnnb_knn_f64", _p(X), X.stride(0), n, 0, _p(X), X.stride(0), n, 0, p, k, _p(best_d2), _p(best_idx), 0,
+              _p(ws), ws.numel(), _stream())
+    return best_idx, best_d2
+
+
 # --------------------------------------------------------------------------------------- K2 / K3
 def build_edges(idx, d2, mode="connectivity", smoothing="laplacian", use_weights=False):
     """Edge list of load.py:61-80 from canonical neighbour lists.

@@ -53,6 +53,12 @@ int gnnb_gather_rows_i8(const int8_t* X, int64_t ldx, const int64_t* rows, int64
                         int8_t* out, int64_t ldo, void* stream);
 /* x_f32 = float(X) -- replaces torch.tensor(df_x.values.tolist(), dtype=float) at load.py:50 */
 int gnnb_i8_to_f32(const int8_t* X, int64_t ldx, int64_t n, int64_t p, float* out, int64_t ldo, void* stream);
+/* `scaled=True` (load.py:45-48; load_ensembles2.py:150-157): per column x -= mean, x /= std (ddof 1), NaN -> 0, with
+ * pandas' arithmetic (exact mean; two-pass variance summed in numpy's pairwise order), so the float64 output equals
+ * `df_x.values` of the reference bit for bit on integer-coded markers.  out64 feeds gnnb_knn_f64, out32 is `x`
+ * (either may be NULL). */
+int gnnb_scale_columns_i8(const int8_t* X, int64_t ldx, int64_t n, int64_t p, double* out64, int64_t ld64,
+                          float* out32, int64_t ld32, void* stream);
 /* sq[i] = sum_j X[i,j]^2 (int64) -- the ||x||^2 term of sklearn's Euclidean kNN (load.py:52-59) */
 int gnnb_row_sqnorm_i8(const int8_t* X, int64_t ldx, int64_t n, int64_t p, int64_t* sq, void* stream);
 
@@ -77,6 +83,16 @@ int gnnb_knn_i8(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q, 
                 const double* extra_q, const double* extra_k, int n_extra,
                 int k, double* best_d2, int32_t* best_idx, int merge, int impl,
                 void* workspace, size_t workspace_bytes, void* stream);
+
+/* Same contract for float64 features (the `scaled` / transformed markers of load.py:45-48, load_ensembles2.py:150-157):
+ * d2 = sum_c fl(fl(q_c - k_c)^2) accumulated left to right in float64 (bit-identical to the oracle).  CUDA-core tiles. */
+int gnnb_knn_f64(const double* Q, int64_t ldq, int64_t n_q, int64_t q_off,
+                 const double* K, int64_t ldk, int64_t n_k, int64_t k_off, int64_t p,
+                 int k, double* best_d2, int32_t* best_idx, int merge,
+                 void* workspace, size_t workspace_bytes, void* stream);
+
+/* include_self=True (load.py:28,57): turns self-excluded lists into the k smallest (d2, j) over all j, in place. */
+int gnnb_knn_insert_self(double* best_d2, int32_t* best_idx, int64_t n_q, int k, int64_t q_off, void* stream);
 
 /* ---- K2/K3: similarity graph -> Laplacian edge list ------------------------------------- */
 /* Replaces gnn/loaders/load.py:61-80 (scipy CSR arithmetic, csgraph.laplacian,

@@ -20,6 +20,10 @@ Fixtures
   wheat_model.npz      seeded forward / backward of the GCN factories
   wheat_train.npz      loss trajectories of train_ensemble2 phase 1 (ensemble2.py:39-124)
   partition_small.npz  naive_partition(util.py:15-45) on small random neighbour streams
+  wheat_features.npz   create_graph with scaled / include_self / hot (load.py:38-48, :57)
+  wheat_ensemble.npz   the seeded-subsample loader (load_ensembles2.py:53-297): rows, labels, edges, feature digests
+
+``python -m oracle.make_golden features`` regenerates only the last two.
 """
 import contextlib
 import io
@@ -65,10 +69,138 @@ def check_against_sklearn(X, k, idx, d2):
     return int(tie_free.sum()), int(same.sum())
 
 
-def main():
+def digest(a):
+    """Bit-exact fingerprint of an array (dtype, shape and bytes)."""
+    import hashlib
+    a = np.ascontiguousarray(a)
+    h = hashlib.sha256(f"{a.dtype.str}{a.shape}".encode() + a.tobytes()).digest()[:8]
+    return np.frombuffer(h, dtype=np.uint64)[0]
+
+
+def features_and_ensemble(ref, df):
+    """wheat_features.npz and wheat_ensemble.npz."""
+    X = df.iloc[:, 1:].values
+    y = df["value"].values
+    out = {}
+
+    def case(tag, rows, k, smoothing, mode, frame=None, int_labels=False, **kw):
+        sub = (df if frame is None else frame).iloc[rows].copy()
+        Xs = sub.iloc[:, 1:].values
+        d = ref.load.create_graph(sub, n_neighbors=k, smoothing=smoothing, use_weights=True, mode=mode,
+                                  algorithm="euclidean", **kw)
+        mine = restate.create_graph(Xs, y[rows], n_neighbors=k, smoothing=smoothing, use_weights=True, mode=mode,
+                                    int_labels=int_labels, **kw)
+        assert np.array_equal(d.edge_index.numpy(), mine["edge_index"]), tag
+        assert np.array_equal(d.edge_weight.numpy(), mine["edge_weight"]), tag
+        assert np.array_equal(d.x.numpy(), mine["x"]) and np.array_equal(d.y.numpy(), mine["y"]), tag
+        out[tag + "_ei"] = mine["edge_index"].astype(np.int32)
+        out[tag + "_ew"] = mine["edge_weight"]
+        out[tag + "_xdigest"] = digest(mine["x"])
+        return mine
+
+    train, test = slice(0, 479), slice(479, 587)
+    for mode in ("distance", "connectivity"):
+        for smoothing in ("laplacian", "none"):
+            m = case(f"scaled_train_k5_{mode}_{smoothing}", train, 5, smoothing, mode, scaled=True)
+            case(f"self_train_k5_{mode}_{smoothing}", train, 5, smoothing, mode, include_self=True)
+            case(f"scaledself_test_k3_{mode}_{smoothing}", test, 3, smoothing, mode, scaled=True, include_self=True)
+    out["scaled_train_x"] = m["x"]
+    out["scaled_train_idx"] = m["knn_idx"].astype(np.int32)
+    out["scaled_train_d2"] = m["knn_d2"]
+    # constant columns: std = 0 -> NaN -> 0 (load.py:48); duplicates under include_self
+    Xd = X[:80].copy()
+    Xd[:, 5] = 1.0
+    Xd[:, 17] = 0.0
+    Xd[9] = Xd[2]
+    Xd[30] = Xd[2]
+    fr = pd.DataFrame(np.column_stack([y[:80], Xd]), columns=list(df.columns))
+    out["const_cols"] = np.array([5, 17], dtype=np.int32)
+    out["const_dup_rows"] = np.array([2, 9, 30], dtype=np.int32)
+    case("const_k4_distance_laplacian", slice(0, 80), 4, "laplacian", "distance", frame=fr, scaled=True, include_self=True)
+    case("const_k4_connectivity_laplacian", slice(0, 80), 4, "laplacian", "connectivity", frame=fr, include_self=True)
+    # hot needs the integer labels that ``bits`` installs (load.py:189-191)
+    bits = [str(i) for i in range(3, 120, 2)]
+    fb = df[["value"] + bits].copy()
+    fb.columns = ["value"] + list(range(1, len(bits) + 1))
+    out["hot_bits"] = np.asarray([int(b) for b in bits], dtype=np.int32)
+    mh = case("hot_train_k5_distance_laplacian", train, 5, "laplacian", "distance", frame=fb, int_labels=True, hot=True)
+    out["hot_train_x"] = mh["x"].astype(np.int8)
+    case("hotscaled_test_k3_distance_none", test, 3, "none", "distance", frame=fb, int_labels=True, hot=True, scaled=True)
+    try:
+        ref.load.create_graph(df.iloc[train].copy(), n_neighbors=3, hot=True)
+        raise AssertionError("hot=True on string labels was expected to fail")
+    except KeyError as e:
+        assert e.args == (1,)
+    save("wheat_features.npz", **out)
+
+    # ---- ensemble loader -----------------------------------------------------------------------
+    ens = {}
+    cases = {
+        "a": dict(seed=11, num_neighbours=3, split=3, use_weights=True, use_validation=True, mode="distance"),
+        "b": dict(seed=5, num_neighbours=2, split=2, use_weights=True, scaled=False, add_full=True),
+        "c": dict(seed=5, num_neighbours=2, split=2, use_weights=True, scaled=False, add_full=True, full_split=0.8),
+        "d": dict(seed=7, num_neighbours=2, split=2, use_weights=False, separate_sets=False, train_size=300),
+        "e": dict(seed=7, num_neighbours=2, split=2, use_weights=True, separate_sets=False, full_split=400,
+                  train_size=0.6, include_self=True),
+    }
+    cwd = os.getcwd()
+    for name, kw in cases.items():
+        kw = dict(kw)
+        seed = kw.pop("seed")
+        with tempfile.TemporaryDirectory() as tmp:
+            os.chdir(tmp)
+            try:
+                np.random.seed(seed)
+                with contextlib.redirect_stdout(io.StringIO()):
+                    ds = ref.load_ensembles2.load_data_ensembles2(WHEAT_CSV, **kw)
+            finally:
+                os.chdir(cwd)
+        np.random.seed(seed)
+        mine = restate.ensemble_graphs(X, y, **kw)
+        np.random.seed(seed)
+        rows, valid = restate.ensemble_rows(len(y), kw["split"], kw.get("train_size", 0.7), kw.get("add_full", False),
+                                            kw.get("full_split"), kw.get("use_validation", False), 0.1,
+                                            kw.get("separate_sets", True))
+        assert len(ds) == len(mine)
+        ens[f"{name}_n"] = np.int64(len(ds))
+        ens[f"{name}_seed"] = np.int64(seed)
+        for i in range(len(ds)):
+            for sub, a, b in (("", ds[i], mine[i]), ("_test", ds[i].test, mine[i]["test"])):
+                assert np.array_equal(a.x.numpy(), b["x"]) and np.array_equal(a.y.numpy(), b["y"]), (name, i, sub)
+                assert np.array_equal(a.edge_index.numpy(), b["edge_index"]), (name, i, sub)
+                if kw.get("use_weights"):
+                    assert np.array_equal(a.edge_weight.numpy(), b["edge_weight"]), (name, i, sub)
+                    ens[f"{name}_{i}{sub}_ew"] = b["edge_weight"]
+                ens[f"{name}_{i}{sub}_ei"] = b["edge_index"].astype(np.int32)
+                ens[f"{name}_{i}{sub}_y"] = b["y"]
+                ens[f"{name}_{i}{sub}_xdigest"] = digest(b["x"])
+        for i, (tr, te) in enumerate(rows):
+            ens[f"{name}_{i}_rows"] = tr.astype(np.int32)
+            ens[f"{name}_{i}_test_rows"] = te.astype(np.int32)
+        if valid is not None:
+            ens[f"{name}_valid_rows"] = valid.astype(np.int32)
+    try:
+        with tempfile.TemporaryDirectory() as tmp:
+            os.chdir(tmp)
+            try:
+                with contextlib.redirect_stdout(io.StringIO()):
+                    ref.load_ensembles2.load_data_ensembles2(WHEAT_CSV, split=1, hot=True, scaled=False)
+            finally:
+                os.chdir(cwd)
+        raise AssertionError("hot=True was expected to fail in the ensemble loader")
+    except KeyError as e:
+        ens["hot_keyerror"] = np.int64(e.args[0])
+    save("wheat_ensemble.npz", **ens)
+
+
+def main(argv=None):
+    argv = sys.argv[1:] if argv is None else argv
     os.makedirs(GOLDEN, exist_ok=True)
     ref = ref_import.load(canonical_knn=True)
     df = wheat_frame()
+    features_and_ensemble(ref, df)
+    if argv and argv[0] == "features":
+        return 0
     N = len(df)
     X = df.iloc[:, 1:].values
     y = df["value"].values

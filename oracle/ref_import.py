@@ -38,6 +38,10 @@ def _install_shim():
     utils = types.ModuleType("torch_geometric.utils")
     utils.from_scipy_sparse_matrix = pyg_shim.from_scipy_sparse_matrix
     utils.add_remaining_self_loops = pyg_shim.add_remaining_self_loops
+
+    def _no_networkx(*_a, **_k):            # imported by load_ensembles2.py:10, only used in commented-out code
+        raise NotImplementedError("from_networkx is not on the path")
+    utils.from_networkx = _no_networkx
     nn = types.ModuleType("torch_geometric.nn")
     nn.GCNConv = pyg_shim.GCNConv
     dense = types.ModuleType("torch_geometric.nn.dense")
@@ -55,6 +59,14 @@ def _install_shim():
         torch_ser.add_safe_globals([pyg_shim.Data, pyg_shim._Collated])
     except Exception:
         pass
+    for name in ("seaborn", "matplotlib", "matplotlib.pyplot"):      # plotting imports of load_ensembles2.py:11-12
+        if name not in sys.modules:
+            try:
+                importlib.import_module(name)
+            except Exception:
+                sys.modules[name] = types.ModuleType(name)
+    if not hasattr(sys.modules["matplotlib"], "pyplot"):
+        sys.modules["matplotlib"].pyplot = sys.modules["matplotlib.pyplot"]
     if "dcor" not in sys.modules:
         try:
             importlib.import_module("dcor")
@@ -80,12 +92,12 @@ def load(canonical_knn=True):
     ns.ensemble2 = importlib.import_module("gnn.trainers.ensemble2")
     ns.batches = importlib.import_module("gnn.trainers.batches")
     ns.plain = importlib.import_module("gnn.trainers.plain")
+    ns.load_ensembles2 = importlib.import_module("gnn.loaders.load_ensembles2")
     if canonical_knn:
-        from .restate import canonical_kneighbors_graph
-        ns.load.kneighbors_graph = canonical_kneighbors_graph
-        ns.util.kneighbors_graph = canonical_kneighbors_graph
+        from .restate import canonical_kneighbors_graph as knn_graph
     else:
-        from sklearn.neighbors import kneighbors_graph
-        ns.load.kneighbors_graph = kneighbors_graph
-        ns.util.kneighbors_graph = kneighbors_graph
+        from sklearn.neighbors import kneighbors_graph as knn_graph
+    ns.load.kneighbors_graph = knn_graph
+    ns.util.kneighbors_graph = knn_graph
+    ns.load_ensembles2.kneighbors_graph = knn_graph
     return ns

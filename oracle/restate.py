@@ -22,6 +22,9 @@ from .pyg_shim import GCNConv
 
 
 # ----------------------------------------------------------------------------- kNN
+MAX_SIDE_COLUMNS = 4      # integer-coded markers plus at most this many float columns (the phenotype) use the exact path
+
+
 def _split_columns(X):
     """Integer-coded columns (exact path) vs the rest (float64 path)."""
     X = np.asarray(X, dtype=np.float64)
@@ -29,7 +32,7 @@ def _split_columns(X):
     return X[:, is_int], X[:, ~is_int]
 
 
-def canonical_knn(X_int, k, extra=None, block=1024):
+def canonical_knn(X_int, k, extra=None, block=1024, include_self=False):
     """k nearest neighbours of every row under squared Euclidean distance with
     the canonical (d2, j) order.  Stands in for the sklearn call at
     gnn/loaders/load.py:52-59 and gnn/loaders/util.py:52-57.
@@ -40,7 +43,10 @@ def canonical_knn(X_int, k, extra=None, block=1024):
     """
     Xf = np.ascontiguousarray(X_int, dtype=np.float64)      # products/sums of small ints are exact in f64
     n = Xf.shape[0]
-    if not 0 < k < n:
+    if include_self:                                            # load.py:28,57: the row competes like any other
+        if not 0 < k <= n:
+            raise ValueError(f"Expected n_neighbors <= n_samples_fit, but n_neighbors = {k}, n_samples_fit = {n}")
+    elif not 0 < k < n:
         raise ValueError(f"Expected n_neighbors <= n_samples_fit, but n_neighbors = {k + 1}, n_samples_fit = {n}")
     sq = np.einsum("ij,ij->i", Xf, Xf)
     idx = np.empty((n, k), dtype=np.int64)
@@ -54,7 +60,8 @@ def canonical_knn(X_int, k, extra=None, block=1024):
             for c in range(extra.shape[1]):
                 diff = extra[r0:r1, c][:, None] - extra[None, :, c]
                 d2 = d2 + diff * diff
-        d2[np.arange(r1 - r0), np.arange(r0, r1)] = np.inf              # never the row itself
+        if not include_self:
+            d2[np.arange(r1 - r0), np.arange(r0, r1)] = np.inf          # never the row itself
         order = np.argsort(d2, axis=1, kind="stable")[:, :k]             # stable => ties by ascending j
         idx[r0:r1] = order
         d2o[r0:r1] = np.take_along_axis(d2, order, axis=1)
@@ -66,11 +73,13 @@ def canonical_kneighbors_graph(X, n_neighbors, mode="connectivity", metric="mink
     """Drop-in for ``sklearn.neighbors.kneighbors_graph`` as the reference calls it
     (load.py:52-59; util.py:52-57): CSR with exactly k entries per row in
     ascending (distance, index) order; data = distances or ones."""
-    if metric not in ("minkowski", "euclidean", "euclidian", "l2") or p != 2 or include_self:
-        raise NotImplementedError("oracle covers the Euclidean, include_self=False call of the reference")
+    if metric not in ("minkowski", "euclidean", "euclidian", "l2") or p != 2:
+        raise NotImplementedError("oracle covers the Euclidean call of the reference")
     A = X.values if hasattr(X, "values") else np.asarray(X)
     xi, xf = _split_columns(A)
-    idx, d2 = canonical_knn(xi, n_neighbors, extra=xf if xf.shape[1] else None)
+    if xf.shape[1] > MAX_SIDE_COLUMNS:      # a float feature matrix (scaled=True): every column, left to right, in float64
+        xi, xf = np.zeros((A.shape[0], 0)), np.asarray(A, dtype=np.float64)
+    idx, d2 = canonical_knn(xi, n_neighbors, extra=xf if xf.shape[1] else None, include_self=include_self)
     n = idx.shape[0]
     data = np.sqrt(d2).ravel() if mode == "distance" else np.ones(n * n_neighbors)
     indptr = np.arange(0, n * n_neighbors + 1, n_neighbors)
@@ -109,9 +118,10 @@ def graph_edges(idx, d2, mode="connectivity", smoothing="laplacian", use_weights
     W.sort_indices()
     deg = np.asarray(W.sum(axis=0)).ravel() - W.diagonal()
     Wc = W.tocoo()
-    e_row = np.concatenate([Wc.row.astype(np.int64), np.arange(n, dtype=np.int64)])
-    e_col = np.concatenate([Wc.col.astype(np.int64), np.arange(n, dtype=np.int64)])
-    e_val = np.concatenate([-Wc.data, deg])
+    off = Wc.row != Wc.col                  # include_self leaves W[i, i]; the Laplacian's setdiag replaces it
+    e_row = np.concatenate([Wc.row[off].astype(np.int64), np.arange(n, dtype=np.int64)])
+    e_col = np.concatenate([Wc.col[off].astype(np.int64), np.arange(n, dtype=np.int64)])
+    e_val = np.concatenate([-Wc.data[off], deg])
     edge_index = np.stack([e_row, e_col])
     if not use_weights:
         return edge_index, None
@@ -119,21 +129,118 @@ def graph_edges(idx, d2, mode="connectivity", smoothing="laplacian", use_weights
     return edge_index, 1.0 - np.abs(e_val) / mx
 
 
+def hot_features(X, int_labels):
+    """load.py:38-43 as it executes: the loops address columns by the integer labels 1..P-1, which exist only after
+    ``bits`` renamed them (load.py:189-191; KeyError otherwise).  Loop 1 overwrites columns 1..P-1 with ``== 1``; loop 2
+    compares the overwritten 0/1 columns with 2, so column P and the P-2 appended columns are zero."""
+    if not int_labels:
+        raise KeyError(1)
+    X = np.asarray(X)
+    n, P = X.shape
+    if P < 2:
+        return X
+    return np.concatenate([(X[:, :P - 1] == 1).astype(np.int64), np.zeros((n, P - 1), dtype=np.int64)], axis=1)
+
+
+def scale_features(X):
+    """load.py:45-48 with the same pandas calls (mean, std with ddof 1, fillna)."""
+    import pandas as pd
+    df = pd.DataFrame(np.asarray(X, dtype=np.float64))
+    df -= df.mean()
+    df /= df.std()
+    return df.fillna(0).values
+
+
 def create_graph(X, y, n_neighbors=1, smoothing="laplacian", use_weights=False, remove_mean=True,
-                 mode="connectivity"):
-    """gnn/loaders/load.py:21-81 for integer-coded markers (hot/scaled off):
+                 mode="connectivity", hot=False, scaled=False, include_self=False, int_labels=False):
+    """gnn/loaders/load.py:21-81:
     x float32 [n, p], y float32 [n, 1] (centred in float64 first, :33-36, :50-51),
     edge_index / edge_weight from ``graph_edges``."""
     X = np.asarray(X)
     y = np.asarray(y, dtype=np.float64).reshape(-1)
     if remove_mean:
         y = y - y.mean()
-    idx, d2 = canonical_knn(X, n_neighbors)
+    if hot:
+        X = hot_features(X, int_labels)
+    if scaled:
+        X = scale_features(X)
+        idx, d2 = canonical_knn(np.zeros((X.shape[0], 0)), n_neighbors, extra=X, include_self=include_self)
+    else:
+        idx, d2 = canonical_knn(X, n_neighbors, include_self=include_self)
     edge_index, edge_weight = graph_edges(idx, d2, mode=mode, smoothing=smoothing, use_weights=use_weights)
     return {
         "x": X.astype(np.float32), "y": y.astype(np.float32).reshape(-1, 1),
         "edge_index": edge_index, "edge_weight": edge_weight, "knn_idx": idx, "knn_d2": d2,
     }
+
+
+# ----------------------------------------------------------------------------- seeded subsampling (ensemble loader)
+def ensemble_rows(n_rows, split, train_size=0.7, add_full=False, full_split=None, use_validation=False,
+                  validation_size=0.1, separate_sets=True):
+    """Which file rows every graph of load_ensembles2.py:74-132 is made of, as positions 0..n_rows-1.
+
+    Follows the frame manipulations literally on a one-column frame holding the row position:
+    validation rows are the FIRST ``valid_size`` rows of the already truncated frame (:82-83), the unseeded
+    ``df_whole.sample(frac)`` (:99) draws from numpy's global generator, and ``whole_test`` (:100) is chosen by index
+    LABEL against the re-numbered 0..m-1 labels of ``whole_train``, i.e. it is every row whose label is >= m, sampled or not.
+    Returns (list of (train_rows, test_rows), valid_rows or None)."""
+    import pandas as pd
+    df_whole = pd.DataFrame({"pos": np.arange(n_rows)})
+    df_valid = None
+    if use_validation:
+        valid_size = validation_size if isinstance(validation_size, int) else int(df_whole.shape[0] * validation_size)
+        df_whole = df_whole[valid_size:]
+        df_valid = df_whole[:valid_size]
+    full_split = int(full_split * len(df_whole)) if isinstance(full_split, float) else full_split
+    frac = train_size if train_size < 1 else train_size / df_whole.shape[0]
+    if separate_sets:
+        whole_train = df_whole.sample(frac=frac).reset_index(drop=True)
+        whole_test = df_whole.loc[~df_whole.index.isin(whole_train.index)].reset_index(drop=True)
+    else:
+        whole_train = whole_test = df_whole
+    out = []
+    for s_ in range(split + (1 if add_full else 0)):
+        if s_ == split and add_full:
+            if full_split is None:
+                df_train = df_whole.sample(frac=frac, random_state=s_).reset_index(drop=True)
+                df_test = df_whole.copy().reset_index(drop=True)
+            else:
+                df_train = df_whole[:full_split].reset_index(drop=True)
+                df_test = df_whole[full_split:].reset_index(drop=True)
+        elif separate_sets:
+            df_train = whole_train.sample(frac=0.5, random_state=s_).reset_index(drop=True)
+            df_test = whole_test
+        elif full_split is None:
+            df_train = df_whole.sample(frac=frac, random_state=s_).reset_index(drop=True)
+            df_test = df_whole.loc[~df_whole.index.isin(df_train.index)].reset_index(drop=True)
+        else:
+            less = df_whole[:full_split]
+            frac = train_size if train_size < 1 else train_size / less.shape[0]
+            df_train = less.sample(frac=frac, random_state=s_).reset_index(drop=True)
+            df_test = less.loc[~less.index.isin(df_train.index)].reset_index(drop=True)
+        out.append((df_train["pos"].values.copy(), df_test["pos"].values.copy()))
+    return out, (None if df_valid is None else df_valid["pos"].values.copy())
+
+
+def ensemble_graphs(X, y, split, num_neighbours=1, smoothing="laplacian", mode="connectivity", scaled=True,
+                    remove_mean=True, add_full=False, train_size=0.7, use_weights=False, use_validation=False,
+                    validation_size=0.1, full_split=None, include_self=False, separate_sets=True):
+    """load_ensembles2.py:53-297 (hot=False; hot=True dies with a KeyError at :139 once ``i`` passes the marker count):
+    one dict per graph as ``create_graph`` returns it, with ``test`` nested; the validation graph last."""
+    rows, valid = ensemble_rows(len(y), split, train_size, add_full, full_split, use_validation, validation_size,
+                                separate_sets)
+    kw = dict(n_neighbors=num_neighbours, smoothing=smoothing, use_weights=use_weights, remove_mean=remove_mean,
+              mode=mode, scaled=scaled, include_self=include_self)
+    out = []
+    for tr, te in rows:
+        g = create_graph(X[tr], y[tr], **kw)
+        g["test"] = create_graph(X[te], y[te], **kw)
+        out.append(g)
+    if valid is not None:
+        g = create_graph(X[valid], y[valid], **kw)
+        g["test"] = g
+        out.append(g)
+    return out
 
 
 # ----------------------------------------------------------------------------- subsampling

@@ -40,3 +40,14 @@ def wheat():
 @pytest.fixture(scope="session")
 def golden():
     return load_golden
+
+
+@pytest.fixture(scope="session")
+def wheat_csv(tmp_path_factory, wheat):
+    """The WHEAT file rebuilt from the packed fixture (headerless: phenotype, then markers as 1.0 / 0.0)."""
+    X, y = wheat
+    path = tmp_path_factory.mktemp("csv") / "WHEAT_combined.csv"
+    with open(path, "w") as fp:
+        for yi, row in zip(y, X):
+            fp.write(repr(float(yi)) + "," + ",".join("1.0" if v else "0.0" for v in row) + "\n")
+    return str(path)

@@ -18,21 +18,30 @@ LR = 0.0020594745443455593
 
 
 @pytest.fixture(scope="module")
-def wheat_csv(tmp_path_factory, wheat):
-    X, y = wheat
-    path = tmp_path_factory.mktemp("csv") / "WHEAT_combined.csv"
-    with open(path, "w") as fp:
-        for yi, row in zip(y, X):
-            fp.write(repr(float(yi)) + "," + ",".join("1.0" if v else "0.0" for v in row) + "\n")
-    return str(path)
-
-
-@pytest.fixture(scope="module")
 def wheat_batches(wheat_csv):
     ds = load_data(wheat_csv, num_neighbours=5, smoothing="laplacian", mode="distance", use_validation=True, split=0.8,
                    use_weights=True, algorithm="euclidean", batches=3, split_algorithm=split_dataset_graph,
                    split_algorithm_params={"partition": naive_partition})
     return ds
+
+
+def test_processed_cache_round_trip(wheat_csv, tmp_path, monkeypatch):
+    """load.py:123-124, 283-284: the dataset is cached under processed/<name built from every loader argument>.pt."""
+    monkeypatch.chdir(tmp_path)
+    kw = dict(num_neighbours=4, smoothing="laplacian", mode="distance", use_validation=True, split=0.8, use_weights=True,
+              algorithm="euclidean", batches=3, split_algorithm=split_dataset_graph, split_algorithm_params={"partition": naive_partition})
+    a = load_data(wheat_csv, **kw)
+    files = os.listdir(tmp_path / "processed")
+    assert len(files) == 1 and files[0].startswith("data-") and "split_dataset_graph-partition:naive_partition;" in files[0]
+    b = load_data(wheat_csv, **kw)                       # served from the cache
+    assert len(a) == len(b) == 4
+    for ga, gb in zip(a, b):
+        for key in ("x", "y", "edge_index", "edge_weight"):
+            assert torch.equal(getattr(ga, key), getattr(gb, key))
+        assert torch.equal(ga.test.edge_index, gb.test.edge_index) and gb.x.stride(0) % 16 == 0
+    gl = [g for g in b]
+    assert gl[0].test.x.data_ptr() == gl[1].test.x.data_ptr()       # the shared test graph is stored once
+    assert torch.equal(gl[-1].test.x, gl[-1].x)                      # valid_data.test = valid_data (load.py:236)
 
 
 def test_loader_structure(wheat_batches, golden):
