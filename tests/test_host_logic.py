@@ -181,3 +181,42 @@ def test_naive_partition_bidirectional_stream():
     assert naive_partition(edges, 3) == [0, 3, 2]          # S = [3, 0, 2, 1, 0, 2]
     assert naive_partition(edges, 4, traversed={0}) == [1, 3, 2]
     assert naive_partition([], 3) == []
+
+
+@pytest.mark.parametrize("name,kw", [
+    ("a", dict(split=3, use_validation=True)),
+    ("b", dict(split=2, add_full=True)),
+    ("c", dict(split=2, add_full=True, full_split=0.8)),
+    ("d", dict(split=2, separate_sets=False, train_size=300)),
+    ("e", dict(split=2, separate_sets=False, full_split=400, train_size=0.6)),
+])
+def test_ensemble_rows_golden(golden, name, kw):
+    """load_ensembles2.py:80-132: the host-side row draws equal the reference's (frozen rows) and the oracle's."""
+    from gnn_b200.loaders.load_ensembles2 import ensemble_rows
+    g = golden("wheat_ensemble.npz")
+    seed = int(g[f"{name}_seed"])
+    np.random.seed(seed)
+    rows, valid = ensemble_rows(599, **kw)
+    np.random.seed(seed)
+    o_rows, o_valid = restate.ensemble_rows(599, **kw)
+    for i, (tr, te) in enumerate(rows):
+        assert np.array_equal(tr, g[f"{name}_{i}_rows"]) and np.array_equal(te, g[f"{name}_{i}_test_rows"])
+        assert np.array_equal(tr, o_rows[i][0]) and np.array_equal(te, o_rows[i][1])
+    if valid is None:
+        assert o_valid is None
+    else:
+        assert np.array_equal(valid, g[f"{name}_valid_rows"]) and np.array_equal(valid, o_valid)
+        assert valid[0] == len(valid)          # the validation rows come from the already truncated frame (:82-83)
+
+
+def test_ensemble_rows_sizes_property():
+    from gnn_b200.loaders.load_ensembles2 import ensemble_rows
+    for n in (10, 57, 200):
+        for split in (1, 4):
+            np.random.seed(n)
+            rows, valid = ensemble_rows(n, split, train_size=0.7)
+            m = round(0.7 * n)
+            assert len(rows) == split and valid is None
+            for tr, te in rows:
+                assert len(tr) == round(0.5 * m) and len(set(tr.tolist())) == len(tr)
+                assert np.array_equal(te, np.arange(m, n))

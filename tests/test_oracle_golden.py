@@ -146,3 +146,83 @@ def test_synth_is_stateless_and_in_range():
     assert 0.0 <= f.min() and f.max() <= 0.75
     y = synth.phenotypes(200, 300, traits=3)
     assert y.shape == (200, 3) and np.allclose(y.mean(axis=0), 0)
+
+
+# ---- feature transforms and the ensemble loader (fixtures frozen from the reference by oracle/make_golden.py) ----
+def test_feature_graphs_golden(wheat, golden):
+    from oracle.make_golden import digest
+    X, y = wheat
+    g = golden("wheat_features.npz")
+    train, test = slice(0, 479), slice(479, 587)
+    for mode, smoothing in (("distance", "laplacian"), ("connectivity", "none")):
+        for tag, rows, k, kw in ((f"scaled_train_k5_{mode}_{smoothing}", train, 5, dict(scaled=True)),
+                                 (f"self_train_k5_{mode}_{smoothing}", train, 5, dict(include_self=True)),
+                                 (f"scaledself_test_k3_{mode}_{smoothing}", test, 3, dict(scaled=True, include_self=True))):
+            m = restate.create_graph(X[rows].astype(np.float64), y[rows], n_neighbors=k, smoothing=smoothing,
+                                     use_weights=True, mode=mode, **kw)
+            assert np.array_equal(m["edge_index"], g[tag + "_ei"]), tag
+            assert np.array_equal(m["edge_weight"], g[tag + "_ew"]), tag
+            assert digest(m["x"]) == g[tag + "_xdigest"], tag
+    cols = g["hot_bits"] - 1
+    m = restate.create_graph(X[train][:, cols].astype(np.float64), y[train], n_neighbors=5, use_weights=True,
+                             mode="distance", hot=True, int_labels=True)
+    assert np.array_equal(m["edge_index"], g["hot_train_k5_distance_laplacian_ei"])
+    assert np.array_equal(m["x"].astype(np.int8), g["hot_train_x"])
+    with pytest.raises(KeyError):
+        restate.create_graph(X[:50].astype(np.float64), y[:50], n_neighbors=2, hot=True)
+
+
+def test_pairwise_sum_restatement_matches_pandas_std():
+    """The summation order the CUDA scaling kernel reproduces (numpy's pairwise sum) is what pandas' std uses."""
+    def pw(a):
+        n = len(a)
+        if n < 8:
+            r = 0.0
+            for v in a:
+                r = r + v
+            return r
+        if n <= 128:
+            r = [a[i] for i in range(8)]
+            i = 8
+            while i < n - (n % 8):
+                for j in range(8):
+                    r[j] = r[j] + a[i + j]
+                i += 8
+            res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]))
+            while i < n:
+                res = res + a[i]
+                i += 1
+            return res
+        n2 = n // 2
+        n2 -= n2 % 8
+        return pw(a[:n2]) + pw(a[n2:])
+
+    rng = np.random.default_rng(3)
+    for n in (5, 8, 100, 129, 300, 1031):
+        X = rng.integers(0, 3, size=(n, 6)).astype(np.float64)
+        want = restate.scale_features(X)
+        for c in range(X.shape[1]):
+            d = X[:, c] - X[:, c].sum() / n
+            avg = pw(list(d)) / n
+            sd = np.sqrt(pw(list((avg - d) ** 2)) / (n - 1))
+            assert np.array_equal(np.nan_to_num(d / sd, nan=0.0) if sd == 0 else d / sd, want[:, c]), (n, c)
+
+
+@pytest.mark.parametrize("name,kw", [
+    ("a", dict(num_neighbours=3, split=3, use_weights=True, use_validation=True, mode="distance")),
+    ("e", dict(num_neighbours=2, split=2, use_weights=True, separate_sets=False, full_split=400, train_size=0.6,
+               include_self=True)),
+])
+def test_ensemble_loader_golden(wheat, golden, name, kw):
+    from oracle.make_golden import digest
+    X, y = wheat
+    g = golden("wheat_ensemble.npz")
+    np.random.seed(int(g[f"{name}_seed"]))
+    graphs = restate.ensemble_graphs(X.astype(np.float64), y, **kw)
+    assert len(graphs) == int(g[f"{name}_n"])
+    for i, m in enumerate(graphs):
+        for sub, d in (("", m), ("_test", m["test"])):
+            key = f"{name}_{i}{sub}"
+            assert np.array_equal(d["edge_index"], g[key + "_ei"]), key
+            assert np.array_equal(d["edge_weight"], g[key + "_ew"]), key
+            assert np.array_equal(d["y"], g[key + "_y"]) and digest(d["x"]) == g[key + "_xdigest"], key
