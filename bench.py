@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--hidden", type=int, default=HIDDEN)
     ap.add_argument("--precision", default="auto")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-format", choices=("packed", "int8"), default="packed",
+                    help="host format of the genotypes in the end-to-end arm: 2-bit packed (default) or int8 codes")
     ap.add_argument("--cuda-graph", default="auto", choices=["auto", "on", "off"],
                     help="replay each subgraph's training step as a CUDA graph (auto: when it captures cleanly)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -260,20 +262,28 @@ def run_ours(a):
     e2e = None
     if not a.no_e2e:
         host = []
+        packed = a.e2e_format == "packed"
         for g in batches:
-            hx = torch.empty(g.x.shape, dtype=torch.int8).pin_memory()
-            hx.copy_(g.x)
+            src = ops.pack_2bit(g.x) if packed else g.x
+            hx = torch.empty(src.shape, dtype=src.dtype).pin_memory()
+            hx.copy_(src)
+            del src
             host.append((hx, g.edge_index.cpu().pin_memory(), g.edge_weight.cpu().pin_memory(), g.y.cpu().pin_memory()))
         h2d = sum(t.numel() * t.element_size() for t in host[0]) if host else 0
         copy_stream = torch.cuda.Stream()
+        main_stream = torch.cuda.current_stream(dev)
         from gnn_b200.data import Data
 
         def stage(i):
             with torch.cuda.stream(copy_stream):
                 hx, hei, hew, hy = host[i]
-                d = Data(x=hx.to(dev, non_blocking=True), edge_index=hei.to(dev, non_blocking=True),
-                         y=hy.to(dev, non_blocking=True))
+                x = hx.to(dev, non_blocking=True)
+                if packed:
+                    x = ops.unpack_2bit(x, p)                             # expanded to int8 codes on the device
+                d = Data(x=x, edge_index=hei.to(dev, non_blocking=True), y=hy.to(dev, non_blocking=True))
                 d.edge_weight = hew.to(dev, non_blocking=True)
+                for t in (d.x, d.edge_index, d.y, d.edge_weight):         # consumed on the compute stream
+                    t.record_stream(main_stream)
                 ev = torch.cuda.Event()
                 ev.record(copy_stream)
             return d, ev
@@ -297,7 +307,8 @@ def run_ours(a):
         ms_e2e, _ = timed(epoch_e2e, max(1, min(a.steps, 2)))
         e2e = {"value": 1000.0 / ms_e2e, "unit": "epochs/s", "h2d_bytes_per_step": int(h2d * len(host)),
                "d2h_bytes_per_step": 4 * (len(host) + 1),
-               "note": "per epoch: every owned subgraph's int8 genotypes + edge list + weights + phenotypes H2D from pinned "
+               "host_format": "2-bit packed genotypes (4 codes per byte), expanded to int8 on the device" if packed else "int8 genotypes",
+               "note": "per epoch: every owned subgraph's genotypes + edge list + weights + phenotypes H2D from pinned "
                        "memory (prefetched one subgraph ahead on a copy stream), gcn_norm/CSR rebuilt per step, loss D2H per step"}
 
     if rank != 0:

@@ -342,6 +342,64 @@ __global__ void scale_columns_kernel(const int8_t* __restrict__ X, int64_t ldx, 
     }
 }
 
+// 2-bit genotype packing (codes 0..3, four per byte, code j of a row in bits 2*(j%4).. of byte j/4): the host / PCIe
+// format of the markers.  One thread expands one 32-bit word (16 codes) into one 16-byte store.
+__device__ __forceinline__ uint32_t expand_2bit_byte(uint32_t b) {
+    return (b & 0x3u) | ((b & 0xcu) << 6) | ((b & 0x30u) << 12) | ((b & 0xc0u) << 18);
+}
+
+__global__ void unpack_2bit_vec_kernel(const uint8_t* __restrict__ P, int64_t ldp, int64_t n, int64_t p,
+                                       int8_t* __restrict__ out, int64_t ldo) {
+    const int64_t words = (p + 15) / 16;
+    const int64_t total = n * words;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = t / words, w = t % words;
+        const uint32_t v = *reinterpret_cast<const uint32_t*>(P + r * ldp + w * 4);
+        uint4 o;
+        o.x = expand_2bit_byte(v & 0xffu);
+        o.y = expand_2bit_byte((v >> 8) & 0xffu);
+        o.z = expand_2bit_byte((v >> 16) & 0xffu);
+        o.w = expand_2bit_byte(v >> 24);
+        int8_t* dst = out + r * ldo + w * 16;
+        if (w * 16 + 16 <= ldo) {
+            *reinterpret_cast<uint4*>(dst) = o;                 // the padding columns of the row receive zeros
+        } else {
+            const uint32_t q[4] = {o.x, o.y, o.z, o.w};
+            for (int64_t j = w * 16; j < p; ++j) dst[j - w * 16] = (int8_t)((q[(j & 15) >> 2] >> (8 * (j & 3))) & 0xffu);
+        }
+    }
+}
+
+__global__ void unpack_2bit_kernel(const uint8_t* __restrict__ P, int64_t ldp, int64_t n, int64_t p,
+                                   int8_t* __restrict__ out, int64_t ldo) {
+    const int64_t total = n * p;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = t / p, j = t % p;
+        out[r * ldo + j] = (int8_t)((P[r * ldp + (j >> 2)] >> (2 * (j & 3))) & 3);
+    }
+}
+
+__global__ void pack_2bit_kernel(const int8_t* __restrict__ X, int64_t ldx, int64_t n, int64_t p,
+                                 uint8_t* __restrict__ out, int64_t ldo, int32_t* __restrict__ bad) {
+    const int64_t nb = (p + 3) / 4;
+    const int64_t total = n * nb;
+    int any_bad = 0;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = t / nb, b = t % nb;
+        uint32_t v = 0;
+        for (int q = 0; q < 4; ++q) {
+            const int64_t j = b * 4 + q;
+            if (j < p) {
+                const int c = X[r * ldx + j];
+                any_bad |= (c < 0 || c > 3);
+                v |= (uint32_t)(c & 3) << (2 * q);
+            }
+        }
+        out[r * ldo + b] = (uint8_t)v;
+    }
+    if (any_bad && bad) atomicExch(bad, 1);
+}
+
 __global__ void sqnorm_kernel(const int8_t* __restrict__ X, int64_t ldx, int64_t n, int64_t p, int64_t* __restrict__ sq) {
     // one warp per row
     int lane = threadIdx.x & 31;
@@ -450,6 +508,36 @@ int gnnb_scale_columns_i8(const int8_t* X, int64_t ldx, int64_t n, int64_t p, do
     GNNB_REQUIRE((!out64 || ld64 >= p) && (!out32 || ld32 >= p), GNNB_E_BADARG, "scale_columns: output stride < p");
     if (n == 0) return GNNB_OK;
     scale_columns_kernel<<<(unsigned)((p + 127) / 128), 128, 0, (cudaStream_t)stream>>>(X, ldx, n, p, out64, ld64, out32, ld32);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+int gnnb_unpack_2bit(const uint8_t* P, int64_t ldp, int64_t n, int64_t p, int8_t* out, int64_t ldo, void* stream) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(P && out && n >= 0 && p > 0 && ldp >= (p + 3) / 4 && ldo >= p, GNNB_E_BADARG, "unpack_2bit: bad argument");
+    if (n == 0) return GNNB_OK;
+    int64_t cap = (int64_t)sm_count() * 32;
+    bool vec = ((uintptr_t)P % 4 == 0) && (ldp % 4 == 0) && ldp >= ((p + 15) / 16) * 4 &&
+               ((uintptr_t)out % 16 == 0) && (ldo % 16 == 0);
+    if (vec) {
+        int64_t blocks = (n * ((p + 15) / 16) + 255) / 256;
+        unpack_2bit_vec_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(P, ldp, n, p, out, ldo);
+    } else {
+        int64_t blocks = (n * p + 255) / 256;
+        unpack_2bit_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(P, ldp, n, p, out, ldo);
+    }
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+int gnnb_pack_2bit(const int8_t* X, int64_t ldx, int64_t n, int64_t p, uint8_t* out, int64_t ldo, int32_t* bad_flag,
+                   void* stream) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(X && out && n >= 0 && p > 0 && ldx >= p && ldo >= (p + 3) / 4, GNNB_E_BADARG, "pack_2bit: bad argument");
+    if (n == 0) return GNNB_OK;
+    int64_t blocks = (n * ((p + 3) / 4) + 255) / 256;
+    int64_t cap = (int64_t)sm_count() * 32;
+    pack_2bit_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(X, ldx, n, p, out, ldo, bad_flag);
     GNNB_LAUNCH_CHECK();
     return GNNB_OK;
 }

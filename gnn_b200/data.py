@@ -136,14 +136,19 @@ class GenotypeTable:
         if X.dtype != np.int8:
             Xi = np.rint(X).astype(np.int8)
             if not np.array_equal(Xi, X) or (X.size and (X.min() < 0 or X.max() > 127)):
-                raise NotImplementedError("gnn_b200 handles integer genotype codes in [0, 127]; "
-                                          "float features (scaled=True) are outside the current path")
+                raise NotImplementedError("a GenotypeTable holds integer genotype codes in [0, 127]; standardised "
+                                          "features are produced on the device by scaled=True (load.py:45-48)")
             X = Xi
         n, p = X.shape
-        ld = (p + 15) // 16 * 16
-        host = torch.zeros((n, ld), dtype=torch.int8).pin_memory() if torch.cuda.is_available() else None
-        if host is None:
+        if not torch.cuda.is_available():
             raise RuntimeError("gnn_b200 needs a CUDA device (no CPU fallback)")
+        from . import ops
+        if X.size and X.min() >= 0 and X.max() <= 3:
+            # 0/1/2 genotypes cross PCIe as 2-bit codes (a quarter of the bytes) and are expanded on the device
+            host = torch.from_numpy(ops.pack_2bit_host(X)).pin_memory()
+            return GenotypeTable(ops.unpack_2bit(host.to(device, non_blocking=True), p), y)
+        ld = (p + 15) // 16 * 16
+        host = torch.zeros((n, ld), dtype=torch.int8).pin_memory()
         host[:, :p] = torch.from_numpy(X)
         dev = host.to(device, non_blocking=True)
         return GenotypeTable(dev[:, :p], y)

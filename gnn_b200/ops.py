@@ -131,6 +131,55 @@ def gather_rows(X, rows, ld_align=16):
     return buf[:, :p]
 
 
+def packed_stride(p):
+    """Row stride in bytes of 2-bit packed markers: four codes per byte, padded to 16 bytes."""
+    return ((p + 3) // 4 + 15) // 16 * 16
+
+
+def pack_2bit_host(X):
+    """numpy int8 codes 0..3 [n, p] -> uint8 [n, packed_stride(p)] (code j in bits 2*(j%4) of byte j//4)."""
+    import numpy as np
+    X = np.asarray(X)
+    n, p = X.shape
+    if X.size and (X.min() < 0 or X.max() > 3):
+        raise ValueError("2-bit packing needs genotype codes in 0..3")
+    q = (p + 3) // 4
+    padded = np.zeros((n, q * 4), dtype=np.uint8)
+    padded[:, :p] = X
+    v = padded.reshape(n, q, 4)
+    out = np.zeros((n, packed_stride(p)), dtype=np.uint8)
+    out[:, :q] = v[:, :, 0] | (v[:, :, 1] << 2) | (v[:, :, 2] << 4) | (v[:, :, 3] << 6)
+    return out
+
+
+def unpack_2bit(P, p, out=None):
+    """uint8 packed markers on the GPU -> int8 codes [n, p] (row stride padded to 16 bytes)."""
+    _need_cuda(P)
+    if P.dtype != torch.uint8 or P.dim() != 2 or P.stride(1) != 1:
+        raise _lib.GnnbError("packed markers must be a 2-D uint8 tensor with unit column stride")
+    n = P.shape[0]
+    if out is None:
+        ld = (p + 15) // 16 * 16
+        out = torch.empty((n, ld), dtype=torch.int8, device=P.device)[:, :p]
+    with torch.cuda.device(P.device):
+        _declare(bytes=float(n * ((p + 3) // 4) + n * p))
+        _call("gnnb_unpack_2bit", _p(P), P.stride(0), n, p, _p(out), out.stride(0), _stream())
+    return out
+
+
+def pack_2bit(X):
+    """int8 codes on the GPU -> packed uint8 [n, packed_stride(p)]; raises if a code is outside 0..3 (synchronises)."""
+    _rows_ok(X)
+    n, p = X.shape
+    out = torch.zeros((n, packed_stride(p)), dtype=torch.uint8, device=X.device)
+    bad = torch.zeros(1, dtype=torch.int32, device=X.device)
+    with torch.cuda.device(X.device):
+        _call("gnnb_pack_2bit", _p(X), X.stride(0), n, p, _p(out), out.stride(0), _p(bad), _stream())
+    if int(bad.item()):
+        raise ValueError("2-bit packing needs genotype codes in 0..3")
+    return out
+
+
 def i8_to_f32(X):
     _need_cuda(X)
     out = torch.empty(X.shape, dtype=torch.float32, device=X.device)

@@ -53,6 +53,13 @@ int gnnb_gather_rows_i8(const int8_t* X, int64_t ldx, const int64_t* rows, int64
                         int8_t* out, int64_t ldo, void* stream);
 /* x_f32 = float(X) -- replaces torch.tensor(df_x.values.tolist(), dtype=float) at load.py:50 */
 int gnnb_i8_to_f32(const int8_t* X, int64_t ldx, int64_t n, int64_t p, float* out, int64_t ldo, void* stream);
+/* 2-bit marker packing -- the host / PCIe format of the genotypes (codes 0..3, four per byte, code j of a row in bits
+ * 2*(j%4) of byte j/4).  No reference counterpart: the reference keeps markers as float64 in a
+ * DataFrame (load.py:182-187).  unpack writes int8 codes (padding columns up to ldo get zeros when ldo % 16 == 0);
+ * pack sets *bad_flag (device int32, may be NULL) to 1 if a code lies outside 0..3. */
+int gnnb_unpack_2bit(const uint8_t* P, int64_t ldp, int64_t n, int64_t p, int8_t* out, int64_t ldo, void* stream);
+int gnnb_pack_2bit(const int8_t* X, int64_t ldx, int64_t n, int64_t p, uint8_t* out, int64_t ldo, int32_t* bad_flag,
+                   void* stream);
 /* `scaled=True` (load.py:45-48; load_ensembles2.py:150-157): per column x -= mean, x /= std (ddof 1), NaN -> 0, with
  * pandas' arithmetic (exact mean; two-pass variance summed in numpy's pairwise order), so the float64 output equals
  * `df_x.values` of the reference bit for bit on integer-coded markers.  out64 feeds gnnb_knn_f64, out32 is `x`

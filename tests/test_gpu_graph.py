@@ -61,8 +61,6 @@ def test_dataframe_input_and_unweighted(wheat):
     ref = restate.create_graph(X[:200], y[:200], 4, "laplacian", False, True, "distance")
     assert d.edge_weight is None and np.array_equal(d.edge_index.cpu().numpy(), ref["edge_index"])
     with pytest.raises(NotImplementedError):
-        create_graph(df, n_neighbors=4, scaled=True)
-    with pytest.raises(NotImplementedError):
         create_graph(df, n_neighbors=4, algorithm="cosine")
     with pytest.raises(ValueError):
         create_graph(df, n_neighbors=4, mode="weird")

@@ -25,3 +25,28 @@ def test_gather_sqnorm_convert():
     assert torch.equal(ops.i8_to_f32(X), X.float())
     A = torch.randn(1000, 100, device="cuda")
     torch.testing.assert_close(ops.colsum(A), A.sum(0), rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("n,p", [(1, 1), (3, 5), (17, 64), (100, 1279), (257, 4099)])
+def test_pack_unpack_2bit_round_trip(n, p):
+    """The PCIe format of the markers: host packer, device packer and device unpacker agree bit for bit."""
+    import numpy as np
+    rng = np.random.default_rng(n * 31 + p)
+    X = rng.integers(0, 4, size=(n, p)).astype(np.int8)
+    host = ops.pack_2bit_host(X)
+    assert host.shape == (n, ops.packed_stride(p)) and host.dtype == np.uint8
+    for j in (0, p // 2, p - 1):
+        assert np.array_equal((host[:, j // 4] >> (2 * (j % 4))) & 3, X[:, j])
+    Xd = torch.from_numpy(X).cuda()
+    dev_packed = ops.pack_2bit(Xd)
+    assert np.array_equal(dev_packed.cpu().numpy(), host)
+    back = ops.unpack_2bit(torch.from_numpy(host).cuda(), p)
+    assert back.stride(0) % 16 == 0 and np.array_equal(back.cpu().numpy(), X)
+    # unaligned destination takes the scalar kernel
+    out = torch.full((n, p + 1), 7, dtype=torch.int8, device="cuda")
+    ops.unpack_2bit(dev_packed, p, out=out[:, 1:])
+    assert np.array_equal(out[:, 1:].cpu().numpy(), X) and bool((out[:, 0] == 7).all())
+    with pytest.raises(ValueError):
+        ops.pack_2bit(torch.full((2, 8), 5, dtype=torch.int8, device="cuda"))
+    with pytest.raises(ValueError):
+        ops.pack_2bit_host(np.full((2, 8), -1, dtype=np.int8))
