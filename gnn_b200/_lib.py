@@ -9,7 +9,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libgnn_b200.so")
+LIB_PATH = os.environ.get("GNNB_LIB") or os.path.join(_HERE, "lib", "libgnn_b200.so")   # GNNB_LIB: a differently tuned build
 CSRC_DIR = os.path.join(_HERE, "csrc")
 
 _c = ctypes

@@ -47,4 +47,63 @@ struct RowSelector {
     }
 };
 
+// The same selection for exact integer distances, built for the tensor-core epilogue where a whole warp pays whenever
+// one of its rows inserts.  The pair (d2, index) is ONE sortable 64-bit key (d2 < 2^32 for int8 codes and p <= 133000);
+// the list is kept UNSORTED with its maximum tracked in registers: an insertion overwrites the maximum and rescans the
+// k keys with independent loads (~150 cycles) instead of walking a dependent insertion-sort chain through shared
+// memory (~1300 cycles).  Unfilled slots hold the all-ones sentinel, so the warm-up needs no special case.  The list is
+// sorted once, when the CTA is done.
+struct RowSelectorU64 {
+    unsigned long long* lk;      // [k][rows]
+    int rows, r, k, maxpos;
+    unsigned long long thr;      // current maximum key: a candidate enters iff key < thr
+
+    static constexpr unsigned long long EMPTY = ~0ULL;
+
+    __device__ __forceinline__ void init(void* list, int rows_, int r_, int k_) {
+        lk = reinterpret_cast<unsigned long long*>(list); rows = rows_; r = r_; k = k_;
+        for (int t = 0; t < k; ++t) lk[t * rows + r] = EMPTY;
+        thr = EMPTY;
+        maxpos = 0;
+    }
+    __device__ __forceinline__ static unsigned long long make_key(long long d2, int j) {
+        return ((unsigned long long)d2 << 32) | (unsigned)j;
+    }
+    __device__ __forceinline__ void offer(unsigned long long key) {
+        if (key >= thr) return;
+        lk[maxpos * rows + r] = key;
+        unsigned long long m = 0;
+        int mp = 0;
+#pragma unroll 8
+        for (int t = 0; t < k; ++t) {
+            const unsigned long long v = lk[t * rows + r];
+            if (v >= m) { m = v; mp = t; }
+        }
+        thr = m;
+        maxpos = mp;
+    }
+    // ascending order in place: repeatedly move the maximum of the unsorted prefix to its end
+    __device__ __forceinline__ void sort() {
+        for (int end = k - 1; end > 0; --end) {
+            unsigned long long m = 0;
+            int mp = 0;
+            for (int t = 0; t <= end; ++t) {
+                const unsigned long long v = lk[t * rows + r];
+                if (v >= m) { m = v; mp = t; }
+            }
+            const unsigned long long last = lk[end * rows + r];
+            lk[end * rows + r] = m;
+            lk[mp * rows + r] = last;
+        }
+    }
+    __device__ __forceinline__ double d(int t) const {
+        const unsigned long long v = lk[t * rows + r];
+        return v == EMPTY ? (double)INFINITY : (double)(v >> 32);
+    }
+    __device__ __forceinline__ int i(int t) const {
+        const unsigned long long v = lk[t * rows + r];
+        return v == EMPTY ? 0x7fffffff : (int)(unsigned)(v & 0xffffffffULL);
+    }
+};
+
 }  // namespace gnnb

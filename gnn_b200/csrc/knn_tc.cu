@@ -5,6 +5,8 @@
 // gnn/loaders/util.py:52-57).  Results are bit-identical to the dp4a kernel in knn.cu and to the oracle:
 // the dot products are exact integers either way and the selection code is shared (knn_select.cuh).
 //
+// Two kernels: knn_tc2_kernel (CTA pairs, cta_group::2, default) and knn_tc_kernel (one CTA per tile; odd shapes and
+// GNNB_KNN_PAIR=0).  Layout of the one-CTA kernel:
 // CTA = 128 query rows x a range of 256-row key tiles; 8 warps:
 //   warp 0    TMA producer      A = Q[128 x 128 B], B = K[256 x 128 B] per k-block into a 2-3 stage ring
 //   warp 1    MMA issuer        4 x (M128 N256 K32) per k-block into one of two 256-column TMEM accumulators
@@ -66,6 +68,49 @@ __device__ inline Smem carve(uint8_t* raw, int stages, int k, bool extra) {
     return s;
 }
 }  // namespace
+
+// One accumulator tile (this thread's row x 256 key columns): distances, one compare per column, rare insertions.
+// Exact integer path (no float side columns): RowSelectorU64; otherwise the float64 RowSelector.
+template <bool HAS_EXTRA>
+__device__ __forceinline__ void scan_accumulator(uint32_t taddr_row, bool valid, long long sqq, const long long* __restrict__ sqk_b,
+                                                 const double* __restrict__ ek_b, const double* eq_r, int n_extra, int ncols,
+                                                 int64_t gi, int64_t gk0, RowSelector& sel, long long& thr_ll, RowSelectorU64& selu) {
+#pragma unroll 1
+    for (int chunk = 0; chunk < BN / 32; ++chunk) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(taddr_row + chunk * 32, v);
+        tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+            for (int c = 0; c < 32; ++c) {
+                const int col = chunk * 32 + c;
+                const long long di = sqq + sqk_b[col] - 2LL * (long long)(int)v[c];
+                if (HAS_EXTRA) {
+                    if (di <= thr_ll && col < ncols) {
+                        const int64_t gj = gk0 + col;
+                        if (gj != gi) {
+                            double d = (double)di;
+                            for (int x = 0; x < n_extra; ++x) {
+                                double diff = __dsub_rn(eq_r[x], ek_b[col * KNN_MAX_EXTRA + x]);
+                                d = __dadd_rn(d, __dmul_rn(diff, diff));
+                            }
+                            sel.offer(d, (int)gj);
+                            thr_ll = (sel.thr_d == INFINITY) ? LLONG_MAX : (long long)sel.thr_d;
+                        }
+                    }
+                } else {
+                    if (di <= thr_ll && col < ncols) {
+                        const int64_t gj = gk0 + col;
+                        if (gj != gi) {
+                            selu.offer(RowSelectorU64::make_key(di, (int)gj));
+                            thr_ll = (long long)(selu.thr >> 32);          // EMPTY >> 32 = 2^32 - 1 >= any distance
+                        }
+                    }
+                }
+            }
+        }
+    }
+}
 
 template <bool HAS_EXTRA>
 __global__ void __launch_bounds__(256, 1)
@@ -161,7 +206,9 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__
         const bool valid = row < n_q;
         const int64_t gi = q_off + row;
         RowSelector sel;
-        sel.init(sm.list_d, sm.list_i, BM, e, k);
+        RowSelectorU64 selu;
+        if (HAS_EXTRA) sel.init(sm.list_d, sm.list_i, BM, e, k);
+        else           selu.init(sm.list_d, BM, e, k);
         long long sqq = 0, thr_ll = LLONG_MAX;
         double eq_r[KNN_MAX_EXTRA];
         if (valid) {
@@ -186,48 +233,223 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__
             mbar_wait(&sm.tfull[b], tph);
             tc_fence_after_sync();
             const int ncols = (int)((n_k - k0) < BN ? (n_k - k0) : BN);
-#pragma unroll 1
-            for (int chunk = 0; chunk < BN / 32; ++chunk) {
-                uint32_t v[32];
-                tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(32 * wq) << 16) + b * BN + chunk * 32, v);
-                tmem_ld_wait();
-                if (valid) {
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) {
-                        const int col = chunk * 32 + c;
-                        const long long di = sqq + sqk_b[col] - 2LL * (long long)(int)v[c];
-                        if (di <= thr_ll && col < ncols) {
-                            const int64_t gj = k_off + k0 + col;
-                            if (gj != gi) {
-                                double d = (double)di;
-                                if (HAS_EXTRA) {
-                                    for (int x = 0; x < n_extra; ++x) {
-                                        double diff = __dsub_rn(eq_r[x], ek_b[col * KNN_MAX_EXTRA + x]);
-                                        d = __dadd_rn(d, __dmul_rn(diff, diff));
-                                    }
-                                }
-                                sel.offer(d, (int)gj);
-                                thr_ll = (sel.thr_d == INFINITY) ? LLONG_MAX : (long long)sel.thr_d;
-                            }
-                        }
-                    }
-                }
-            }
+            scan_accumulator<HAS_EXTRA>(tmem_base + ((uint32_t)(32 * wq) << 16) + b * BN, valid, sqq, sqk_b, ek_b, eq_r, n_extra,
+                                        ncols, gi, k_off + k0, sel, thr_ll, selu);
             tc_fence_before_sync();
             mbar_arrive(&sm.tempty[b]);
         }
         if (valid) {
             double* od = part_d2 + ((int64_t)split * n_q + row) * k;
             int32_t* oi = part_idx + ((int64_t)split * n_q + row) * k;
+            if (!HAS_EXTRA) selu.sort();
             for (int t = 0; t < k; ++t) {
-                od[t] = sel.d(t);
-                oi[t] = sel.i(t);
+                od[t] = HAS_EXTRA ? sel.d(t) : selu.d(t);
+                oi[t] = HAS_EXTRA ? sel.i(t) : selu.i(t);
             }
         }
     }
     tc_fence_before_sync();
     __syncthreads();
     if (warp == 2) tmem_dealloc<512>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// CTA-pair version (tcgen05 cta_group::2): two CTAs on the two SMs of a TPC compute a 256-query x 256-key tile together.
+// Each CTA stages its own 128 query rows and only HALF of the key tile (128 rows); the pair's MMA reads both halves.
+// Per k-block a CTA therefore takes in 32 KB instead of 48 KB for the same 128 x 256 dot products -- the one-CTA kernel
+// is bound by exactly that stream (L2 -> SM ~ 8 TB/s, profiles/r01a) -- and the smaller stage buys a fourth ring slot.
+// The leader (cluster rank 0) issues every MMA; `full` / `tempty` live in the leader, `empty` / `tfull` in each CTA and
+// are signalled by multicast commits.  Each CTA's TMEM holds the accumulator rows of its own queries, so the epilogue
+// (distance + selection, one thread per query row) is the one-CTA epilogue unchanged.
+namespace {
+constexpr int B_HALF_BYTES = (BN / 2) * BKB, STAGE2_BYTES = A_BYTES + B_HALF_BYTES;
+constexpr int QGP = QG / 2;                               // query-tile PAIRS per raster group
+
+__host__ __device__ inline size_t smem_bytes2(int stages, int k, bool extra) {
+    return 1024 + (size_t)stages * STAGE2_BYTES + 128 + 2 * BN * sizeof(long long) +
+           (extra ? 2 * BN * KNN_MAX_EXTRA * sizeof(double) : 0) + (size_t)k * BM * (sizeof(double) + sizeof(int));
+}
+__device__ inline Smem carve2(uint8_t* raw, int stages, int k, bool extra) {
+    Smem s;
+    uint8_t* base = raw + ((1024 - (smem_u32(raw) & 1023)) & 1023);
+    s.tiles = base;
+    uint8_t* p = base + (size_t)stages * STAGE2_BYTES;
+    s.full = reinterpret_cast<uint64_t*>(p);
+    s.empty = s.full + MAX_STAGES;
+    s.tfull = s.empty + MAX_STAGES;
+    s.tempty = s.tfull + 2;
+    s.tmem_ptr = reinterpret_cast<uint32_t*>(s.tempty + 2);
+    p += 128;
+    s.sqk = reinterpret_cast<long long*>(p);
+    p += 2 * BN * sizeof(long long);
+    s.ek = reinterpret_cast<double*>(p);
+    if (extra) p += 2 * BN * KNN_MAX_EXTRA * sizeof(double);
+    s.list_d = reinterpret_cast<double*>(p);
+    s.list_i = reinterpret_cast<int*>(s.list_d + (size_t)k * BM);
+    return s;
+}
+}  // namespace
+
+template <bool HAS_EXTRA>
+__global__ void __launch_bounds__(256, 1)
+knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
+               const int64_t* __restrict__ sq_q, int64_t n_q, int64_t q_off,
+               const int64_t* __restrict__ sq_k, int64_t n_k, int64_t k_off, int64_t p,
+               const double* __restrict__ extra_q, const double* __restrict__ extra_k, int n_extra,
+               int k, int n_splits, int q_pairs, int stages, double* __restrict__ part_d2, int32_t* __restrict__ part_idx,
+               int ablate) {      // measurement only (results invalid): 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue work
+    extern __shared__ uint8_t smem_raw[];
+    const int warp = threadIdx.x >> 5;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+
+    const int pair = blockIdx.x >> 1;                           // cluster = 2 consecutive CTAs
+    const int per_group = QGP * n_splits;
+    const int group = pair / per_group, rem = pair % per_group;
+    const int q_pair = group * QGP + rem % QGP;
+    const int split = rem / QGP;
+    if (q_pair >= q_pairs) return;                              // both CTAs of the pair leave together
+    const int q_tile = 2 * q_pair + (int)rank;                  // may be one past the last tile: TMA zero-fills, rows are skipped
+
+    Smem sm = carve2(smem_raw, stages, k, HAS_EXTRA);
+    const int64_t n_ktiles = (n_k + BN - 1) / BN;
+    const int64_t kt_begin = n_ktiles * split / n_splits;
+    const int64_t kt_end = n_ktiles * (split + 1) / n_splits;
+    const int n_kb = (int)((p + BKB - 1) / BKB);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < stages; ++s) {
+            mbar_init(&sm.full[s], 2);                          // one arrival per CTA's producer (+ the bytes of both)
+            mbar_init(&sm.empty[s], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&sm.tfull[b], 1);
+            mbar_init(&sm.tempty[b], 2 * EPI_THREADS);          // the epilogue threads of both CTAs
+        }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc_pair<512>(sm.tmem_ptr);
+    tc_fence_before_sync();
+    cluster_sync_all();                                         // barriers and TMEM of both CTAs exist from here on
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *sm.tmem_ptr;
+
+    if (warp == 0) {
+        // ===================================================== TMA producer (both CTAs)
+        if (elect_one()) {
+            prefetch_tensormap(&map_q);
+            prefetch_tensormap(&map_k);
+            uint32_t it = 0;
+            for (int64_t kt = kt_begin; kt < kt_end; ++kt) {
+                for (int kb = 0; kb < n_kb; ++kb, ++it) {
+                    const int s = it % stages;
+                    const uint32_t ph = (it / stages) & 1;
+                    mbar_wait(&sm.empty[s], ph ^ 1);            // own slot freed by the pair's MMAs (multicast commit)
+                    const uint32_t full_leader = mapa_u32(smem_u32(&sm.full[s]), 0);
+                    if (ablate & 1) {
+                        mbar_arrive_cluster(full_leader);
+                        continue;
+                    }
+                    if (leader) mbar_arrive_expect_tx(&sm.full[s], 2 * STAGE2_BYTES);
+                    else        mbar_arrive_cluster(full_leader);
+                    uint8_t* a = sm.tiles + (size_t)s * STAGE2_BYTES;
+                    tma_load_2d_pair(a, &map_q, full_leader, kb * BKB, q_tile * BM);
+                    tma_load_2d_pair(a + A_BYTES, &map_k, full_leader, kb * BKB, (int32_t)(kt * BN + rank * (BN / 2)));
+                }
+            }
+        }
+    } else if (warp == 1 && leader) {
+        // ===================================================== MMA issuer (one thread of the leader CTA)
+        if (elect_one()) {
+            constexpr uint32_t idesc = make_idesc(/*S32*/ 2, /*int8*/ 1, 0, 0, 2 * BM, BN);
+            uint32_t it = 0, tile = 0;
+            for (int64_t kt = kt_begin; kt < kt_end; ++kt, ++tile) {
+                const uint32_t b = tile & 1, tph = (tile >> 1) & 1;
+                mbar_wait(&sm.tempty[b], tph ^ 1);              // both epilogues have drained this accumulator
+                tc_fence_after_sync();
+                const uint32_t d_tmem = tmem_base + b * BN;
+                for (int kb = 0; kb < n_kb; ++kb, ++it) {
+                    const int s = it % stages;
+                    const uint32_t ph = (it / stages) & 1;
+                    mbar_wait(&sm.full[s], ph);                 // the bytes of both CTAs have landed
+                    tc_fence_after_sync();
+                    const uint32_t a_addr = smem_u32(sm.tiles + (size_t)s * STAGE2_BYTES);
+                    const uint32_t b_addr = a_addr + A_BYTES;
+                    if (ablate & 2) {
+                        mbar_arrive(&sm.empty[s]);
+                        mbar_arrive_cluster(mapa_u32(smem_u32(&sm.empty[s]), 1));
+                        continue;
+                    }
+#pragma unroll
+                    for (int k4 = 0; k4 < BKB / 32; ++k4) {
+                        const uint64_t da = make_smem_desc(a_addr + k4 * 32, 16, 1024);
+                        const uint64_t db = make_smem_desc(b_addr + k4 * 32, 16, 1024);
+                        mma_i8_ss_pair(d_tmem, da, db, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+                    }
+                    tc_commit_pair(&sm.empty[s], 3);            // frees the slot in both CTAs
+                }
+                tc_commit_pair(&sm.tfull[b], 3);                // accumulator complete, both epilogues may read
+            }
+        }
+    } else if (warp >= 4) {
+        // ===================================================== epilogue: distances + selection (both CTAs, own rows)
+        const int e = threadIdx.x - 128;
+        const int wq = warp & 3;
+        const int64_t row = (int64_t)q_tile * BM + e;
+        const bool valid = row < n_q;
+        const int64_t gi = q_off + row;
+        RowSelector sel;
+        RowSelectorU64 selu;
+        if (HAS_EXTRA) sel.init(sm.list_d, sm.list_i, BM, e, k);
+        else           selu.init(sm.list_d, BM, e, k);
+        long long sqq = 0, thr_ll = LLONG_MAX;
+        double eq_r[KNN_MAX_EXTRA];
+        if (valid) {
+            sqq = sq_q[row];
+            if (HAS_EXTRA)
+                for (int c = 0; c < n_extra; ++c) eq_r[c] = extra_q[row * n_extra + c];
+        }
+        uint32_t tile = 0;
+        for (int64_t kt = kt_begin; kt < kt_end; ++kt, ++tile) {
+            const uint32_t b = tile & 1, tph = (tile >> 1) & 1;
+            const int64_t k0 = kt * BN;
+            long long* sqk_b = sm.sqk + b * BN;
+            double* ek_b = sm.ek + (size_t)b * BN * KNN_MAX_EXTRA;
+#pragma unroll
+            for (int t = e; t < BN; t += EPI_THREADS) {
+                const int64_t gk = k0 + t;
+                sqk_b[t] = (gk < n_k) ? sq_k[gk] : 0;
+                if (HAS_EXTRA)
+                    for (int c = 0; c < n_extra; ++c) ek_b[t * KNN_MAX_EXTRA + c] = (gk < n_k) ? extra_k[gk * n_extra + c] : 0.0;
+            }
+            named_bar_sync(1, EPI_THREADS);
+            mbar_wait(&sm.tfull[b], tph);
+            tc_fence_after_sync();
+            if (ablate & 4) {                                  // measurement only: no accumulator reads, no selection
+                if (leader) mbar_arrive(&sm.tempty[b]);
+                else        mbar_arrive_cluster(mapa_u32(smem_u32(&sm.tempty[b]), 0));
+                continue;
+            }
+            const int ncols = (int)((n_k - k0) < BN ? (n_k - k0) : BN);
+            scan_accumulator<HAS_EXTRA>(tmem_base + ((uint32_t)(32 * wq) << 16) + b * BN, valid, sqq, sqk_b, ek_b, eq_r, n_extra,
+                                        ncols, gi, k_off + k0, sel, thr_ll, selu);
+            tc_fence_before_sync();
+            if (leader) mbar_arrive(&sm.tempty[b]);
+            else        mbar_arrive_cluster(mapa_u32(smem_u32(&sm.tempty[b]), 0));
+        }
+        if (valid) {
+            double* od = part_d2 + ((int64_t)split * n_q + row) * k;
+            int32_t* oi = part_idx + ((int64_t)split * n_q + row) * k;
+            if (!HAS_EXTRA) selu.sort();
+            for (int t = 0; t < k; ++t) {
+                od[t] = HAS_EXTRA ? sel.d(t) : selu.d(t);
+                oi[t] = HAS_EXTRA ? sel.i(t) : selu.i(t);
+            }
+        }
+    }
+    tc_fence_before_sync();
+    cluster_sync_all();                                         // nobody leaves while the peer can still signal its barriers
+    if (warp == 2) tmem_dealloc_pair<512>(tmem_base);
 }
 
 bool knn_tc_supported(int64_t ldq, int64_t ldk, const void* Q, const void* K, int k) {
@@ -249,15 +471,57 @@ int knn_tc_launch(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q
                   const int8_t* K, int64_t ldk, const int64_t* sq_k, int64_t n_k, int64_t k_off, int64_t p,
                   const double* extra_q, const double* extra_k, int n_extra, int k, int n_splits,
                   double* part_d2, int32_t* part_idx, cudaStream_t stream) {
+    const int q_tiles = (int)((n_q + BM - 1) / BM);
+    static int use_pair = -1, ablate = 0;
+    if (use_pair < 0) {
+        const char* e = getenv("GNNB_KNN_PAIR");
+        use_pair = e ? atoi(e) : 1;
+        const char* a = getenv("GNNB_KNN_ABLATE");             // measurement only: 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue
+        ablate = a ? atoi(a) : 0;
+    }
+    const bool extra = n_extra > 0;
+    if (use_pair && q_tiles >= 2) {
+        // CTA pairs: 256 queries x 256 keys per pair, each CTA stages its 128 queries and one half of the key tile
+        CUtensorMap map_q, map_k;
+        int rc = make_tensor_map_2d(&map_q, Q, 1, (uint64_t)p, (uint64_t)n_q, (uint64_t)ldq, BKB, BM);
+        if (rc != GNNB_OK) return rc;
+        rc = make_tensor_map_2d(&map_k, K, 1, (uint64_t)p, (uint64_t)n_k, (uint64_t)ldk, BKB, BN / 2);
+        if (rc != GNNB_OK) return rc;
+        int stages = MAX_STAGES;
+        while (stages > 2 && smem_bytes2(stages, k, extra) > 232448) --stages;
+        const size_t smem = smem_bytes2(stages, k, extra);
+        const int q_pairs = (q_tiles + 1) / 2;
+        const int groups = (q_pairs + QGP - 1) / QGP;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(groups * QGP * n_splits * 2));
+        cfg.blockDim = dim3(256);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        if (extra) {
+            { static size_t hw_ = 0; if (smem > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_tc2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); hw_ = smem; } }
+            GNNB_CUDA(cudaLaunchKernelEx(&cfg, knn_tc2_kernel<true>, map_q, map_k, sq_q, n_q, q_off, sq_k, n_k, k_off, p, extra_q, extra_k,
+                                         n_extra, k, n_splits, q_pairs, stages, part_d2, part_idx, ablate));
+        } else {
+            { static size_t hw_ = 0; if (smem > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_tc2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); hw_ = smem; } }
+            GNNB_CUDA(cudaLaunchKernelEx(&cfg, knn_tc2_kernel<false>, map_q, map_k, sq_q, n_q, q_off, sq_k, n_k, k_off, p, extra_q, extra_k,
+                                         n_extra, k, n_splits, q_pairs, stages, part_d2, part_idx, ablate));
+        }
+        return GNNB_OK;
+    }
     CUtensorMap map_q, map_k;
     int rc = make_tensor_map_2d(&map_q, Q, 1, (uint64_t)p, (uint64_t)n_q, (uint64_t)ldq, BKB, BM);
     if (rc != GNNB_OK) return rc;
     rc = make_tensor_map_2d(&map_k, K, 1, (uint64_t)p, (uint64_t)n_k, (uint64_t)ldk, BKB, BN);
     if (rc != GNNB_OK) return rc;
     const int stages = k <= 32 ? 3 : 2;
-    const bool extra = n_extra > 0;
     const size_t smem = smem_bytes(stages, k, extra);
-    const int q_tiles = (int)((n_q + BM - 1) / BM);
     const int groups = (q_tiles + QG - 1) / QG;
     const unsigned grid = (unsigned)(groups * QG * n_splits);
     if (extra) {

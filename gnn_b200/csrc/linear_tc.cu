@@ -349,7 +349,20 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 // Thread = row of the tile = TMEM lane, so all four converter warps work on every k-block (a warp can only touch its
 // own 32 lanes).  The int8 staging tile uses the 64-byte TMA swizzle so that 32 rows can be read without bank conflicts.
 namespace {
-constexpr int TA_NX = 12, TA_NA = 8, TA_NB_MAX = 4;
+#ifndef TA_NX_
+#define TA_NX_ 6
+#endif
+#ifndef TA_NB_
+#define TA_NB_ 8
+#endif
+constexpr int TA_NX = TA_NX_, TA_NA = 8, TA_NB_MAX = TA_NB_;
+#ifndef TA_CW
+#define TA_CW 2
+#endif
+// Converter warps per TMEM lane quarter.  One warp needs ~600 cycles per k-block (two barrier waits, the shared-memory
+// reads, the int8 -> bf16 arithmetic, tcgen05.st and its wait, two arrivals -- one dependent chain), more than the
+// ~450 cycles of tensor work in a k-block at T = 2; TA_CW warps take k-blocks round-robin.
+constexpr int TA_THREADS = 128 + 128 * TA_CW;
 // One "full" and one "empty" barrier per k-block slot (ring of TA_NA): `full` collects the four converter warps AND the
 // TMA bytes of the term tiles, `empty` is one tcgen05.commit that both the converters and the term producer watch.
 // The MMA-issuing thread therefore pays one wait and one commit per k-block (a hop over an mbarrier costs ~230 cycles).
@@ -365,7 +378,7 @@ __host__ __device__ inline int ta_nb(int terms, int b_tile_bytes) {
 }  // namespace
 
 template <bool BWD>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(TA_THREADS, 1)
 linear_ta_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
                  int64_t k_total, int terms, int n_pad, int64_t b_term_rows,
                  float* __restrict__ out, int64_t ld_out, int64_t m_total, int n_valid) {
@@ -454,10 +467,10 @@ linear_ta_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         }
     } else if (warp >= 4) {
         // ===================================================== converter: int8 staging (smem) -> bf16 A slot (TMEM)
-        const int wq = warp & 3;
+        const int wq = warp & 3, turn = (warp - 4) >> 2;       // lane quarter; which k-blocks (u % TA_CW == turn) are this warp's
         const int r = 32 * wq + lane;                          // row of the tile == TMEM lane
         const uint32_t sw = (uint32_t)((r >> 1) & 3);          // 64-byte swizzle: 16-byte chunk index ^= (row / 2) % 4
-        for (int u = 0; u < n_kb; ++u) {
+        for (int u = turn; u < n_kb; u += TA_CW) {
             const int sx = u % TA_NX, sa = u % TA_NA;
             mbar_wait(&bars->x_full[sx], (u / TA_NX) & 1);
             mbar_wait(&bars->empty[sa], ((u / TA_NA) & 1) ^ 1);
@@ -507,7 +520,7 @@ linear_ta_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         tc_fence_after_sync();
         const int64_t m = m0 + r;
 #pragma unroll 1
-        for (int chunk = 0; chunk * 32 < n_pad; ++chunk) {
+        for (int chunk = turn; chunk * 32 < n_pad; chunk += TA_CW) {      // the warps of a lane quarter share the column chunks
             uint32_t a[32], b[32];
             const uint32_t taddr = tmem_base + ((uint32_t)(32 * wq) << 16) + chunk * 32;
             tmem_ld_32x32b_x32(taddr, a);
@@ -640,7 +653,10 @@ int linear_tc_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
     if (!x_is_i8 || !tc_shape_ok(X, ldx, h) || p < 64 || n < 1)
         return linear_simt_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, ws, ws_bytes, stream);    // small / float inputs: exact fp32 tiles
     // h is padded to a multiple of 32 so that a quarter of the term tile (a multicast slice) is whole 8-row swizzle atoms
-    const int64_t p_ld = (int64_t)align_up((size_t)p, 8), h_pad = (int64_t)align_up((size_t)h, 32);
+    static int use_ta = -1;
+    if (use_ta < 0) { const char* e = getenv("GNNB_LINEAR_TA"); use_ta = e ? atoi(e) : 1; }
+    // the TMEM-operand kernel pads h to the UMMA granule of 16 (h = 100 -> N = 2 x 112); the legacy kernel to 32
+    const int64_t p_ld = (int64_t)align_up((size_t)p, 8), h_pad = (int64_t)align_up((size_t)h, use_ta ? 16 : 32);
     const size_t need = linear_tc_workspace(n, p, h, terms);
     GNNB_REQUIRE(ws && ws_bytes >= need, GNNB_E_WORKSPACE, "linear_fwd: workspace %zu < %zu bytes", ws_bytes, need);
     uint8_t* wsb = reinterpret_cast<uint8_t*>(align_up((size_t)(uintptr_t)ws, 1024));
@@ -652,8 +668,6 @@ int linear_tc_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
         GNNB_LAUNCH_CHECK();
     }
     const int64_t tiles = (n + BM - 1) / BM;
-    static int use_ta = -1;
-    if (use_ta < 0) { const char* e = getenv("GNNB_LINEAR_TA"); use_ta = e ? atoi(e) : 1; }
     if (use_ta && h_pad <= 128) {
         // A operand in tensor memory (see linear_fwd_ta_kernel)
         CUtensorMap mx, mb;
@@ -664,7 +678,7 @@ int linear_tc_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
         const int btile = (int)(h_pad * BK * 2);
         const size_t smem_ta = ta_fixed() + (size_t)ta_nb(terms, btile) * terms * btile;
         { static size_t hw_ = 0; if ((size_t)(smem_ta) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(linear_ta_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem_ta))); hw_ = (size_t)(smem_ta); } }
-        linear_ta_kernel<false><<<(unsigned)tiles, 256, smem_ta, stream>>>(mx, mb, p, terms, (int)h_pad, h_pad, H, ldh, n, (int)h);
+        linear_ta_kernel<false><<<(unsigned)tiles, TA_THREADS, smem_ta, stream>>>(mx, mb, p, terms, (int)h_pad, h_pad, H, ldh, n, (int)h);
         GNNB_LAUNCH_CHECK();
         return GNNB_OK;
     }
@@ -706,7 +720,7 @@ int linear_tc_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t 
         const int btile = BK * 128 * 2;
         const size_t smem_ta = ta_fixed() + (size_t)ta_nb(terms, btile) * terms * btile;
         { static size_t hw_ = 0; if ((size_t)(smem_ta) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(linear_ta_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem_ta))); hw_ = (size_t)(smem_ta); } }
-        linear_ta_kernel<true><<<(unsigned)tiles, 256, smem_ta, stream>>>(mx, mb, n, terms, 128, n, dW, lddw, p, (int)h);
+        linear_ta_kernel<true><<<(unsigned)tiles, TA_THREADS, smem_ta, stream>>>(mx, mb, n, terms, 128, n, dW, lddw, p, (int)h);
         GNNB_LAUNCH_CHECK();
         return GNNB_OK;
     }
