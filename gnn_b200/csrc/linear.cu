@@ -125,6 +125,13 @@ int linear_tc_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
 int linear_tc_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
                     float* dW, int64_t lddw, int terms, void* ws, size_t ws_bytes, cudaStream_t stream);
 size_t linear_tc_workspace(int64_t n, int64_t p, int64_t h, int terms);
+// int8-limb implementation (linear_i8.cu), precision 4; shapes it does not take fall back to two bf16 terms
+bool linear_i8_supported(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, int64_t h);
+size_t linear_i8_workspace(int64_t n, int64_t p, int64_t h);
+int linear_i8_fwd(const int8_t* X, int64_t ldx, int64_t n, int64_t p, const float* W, int64_t ldw, int64_t h,
+                  float* H, int64_t ldh, void* ws, size_t ws_bytes, cudaStream_t stream);
+int linear_i8_bwd_w(const int8_t* X, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
+                    float* dW, int64_t lddw, void* ws, size_t ws_bytes, cudaStream_t stream);
 
 int linear_simt_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* W, int64_t ldw, int64_t h,
                     float* H, int64_t ldh, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
@@ -160,7 +167,7 @@ using namespace gnnb;
 extern "C" {
 
 int gnnb_linear_workspace_bytes(int64_t n, int64_t p, int64_t h, int precision, size_t* bytes) {
-    GNNB_REQUIRE(bytes && n >= 0 && p > 0 && h > 0 && precision >= 0 && precision <= 3, GNNB_E_BADARG,
+    GNNB_REQUIRE(bytes && n >= 0 && p > 0 && h > 0 && precision >= 0 && precision <= 4, GNNB_E_BADARG,
                  "linear_workspace_bytes: bad argument");
     size_t out_max = (size_t)h * (size_t)(p > n ? p : n);
     // split-K partials (fwd: n*h, bwd_w: h*p): at most 64 splits, and never more than ~2 waves of 64x64 tiles
@@ -169,7 +176,11 @@ int gnnb_linear_workspace_bytes(int64_t n, int64_t p, int64_t h, int precision, 
     if (max_splits > 64) max_splits = 64;
     if (max_splits < 1) max_splits = 1;
     size_t simt = max_splits * out_max * sizeof(float) + 256;
-    size_t tc = precision > 0 ? linear_tc_workspace(n, p, h, precision) : 0;
+    size_t tc = precision > 0 ? linear_tc_workspace(n, p, h, precision == 4 ? 2 : precision) : 0;
+    if (precision == 4) {
+        size_t i8 = linear_i8_workspace(n, p, h);
+        if (i8 > tc) tc = i8;
+    }
     *bytes = simt > tc ? simt : tc;
     return GNNB_OK;
 }
@@ -180,8 +191,13 @@ int gnnb_linear_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t 
     GNNB_ENTER();
     cudaStream_t stream = (cudaStream_t)stream_;
     GNNB_REQUIRE(X && W && H && n >= 0 && p > 0 && h > 0 && ldx >= p && ldw >= p && ldh >= h, GNNB_E_BADARG, "linear_fwd: bad argument");
-    GNNB_REQUIRE(precision >= 0 && precision <= 3, GNNB_E_BADARG, "linear_fwd: precision must be 0..3");
+    GNNB_REQUIRE(precision >= 0 && precision <= 4, GNNB_E_BADARG, "linear_fwd: precision must be 0..4");
     if (n == 0) return GNNB_OK;
+    if (precision == 4) {
+        if (linear_i8_supported(X, x_is_i8, ldx, n, p, h))
+            return linear_i8_fwd((const int8_t*)X, ldx, n, p, W, ldw, h, H, ldh, workspace, workspace_bytes, stream);
+        precision = 2;
+    }
     if (precision > 0) return linear_tc_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, precision, workspace, workspace_bytes, stream);
     return linear_simt_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, workspace, workspace_bytes, stream);
 }
@@ -192,10 +208,15 @@ int gnnb_linear_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_
     GNNB_ENTER();
     cudaStream_t stream = (cudaStream_t)stream_;
     GNNB_REQUIRE(X && dH && dW && n >= 0 && p > 0 && h > 0 && ldx >= p && lddh >= h && lddw >= p, GNNB_E_BADARG, "linear_bwd_w: bad argument");
-    GNNB_REQUIRE(precision >= 0 && precision <= 3, GNNB_E_BADARG, "linear_bwd_w: precision must be 0..3");
+    GNNB_REQUIRE(precision >= 0 && precision <= 4, GNNB_E_BADARG, "linear_bwd_w: precision must be 0..4");
     if (n == 0) {
         GNNB_CUDA(cudaMemset2DAsync(dW, lddw * sizeof(float), 0, p * sizeof(float), h, stream));
         return GNNB_OK;
+    }
+    if (precision == 4) {
+        if (linear_i8_supported(X, x_is_i8, ldx, n, p, h))
+            return linear_i8_bwd_w((const int8_t*)X, ldx, n, p, dH, lddh, h, dW, lddw, workspace, workspace_bytes, stream);
+        precision = 2;
     }
     if (precision > 0)
         return linear_tc_bwd_w(X, x_is_i8, ldx, n, p, dH, lddh, h, dW, lddw, precision, workspace, workspace_bytes, stream);

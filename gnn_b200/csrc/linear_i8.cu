@@ -1,0 +1,354 @@
+// K5 on the int8 tensor path (precision 4): H = X . W^T and dW = dH^T . X with X as int8 genotype codes.
+//
+// The float operand (W for the forward pass, dH for the weight gradient) is quantised per output feature to 21 bits and
+// split into three balanced base-128 digits ("limbs", each an int8 in [-64, 64]):
+//     w ~= s_f * (d0 + 128 d1 + 16384 d2),   s_f = max|w_f| / 2^20.
+// Three int8 MMAs (tcgen05 kind::i8, exact int32 accumulation) give the three digit sums; the epilogue combines them
+// as ONE exact 64-bit integer and rounds once: the result is the exact dot product of X with the quantised operand.
+// Against the split-bf16 kernels of linear_tc.cu: the 8-bit pipe retires ~2.5x the MACs per clock of the bf16 pipe on
+// B200 (scripts/ubench/mma_rate.cu: 7080 vs 2850 MAC/clk/SM), X goes from TMA straight into the MMA (no int8 -> bf16
+// converter, no TMEM staging), and 21 bits relative to the row maximum beat the 16 bits of two bf16 terms.
+//
+// Kernel = the CTA-pair pipeline of knn_tc.cu (cta_group::2): a pair owns 256 rows of the M side, each CTA stages its
+// own 128-row A tile and HALF of the limb tile; the leader issues, per 128-byte k-block, 4 x [N = 224 (digits 0, 1) +
+// N = 128 (digit 2)].
+//   forward : M = individuals (A = X tile, K-major),             K = markers,     B = W limbs    [352, p]  K-major
+//   backward: M = markers     (A = X tile read MN-major),        K = individuals, B = dH^T limbs [352, n]  K-major
+#include <math.h>
+
+#include "tc_common.cuh"
+
+namespace gnnb {
+
+using namespace tc;
+
+namespace {
+constexpr int BM = 128, BKB = 128;                       // A tile: 128 rows (or 128 markers) x 128 bytes of K
+constexpr int HP = 112;                                  // rows per digit for digits 0 and 1 (h <= 112)
+constexpr int N0 = 2 * HP, N1 = 128;                     // the two MMAs of a k-step
+constexpr int LIMB_ROWS = N0 + N1;                       // 352 rows of the limb matrix: [0,112) d0, [112,224) d1, [224,352) d2
+constexpr int A_BYTES = BM * BKB, B0_HALF = (N0 / 2) * BKB, B1_HALF = (N1 / 2) * BKB;
+constexpr int STAGE = A_BYTES + B0_HALF + B1_HALF;       // 38 KB
+constexpr int STAGES = 5;
+constexpr int ACC1_COL = 256;                            // TMEM column of the digit-2 accumulator
+
+struct Bars {
+    uint64_t full[STAGES], empty[STAGES], acc_full;
+    uint32_t tmem_ptr;
+};
+constexpr size_t SMEM = 1024 + (size_t)STAGES * STAGE + sizeof(Bars) + 64;
+
+// ---- quantisation -----------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void digits3(float w, float inv_scale, int8_t& d0, int8_t& d1, int8_t& d2) {
+    int q = __float2int_rn(w * inv_scale);               // |q| <= 2^20
+    int t0 = ((q + 64) & 127) - 64;                      // balanced digit in [-64, 63]
+    int q1 = (q - t0) >> 7;
+    int t1 = ((q1 + 64) & 127) - 64;
+    int q2 = (q1 - t1) >> 7;                             // in [-64, 64]
+    d0 = (int8_t)t0; d1 = (int8_t)t1; d2 = (int8_t)q2;
+}
+
+// amax_bits[r] = bits of max_c |in[r, c]|: grid (rows, chunks), one atomicMax per CTA (|x| >= 0 orders like its bit pattern)
+__global__ void row_absmax_kernel(const float* __restrict__ in, int64_t ld, int64_t cols, unsigned* __restrict__ amax_bits) {
+    const float* row = in + (int64_t)blockIdx.x * ld;
+    const int64_t per = (cols + gridDim.y - 1) / gridDim.y;
+    const int64_t c0 = (int64_t)blockIdx.y * per, c1 = c0 + per < cols ? c0 + per : cols;
+    float m = 0.f;
+    for (int64_t c = c0 + threadIdx.x; c < c1; c += blockDim.x) m = fmaxf(m, fabsf(row[c]));
+    __shared__ float red[32];
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        m = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (threadIdx.x == 0) atomicMax(&amax_bits[blockIdx.x], __float_as_uint(m));
+    }
+}
+
+// amax_bits[c] = bits of max_r |in[r, c]|  (backward: columns of dH); amax must be zeroed
+__global__ void col_absmax_kernel(const float* __restrict__ in, int64_t ld, int64_t rows, int cols, unsigned* __restrict__ amax_bits) {
+    const int c = threadIdx.x;
+    if (c >= cols) return;
+    const int64_t r0 = (int64_t)blockIdx.x * 64, r1 = r0 + 64 < rows ? r0 + 64 : rows;
+    float m = 0.f;
+    for (int64_t r = r0; r < r1; ++r) m = fmaxf(m, fabsf(in[r * ld + c]));
+    atomicMax(&amax_bits[c], __float_as_uint(m));
+}
+
+// limbs[(digit rows), c] of W[f, c].  One thread = 16 consecutive columns of one limb-matrix row triple (f, 112 + f, 224 + f):
+// four float4 loads, three 16-byte stores.  Rows f >= h (padding of the MMA N dimension) and columns >= cols are zeroed here,
+// so the workspace needs no separate clear.
+__global__ void quantize_rows_kernel(const float* __restrict__ W, int64_t ldw, int h, int64_t cols, const unsigned* __restrict__ amax_bits,
+                                     int8_t* __restrict__ limbs, int64_t ldl, float* __restrict__ scale) {
+    const int64_t groups = ldl / 16;                     // ldl is a multiple of 16
+    const int64_t total = (int64_t)N1 * groups;          // f runs over 0..127: rows [0,112) carry digits 0/1, [0,128) digit 2
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int f = (int)(i / groups);
+        const int64_t c0 = (i % groups) * 16;
+        __align__(16) int8_t d[3][16];
+        if (f < h) {
+            const float a = __uint_as_float(amax_bits[f]);
+            const float inv = a > 0.f ? 1048576.0f / a : 0.f;
+            const float* src = W + (int64_t)f * ldw + c0;
+            const bool vec = (c0 + 16 <= cols) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0);
+            float w[16];
+            if (vec) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float4 v = reinterpret_cast<const float4*>(src)[q];
+                    w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
+                }
+            } else {
+#pragma unroll
+                for (int q = 0; q < 16; ++q) w[q] = (c0 + q < cols) ? src[q] : 0.f;
+            }
+#pragma unroll
+            for (int q = 0; q < 16; ++q) digits3(w[q], inv, d[0][q], d[1][q], d[2][q]);
+            if (c0 == 0) scale[f] = a * (1.0f / 1048576.0f);
+        } else {
+#pragma unroll
+            for (int q = 0; q < 16; ++q) d[0][q] = d[1][q] = d[2][q] = 0;
+        }
+        if (f < HP) {
+            *reinterpret_cast<uint4*>(limbs + (int64_t)f * ldl + c0) = *reinterpret_cast<const uint4*>(d[0]);
+            *reinterpret_cast<uint4*>(limbs + (int64_t)(HP + f) * ldl + c0) = *reinterpret_cast<const uint4*>(d[1]);
+        }
+        *reinterpret_cast<uint4*>(limbs + (int64_t)(N0 + f) * ldl + c0) = *reinterpret_cast<const uint4*>(d[2]);
+    }
+}
+
+// limbs[(digit rows), r] of dH[r, f]: transposed through shared memory.  CTA = 128 rows x a quarter of the 128 limb-row
+// triples; a thread packs 4 consecutive rows of one triple into 32-bit stores (a warp writes 128 consecutive bytes).
+__global__ void quantize_cols_kernel(const float* __restrict__ dH, int64_t ld, int64_t rows, int h, const unsigned* __restrict__ amax_bits,
+                                     int8_t* __restrict__ limbs, int64_t ldl, float* __restrict__ scale) {
+    __shared__ float tile[128][33];                      // [row][feature of this quarter]
+    const int64_t r0 = (int64_t)blockIdx.x * 128;
+    const int f0 = blockIdx.y * 32;
+    for (int i = threadIdx.x; i < 128 * 32; i += blockDim.x) {
+        const int rr = i >> 5, ff = i & 31;
+        tile[rr][ff] = (r0 + rr < rows && f0 + ff < h) ? dH[(r0 + rr) * ld + f0 + ff] : 0.f;
+    }
+    __syncthreads();
+    // 256 threads: lane group of 32 covers 128 rows (4 each) of one feature; 8 features per pass
+    const int quad = threadIdx.x & 31, fsub = threadIdx.x >> 5;
+    for (int ff = fsub; ff < 32; ff += 8) {
+        const int f = f0 + ff;
+        const float a = f < h ? __uint_as_float(amax_bits[f]) : 0.f;
+        const float inv = a > 0.f ? 1048576.0f / a : 0.f;
+        __align__(4) int8_t d[3][4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) digits3(tile[4 * quad + q][ff], inv, d[0][q], d[1][q], d[2][q]);
+        const int64_t col = r0 + 4 * quad;               // ldl % 16 == 0 and r0 % 128 == 0: the 4-byte store stays inside the row
+        if (col < ldl) {
+            if (f < HP) {
+                *reinterpret_cast<uint32_t*>(limbs + (int64_t)f * ldl + col) = *reinterpret_cast<const uint32_t*>(d[0]);
+                *reinterpret_cast<uint32_t*>(limbs + (int64_t)(HP + f) * ldl + col) = *reinterpret_cast<const uint32_t*>(d[1]);
+            }
+            *reinterpret_cast<uint32_t*>(limbs + (int64_t)(N0 + f) * ldl + col) = *reinterpret_cast<const uint32_t*>(d[2]);
+        }
+        if (blockIdx.x == 0 && quad == 0 && f < h) scale[f] = a * (1.0f / 1048576.0f);
+    }
+}
+
+// ---- the pair GEMM ------------------------------------------------------------------------------------------------------
+template <bool BWD>
+__global__ void __launch_bounds__(256, 1)
+linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b0,
+                 const __grid_constant__ CUtensorMap map_b1, int64_t k_total, const float* __restrict__ scale,
+                 float* __restrict__ out, int64_t ld_out, int64_t m_total, int h,
+                 int ablate) {      // measurement only (results invalid): 1 = no TMA loads, 2 = no MMAs
+    extern __shared__ uint8_t smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    uint8_t* tiles = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);
+    Bars* bars = reinterpret_cast<Bars*>(tiles + (size_t)STAGES * STAGE);
+    const int n_kb = (int)((k_total + BKB - 1) / BKB);
+    const int64_t m0 = ((int64_t)(blockIdx.x >> 1) * 2 + rank) * BM;      // this CTA's rows of the M side (may lie past the end)
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&bars->full[s], 2); mbar_init(&bars->empty[s], 1); }
+        mbar_init(&bars->acc_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc_pair<512>(&bars->tmem_ptr);
+    tc_fence_before_sync();
+    cluster_sync_all();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = bars->tmem_ptr;
+
+    if (warp == 0) {
+        if (elect_one()) {                                             // TMA producer (both CTAs)
+            prefetch_tensormap(&map_x);
+            prefetch_tensormap(&map_b0);
+            prefetch_tensormap(&map_b1);
+            for (int u = 0; u < n_kb; ++u) {
+                const int s = u % STAGES;
+                mbar_wait(&bars->empty[s], ((u / STAGES) & 1) ^ 1);
+                const uint32_t full_leader = mapa_u32(smem_u32(&bars->full[s]), 0);
+                if (ablate & 1) { mbar_arrive_cluster(full_leader); continue; }
+                if (leader) mbar_arrive_expect_tx(&bars->full[s], 2 * STAGE);
+                else        mbar_arrive_cluster(full_leader);
+                uint8_t* a = tiles + (size_t)s * STAGE;
+                if (BWD) tma_load_2d_pair(a, &map_x, full_leader, (int32_t)m0, u * BKB);            // [128 k-rows x 128 markers]
+                else     tma_load_2d_pair(a, &map_x, full_leader, u * BKB, (int32_t)m0);            // [128 rows x 128 k]
+                tma_load_2d_pair(a + A_BYTES, &map_b0, full_leader, u * BKB, (int32_t)(rank * (N0 / 2)));
+                tma_load_2d_pair(a + A_BYTES + B0_HALF, &map_b1, full_leader, u * BKB, (int32_t)(N0 + rank * (N1 / 2)));
+            }
+        }
+    } else if (warp == 1 && leader) {
+        if (elect_one()) {                                             // MMA issuer (leader only)
+            constexpr uint32_t idesc0 = make_idesc(/*S32*/ 2, /*int8*/ 1, BWD ? 1 : 0, 0, 2 * BM, N0);
+            constexpr uint32_t idesc1 = make_idesc(/*S32*/ 2, /*int8*/ 1, BWD ? 1 : 0, 0, 2 * BM, N1);
+            for (int u = 0; u < n_kb; ++u) {
+                const int s = u % STAGES;
+                mbar_wait(&bars->full[s], (u / STAGES) & 1);
+                tc_fence_after_sync();
+                const uint32_t a_addr = smem_u32(tiles + (size_t)s * STAGE);
+                const uint32_t b0_addr = a_addr + A_BYTES, b1_addr = b0_addr + B0_HALF;
+                if (ablate & 2) {
+                    mbar_arrive(&bars->empty[s]);
+                    mbar_arrive_cluster(mapa_u32(smem_u32(&bars->empty[s]), 1));
+                    continue;
+                }
+#pragma unroll
+                for (int k4 = 0; k4 < BKB / 32; ++k4) {
+                    // K-major: 32 bytes further along the 128-byte swizzle row; MN-major (A of the backward pass): 32 k-rows =
+                    // four 8-row atoms of 1024 bytes further
+                    const uint64_t da = BWD ? make_smem_desc(a_addr + k4 * 4096, 16384, 1024) : make_smem_desc(a_addr + k4 * 32, 16, 1024);
+                    const uint64_t db0 = make_smem_desc(b0_addr + k4 * 32, 16, 1024);
+                    const uint64_t db1 = make_smem_desc(b1_addr + k4 * 32, 16, 1024);
+                    const uint32_t acc = (u > 0 || k4 > 0) ? 1u : 0u;
+                    mma_i8_ss_pair(tmem_base, da, db0, idesc0, acc);
+                    mma_i8_ss_pair(tmem_base + ACC1_COL, da, db1, idesc1, acc);
+                }
+                // a commit costs the tensor pipe a ~100-cycle bubble (scripts/ubench/mma_rate.cu): release slots two at a time
+                if ((u & 1) || u == n_kb - 1) {
+                    if (u & 1) tc_commit_pair(&bars->empty[(u - 1) % STAGES], 3);
+                    tc_commit_pair(&bars->empty[s], 3);
+                }
+            }
+            tc_commit_pair(&bars->acc_full, 3);
+        }
+    } else if (warp >= 4) {
+        // ===================================================== epilogue (both CTAs): three digit sums -> one rounding
+        const int wq = warp & 3;
+        const int64_t m = m0 + 32 * wq + lane;                         // row of the M side == TMEM lane
+        mbar_wait(&bars->acc_full, 0);
+        tc_fence_after_sync();
+        const uint32_t trow = tmem_base + ((uint32_t)(32 * wq) << 16);
+#pragma unroll 1
+        for (int c0 = 0; c0 < h; c0 += 32) {
+            uint32_t a0[32], a1[32], a2[32];
+            tmem_ld_32x32b_x32(trow + c0, a0);
+            tmem_ld_32x32b_x32(trow + HP + c0, a1);
+            tmem_ld_32x32b_x32(trow + ACC1_COL + c0, a2);
+            tmem_ld_wait();
+            if (m < m_total) {
+#pragma unroll
+                for (int c = 0; c < 32; ++c) {
+                    const int f = c0 + c;
+                    if (f < h) {
+                        const long long sum = (long long)(int)a0[c] + 128LL * (long long)(int)a1[c] + 16384LL * (long long)(int)a2[c];
+                        const float r = (float)((double)sum * (double)scale[f]);
+                        if (BWD) out[(int64_t)f * ld_out + m] = r;     // dW[f, marker]: a warp writes 32 consecutive markers
+                        else     out[m * ld_out + f] = r;              // H[row, f]
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before_sync();
+    cluster_sync_all();
+    if (warp == 2) tmem_dealloc_pair<512>(tmem_base);
+}
+
+template <bool BWD>
+int launch_i8(const CUtensorMap& mx, const CUtensorMap& mb0, const CUtensorMap& mb1, int64_t k_total, const float* scale, float* out,
+              int64_t ld_out, int64_t m_total, int h, cudaStream_t stream) {
+    const int64_t tiles = (m_total + BM - 1) / BM, pairs = (tiles + 1) / 2;
+    { static bool done = false; if (!done) { GNNB_CUDA(cudaFuncSetAttribute(linear_i8_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM)); done = true; } }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * pairs));
+    cfg.blockDim = dim3(256);
+    cfg.dynamicSmemBytes = SMEM;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    static int ablate = -1;
+    if (ablate < 0) { const char* e = getenv("GNNB_LINEAR_ABLATE"); ablate = e ? atoi(e) : 0; }      // measurement only
+    GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_i8_kernel<BWD>, mx, mb0, mb1, k_total, scale, out, ld_out, m_total, h, ablate));
+    return GNNB_OK;
+}
+}  // namespace
+
+static size_t limb_bytes(int64_t k_len) { return align_up((size_t)LIMB_ROWS * align_up((size_t)k_len, 16), 1024); }
+
+bool linear_i8_supported(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, int64_t h) {
+    return x_is_i8 && (uintptr_t)X % 16 == 0 && ldx % 16 == 0 && h >= 1 && h <= HP && n >= 128 && p >= 128;
+}
+
+size_t linear_i8_workspace(int64_t n, int64_t p, int64_t h) {
+    (void)h;
+    const size_t k_len = (size_t)(n > p ? n : p);
+    return limb_bytes((int64_t)k_len) + 4096 + 2048;      // limbs + (amax, scale) + alignment slack
+}
+
+int linear_i8_fwd(const int8_t* X, int64_t ldx, int64_t n, int64_t p, const float* W, int64_t ldw, int64_t h,
+                  float* H, int64_t ldh, void* ws, size_t ws_bytes, cudaStream_t stream) {
+    const size_t need = linear_i8_workspace(n, p, h);
+    GNNB_REQUIRE(ws && ws_bytes >= need, GNNB_E_WORKSPACE, "linear_fwd: workspace %zu < %zu bytes", ws_bytes, need);
+    uint8_t* wsb = reinterpret_cast<uint8_t*>(align_up((size_t)(uintptr_t)ws, 1024));
+    int8_t* limbs = reinterpret_cast<int8_t*>(wsb);
+    const int64_t ldl = (int64_t)align_up((size_t)p, 16);
+    unsigned* amax_bits = reinterpret_cast<unsigned*>(wsb + limb_bytes(p));
+    float* scale = reinterpret_cast<float*>(amax_bits + 512);
+    GNNB_CUDA(cudaMemsetAsync(amax_bits, 0, 512 * sizeof(unsigned), stream));
+    row_absmax_kernel<<<dim3((unsigned)h, 16), 256, 0, stream>>>(W, ldw, p, amax_bits);
+    GNNB_LAUNCH_CHECK();
+    {
+        int64_t total = (int64_t)N1 * (ldl / 16), blocks = (total + 255) / 256, cap = (int64_t)sm_count() * 16;
+        quantize_rows_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, stream>>>(W, ldw, (int)h, p, amax_bits, limbs, ldl, scale);
+        GNNB_LAUNCH_CHECK();
+    }
+    CUtensorMap mx, mb0, mb1;
+    int rc = make_tensor_map_2d(&mx, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, BKB, BM);
+    if (rc != GNNB_OK) return rc;
+    rc = make_tensor_map_2d(&mb0, limbs, 1, (uint64_t)p, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N0 / 2);
+    if (rc != GNNB_OK) return rc;
+    rc = make_tensor_map_2d(&mb1, limbs, 1, (uint64_t)p, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N1 / 2);
+    if (rc != GNNB_OK) return rc;
+    return launch_i8<false>(mx, mb0, mb1, p, scale, H, ldh, n, (int)h, stream);
+}
+
+int linear_i8_bwd_w(const int8_t* X, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
+                    float* dW, int64_t lddw, void* ws, size_t ws_bytes, cudaStream_t stream) {
+    const size_t need = linear_i8_workspace(n, p, h);
+    GNNB_REQUIRE(ws && ws_bytes >= need, GNNB_E_WORKSPACE, "linear_bwd_w: workspace %zu < %zu bytes", ws_bytes, need);
+    uint8_t* wsb = reinterpret_cast<uint8_t*>(align_up((size_t)(uintptr_t)ws, 1024));
+    int8_t* limbs = reinterpret_cast<int8_t*>(wsb);
+    const int64_t ldl = (int64_t)align_up((size_t)n, 16);
+    unsigned* amax_bits = reinterpret_cast<unsigned*>(wsb + limb_bytes(n));
+    float* scale = reinterpret_cast<float*>(amax_bits + 512);
+    GNNB_CUDA(cudaMemsetAsync(amax_bits, 0, 512 * sizeof(unsigned), stream));
+    col_absmax_kernel<<<(unsigned)((n + 63) / 64), 128, 0, stream>>>(dH, lddh, n, (int)h, amax_bits);
+    GNNB_LAUNCH_CHECK();
+    quantize_cols_kernel<<<dim3((unsigned)((ldl + 127) / 128), 4), 256, 0, stream>>>(dH, lddh, n, (int)h, amax_bits, limbs, ldl, scale);
+    GNNB_LAUNCH_CHECK();
+    CUtensorMap mx, mb0, mb1;
+    int rc = make_tensor_map_2d(&mx, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, 128, BKB);       // box: 128 markers x 128 individuals
+    if (rc != GNNB_OK) return rc;
+    rc = make_tensor_map_2d(&mb0, limbs, 1, (uint64_t)n, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N0 / 2);
+    if (rc != GNNB_OK) return rc;
+    rc = make_tensor_map_2d(&mb1, limbs, 1, (uint64_t)n, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N1 / 2);
+    if (rc != GNNB_OK) return rc;
+    return launch_i8<true>(mx, mb0, mb1, n, scale, dW, lddw, p, (int)h, stream);
+}
+
+}  // namespace gnnb

@@ -433,8 +433,8 @@ def spmm(rowptr, col, val, H, bias=None, n=None, hub=None):
 # --------------------------------------------------------------------------------------- K5
 def _precision(n, p, h, x_is_i8):
     prec = config["linear_precision"]
-    if prec == "auto":          # int8 genotypes: tcgen05 with a 2-term bf16 split (rel. error ~1e-5); float x: fp32 tiles
-        return 2 if x_is_i8 else 0
+    if prec == "auto":          # int8 genotypes: int8 tensor cores, float operand as three 7-bit digits (rel. error ~1e-6;
+        return 4 if x_is_i8 else 0      # shapes that path does not take fall back to two bf16 terms); float x: fp32 tiles
     return int(prec)
 
 

@@ -165,10 +165,13 @@ int gnnb_spmm_workspace_bytes(int64_t n_hub_tasks, int64_t F, size_t* bytes);
  *   fwd   : H [n, h]  = X [n, p] . W [h, p]^T
  *   bwd_w : dW [h, p] = dH [n, h]^T . X [n, p]
  *   bwd_x : dX [n, p] = dH [n, h] . W [h, p]                      (inner layers only)
- * X is either int8 genotype codes in [0, 127] (x_is_i8 = 1) or float32.
+ * X is either int8 genotype codes (x_is_i8 = 1; [0, 127] for precision 1..3, any int8 for 0 and 4) or float32.
  * precision: 0 = fp32 CUDA-core tiles (exact reference arithmetic),
  *            1 / 2 / 3 = tcgen05 bf16 tensor-core tiles with the fp32 operand split into that many
- *            bf16 terms (3 ~ fp32-exact for integer-coded X; 1 = plain bf16 projection), fp32 accumulate.
+ *            bf16 terms (3 ~ fp32-exact for integer-coded X; 1 = plain bf16 projection), fp32 accumulate;
+ *            4 = int8 tensor cores (int8 X only, n >= 128, p >= 128, h <= 112; other shapes run as 2): the float
+ *            operand is quantised per output feature to 21 bits and split into three int8 digits, the three
+ *            exact int32 digit sums are combined as one 64-bit integer and rounded once (rel. error ~1e-6).
  */
 int gnnb_linear_workspace_bytes(int64_t n, int64_t p, int64_t h, int precision, size_t* bytes);
 int gnnb_linear_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,

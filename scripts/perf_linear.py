@@ -18,7 +18,7 @@ W = torch.randn(h, p, device="cuda") * 0.01
 dH = torch.randn(n, h, device="cuda")
 ref_f = X.float() @ W.t()
 ref_b = dH.t() @ X.float()
-for prec in (1, 2, 3):
+for prec in (2, 4):
     ms_f = timeit(lambda: ops.linear_fwd(X, W, precision=prec))
     ms_b = timeit(lambda: ops.linear_bwd_w(X, dH, precision=prec))
     ef = float((ops.linear_fwd(X, W, precision=prec) - ref_f).abs().max() / ref_f.abs().max())

@@ -132,6 +132,39 @@ def test_linear_tensor_core_path(n, p, h, terms, tol):
     assert rel_err(ops.linear_bwd_w(buf[:, :p], dH, precision=3), dH.double().t() @ Xg.double()) < 3e-5
 
 
+@pytest.mark.parametrize("n,p,h", [(128, 128, 16), (479, 1279, 100), (1000, 4096, 100), (129, 200, 7), (4000, 512, 32),
+                                   (700, 130, 112), (15625 // 4, 5000, 100)])
+def test_linear_int8_limb_path(n, p, h):
+    """precision 4: the float operand as three int8 digits per feature (21 bits), exact int32 tensor-core sums, one rounding."""
+    X = synth.genotypes(n, p, seed=n + p)
+    buf = torch.zeros((n, (p + 15) // 16 * 16), dtype=torch.int8, device=DEV)
+    buf[:, :p] = torch.from_numpy(X).to(DEV)
+    Xd = buf[:, :p]
+    g = torch.Generator(device="cpu").manual_seed(n + 1)
+    W = (torch.randn(h, p, generator=g) * 0.05).to(DEV)
+    W[0] *= 1e-3                                         # a feature on a very different scale: the scale is per feature
+    W[-1, ::2] = 0.0
+    dH = torch.randn(n, h, generator=g).to(DEV)
+    dH[:, 0] *= 1e4
+    Xf = Xd.double()
+    fwd = ops.linear_fwd(Xd, W, precision=4)
+    bwd = ops.linear_bwd_w(Xd, dH, precision=4)
+    torch.cuda.synchronize()
+    ref_f, ref_b = Xf @ W.double().t(), dH.double().t() @ Xf
+    # per output feature: the error is relative to that feature's own magnitude
+    for f in range(h):
+        assert rel_err(fwd[:, f], ref_f[:, f]) < 3e-6, ("fwd", f)
+        assert rel_err(bwd[f], ref_b[f]) < 3e-6, ("bwd", f)
+    # shapes the int8 kernels do not take fall back to two bf16 terms
+    W2 = torch.randn(120, p, device=DEV) * 0.05
+    assert rel_err(ops.linear_fwd(Xd, W2, precision=4), Xf @ W2.double().t()) < 6e-5
+    # any int8 code, negative ones included
+    Xg = torch.randint(-128, 128, (n, p), dtype=torch.int8, device=DEV)
+    buf[:, :p] = Xg
+    assert rel_err(ops.linear_fwd(buf[:, :p], W, precision=4), Xg.double() @ W.double().t()) < 3e-6
+    assert rel_err(ops.linear_bwd_w(buf[:, :p], dH, precision=4), dH.double().t() @ Xg.double()) < 3e-6
+
+
 @pytest.mark.parametrize("F", [4, 100, 256])
 def test_spmm_hub_rows_planned_and_unplanned(F):
     """A graph with hubs (rows of 300 .. 5000 entries): the planned path (tasks + last-arriver reduction) and the
