@@ -12,8 +12,14 @@
 
 namespace gnnb {
 
-constexpr int GATHER_UNROLL = 4;
-constexpr int LONG_ROW = 256;       // rows with more entries than this (hubs of the kNN graph) get a whole CTA
+#ifndef GATHER_UNROLL_
+#define GATHER_UNROLL_ 8
+#endif
+#ifndef LONG_ROW_
+#define LONG_ROW_ 64
+#endif
+constexpr int GATHER_UNROLL = GATHER_UNROLL_;
+constexpr int LONG_ROW = LONG_ROW_;       // rows with more entries than this (hubs of the kNN graph) get a whole CTA
 
 __device__ __forceinline__ float4 ld_row4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 
