@@ -335,6 +335,18 @@ def run_ours(a):
             roofline = {"kernel": name, "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                         "traffic": None}
         roofline["peak_source"] = "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)"
+        try:    # DRAM bytes per launch of this kernel from the committed ncu capture (same shape as a training subgraph)
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json"))).get(name)
+            if tr and tr["shape"][:2] == [per, p]:
+                roofline["traffic"] = tr["dram_bytes"]
+                roofline["traffic_source"] = "profiles/r01_traffic.json (" + tr["kernel"] + ", ncu --set full)"
+        except Exception:
+            pass
+        if name.startswith("gnnb_linear"):
+            roofline["note"] = ("the projection runs on the int8 tensor pipe (three 7-bit digits of the float operand, 3 x the "
+                                "algorithmic MACs issued); `achieved` counts the algorithmic 2*n*p*h against the measured bf16 peak; "
+                                "as an HBM stream it moves n*p int8 bytes per launch: "
+                                f"{st['bytes'] / st['calls'] / (avg_ms * 1e-3) / 1e9:.0f} GB/s of {peaks.get('hbm_gbs', 6650.0):.0f}")
         roofline["avg_launch_ms"] = avg_ms
         roofline["share_of_step"] = st["ms"] / (ms_per_epoch * prof_steps)
         roofline["by_kernel_ms_per_epoch"] = {k2: v["ms"] / prof_steps for k2, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}
@@ -344,10 +356,12 @@ def run_ours(a):
         if agg:
             roofline["aggregation_gbs"] = agg["bytes"] / (agg["ms"] * 1e-3) / 1e9
             roofline["aggregation_frac_of_hbm"] = roofline["aggregation_gbs"] / peaks.get("hbm_gbs", 6650.0)
+            roofline["aggregation_note"] = ("algorithmic AGG_BYTES (SURVEY 8d: every edge's neighbour row counted, no cache credit) / time; "
+                                            "the gathered matrix fits L2, ncu shows ~14 MB of DRAM traffic per launch (L2-assisted)")
     line = {
         "metric": "train epochs/sec", "value": 1000.0 / ms_per_epoch, "unit": "epochs/s", "n_gpus": world, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": ms_per_epoch, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "f32 (int8 genotypes; bf16-split tensor-core projection when precision > 0)", "data": "synthetic",
+        "dtype": "f32 (int8 genotypes; marker projection on int8 tensor cores with the float operand quantised to 21 bits per feature)", "data": "synthetic",
         "config": {"workload": f"C5: synthetic {N} individuals x {p} SNPs, k={k} kNN Laplacian graphs, {B} subgraph batches of "
                                f"{per} (split_dataset), test graph {test_hi - test_lo} nodes, create_network_two_no_conv_dropout "
                                f"hidden {a.hidden} dropout {DROPOUT:.4f}, Adam",
