@@ -451,6 +451,11 @@ def run_reference(a):
 
 def main():
     a = parse()
+    # stdout carries exactly ONE line, the JSON result: anything a library prints (NCCL's version banner at N > 1, ...)
+    # is sent to stderr by pointing fd 1 at fd 2 for the duration of the run
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     if a.impl == "reference":
         line = run_reference(a)
     else:
@@ -458,8 +463,9 @@ def main():
         if line is not None and not a.no_cpu_baseline and line["n_gpus"] == 1:
             v, desc, cores = cpu_epoch_rate(a, a.cpu_sample)
             line["cpu_baseline"] = {"value": v, "unit": "epochs/s", "cores": cores, "kind": "port", "sample": desc}
+    sys.stdout.flush()
     if line is not None:
-        print(json.dumps(line), flush=True)
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
     try:
         import torch.distributed as dist
         if dist.is_initialized():

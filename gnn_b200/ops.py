@@ -408,14 +408,16 @@ def clear_graph_cache():
 
 
 # --------------------------------------------------------------------------------------- K6 / K7
-def spmm(rowptr, col, val, H, bias=None, n=None, hub=None):
-    """out[i] = sum_e val[e] * H[col[e]] (+ bias) over CSR row i.  ``hub``: optional task plan from ``hub_plan``."""
+def spmm(rowptr, col, val, H, bias=None, n=None, hub=None, nnz=None):
+    """out[i] = sum_e val[e] * H[col[e]] (+ bias) over CSR row i.  ``hub``: optional task plan from ``hub_plan``.
+    ``rowptr`` may be a slice of a larger row pointer (its offsets stay absolute): the rows of one shard; ``nnz`` then
+    states the shard's entry count for the work accounting."""
     _need_cuda(rowptr, H)
     if H.dtype != torch.float32 or H.stride(1) != 1:
         H = H.to(torch.float32).contiguous()
     n = rowptr.numel() - 1 if n is None else n
     out = torch.empty((n, H.shape[1]), dtype=torch.float32, device=H.device)
-    nnz = int(col.numel())
+    nnz = int(col.numel()) if nnz is None else int(nnz)
     F = int(H.shape[1])
     _declare(bytes=float(nnz * (F * 4 + 8) + n * F * 4 + (n + 1) * 4 + n * 4 + F * 4))    # AGG_BYTES, SURVEY.md 8d
     with torch.cuda.device(H.device):

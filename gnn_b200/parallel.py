@@ -98,9 +98,26 @@ def dp_step(model, flat, optimizer, batch, world, loss_func, args_of):
     return loss.detach()
 
 
+_shard_plans = {}
+
+
+def _row_plan(g, lo, hi):
+    """The CSR rows [lo, hi) of a cached GcnGraph as their own row pointer (offsets stay absolute) + hub-row plan."""
+    from . import ops
+    key = (g.rowptr.data_ptr(), lo, hi)
+    plan = _shard_plans.get(key)
+    if plan is None:
+        rp = g.rowptr[lo:hi + 1].contiguous()
+        nnz = int(rp[-1] - rp[0]) if hi > lo else 0
+        plan = _shard_plans[key] = (rp, ops.hub_plan(rp) if hi > lo else None, nnz, g.rowptr)   # g.rowptr: keeps the key's address alive
+    return plan[0], plan[1], plan[2]
+
+
 @torch.no_grad()
 def sharded_eval(model, data, rank, world, args_of):
-    """Eval-mode forward on the test graph with the first layer's projection sharded by rows."""
+    """Eval-mode forward on the test graph with every GCN layer sharded by node rows: rank r projects and aggregates the
+    rows [lo_r, hi_r) only (each output row is one rank's complete, deterministic sum) and the [n, h] activations are
+    all-gathered where the next aggregation needs every neighbour's row.  Row-wise modules run on the local rows."""
     from . import ops
     from .networks.gcn_conv import GCNConv
     model.eval()
@@ -112,17 +129,18 @@ def sharded_eval(model, data, rank, world, args_of):
     edge_weight = args[2] if len(args) > 2 else None
     n = x.shape[0]
     lo, hi = row_shard(n, rank, world)
-    h_local = ops.linear_fwd(x[lo:hi], first.lin.weight)
-    h = allgather_rows(h_local, n, rank, world)
-    g = ops.gcn_graph(edge_index, edge_weight, n, first.add_self_loops)
-    out = ops.spmm(g.rowptr, g.col, g.val, h, first.bias, n=n, hub=g.hub)
-    for m, f, (ins, _) in list(zip(model.nns, model.fns, model.descs))[1:]:
-        call = m if f is None else f
-        if isinstance(m, GCNConv):
-            out = call(out, edge_index, edge_weight) if edge_weight is not None else call(out, edge_index)
+    cur = x[lo:hi]
+    for m, f in zip(model.nns, model.fns):
+        if f is not None:
+            cur = f(cur)
+        elif isinstance(m, GCNConv):
+            h = allgather_rows(ops.linear_fwd(cur, m.lin.weight), n, rank, world)
+            g = ops.gcn_graph(edge_index, edge_weight, n, m.add_self_loops)
+            rp, hub, nnz = _row_plan(g, lo, hi)
+            cur = ops.spmm(rp, g.col, g.val, h, m.bias, n=hi - lo, hub=hub, nnz=nnz)
         else:
-            out = call(out)
-    return out
+            cur = m(cur)
+    return allgather_rows(cur, n, rank, world)
 
 
 def knn_sharded(X_local, row0, n_total, k, rank, world, extra_local=None):
