@@ -174,6 +174,7 @@ def run_ours(a):
         with torch.cuda.stream(side):
             for g in batches[:2]:                                    # warm-up outside capture (allocator, NCCL, autograd)
                 parallel.dp_step(model, flat, opt, g, world, loss_func, get_args_tuple)
+            loss_func(parallel.sharded_eval(model, test, rank, world, get_args_tuple), test.y)
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         for i, g in enumerate(batches):
@@ -181,6 +182,10 @@ def run_ours(a):
             with torch.cuda.graph(cg, pool=pool):
                 loss = parallel.dp_step(model, flat, opt, g, world, loss_func, get_args_tuple)
             graphed[i] = (cg, loss)
+        cg = torch.cuda.CUDAGraph()                                  # the eval forward on the test graph (row-sharded, all-gathers)
+        with torch.cuda.graph(cg, pool=pool):
+            test_loss = loss_func(parallel.sharded_eval(model, test, rank, world, get_args_tuple), test.y)
+        graphed["eval"] = (cg, test_loss)
 
     use_graphs = False
     if a.cuda_graph != "off":
@@ -207,8 +212,12 @@ def run_ours(a):
                 losses.append(loss)
             else:
                 losses.append(parallel.dp_step(model, flat, opt, g, world, loss_func, get_args_tuple))
-        out_test = parallel.sharded_eval(model, test, rank, world, get_args_tuple)
-        test_loss = loss_func(out_test, test.y)
+        if use_graphs and not eager:
+            cg, test_loss = graphed["eval"]
+            cg.replay()
+        else:
+            out_test = parallel.sharded_eval(model, test, rank, world, get_args_tuple)
+            test_loss = loss_func(out_test, test.y)
         return torch.stack(losses + [test_loss])
 
     def barrier():
