@@ -314,8 +314,12 @@ def run_ours(a):
         for _ in range(max(1, min(a.warmup, 1))):
             epoch_e2e()
         ms_e2e, _ = timed(epoch_e2e, max(1, min(a.steps, 2)))
-        e2e = {"value": 1000.0 / ms_e2e, "unit": "epochs/s", "h2d_bytes_per_step": int(h2d * len(host)),
-               "d2h_bytes_per_step": 4 * (len(host) + 1),
+        moved = torch.tensor([float(sum(sum(t.numel() * t.element_size() for t in hb) for hb in host)), 4.0 * (len(host) + 1)],
+                             dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(moved)                                       # whole job: every rank copies its own subgraphs
+        e2e = {"value": 1000.0 / ms_e2e, "unit": "epochs/s", "h2d_bytes_per_step": int(moved[0]),
+               "d2h_bytes_per_step": int(moved[1]),
                "host_format": "2-bit packed genotypes (4 codes per byte), expanded to int8 on the device" if packed else "int8 genotypes",
                "note": "per epoch: every owned subgraph's genotypes + edge list + weights + phenotypes H2D from pinned "
                        "memory (prefetched one subgraph ahead on a copy stream), gcn_norm/CSR rebuilt per step, loss D2H per step"}
