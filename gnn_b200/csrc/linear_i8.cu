@@ -11,7 +11,10 @@
 //
 // Kernel = the CTA-pair pipeline of knn_tc.cu (cta_group::2): a pair owns 256 rows of the M side, each CTA stages its
 // own 128-row A tile and HALF of the limb tile; the leader issues, per 128-byte k-block, 4 x [N = 224 (digits 0, 1) +
-// N = 128 (digit 2)].
+// N = 128 (digit 2)].  The kernel is bound by the L2 -> SM operand stream, and the limb tile is the same for every pair:
+// clusters of 4 (two pairs, GNNB_LINEAR_QUAD, default on) fetch each limb half-tile once -- each of the two CTAs that
+// need it issues half of it as a TMA multicast to both -- and run the two pairs in lockstep per ring slot (the slot's
+// `empty` barrier collects the commits of both leaders).  Measured 0.240 -> 0.226 ms forward, 0.245 -> 0.224 backward.
 //   forward : M = individuals (A = X tile, K-major),             K = markers,     B = W limbs    [352, p]  K-major
 //   backward: M = markers     (A = X tile read MN-major),        K = individuals, B = dH^T limbs [352, n]  K-major
 #include <math.h>
@@ -157,18 +160,23 @@ __global__ void __launch_bounds__(256, 1)
 linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b0,
                  const __grid_constant__ CUtensorMap map_b1, int64_t k_total, const float* __restrict__ scale,
                  float* __restrict__ out, int64_t ld_out, int64_t m_total, int h,
+                 int quad,          // 1: clusters of 4 = two pairs; each digit half-tile is fetched once and multicast to both pairs
+                                    //    (map_b0 / map_b1 then have boxes of 56 / 32 rows instead of 112 / 64)
                  int ablate) {      // measurement only (results invalid): 1 = no TMA loads, 2 = no MMAs
     extern __shared__ uint8_t smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t rank = cluster_ctarank();
+    const uint32_t crank = cluster_ctarank();                          // 0..1, or 0..3 in quad mode
+    const uint32_t rank = crank & 1, lead_rank = crank & ~1u;          // position inside the pair; cluster rank of the pair's leader
+    const uint32_t twin = crank >> 1;                                  // which of the two pairs (quad mode)
     const bool leader = rank == 0;
+    const uint16_t pair_mask = (uint16_t)(3u << lead_rank), all_mask = quad ? 15 : 3;
     uint8_t* tiles = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);
     Bars* bars = reinterpret_cast<Bars*>(tiles + (size_t)STAGES * STAGE);
     const int n_kb = (int)((k_total + BKB - 1) / BKB);
     const int64_t m0 = ((int64_t)(blockIdx.x >> 1) * 2 + rank) * BM;      // this CTA's rows of the M side (may lie past the end)
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; ++s) { mbar_init(&bars->full[s], 2); mbar_init(&bars->empty[s], 1); }
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&bars->full[s], 2); mbar_init(&bars->empty[s], quad ? 2 : 1); }
         mbar_init(&bars->acc_full, 1);
         fence_barrier_init();
     }
@@ -186,15 +194,24 @@ linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             for (int u = 0; u < n_kb; ++u) {
                 const int s = u % STAGES;
                 mbar_wait(&bars->empty[s], ((u / STAGES) & 1) ^ 1);
-                const uint32_t full_leader = mapa_u32(smem_u32(&bars->full[s]), 0);
+                const uint32_t full_leader = mapa_u32(smem_u32(&bars->full[s]), lead_rank);
                 if (ablate & 1) { mbar_arrive_cluster(full_leader); continue; }
                 if (leader) mbar_arrive_expect_tx(&bars->full[s], 2 * STAGE);
                 else        mbar_arrive_cluster(full_leader);
                 uint8_t* a = tiles + (size_t)s * STAGE;
                 if (BWD) tma_load_2d_pair(a, &map_x, full_leader, (int32_t)m0, u * BKB);            // [128 k-rows x 128 markers]
                 else     tma_load_2d_pair(a, &map_x, full_leader, u * BKB, (int32_t)m0);            // [128 rows x 128 k]
-                tma_load_2d_pair(a + A_BYTES, &map_b0, full_leader, u * BKB, (int32_t)(rank * (N0 / 2)));
-                tma_load_2d_pair(a + A_BYTES + B0_HALF, &map_b1, full_leader, u * BKB, (int32_t)(N0 + rank * (N1 / 2)));
+                if (quad) {
+                    // this CTA fetches half of the digit rows its pair position needs and delivers them to both pairs
+                    const uint16_t mc = (uint16_t)((1u << rank) | (1u << (rank + 2)));
+                    tma_load_2d_pair_multicast(a + A_BYTES + twin * (B0_HALF / 2), &map_b0, &bars->full[s], u * BKB,
+                                               (int32_t)(rank * (N0 / 2) + twin * (N0 / 4)), mc);
+                    tma_load_2d_pair_multicast(a + A_BYTES + B0_HALF + twin * (B1_HALF / 2), &map_b1, &bars->full[s], u * BKB,
+                                               (int32_t)(N0 + rank * (N1 / 2) + twin * (N1 / 4)), mc);
+                } else {
+                    tma_load_2d_pair(a + A_BYTES, &map_b0, full_leader, u * BKB, (int32_t)(rank * (N0 / 2)));
+                    tma_load_2d_pair(a + A_BYTES + B0_HALF, &map_b1, full_leader, u * BKB, (int32_t)(N0 + rank * (N1 / 2)));
+                }
             }
         }
     } else if (warp == 1 && leader) {
@@ -208,8 +225,7 @@ linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 const uint32_t a_addr = smem_u32(tiles + (size_t)s * STAGE);
                 const uint32_t b0_addr = a_addr + A_BYTES, b1_addr = b0_addr + B0_HALF;
                 if (ablate & 2) {
-                    mbar_arrive(&bars->empty[s]);
-                    mbar_arrive_cluster(mapa_u32(smem_u32(&bars->empty[s]), 1));
+                    for (uint32_t c = 0; c < (quad ? 4u : 2u); ++c) mbar_arrive_cluster(mapa_u32(smem_u32(&bars->empty[s]), c));
                     continue;
                 }
 #pragma unroll
@@ -225,11 +241,11 @@ linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 }
                 // a commit costs the tensor pipe a ~100-cycle bubble (scripts/ubench/mma_rate.cu): release slots two at a time
                 if ((u & 1) || u == n_kb - 1) {
-                    if (u & 1) tc_commit_pair(&bars->empty[(u - 1) % STAGES], 3);
-                    tc_commit_pair(&bars->empty[s], 3);
+                    if (u & 1) tc_commit_pair(&bars->empty[(u - 1) % STAGES], all_mask);
+                    tc_commit_pair(&bars->empty[s], all_mask);
                 }
             }
-            tc_commit_pair(&bars->acc_full, 3);
+            tc_commit_pair(&bars->acc_full, pair_mask);
         }
     } else if (warp >= 4) {
         // ===================================================== epilogue (both CTAs): three digit sums -> one rounding
@@ -268,26 +284,34 @@ template <bool BWD>
 int launch_i8(const CUtensorMap& mx, const CUtensorMap& mb0, const CUtensorMap& mb1, int64_t k_total, const float* scale, float* out,
               int64_t ld_out, int64_t m_total, int h, cudaStream_t stream) {
     const int64_t tiles = (m_total + BM - 1) / BM, pairs = (tiles + 1) / 2;
+    static int quad = -1;
+    if (quad < 0) { const char* e = getenv("GNNB_LINEAR_QUAD"); quad = e ? atoi(e) : 1; }
+    const int64_t groups = quad ? (pairs + 1) / 2 : pairs;
     { static bool done = false; if (!done) { GNNB_CUDA(cudaFuncSetAttribute(linear_i8_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM)); done = true; } }
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)(2 * pairs));
+    cfg.gridDim = dim3((unsigned)((quad ? 4 : 2) * groups));
     cfg.blockDim = dim3(256);
     cfg.dynamicSmemBytes = SMEM;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.x = quad ? 4 : 2;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     static int ablate = -1;
     if (ablate < 0) { const char* e = getenv("GNNB_LINEAR_ABLATE"); ablate = e ? atoi(e) : 0; }      // measurement only
-    GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_i8_kernel<BWD>, mx, mb0, mb1, k_total, scale, out, ld_out, m_total, h, ablate));
+    GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_i8_kernel<BWD>, mx, mb0, mb1, k_total, scale, out, ld_out, m_total, h, quad, ablate));
     return GNNB_OK;
 }
 }  // namespace
 
+static uint32_t box_div() {          // quad mode fetches the digit half-tiles in two halves
+    static int quad = -1;
+    if (quad < 0) { const char* e = getenv("GNNB_LINEAR_QUAD"); quad = e ? atoi(e) : 1; }
+    return quad ? 2 : 1;
+}
 static size_t limb_bytes(int64_t k_len) { return align_up((size_t)LIMB_ROWS * align_up((size_t)k_len, 16), 1024); }
 
 bool linear_i8_supported(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, int64_t h) {
@@ -320,9 +344,9 @@ int linear_i8_fwd(const int8_t* X, int64_t ldx, int64_t n, int64_t p, const floa
     CUtensorMap mx, mb0, mb1;
     int rc = make_tensor_map_2d(&mx, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, BKB, BM);
     if (rc != GNNB_OK) return rc;
-    rc = make_tensor_map_2d(&mb0, limbs, 1, (uint64_t)p, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N0 / 2);
+    rc = make_tensor_map_2d(&mb0, limbs, 1, (uint64_t)p, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N0 / 2 / box_div());
     if (rc != GNNB_OK) return rc;
-    rc = make_tensor_map_2d(&mb1, limbs, 1, (uint64_t)p, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N1 / 2);
+    rc = make_tensor_map_2d(&mb1, limbs, 1, (uint64_t)p, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N1 / 2 / box_div());
     if (rc != GNNB_OK) return rc;
     return launch_i8<false>(mx, mb0, mb1, p, scale, H, ldh, n, (int)h, stream);
 }
@@ -344,9 +368,9 @@ int linear_i8_bwd_w(const int8_t* X, int64_t ldx, int64_t n, int64_t p, const fl
     CUtensorMap mx, mb0, mb1;
     int rc = make_tensor_map_2d(&mx, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, 128, BKB);       // box: 128 markers x 128 individuals
     if (rc != GNNB_OK) return rc;
-    rc = make_tensor_map_2d(&mb0, limbs, 1, (uint64_t)n, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N0 / 2);
+    rc = make_tensor_map_2d(&mb0, limbs, 1, (uint64_t)n, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N0 / 2 / box_div());
     if (rc != GNNB_OK) return rc;
-    rc = make_tensor_map_2d(&mb1, limbs, 1, (uint64_t)n, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N1 / 2);
+    rc = make_tensor_map_2d(&mb1, limbs, 1, (uint64_t)n, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N1 / 2 / box_div());
     if (rc != GNNB_OK) return rc;
     return launch_i8<true>(mx, mb0, mb1, n, scale, dW, lddw, p, (int)h, stream);
 }

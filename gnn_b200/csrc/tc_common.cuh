@@ -117,6 +117,17 @@ __device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorM
         : "memory");
 }
 
+// CTA-pair TMA load multicast to the CTAs of `cta_mask`: the bytes land at the same shared-memory offset in every
+// destination CTA; the transaction count goes, in every destination CTA, to the mbarrier at `bar`'s offset in the EVEN
+// CTA of that destination's pair (the pair bit of the shared::cluster address is cleared, as CUTLASS does for 2-SM loads)
+__device__ __forceinline__ void tma_load_2d_pair_multicast(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int32_t c0, int32_t c1,
+                                                           uint16_t cta_mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1), "h"(cta_mask)
+        : "memory");
+}
+
 // ------------------------------------------------------------------------------------------ tcgen05 / TMEM
 template <int COLS>
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_result) {      // one full warp
