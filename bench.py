@@ -119,6 +119,16 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+def workload_name(a):
+    """config.workload, identical for both arms."""
+    N, p, k, B = a.individuals, a.markers, a.neighbours, a.batches
+    split = int(N * 0.8)
+    valid = int(0.1 * (N - split))
+    return (f"C5: synthetic {N} individuals x {p} SNPs, k={k} kNN Laplacian graphs, {B} subgraph batches of {N // B} "
+            f"(split_dataset), test graph {N - valid - split} nodes, create_network_two_no_conv_dropout hidden {a.hidden} "
+            f"dropout {DROPOUT:.4f}, Adam")
+
+
 # ----------------------------------------------------------------------------------------- our arm
 def run_ours(a):
     import torch.distributed as dist
@@ -375,9 +385,7 @@ def run_ours(a):
         "metric": "train epochs/sec", "value": 1000.0 / ms_per_epoch, "unit": "epochs/s", "n_gpus": world, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": ms_per_epoch, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32 (int8 genotypes; marker projection on int8 tensor cores with the float operand quantised to 21 bits per feature)", "data": "synthetic",
-        "config": {"workload": f"C5: synthetic {N} individuals x {p} SNPs, k={k} kNN Laplacian graphs, {B} subgraph batches of "
-                               f"{per} (split_dataset), test graph {test_hi - test_lo} nodes, create_network_two_no_conv_dropout "
-                               f"hidden {a.hidden} dropout {DROPOUT:.4f}, Adam",
+        "config": {"workload": workload_name(a),
                    "parallelism": f"dp{world} (subgraphs sharded, flat-gradient all-reduce)",
                    "linear_precision": ops.config["linear_precision"], "cuda_graphs": bool(use_graphs),
                    "l2": "inputs per epoch far exceed L2 (genotypes >= 0.78 GB per subgraph); no flush needed",
@@ -456,7 +464,7 @@ def run_reference(a):
         "impl": "reference", "metric": "train epochs/sec", "value": value, "unit": "epochs/s", "n_gpus": a.gpus,
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1000.0 / value, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"C5: synthetic {N} individuals x {p} SNPs, k={k}, {B} subgraph batches (CPU: bounded sample, scaled)"},
+        "config": {"workload": workload_name(a), "measured_on": "bounded sample of the workload, scaled to one epoch (see cpu_baseline.sample)"},
         "cpu_baseline": {"value": value, "unit": "epochs/s", "cores": cores, "kind": "port", "sample": desc},
         "e2e": {"value": value, "unit": "epochs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }

@@ -31,15 +31,26 @@ constexpr int HP = 112;                                  // rows per digit for d
 constexpr int N0 = 2 * HP, N1 = 128;                     // the two MMAs of a k-step
 constexpr int LIMB_ROWS = N0 + N1;                       // 352 rows of the limb matrix: [0,112) d0, [112,224) d1, [224,352) d2
 constexpr int A_BYTES = BM * BKB, B0_HALF = (N0 / 2) * BKB, B1_HALF = (N1 / 2) * BKB;
-constexpr int STAGE = A_BYTES + B0_HALF + B1_HALF;       // 38 KB
-constexpr int STAGES = 5;
+constexpr int B_BYTES = B0_HALF + B1_HALF;               // 22 KB: this CTA's half of the digit tile
+// Two rings with a producer thread each (X tiles from HBM, digit tiles multicast from L2), so that neither stream waits
+// for the other's slot.  Both are latency-bound on the bytes in flight, i.e. on shared memory: measured (XS, BS) ->
+// forward / weight gradient ms: (8,3) 0.268/0.263, (10,2) 0.360/0.356, (6,4) 0.221/0.219, (5,5) 0.210/0.202,
+// (4,6) 0.228/0.220, (3,7) 0.272/0.260; one ring of 5 whole stages was 0.226/0.224.
+#ifndef LI_XS
+#define LI_XS 5
+#endif
+#ifndef LI_BS
+#define LI_BS 5
+#endif
+constexpr int XS = LI_XS, BS = LI_BS;
 constexpr int ACC1_COL = 256;                            // TMEM column of the digit-2 accumulator
 
 struct Bars {
-    uint64_t full[STAGES], empty[STAGES], acc_full;
+    uint64_t xfull[XS], xempty[XS], bfull[BS], bempty[BS], acc_full;
     uint32_t tmem_ptr;
 };
-constexpr size_t SMEM = 1024 + (size_t)STAGES * STAGE + sizeof(Bars) + 64;
+constexpr size_t SMEM = 1024 + (size_t)XS * A_BYTES + (size_t)BS * B_BYTES + sizeof(Bars) + 64;
+static_assert(SMEM <= 232448, "shared memory of linear_i8_kernel");
 
 // ---- quantisation -----------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void digits3(float w, float inv_scale, int8_t& d0, int8_t& d1, int8_t& d2) {
@@ -170,13 +181,15 @@ linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     const uint32_t twin = crank >> 1;                                  // which of the two pairs (quad mode)
     const bool leader = rank == 0;
     const uint16_t pair_mask = (uint16_t)(3u << lead_rank), all_mask = quad ? 15 : 3;
-    uint8_t* tiles = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);
-    Bars* bars = reinterpret_cast<Bars*>(tiles + (size_t)STAGES * STAGE);
+    uint8_t* xt = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);      // X ring
+    uint8_t* bt = xt + (size_t)XS * A_BYTES;                                   // digit ring
+    Bars* bars = reinterpret_cast<Bars*>(bt + (size_t)BS * B_BYTES);
     const int n_kb = (int)((k_total + BKB - 1) / BKB);
     const int64_t m0 = ((int64_t)(blockIdx.x >> 1) * 2 + rank) * BM;      // this CTA's rows of the M side (may lie past the end)
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; ++s) { mbar_init(&bars->full[s], 2); mbar_init(&bars->empty[s], quad ? 2 : 1); }
+        for (int s = 0; s < XS; ++s) { mbar_init(&bars->xfull[s], 2); mbar_init(&bars->xempty[s], 1); }
+        for (int s = 0; s < BS; ++s) { mbar_init(&bars->bfull[s], 2); mbar_init(&bars->bempty[s], quad ? 2 : 1); }
         mbar_init(&bars->acc_full, 1);
         fence_barrier_init();
     }
@@ -187,30 +200,42 @@ linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     const uint32_t tmem_base = bars->tmem_ptr;
 
     if (warp == 0) {
-        if (elect_one()) {                                             // TMA producer (both CTAs)
+        if (elect_one()) {                                             // TMA producer of the X ring (both CTAs)
             prefetch_tensormap(&map_x);
+            for (int u = 0; u < n_kb; ++u) {
+                const int s = u % XS;
+                mbar_wait(&bars->xempty[s], ((u / XS) & 1) ^ 1);
+                const uint32_t full_leader = mapa_u32(smem_u32(&bars->xfull[s]), lead_rank);
+                if (ablate & 1) { mbar_arrive_cluster(full_leader); continue; }
+                if (leader) mbar_arrive_expect_tx(&bars->xfull[s], 2 * A_BYTES);
+                else        mbar_arrive_cluster(full_leader);
+                uint8_t* a = xt + (size_t)s * A_BYTES;
+                if (BWD) tma_load_2d_pair(a, &map_x, full_leader, (int32_t)m0, u * BKB);            // [128 k-rows x 128 markers]
+                else     tma_load_2d_pair(a, &map_x, full_leader, u * BKB, (int32_t)m0);            // [128 rows x 128 k]
+            }
+        }
+    } else if (warp == 3) {
+        if (elect_one()) {                                             // TMA producer of the digit ring (both CTAs)
             prefetch_tensormap(&map_b0);
             prefetch_tensormap(&map_b1);
             for (int u = 0; u < n_kb; ++u) {
-                const int s = u % STAGES;
-                mbar_wait(&bars->empty[s], ((u / STAGES) & 1) ^ 1);
-                const uint32_t full_leader = mapa_u32(smem_u32(&bars->full[s]), lead_rank);
+                const int s = u % BS;
+                mbar_wait(&bars->bempty[s], ((u / BS) & 1) ^ 1);
+                const uint32_t full_leader = mapa_u32(smem_u32(&bars->bfull[s]), lead_rank);
                 if (ablate & 1) { mbar_arrive_cluster(full_leader); continue; }
-                if (leader) mbar_arrive_expect_tx(&bars->full[s], 2 * STAGE);
+                if (leader) mbar_arrive_expect_tx(&bars->bfull[s], 2 * B_BYTES);
                 else        mbar_arrive_cluster(full_leader);
-                uint8_t* a = tiles + (size_t)s * STAGE;
-                if (BWD) tma_load_2d_pair(a, &map_x, full_leader, (int32_t)m0, u * BKB);            // [128 k-rows x 128 markers]
-                else     tma_load_2d_pair(a, &map_x, full_leader, u * BKB, (int32_t)m0);            // [128 rows x 128 k]
+                uint8_t* b = bt + (size_t)s * B_BYTES;
                 if (quad) {
                     // this CTA fetches half of the digit rows its pair position needs and delivers them to both pairs
                     const uint16_t mc = (uint16_t)((1u << rank) | (1u << (rank + 2)));
-                    tma_load_2d_pair_multicast(a + A_BYTES + twin * (B0_HALF / 2), &map_b0, &bars->full[s], u * BKB,
+                    tma_load_2d_pair_multicast(b + twin * (B0_HALF / 2), &map_b0, &bars->bfull[s], u * BKB,
                                                (int32_t)(rank * (N0 / 2) + twin * (N0 / 4)), mc);
-                    tma_load_2d_pair_multicast(a + A_BYTES + B0_HALF + twin * (B1_HALF / 2), &map_b1, &bars->full[s], u * BKB,
+                    tma_load_2d_pair_multicast(b + B0_HALF + twin * (B1_HALF / 2), &map_b1, &bars->bfull[s], u * BKB,
                                                (int32_t)(N0 + rank * (N1 / 2) + twin * (N1 / 4)), mc);
                 } else {
-                    tma_load_2d_pair(a + A_BYTES, &map_b0, full_leader, u * BKB, (int32_t)(rank * (N0 / 2)));
-                    tma_load_2d_pair(a + A_BYTES + B0_HALF, &map_b1, full_leader, u * BKB, (int32_t)(N0 + rank * (N1 / 2)));
+                    tma_load_2d_pair(b, &map_b0, full_leader, u * BKB, (int32_t)(rank * (N0 / 2)));
+                    tma_load_2d_pair(b + B0_HALF, &map_b1, full_leader, u * BKB, (int32_t)(N0 + rank * (N1 / 2)));
                 }
             }
         }
@@ -219,13 +244,15 @@ linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             constexpr uint32_t idesc0 = make_idesc(/*S32*/ 2, /*int8*/ 1, BWD ? 1 : 0, 0, 2 * BM, N0);
             constexpr uint32_t idesc1 = make_idesc(/*S32*/ 2, /*int8*/ 1, BWD ? 1 : 0, 0, 2 * BM, N1);
             for (int u = 0; u < n_kb; ++u) {
-                const int s = u % STAGES;
-                mbar_wait(&bars->full[s], (u / STAGES) & 1);
+                const int sx = u % XS, sb = u % BS;
+                mbar_wait(&bars->xfull[sx], (u / XS) & 1);
+                mbar_wait(&bars->bfull[sb], (u / BS) & 1);
                 tc_fence_after_sync();
-                const uint32_t a_addr = smem_u32(tiles + (size_t)s * STAGE);
-                const uint32_t b0_addr = a_addr + A_BYTES, b1_addr = b0_addr + B0_HALF;
+                const uint32_t a_addr = smem_u32(xt + (size_t)sx * A_BYTES);
+                const uint32_t b0_addr = smem_u32(bt + (size_t)sb * B_BYTES), b1_addr = b0_addr + B0_HALF;
                 if (ablate & 2) {
-                    for (uint32_t c = 0; c < (quad ? 4u : 2u); ++c) mbar_arrive_cluster(mapa_u32(smem_u32(&bars->empty[s]), c));
+                    for (uint32_t c = 0; c < 2u; ++c) mbar_arrive_cluster(mapa_u32(smem_u32(&bars->xempty[sx]), lead_rank + c));
+                    for (uint32_t c = 0; c < (quad ? 4u : 2u); ++c) mbar_arrive_cluster(mapa_u32(smem_u32(&bars->bempty[sb]), c));
                     continue;
                 }
 #pragma unroll
@@ -239,11 +266,8 @@ linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     mma_i8_ss_pair(tmem_base, da, db0, idesc0, acc);
                     mma_i8_ss_pair(tmem_base + ACC1_COL, da, db1, idesc1, acc);
                 }
-                // a commit costs the tensor pipe a ~100-cycle bubble (scripts/ubench/mma_rate.cu): release slots two at a time
-                if ((u & 1) || u == n_kb - 1) {
-                    if (u & 1) tc_commit_pair(&bars->empty[(u - 1) % STAGES], all_mask);
-                    tc_commit_pair(&bars->empty[s], all_mask);
-                }
+                tc_commit_pair(&bars->xempty[sx], pair_mask);          // X slots are private to the pair
+                tc_commit_pair(&bars->bempty[sb], all_mask);           // digit slots are written by both pairs' producers
             }
             tc_commit_pair(&bars->acc_full, pair_mask);
         }
