@@ -29,7 +29,7 @@ using namespace tc;
 namespace {
 constexpr int BM = 128, BN = 256, BKB = 128;              // BKB: bytes (= int8 elements) of K per stage
 constexpr int A_BYTES = BM * BKB, B_BYTES = BN * BKB, STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int MAX_STAGES = 4;
+constexpr int MAX_STAGES = 5;
 constexpr int QG = 18;                                    // query tiles per raster group
 constexpr int EPI_THREADS = 128;
 
@@ -263,7 +263,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__
 // (distance + selection, one thread per query row) is the one-CTA epilogue unchanged.
 namespace {
 constexpr int B_HALF_BYTES = (BN / 2) * BKB, STAGE2_BYTES = A_BYTES + B_HALF_BYTES;
-constexpr int QGP = QG / 2;                               // query-tile PAIRS per raster group
+constexpr int QGP = 8;                                    // query-tile PAIRS per raster group (even: a quad = two pairs of one split)
 
 __host__ __device__ inline size_t smem_bytes2(int stages, int k, bool extra) {
     return 1024 + (size_t)stages * STAGE2_BYTES + 128 + 2 * BN * sizeof(long long) +
@@ -297,18 +297,24 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                const int64_t* __restrict__ sq_k, int64_t n_k, int64_t k_off, int64_t p,
                const double* __restrict__ extra_q, const double* __restrict__ extra_k, int n_extra,
                int k, int n_splits, int q_pairs, int stages, double* __restrict__ part_d2, int32_t* __restrict__ part_idx,
+               int quad,          // 1: clusters of 4 = two pairs with neighbouring query tiles and the same key range; each key
+                                  //    half-tile is fetched once (half by each of the two CTAs that need it) and multicast to both
                int ablate) {      // measurement only (results invalid): 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue work
     extern __shared__ uint8_t smem_raw[];
     const int warp = threadIdx.x >> 5;
-    const uint32_t rank = cluster_ctarank();
+    const uint32_t crank = cluster_ctarank();                   // 0..1, or 0..3 in quad mode
+    const uint32_t rank = crank & 1, lead_rank = crank & ~1u, twin = crank >> 1;
     const bool leader = rank == 0;
+    const uint16_t pair_mask = (uint16_t)(3u << lead_rank), all_mask = quad ? 15 : 3;
 
-    const int pair = blockIdx.x >> 1;                           // cluster = 2 consecutive CTAs
+    const int pair = blockIdx.x >> 1;                           // pair = 2 consecutive CTAs
     const int per_group = QGP * n_splits;
     const int group = pair / per_group, rem = pair % per_group;
     const int q_pair = group * QGP + rem % QGP;
     const int split = rem / QGP;
-    if (q_pair >= q_pairs) return;                              // both CTAs of the pair leave together
+    // a whole cluster leaves together; in quad mode the second pair of a quad may lie past the last query tile and then
+    // runs on zero-filled tiles (its key loads and barrier traffic are part of the first pair's pipeline)
+    if ((quad ? (q_pair & ~1) : q_pair) >= q_pairs) return;
     const int q_tile = 2 * q_pair + (int)rank;                  // may be one past the last tile: TMA zero-fills, rows are skipped
 
     Smem sm = carve2(smem_raw, stages, k, HAS_EXTRA);
@@ -320,7 +326,7 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
     if (threadIdx.x == 0) {
         for (int s = 0; s < stages; ++s) {
             mbar_init(&sm.full[s], 2);                          // one arrival per CTA's producer (+ the bytes of both)
-            mbar_init(&sm.empty[s], 1);
+            mbar_init(&sm.empty[s], quad ? 2 : 1);              // quad: both pairs must be done before a twin refills the slot
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(&sm.tfull[b], 1);
@@ -345,7 +351,7 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                     const int s = it % stages;
                     const uint32_t ph = (it / stages) & 1;
                     mbar_wait(&sm.empty[s], ph ^ 1);            // own slot freed by the pair's MMAs (multicast commit)
-                    const uint32_t full_leader = mapa_u32(smem_u32(&sm.full[s]), 0);
+                    const uint32_t full_leader = mapa_u32(smem_u32(&sm.full[s]), lead_rank);
                     if (ablate & 1) {
                         mbar_arrive_cluster(full_leader);
                         continue;
@@ -354,7 +360,12 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                     else        mbar_arrive_cluster(full_leader);
                     uint8_t* a = sm.tiles + (size_t)s * STAGE2_BYTES;
                     tma_load_2d_pair(a, &map_q, full_leader, kb * BKB, q_tile * BM);
-                    tma_load_2d_pair(a + A_BYTES, &map_k, full_leader, kb * BKB, (int32_t)(kt * BN + rank * (BN / 2)));
+                    if (quad)
+                        tma_load_2d_pair_multicast(a + A_BYTES + twin * (B_HALF_BYTES / 2), &map_k, &sm.full[s], kb * BKB,
+                                                   (int32_t)(kt * BN + rank * (BN / 2) + twin * (BN / 4)),
+                                                   (uint16_t)((1u << rank) | (1u << (rank + 2))));
+                    else
+                        tma_load_2d_pair(a + A_BYTES, &map_k, full_leader, kb * BKB, (int32_t)(kt * BN + rank * (BN / 2)));
                 }
             }
         }
@@ -376,8 +387,7 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                     const uint32_t a_addr = smem_u32(sm.tiles + (size_t)s * STAGE2_BYTES);
                     const uint32_t b_addr = a_addr + A_BYTES;
                     if (ablate & 2) {
-                        mbar_arrive(&sm.empty[s]);
-                        mbar_arrive_cluster(mapa_u32(smem_u32(&sm.empty[s]), 1));
+                        for (uint32_t c = 0; c < (quad ? 4u : 2u); ++c) mbar_arrive_cluster(mapa_u32(smem_u32(&sm.empty[s]), c));
                         continue;
                     }
 #pragma unroll
@@ -386,9 +396,10 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                         const uint64_t db = make_smem_desc(b_addr + k4 * 32, 16, 1024);
                         mma_i8_ss_pair(d_tmem, da, db, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
                     }
-                    tc_commit_pair(&sm.empty[s], 3);            // frees the slot in both CTAs
+                    // (releasing slots two at a time to halve the commits was measured: 9.3 -> 10.9 ms, the loads need the slot early)
+                    tc_commit_pair(&sm.empty[s], all_mask);     // frees the slot in both CTAs (and tells the twin pair in quad mode)
                 }
-                tc_commit_pair(&sm.tfull[b], 3);                // accumulator complete, both epilogues may read
+                tc_commit_pair(&sm.tfull[b], pair_mask);        // accumulator complete, both epilogues may read
             }
         }
     } else if (warp >= 4) {
@@ -427,7 +438,7 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             tc_fence_after_sync();
             if (ablate & 4) {                                  // measurement only: no accumulator reads, no selection
                 if (leader) mbar_arrive(&sm.tempty[b]);
-                else        mbar_arrive_cluster(mapa_u32(smem_u32(&sm.tempty[b]), 0));
+                else        mbar_arrive_cluster(mapa_u32(smem_u32(&sm.tempty[b]), lead_rank));
                 continue;
             }
             const int ncols = (int)((n_k - k0) < BN ? (n_k - k0) : BN);
@@ -435,7 +446,7 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                                         ncols, gi, k_off + k0, sel, thr_ll, selu);
             tc_fence_before_sync();
             if (leader) mbar_arrive(&sm.tempty[b]);
-            else        mbar_arrive_cluster(mapa_u32(smem_u32(&sm.tempty[b]), 0));
+            else        mbar_arrive_cluster(mapa_u32(smem_u32(&sm.tempty[b]), lead_rank));
         }
         if (valid) {
             double* od = part_d2 + ((int64_t)split * n_q + row) * k;
@@ -472,20 +483,25 @@ int knn_tc_launch(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q
                   const double* extra_q, const double* extra_k, int n_extra, int k, int n_splits,
                   double* part_d2, int32_t* part_idx, cudaStream_t stream) {
     const int q_tiles = (int)((n_q + BM - 1) / BM);
-    static int use_pair = -1, ablate = 0;
+    static int use_pair = -1, ablate = 0, quad = 1;
     if (use_pair < 0) {
         const char* e = getenv("GNNB_KNN_PAIR");
         use_pair = e ? atoi(e) : 1;
         const char* a = getenv("GNNB_KNN_ABLATE");             // measurement only: 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue
         ablate = a ? atoi(a) : 0;
+        const char* q = getenv("GNNB_KNN_QUAD");
+        quad = q ? atoi(q) : -1;                               // -1: pick by shape
     }
     const bool extra = n_extra > 0;
+    // quads pay off on long K loops (15625 x 50000: 9.8 -> 9.3 ms); on short ones the lockstep of the two pairs costs more
+    // than the shared key tile saves (65536 x 8192: 60 -> 65 ms)
+    const int use_quad = quad >= 0 ? quad : (p >= 16384 ? 1 : 0);
     if (use_pair && q_tiles >= 2) {
         // CTA pairs: 256 queries x 256 keys per pair, each CTA stages its 128 queries and one half of the key tile
         CUtensorMap map_q, map_k;
         int rc = make_tensor_map_2d(&map_q, Q, 1, (uint64_t)p, (uint64_t)n_q, (uint64_t)ldq, BKB, BM);
         if (rc != GNNB_OK) return rc;
-        rc = make_tensor_map_2d(&map_k, K, 1, (uint64_t)p, (uint64_t)n_k, (uint64_t)ldk, BKB, BN / 2);
+        rc = make_tensor_map_2d(&map_k, K, 1, (uint64_t)p, (uint64_t)n_k, (uint64_t)ldk, BKB, use_quad ? BN / 4 : BN / 2);
         if (rc != GNNB_OK) return rc;
         int stages = MAX_STAGES;
         while (stages > 2 && smem_bytes2(stages, k, extra) > 232448) --stages;
@@ -499,7 +515,7 @@ int knn_tc_launch(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q
         cfg.stream = stream;
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.x = use_quad ? 4 : 2;             // grid = groups * QGP * n_splits * 2 is a multiple of 4 (QGP even)
         attr[0].val.clusterDim.y = 1;
         attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
@@ -507,11 +523,11 @@ int knn_tc_launch(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q
         if (extra) {
             { static size_t hw_ = 0; if (smem > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_tc2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); hw_ = smem; } }
             GNNB_CUDA(cudaLaunchKernelEx(&cfg, knn_tc2_kernel<true>, map_q, map_k, sq_q, n_q, q_off, sq_k, n_k, k_off, p, extra_q, extra_k,
-                                         n_extra, k, n_splits, q_pairs, stages, part_d2, part_idx, ablate));
+                                         n_extra, k, n_splits, q_pairs, stages, part_d2, part_idx, use_quad, ablate));
         } else {
             { static size_t hw_ = 0; if (smem > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_tc2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); hw_ = smem; } }
             GNNB_CUDA(cudaLaunchKernelEx(&cfg, knn_tc2_kernel<false>, map_q, map_k, sq_q, n_q, q_off, sq_k, n_k, k_off, p, extra_q, extra_k,
-                                         n_extra, k, n_splits, q_pairs, stages, part_d2, part_idx, ablate));
+                                         n_extra, k, n_splits, q_pairs, stages, part_d2, part_idx, use_quad, ablate));
         }
         return GNNB_OK;
     }
