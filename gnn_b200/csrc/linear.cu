@@ -109,6 +109,156 @@ static int launch_gemm(const AT* A, int64_t sam, int64_t sak, const float* B, in
     return GNNB_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Inner layers (h x h weights, float activations): both small dimensions fit one CTA tile, so the generic 64x64x16 kernel
+// spends its time on tile overhead (29 / 25 / 34+14 us for 15625 x 100 x 100 -- 11 % of a C5 epoch).  Here a CTA keeps BOTH
+// operands of a 128-deep product in shared memory and every thread owns an 8 x 8 block of the 128 x 128 output tile
+// (64 FMAs per 4 128-bit shared loads), fp32 FMA in ascending k like the generic kernel.
+//   MODE 0  C[m, n] = sum_k A[m, k] * W[n, k]      forward      (K, N <= 128; CTA = 128 rows m)
+//   MODE 1  C[m, n] = sum_k A[m, k] * W[k, n]      dX           (K, N <= 128; CTA = 128 rows m)
+//   MODE 2  P[c][i, j] = sum_{m in chunk c} A[m, i] * B[m, j]   weight gradient partials (I, J <= 128; chunk = 128 rows),
+//           summed over chunks in ascending order by splitk_reduce_kernel
+constexpr int SK = 128, SK_LD = SK + 4;
+
+template <int MODE>
+__global__ void __launch_bounds__(256, 2)
+skinny_kernel(const float* __restrict__ A, int64_t lda, const float* __restrict__ B, int64_t ldb,
+              float* __restrict__ C, int64_t ldc, int64_t M, int N, int K) {
+    extern __shared__ float sk_smem[];
+    const int kdim = MODE == 2 ? SK : K;                       // depth of the product held in shared memory
+    float* As = sk_smem;                                       // [kdim][SK_LD]: As[k][row of the output tile]
+    float* Bs = sk_smem + (size_t)kdim * SK_LD;                // [kdim][SK_LD]: Bs[k][column of the output tile]
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int64_t m0 = (int64_t)blockIdx.x * SK;
+    // Loads are issued in batches of 8 per thread before the first store, so that their latencies overlap.
+    if (MODE == 2) {
+        // A[m, i] and B[m, j] are already k-major (k = m): straight copies, zero padding past the matrices
+        for (int e0 = tid; e0 < SK * SK; e0 += 256 * 8) {
+            float va[8], vb[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int e = e0 + q * 256, k = e >> 7, c = e & 127;
+                const int64_t m = m0 + k;
+                va[q] = (m < M && c < N) ? A[m * lda + c] : 0.f;
+                vb[q] = (m < M && c < K) ? B[m * ldb + c] : 0.f;
+            }
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int e = e0 + q * 256, k = e >> 7, c = e & 127;
+                As[k * SK_LD + c] = va[q];
+                Bs[k * SK_LD + c] = vb[q];
+            }
+        }
+    } else {
+        // A[m, k] is contiguous along k: read along k (rows padded to 128 columns in the index space), store transposed
+        for (int e0 = tid; e0 < SK * SK; e0 += 256 * 8) {
+            float va[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int e = e0 + q * 256, r = e >> 7, k = e & 127;
+                const int64_t m = m0 + r;
+                va[q] = (m < M && k < kdim) ? A[m * lda + k] : 0.f;
+            }
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int e = e0 + q * 256, r = e >> 7, k = e & 127;
+                if (k < kdim) As[k * SK_LD + r] = va[q];
+            }
+        }
+        for (int e0 = tid; e0 < SK * SK; e0 += 256 * 8) {
+            float vb[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int e = e0 + q * 256, hi = e >> 7, lo = e & 127;
+                if (MODE == 0) vb[q] = (hi < N && lo < kdim) ? B[(int64_t)hi * ldb + lo] : 0.f;      // W[n = hi, k = lo]
+                else           vb[q] = (hi < kdim && lo < N) ? B[(int64_t)hi * ldb + lo] : 0.f;      // W[k = hi, n = lo]
+            }
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int e = e0 + q * 256, hi = e >> 7, lo = e & 127;
+                if (MODE == 0) { if (lo < kdim) Bs[lo * SK_LD + hi] = vb[q]; }
+                else           { if (hi < kdim) Bs[hi * SK_LD + lo] = vb[q]; }
+            }
+        }
+    }
+    __syncthreads();
+    float acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+#pragma unroll 4
+    for (int k = 0; k < kdim; ++k) {
+        // rows ty*4 + {0..3} and 64 + ty*4 + {0..3}, columns likewise in tx: a quarter warp's 128-bit loads then cover 128
+        // contiguous bytes (no bank conflicts); with 8 consecutive columns per thread they were 2-way conflicted
+        const float4 a0 = *reinterpret_cast<const float4*>(As + k * SK_LD + ty * 4);
+        const float4 a1 = *reinterpret_cast<const float4*>(As + k * SK_LD + 64 + ty * 4);
+        const float4 b0 = *reinterpret_cast<const float4*>(Bs + k * SK_LD + tx * 4);
+        const float4 b1 = *reinterpret_cast<const float4*>(Bs + k * SK_LD + 64 + tx * 4);
+        const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+        const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    if (MODE == 2) {
+        // partial [N (= I) rows][K (= J) columns], dense, one per chunk
+        float* P = C + (int64_t)blockIdx.x * N * K;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int r = (i < 4 ? 0 : 60) + ty * 4 + i;
+            if (r < N)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int c = (j < 4 ? 0 : 60) + tx * 4 + j;
+                    if (c < K) P[r * K + c] = acc[i][j];
+                }
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int64_t m = m0 + (i < 4 ? 0 : 60) + ty * 4 + i;
+            if (m < M)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int c = (j < 4 ? 0 : 60) + tx * 4 + j;
+                    if (c < N) C[m * ldc + c] = acc[i][j];
+                }
+        }
+    }
+}
+
+// C[i] = sum_c part[c][i] for the chunk partials of MODE 2: 64 outputs per CTA, four thread groups each add a quarter of the
+// chunks in ascending order, then the four sums are added in group order -- a fixed tree, so the result is reproducible.
+__global__ void __launch_bounds__(256)
+chunk_reduce_kernel(const float* __restrict__ part, int n_chunks, int64_t total, int64_t N, float* __restrict__ C, int64_t ldc) {
+    __shared__ float red[4][64];
+    const int o = threadIdx.x & 63, g = threadIdx.x >> 6;
+    const int64_t i = (int64_t)blockIdx.x * 64 + o;
+    const int per = (n_chunks + 3) / 4, c0 = g * per, c1 = min(n_chunks, c0 + per);
+    float s = 0.f;
+    if (i < total) {
+#pragma unroll 8
+        for (int c = c0; c < c1; ++c) s += part[(int64_t)c * total + i];
+    }
+    red[g][o] = s;
+    __syncthreads();
+    if (g == 0 && i < total) C[(i / N) * ldc + (i % N)] = ((red[0][o] + red[1][o]) + red[2][o]) + red[3][o];
+}
+
+static size_t skinny_smem(int kdim) { return (size_t)2 * kdim * SK_LD * sizeof(float); }
+
+template <int MODE>
+static int launch_skinny(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M, int N, int K,
+                         cudaStream_t stream) {
+    const size_t smem = skinny_smem(MODE == 2 ? SK : K);
+    { static size_t hw_ = 0; if (smem > hw_) { GNNB_CUDA(cudaFuncSetAttribute(skinny_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); hw_ = smem; } }
+    skinny_kernel<MODE><<<(unsigned)((M + SK - 1) / SK), 256, smem, stream>>>(A, lda, B, ldb, C, ldc, M, N, K);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
 static int pick_splits(int64_t M, int64_t N, int64_t K) {
     int64_t tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
     int64_t want = (2LL * sm_count() + tiles - 1) / tiles;
@@ -135,6 +285,8 @@ int linear_i8_bwd_w(const int8_t* X, int64_t ldx, int64_t n, int64_t p, const fl
 
 int linear_simt_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* W, int64_t ldw, int64_t h,
                     float* H, int64_t ldh, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+    if (!x_is_i8 && p <= SK && h <= SK && n >= SK)                           // inner layer: both small dimensions in one tile
+        return launch_skinny<0>((const float*)X, ldx, W, ldw, H, ldh, n, (int)h, (int)p, stream);
     int splits = pick_splits(n, h, p);
     size_t need = splits > 1 ? (size_t)splits * n * h * sizeof(float) : 0;
     if (need > 0 && (!workspace || workspace_bytes < need)) splits = 1;      // no scratch: single pass over K
@@ -150,6 +302,18 @@ int linear_simt_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_
     // dW[f, j] = sum_i dH[i, f] * X[i, j], run as dW^T so that the typed operand X is A:
     //   M = p, N = h, K = n, A(m, k) = X[k, m] (contiguous along m), B(k, n) = dH[k, n] (contiguous along n),
     //   C(m, n) -> dW[n * lddw + m]
+    if (!x_is_i8 && p <= SK && h <= SK && n >= SK) {
+        // dW[f, j] = sum_i dH[i, f] * X[i, j]: one [h, p] partial per 128-row chunk, then the fixed-order sum over chunks
+        const int64_t chunks = (n + SK - 1) / SK;
+        const size_t need_sk = (size_t)chunks * h * p * sizeof(float);
+        if (workspace && workspace_bytes >= need_sk) {
+            int rc = launch_skinny<2>(dH, lddh, (const float*)X, ldx, (float*)workspace, 0, n, (int)h, (int)p, stream);
+            if (rc != GNNB_OK) return rc;
+            chunk_reduce_kernel<<<(unsigned)((h * p + 63) / 64), 256, 0, stream>>>((const float*)workspace, (int)chunks, h * p, p, dW, lddw);
+            GNNB_LAUNCH_CHECK();
+            return GNNB_OK;
+        }
+    }
     int splits = pick_splits(p, h, n);
     size_t need = splits > 1 ? (size_t)splits * h * p * sizeof(float) : 0;
     if (need > 0 && (!workspace || workspace_bytes < need)) splits = 1;
@@ -176,6 +340,10 @@ int gnnb_linear_workspace_bytes(int64_t n, int64_t p, int64_t h, int precision, 
     if (max_splits > 64) max_splits = 64;
     if (max_splits < 1) max_splits = 1;
     size_t simt = max_splits * out_max * sizeof(float) + 256;
+    if (p <= SK && h <= SK) {                                  // inner-layer weight gradient: one [h, p] partial per 128 rows
+        size_t sk = (size_t)((n + SK - 1) / SK) * (size_t)h * (size_t)p * sizeof(float) + 256;
+        if (sk > simt) simt = sk;
+    }
     size_t tc = precision > 0 ? linear_tc_workspace(n, p, h, precision == 4 ? 2 : precision) : 0;
     if (precision == 4) {
         size_t i8 = linear_i8_workspace(n, p, h);
@@ -230,6 +398,7 @@ int gnnb_linear_bwd_x(const float* dH, int64_t lddh, int64_t n, int64_t h,
     GNNB_REQUIRE(dH && W && dX && n >= 0 && p > 0 && h > 0 && lddh >= h && ldw >= p && lddx >= p, GNNB_E_BADARG, "linear_bwd_x: bad argument");
     if (n == 0) return GNNB_OK;
     // dX[i, j] = sum_f dH[i, f] * W[f, j]: A = dH (contiguous along k), B = W (contiguous along n)
+    if (p <= SK && h <= SK && n >= SK) return launch_skinny<1>(dH, lddh, W, ldw, dX, lddx, n, (int)p, (int)h, stream);
     return launch_gemm<float, true, false>(dH, lddh, 1, W, ldw, 1, dX, lddx, 1, n, p, h, 1, nullptr, stream);
 }
 
