@@ -62,9 +62,11 @@ def test_synthetic_shapes(n, p, k, impl):
     check(synth.genotypes(n, p, seed=11 + n), k, impl=impl)
 
 
-@pytest.mark.parametrize("n,p,k", [(128, 128, 3), (129, 257, 32), (1000, 4096, 33), (2500, 130, 64), (5000, 1279, 16)])
+@pytest.mark.parametrize("n,p,k", [(128, 128, 3), (129, 257, 32), (1000, 4096, 33), (2500, 130, 64), (5000, 1279, 16),
+                                   (640, 16384 + 96, 8), (1300, 20000, 32), (300, 16384, 64)])
 def test_tensor_core_path_equals_cuda_core_path(n, p, k):
-    """impl=2 (tcgen05 int8 tiles) and impl=1 (dp4a tiles) must produce the same bits."""
+    """impl=2 (tcgen05 int8 tiles) and impl=1 (dp4a tiles) must produce the same bits.  p >= 16384 runs the clusters of two
+    CTA pairs with multicast key tiles (odd pair counts leave the last cluster with an empty second pair)."""
     X = dev_i8(synth.genotypes(n, p, seed=n + p))
     a_i, a_d = ops.knn(X, k, impl=1)
     b_i, b_d = ops.knn(X, k, impl=2)
