@@ -9,15 +9,17 @@
 // T = 1 is a plain bf16 projection, T = 2 carries ~16 mantissa bits (rel. error ~1e-5), T = 3 is fp32-faithful.
 //
 // X stays int8 in HBM (1 byte per element, the only large stream).  Per k-block a TMA load brings the raw int8
-// tile into a staging ring; four converter warps expand it to bf16 directly into the 128-byte-swizzled UMMA
-// operand layout (prmt + one packed bf16 subtract per pair); the fp32 operand's bf16 terms arrive by TMA from
-// an L2-resident workspace that a small prep kernel fills once per call.
+// tile into a staging ring; converter warps expand it to bf16 (prmt + one packed bf16 subtract per pair) and write
+// it with tcgen05.st into an A slot in TENSOR MEMORY; the fp32 operand's bf16 terms arrive by TMA from an L2-resident
+// workspace that a small prep kernel fills once per call.  (A first version kept both operands in shared memory and ran
+// at 0.46 ms against 0.33 ms; its history is in profiles/README.md.)  These kernels serve precision 1..3; the default
+// for int8 genotypes is the int8-digit kernel of linear_i8.cu (precision 4).
 //
-//   forward  : CTA = 128 rows of X.     A = X tile (K-major),     B = W terms  [h_pad x 64]  (K-major),  D[128 x h_pad]
-//   backward : CTA = 128 columns of X.  A = X^T tile (MN-major),  B = dH terms [64 x 128]    (MN-major), D[128 x 128]
+//   forward  : CTA = 128 rows of X.     A = X tile (TMEM),     B = W terms  [h_pad x 64]  (K-major),  D[128 x h_pad]
+//   backward : CTA = 128 columns of X.  A = X^T tile (TMEM),   B = dH terms [64 x 128]    (MN-major), D[128 x 128]
 //
 // warps: 0 = TMA producer (X), 3 = TMA producer (terms), 1 = MMA issuer, 2 = TMEM allocator,
-//        4-7 = converter, then epilogue (TMEM -> registers -> global).
+//        4.. = converters, then epilogue (TMEM -> registers -> global).
 #include <cuda_bf16.h>
 #include <stdlib.h>
 
@@ -30,33 +32,9 @@ using namespace tc;
 namespace {
 constexpr int BM = 128;                 // rows (fwd) / columns (bwd) of X per CTA == UMMA M
 constexpr int BK = 64;                  // k elements per block
-constexpr int CW = 4;                   // converter warps; warp c owns k-blocks c, c + CW, ... (whole tiles, so that
-                                        // four conversions are in flight and their latencies overlap)
-constexpr int NX = 8, NA = 4, NB_MAX = 4;   // ring depths; NX and NA are multiples of CW so that a ring slot is only
-                                            // ever touched by one converter warp (no phase aliasing between warps)
-static_assert(NX % CW == 0 && NA % CW == 0, "ring slots must map to a single converter warp");
 constexpr int X_STAGE_BYTES = BM * BK;              // int8: fwd 128 rows x 64 B, bwd 64 rows x 128 B
-constexpr int A_BYTES = BM * BK * 2;                // bf16 operand tile
 constexpr int MAX_TERMS = 3;
-constexpr int MAX_SPLITS = 8;
-constexpr int ACC_COLS = 256;            // TMEM columns per X tile: [0, n_pad) hi (+ third term), [n_pad, 2 n_pad) lo
-
-struct Bars {
-    uint64_t x_full[NX], x_empty[NX], a_full[NA], a_empty[NA], b_full[NB_MAX], b_empty[NB_MAX], acc_full;
-    uint32_t tmem_ptr;
-};
-
 constexpr size_t SMEM_LIMIT = 232448;       // 227 KB of dynamic shared memory per CTA
-__host__ __device__ inline size_t tc_smem_fixed() { return 1024 + (size_t)NX * X_STAGE_BYTES + (size_t)NA * A_BYTES + sizeof(Bars) + 64; }
-// stages of the bf16-term ring that fit next to the int8 staging ring and the operand ring
-__host__ __device__ inline int nb_stages(int terms, int b_tile_bytes) {
-    size_t per = (size_t)terms * b_tile_bytes;
-    int nb = (int)((SMEM_LIMIT - tc_smem_fixed()) / per);
-    return nb > NB_MAX ? NB_MAX : nb;
-}
-__host__ __device__ inline size_t tc_smem_bytes(int terms, int b_tile_bytes) {
-    return tc_smem_fixed() + (size_t)nb_stages(terms, b_tile_bytes) * terms * b_tile_bytes;
-}
 
 // fp32 -> up to three bf16 terms: x ~ hi + mid + lo
 __device__ __forceinline__ void split3(float x, __nv_bfloat16& hi, __nv_bfloat16& mid, __nv_bfloat16& lo) {
@@ -100,245 +78,6 @@ __device__ __forceinline__ void cvt16(const uint4& in, uint4& lo, uint4& hi) {
     hi = make_uint4(o[4], o[5], o[6], o[7]);
 }
 }  // namespace
-
-// BWD = false: D[m = row of X, n = feature]   += sum_k X[m, k] * W_t[n, k]
-// BWD = true : D[m = column of X, n = feature] += sum_k X[k, m] * dH_t[k, n]
-//
-// A CTA owns `rt` (1, 2 or 4) adjacent 128-wide X tiles -- one TMEM accumulator each -- and a range of k-blocks
-// (split-K over blockIdx.y).  Every term tile fetched from L2 is re-used by all `rt` X tiles: an SM takes in about
-// 32 B/clk, and with one X tile per CTA the term tiles (32 KB per k-block at 2 terms) are 80 % of that traffic.
-// The X and A rings run over "units" u = local k-block * rt + tile; the term ring runs over k-blocks.
-template <bool BWD>
-__global__ void __launch_bounds__(256, 1)
-linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
-                 int64_t k_total, int terms, int n_pad, int64_t b_term_rows,
-                 float* __restrict__ out, int64_t ld_out, int64_t split_stride, int64_t m_total, int n_valid, int csize, int rt) {
-    extern __shared__ uint8_t smem_raw[];
-    const int warp = threadIdx.x >> 5;
-    uint8_t* base = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);
-    const int b_tile_bytes = BWD ? (BK * 128 * 2) : (n_pad * BK * 2);     // one term: bwd 2 groups x 64 k x 128 B; fwd n_pad x 128 B
-    const int NB = nb_stages(terms, b_tile_bytes);
-    uint8_t* x_stage = base;
-    uint8_t* a_tiles = x_stage + NX * X_STAGE_BYTES;
-    uint8_t* b_tiles = a_tiles + NA * A_BYTES;
-    Bars* bars = reinterpret_cast<Bars*>(b_tiles + (size_t)NB * terms * b_tile_bytes);
-    const int n_kb_all = (int)((k_total + BK - 1) / BK);
-    const int kb0 = (int)((int64_t)n_kb_all * blockIdx.y / gridDim.y);
-    const int n_kb = (int)((int64_t)n_kb_all * (blockIdx.y + 1) / gridDim.y) - kb0;      // k-blocks of this split
-    const int n_units = n_kb * rt;
-    const int64_t m0 = (int64_t)blockIdx.x * BM * rt;
-    // Optional cluster of `csize` CTAs (neighbouring X tiles) that multicast the term tiles to each other.
-    const uint32_t crank = csize > 1 ? cluster_ctarank() : 0;
-    const uint16_t cmask = (uint16_t)((1u << csize) - 1);
-
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < NX; ++s) { mbar_init(&bars->x_full[s], 1); mbar_init(&bars->x_empty[s], 1); }
-        for (int s = 0; s < NA; ++s) { mbar_init(&bars->a_full[s], 1); mbar_init(&bars->a_empty[s], 1); }
-        for (int s = 0; s < NB; ++s) { mbar_init(&bars->b_full[s], 1); mbar_init(&bars->b_empty[s], (uint32_t)csize); }
-        mbar_init(&bars->acc_full, 1);
-        fence_barrier_init();
-    }
-    if (warp == 2) tmem_alloc<512>(&bars->tmem_ptr);
-    tc_fence_before_sync();
-    __syncthreads();
-    if (csize > 1) cluster_sync_all();                 // every peer's barriers exist before anyone multicasts into them
-    tc_fence_after_sync();
-    const uint32_t tmem_base = bars->tmem_ptr;
-
-    if (warp == 0) {
-        // ===================================================== TMA producer: raw int8 tiles of X
-        if (elect_one()) {
-            prefetch_tensormap(&map_x);
-            for (int u = 0; u < n_units; ++u) {
-                const int s = u % NX, kb = kb0 + u / rt, j = u % rt;
-                mbar_wait(&bars->x_empty[s], ((u / NX) & 1) ^ 1);
-                mbar_arrive_expect_tx(&bars->x_full[s], X_STAGE_BYTES);
-                const int32_t mj = (int32_t)(m0 + (int64_t)j * BM);
-                if (BWD) tma_load_2d(x_stage + s * X_STAGE_BYTES, &map_x, &bars->x_full[s], mj, kb * BK);   // [64 k-rows x 128 cols]
-                else     tma_load_2d(x_stage + s * X_STAGE_BYTES, &map_x, &bars->x_full[s], kb * BK, mj);   // [128 rows x 64 k]
-            }
-        }
-    } else if (warp == 3) {
-        // ===================================================== TMA producer: bf16 terms of the fp32 operand
-        if (elect_one()) {
-            prefetch_tensormap(&map_b);
-            for (int i = 0; i < n_kb; ++i) {
-                const int s = i % NB, kb = kb0 + i;
-                mbar_wait(&bars->b_empty[s], ((i / NB) & 1) ^ 1);
-                mbar_arrive_expect_tx(&bars->b_full[s], (uint32_t)(terms * b_tile_bytes));
-                uint8_t* dst = b_tiles + (size_t)s * terms * b_tile_bytes;
-                for (int t = 0; t < terms; ++t) {
-                    uint8_t* tile = dst + t * b_tile_bytes;
-                    if (BWD) {   // two 64-feature groups of [64 k-rows x 128 B]; a CTA fetches BK / csize k-rows of each
-                        const int rows = BK / csize, r0 = (int)crank * rows;
-                        const int32_t grow = (int32_t)(t * b_term_rows + kb * BK + r0);
-                        if (csize > 1) {
-                            tma_load_2d_multicast(tile + r0 * 128, &map_b, &bars->b_full[s], 0, grow, cmask);
-                            tma_load_2d_multicast(tile + BK * 128 + r0 * 128, &map_b, &bars->b_full[s], 64, grow, cmask);
-                        } else {
-                            tma_load_2d(tile, &map_b, &bars->b_full[s], 0, grow);
-                            tma_load_2d(tile + BK * 128, &map_b, &bars->b_full[s], 64, grow);
-                        }
-                    } else {     // [n_pad rows x 64 k]; a CTA fetches n_pad / csize rows
-                        const int rows = n_pad / csize, r0 = (int)crank * rows;
-                        if (csize > 1)
-                            tma_load_2d_multicast(tile + r0 * 128, &map_b, &bars->b_full[s], kb * BK, (int32_t)(t * b_term_rows + r0), cmask);
-                        else
-                            tma_load_2d(tile, &map_b, &bars->b_full[s], kb * BK, (int32_t)(t * b_term_rows));
-                    }
-                }
-            }
-        }
-    } else if (warp == 1) {
-        // ===================================================== MMA issuer (one thread)
-        if (elect_one()) {
-            const uint32_t idesc = make_idesc(/*F32*/ 1, /*BF16*/ 1, BWD ? 1 : 0, BWD ? 1 : 0, BM, (uint32_t)n_pad);
-            const uint32_t idesc2 = make_idesc(1, 1, BWD ? 1 : 0, BWD ? 1 : 0, BM, (uint32_t)(2 * n_pad));
-            for (int u = 0; u < n_units; ++u) {
-                const int i = u / rt, j = u % rt;
-                const int sa = u % NA, sb = i % NB;
-                mbar_wait(&bars->a_full[sa], (u / NA) & 1);
-                if (j == 0) mbar_wait(&bars->b_full[sb], (i / NB) & 1);
-                tc_fence_after_sync();
-                const uint32_t a_addr = smem_u32(a_tiles + sa * A_BYTES);
-                const uint32_t b_addr0 = smem_u32(b_tiles + (size_t)sb * terms * b_tile_bytes);
-                const uint32_t d_tmem = tmem_base + (uint32_t)j * ACC_COLS;
-                // Terms are stacked along N in shared memory, so two of them form ONE operand of N = 2 * n_pad: the
-                // hi and lo products land in adjacent accumulator column blocks (summed in the epilogue) and the A tile
-                // is read from shared memory once per k16 instead of once per term (UMMA operand reads are what
-                // saturates the 128 B/clk of shared memory here).
-                for (int t = 0; t < terms; t += 2) {
-                    const bool pair = (t + 1 < terms) && (2 * n_pad <= 256);
-                    const uint32_t b_addr = b_addr0 + t * b_tile_bytes;
-                    const uint32_t idesc_t = pair ? idesc2 : idesc;
-                    const uint32_t d_col = d_tmem;
-#pragma unroll
-                    for (int k16 = 0; k16 < BK / 16; ++k16) {
-                        uint64_t da, db;
-                        if (BWD) {   // MN-major: 16 k = two 8-row atoms (2048 B); 64-element groups BK * 128 B apart
-                            da = make_smem_desc(a_addr + k16 * 2048, BK * 128, 1024);
-                            db = make_smem_desc(b_addr + k16 * 2048, BK * 128, 1024);
-                        } else {     // K-major: 16 k = 32 B inside the 128-byte row
-                            da = make_smem_desc(a_addr + k16 * 32, 16, 1024);
-                            db = make_smem_desc(b_addr + k16 * 32, 16, 1024);
-                        }
-                        // a paired MMA writes columns [0, 2 n_pad); a single one (third term) accumulates into [0, n_pad)
-                        mma_bf16_ss(d_col, da, db, idesc_t, (i > 0 || t > 0 || k16 > 0) ? 1u : 0u);
-                    }
-                    if (!pair && t + 1 < terms) {      // n_pad too wide to pair: fall back to one MMA per term
-                        const uint32_t b_addr1 = b_addr + b_tile_bytes;
-#pragma unroll
-                        for (int k16 = 0; k16 < BK / 16; ++k16) {
-                            uint64_t da, db;
-                            if (BWD) {
-                                da = make_smem_desc(a_addr + k16 * 2048, BK * 128, 1024);
-                                db = make_smem_desc(b_addr1 + k16 * 2048, BK * 128, 1024);
-                            } else {
-                                da = make_smem_desc(a_addr + k16 * 32, 16, 1024);
-                                db = make_smem_desc(b_addr1 + k16 * 32, 16, 1024);
-                            }
-                            mma_bf16_ss(d_col, da, db, idesc, 1u);
-                        }
-                    }
-                }
-                tc_commit(&bars->a_empty[sa]);
-                if (j == rt - 1) {
-                    if (csize > 1) tc_commit_multicast(&bars->b_empty[sb], cmask);     // every producer of the cluster may refill this slot
-                    else           tc_commit(&bars->b_empty[sb]);
-                }
-            }
-            tc_commit(&bars->acc_full);
-        }
-    } else if (warp >= 4) {
-        // ===================================================== converter: int8 staging -> bf16 UMMA operand
-        const int t = threadIdx.x - 128;
-        const int lane = threadIdx.x & 31, cw = warp - 4;
-        for (int u = cw; u < n_units; u += CW) {
-            const int sx = u % NX, sa = u % NA;
-            mbar_wait(&bars->x_full[sx], (u / NX) & 1);
-            mbar_wait(&bars->a_empty[sa], ((u / NA) & 1) ^ 1);
-            const uint8_t* src = x_stage + sx * X_STAGE_BYTES;
-            uint8_t* dst = a_tiles + sa * A_BYTES;
-            // 512 16-byte chunks per tile, 16 per lane, in batches of 8: all loads of a batch are issued before any
-            // conversion or store so that their shared-memory latencies overlap (explicit ld/st.shared: no alias stalls)
-            const uint32_t src_s = smem_u32(src), dst_s = smem_u32(dst);
-#pragma unroll 1
-            for (int b0 = 0; b0 < 16; b0 += 8) {
-                uint4 in[8];
-#pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    const int task = (b0 + q) * 32 + lane;
-                    // fwd staging [128 rows][64 B]: chunk c = task & 3 of row task >> 2  -> byte offset task * 16
-                    // bwd staging [64 k-rows][128 B]: chunk c = task & 7 of row task >> 3 -> byte offset task * 16
-                    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                                 : "=r"(in[q].x), "=r"(in[q].y), "=r"(in[q].z), "=r"(in[q].w) : "r"(src_s + task * 16));
-                }
-#pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    const int task = (b0 + q) * 32 + lane;
-                    uint4 lo, hi;
-                    cvt16(in[q], lo, hi);
-                    uint32_t row_off, j0, sw;
-                    if (BWD) {
-                        // MN-major operand: group g = 64 columns, k-row r: 128 B = 8 chunks, chunk j stored at j ^ (r % 8)
-                        const int c = task & 7, r = task >> 3;
-                        row_off = (uint32_t)((c >> 2) * (BK * 128) + (r >> 3) * 1024 + (r & 7) * 128);
-                        j0 = 2 * (c & 3);
-                        sw = r & 7;
-                    } else {
-                        // K-major operand: row r holds 64 k = 128 B = 8 chunks, chunk j stored at j ^ (r % 8)
-                        const int c = task & 3, r = task >> 2;
-                        row_off = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128);
-                        j0 = 2 * c;
-                        sw = r & 7;
-                    }
-                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};"
-                                 :: "r"(dst_s + row_off + ((j0 ^ sw) << 4)), "r"(lo.x), "r"(lo.y), "r"(lo.z), "r"(lo.w) : "memory");
-                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};"
-                                 :: "r"(dst_s + row_off + (((j0 + 1) ^ sw) << 4)), "r"(hi.x), "r"(hi.y), "r"(hi.z), "r"(hi.w) : "memory");
-                }
-            }
-            fence_proxy_async();                       // generic-proxy stores -> visible to the tensor-core (async) proxy
-            __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(&bars->a_full[sa]);
-                mbar_arrive(&bars->x_empty[sx]);
-            }
-        }
-        // ===================================================== epilogue: accumulators -> (partial) output
-        mbar_wait(&bars->acc_full, 0);
-        tc_fence_after_sync();
-        const int wq = warp & 3;
-        float* dst_out = out + (int64_t)blockIdx.y * split_stride;
-        const bool paired = terms >= 2 && 2 * n_pad <= 256;
-        for (int j = 0; j < rt; ++j) {
-            const int64_t m = m0 + (int64_t)j * BM + t;        // fwd: row of X; bwd: column of X (marker)
-#pragma unroll 1
-            for (int chunk = 0; chunk * 32 < n_pad; ++chunk) {
-                uint32_t v[32], w[32];
-                const uint32_t taddr = tmem_base + ((uint32_t)(32 * wq) << 16) + (uint32_t)j * ACC_COLS + chunk * 32;
-                tmem_ld_32x32b_x32(taddr, v);
-                if (paired) tmem_ld_32x32b_x32(taddr + (uint32_t)n_pad, w);      // the lo-term products
-                tmem_ld_wait();
-                if (m < m_total && n_kb > 0) {
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) {
-                        const int f = chunk * 32 + c;
-                        if (f < n_valid) {
-                            const float r = paired ? __uint_as_float(v[c]) + __uint_as_float(w[c]) : __uint_as_float(v[c]);
-                            if (BWD) dst_out[(int64_t)f * ld_out + m] = r;    // dW[f, marker]: a warp writes 32 consecutive markers
-                            else     dst_out[m * ld_out + f] = r;             // H[row, f]
-                        }
-                    }
-                }
-            }
-        }
-    }
-    tc_fence_before_sync();
-    __syncthreads();
-    if (csize > 1) cluster_sync_all();                 // no CTA leaves while a peer can still write into its shared memory
-    if (warp == 2) tmem_dealloc<512>(tmem_base);
-}
 
 // ------------------------------------------------------------------------------------------------------------------
 // Projection kernels with the A operand (the X tile) in TENSOR MEMORY.
@@ -544,88 +283,6 @@ linear_ta_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     if (warp == 2) tmem_dealloc<512>(tmem_base);
 }
 
-// out[i] = sum_s part[s * stride + i] in a fixed order (split-K partials -> result)
-__global__ void splitk_sum_kernel(const float* __restrict__ part, int n_splits, int64_t stride, int64_t rows, int64_t cols,
-                                  int64_t ld_part, float* __restrict__ out, int64_t ld_out) {
-    const int64_t total = rows * cols;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t r = i / cols, c = i % cols;
-        float s = 0.f;
-        for (int sp = 0; sp < n_splits; ++sp) s += part[(int64_t)sp * stride + r * ld_part + c];
-        out[r * ld_out + c] = s;
-    }
-}
-
-// cluster size for the multicast of the term tiles: GNNB_LINEAR_CLUSTER (1, 2, 4 or 8); default 1 -- measured no gain,
-// because what limits the kernel is the bytes an SM can take in per clock, and a multicast still delivers every byte.
-static int cluster_size(int64_t supertiles) {
-    static int forced = -1;
-    if (forced < 0) {
-        const char* e = getenv("GNNB_LINEAR_CLUSTER");
-        int v = e ? atoi(e) : 0;
-        forced = (v == 1 || v == 2 || v == 4 || v == 8) ? v : 1;
-    }
-    int c = forced;
-    while (c > 1 && supertiles < 2 * c) c >>= 1;
-    return c;
-}
-
-// X tiles per CTA (GNNB_LINEAR_RT overrides) and k-splits so that the grid still fills the GPU
-static void plan_tiles(int64_t tiles, int64_t n_kb, int* rt_out, int* splits_out) {
-    static int forced = -1;
-    if (forced < 0) {
-        const char* e = getenv("GNNB_LINEAR_RT");
-        int v = e ? atoi(e) : 0;
-        forced = (v == 1 || v == 2 || v == 4) ? v : 0;
-    }
-    // default 1: measured on B200, sharing a term tile between 2 or 4 X tiles does not pay -- the kernel is bound by
-    // shared-memory bandwidth (UMMA operand reads + TMA writes + the converter), not by L2 -> SM traffic
-    int rt = forced ? forced : 1;
-    if (rt > 512 / ACC_COLS) rt = 512 / ACC_COLS;          // TMEM holds 512 columns
-    int64_t supertiles = (tiles + rt - 1) / rt;
-    int64_t s = sm_count() / supertiles;
-    if (s > n_kb / 16) s = n_kb / 16;
-    if (s > MAX_SPLITS) s = MAX_SPLITS;
-    if (s < 1) s = 1;
-    *rt_out = rt;
-    *splits_out = (int)s;
-}
-
-template <bool BWD>
-static int launch_tc(const CUtensorMap& map_x, const CUtensorMap& map_b, int64_t k_total, int terms, int n_pad, int64_t b_term_rows,
-                     float* out, int64_t ld_out, int64_t out_rows, int64_t out_cols, float* partial, int64_t m_total, int n_valid,
-                     int64_t tiles, size_t smem, cudaStream_t stream) {
-    int rt, splits;
-    plan_tiles(tiles, (k_total + BK - 1) / BK, &rt, &splits);
-    const int64_t supertiles = (tiles + rt - 1) / rt;
-    const int csize = cluster_size(supertiles);
-    { static size_t hw_ = 0; if ((size_t)(smem) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(linear_tc_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem))); hw_ = (size_t)(smem); } }
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)((supertiles + csize - 1) / csize * csize), (unsigned)splits);
-    cfg.blockDim = dim3(256);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = (unsigned)csize;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    float* dst = splits > 1 ? partial : out;
-    const int64_t ld_dst = splits > 1 ? out_cols : ld_out;
-    const int64_t stride = splits > 1 ? out_rows * out_cols : 0;
-    GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_tc_kernel<BWD>, map_x, map_b, k_total, terms, n_pad, b_term_rows, dst, ld_dst, stride,
-                                 m_total, n_valid, csize, rt));
-    if (splits > 1) {
-        int64_t total = out_rows * out_cols, blocks = (total + 255) / 256, cap = (int64_t)sm_count() * 16;
-        splitk_sum_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, stream>>>(partial, splits, stride, out_rows, out_cols,
-                                                                                     out_cols, out, ld_out);
-        GNNB_LAUNCH_CHECK();
-    }
-    return GNNB_OK;
-}
-
 static bool tc_shape_ok(const void* X, int64_t ldx, int64_t h) {
     return (uintptr_t)X % 16 == 0 && ldx % 16 == 0 && h >= 1 && h <= 128;
 }
@@ -637,8 +294,7 @@ static size_t terms_bytes_bwd(int64_t n, int terms) { return align_up((size_t)te
 
 size_t linear_tc_workspace(int64_t n, int64_t p, int64_t h, int terms) {
     if (h > 128 || terms < 1 || terms > MAX_TERMS) return 0;
-    size_t fwd = terms_bytes_fwd(p, h, terms) + (size_t)MAX_SPLITS * n * h * sizeof(float);     // W terms + split-K partials of H
-    size_t bwd = terms_bytes_bwd(n, terms) + (size_t)MAX_SPLITS * h * p * sizeof(float);        // dH terms + partials of dW
+    size_t fwd = terms_bytes_fwd(p, h, terms), bwd = terms_bytes_bwd(n, terms);          // bf16 terms of W / of dH
     return (fwd > bwd ? fwd : bwd) + 2048;
 }
 
@@ -652,46 +308,29 @@ int linear_tc_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
                   float* H, int64_t ldh, int terms, void* ws, size_t ws_bytes, cudaStream_t stream) {
     if (!x_is_i8 || !tc_shape_ok(X, ldx, h) || p < 64 || n < 1)
         return linear_simt_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, ws, ws_bytes, stream);    // small / float inputs: exact fp32 tiles
-    // h is padded to a multiple of 32 so that a quarter of the term tile (a multicast slice) is whole 8-row swizzle atoms
-    static int use_ta = -1;
-    if (use_ta < 0) { const char* e = getenv("GNNB_LINEAR_TA"); use_ta = e ? atoi(e) : 1; }
-    // the TMEM-operand kernel pads h to the UMMA granule of 16 (h = 100 -> N = 2 x 112); the legacy kernel to 32
-    const int64_t p_ld = (int64_t)align_up((size_t)p, 8), h_pad = (int64_t)align_up((size_t)h, use_ta ? 16 : 32);
+    // h is padded to the UMMA granule of 16 (h = 100 -> hi | lo = one operand of N = 2 x 112)
+    const int64_t p_ld = (int64_t)align_up((size_t)p, 8), h_pad = (int64_t)align_up((size_t)h, 16);
     const size_t need = linear_tc_workspace(n, p, h, terms);
     GNNB_REQUIRE(ws && ws_bytes >= need, GNNB_E_WORKSPACE, "linear_fwd: workspace %zu < %zu bytes", ws_bytes, need);
     uint8_t* wsb = reinterpret_cast<uint8_t*>(align_up((size_t)(uintptr_t)ws, 1024));
     __nv_bfloat16* Wt = reinterpret_cast<__nv_bfloat16*>(wsb);
-    float* partial = reinterpret_cast<float*>(wsb + terms_bytes_fwd(p, h, terms));
     {
         int64_t total = h_pad * p_ld, blocks = (total + 255) / 256, cap = (int64_t)sm_count() * 16;
         split_terms_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, stream>>>(W, ldw, h, p, Wt, h_pad, p_ld, p_ld, terms);
         GNNB_LAUNCH_CHECK();
     }
     const int64_t tiles = (n + BM - 1) / BM;
-    if (use_ta && h_pad <= 128) {
-        // A operand in tensor memory (see linear_fwd_ta_kernel)
-        CUtensorMap mx, mb;
-        int rc2 = make_tensor_map_2d(&mx, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, BK, BM, false, /*swizzle64*/ true);
-        if (rc2 != GNNB_OK) return rc2;
-        rc2 = make_tensor_map_2d(&mb, Wt, 2, (uint64_t)p_ld, (uint64_t)(terms * h_pad), (uint64_t)p_ld * 2, BK, (uint32_t)h_pad, true);
-        if (rc2 != GNNB_OK) return rc2;
-        const int btile = (int)(h_pad * BK * 2);
-        const size_t smem_ta = ta_fixed() + (size_t)ta_nb(terms, btile) * terms * btile;
-        { static size_t hw_ = 0; if ((size_t)(smem_ta) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(linear_ta_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem_ta))); hw_ = (size_t)(smem_ta); } }
-        linear_ta_kernel<false><<<(unsigned)tiles, TA_THREADS, smem_ta, stream>>>(mx, mb, p, terms, (int)h_pad, h_pad, H, ldh, n, (int)h);
-        GNNB_LAUNCH_CHECK();
-        return GNNB_OK;
-    }
-    int rt, splits;
-    plan_tiles(tiles, (p + BK - 1) / BK, &rt, &splits);
-    const int csize = cluster_size((tiles + rt - 1) / rt);
-    CUtensorMap map_x, map_b;
-    int rc = make_tensor_map_2d(&map_x, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, BK, BM, /*swizzle*/ false);
+    CUtensorMap mx, mb;
+    int rc = make_tensor_map_2d(&mx, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, BK, BM, false, /*swizzle64*/ true);
     if (rc != GNNB_OK) return rc;
-    rc = make_tensor_map_2d(&map_b, Wt, 2, (uint64_t)p_ld, (uint64_t)(terms * h_pad), (uint64_t)p_ld * 2, BK, (uint32_t)(h_pad / csize), true);
+    rc = make_tensor_map_2d(&mb, Wt, 2, (uint64_t)p_ld, (uint64_t)(terms * h_pad), (uint64_t)p_ld * 2, BK, (uint32_t)h_pad, true);
     if (rc != GNNB_OK) return rc;
-    const size_t smem = tc_smem_bytes(terms, (int)(h_pad * BK * 2));
-    return launch_tc<false>(map_x, map_b, p, terms, (int)h_pad, h_pad, H, ldh, n, h, partial, n, (int)h, tiles, smem, stream);
+    const int btile = (int)(h_pad * BK * 2);
+    const size_t smem_ta = ta_fixed() + (size_t)ta_nb(terms, btile) * terms * btile;
+    { static size_t hw_ = 0; if (smem_ta > hw_) { GNNB_CUDA(cudaFuncSetAttribute(linear_ta_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ta)); hw_ = smem_ta; } }
+    linear_ta_kernel<false><<<(unsigned)tiles, TA_THREADS, smem_ta, stream>>>(mx, mb, p, terms, (int)h_pad, h_pad, H, ldh, n, (int)h);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
 }
 
 int linear_tc_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
@@ -702,38 +341,23 @@ int linear_tc_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t 
     GNNB_REQUIRE(ws && ws_bytes >= need, GNNB_E_WORKSPACE, "linear_bwd_w: workspace %zu < %zu bytes", ws_bytes, need);
     uint8_t* wsb = reinterpret_cast<uint8_t*>(align_up((size_t)(uintptr_t)ws, 1024));
     __nv_bfloat16* Dt = reinterpret_cast<__nv_bfloat16*>(wsb);
-    float* partial = reinterpret_cast<float*>(wsb + terms_bytes_bwd(n, terms));
     {
         int64_t total = n * 128, blocks = (total + 255) / 256, cap = (int64_t)sm_count() * 16;
         split_terms_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, stream>>>(dH, lddh, n, h, Dt, n, 128, 128, terms);
         GNNB_LAUNCH_CHECK();
     }
     const int64_t tiles = (p + BM - 1) / BM;
-    static int use_ta = -1;
-    if (use_ta < 0) { const char* e = getenv("GNNB_LINEAR_TA"); use_ta = e ? atoi(e) : 1; }
-    if (use_ta) {
-        CUtensorMap mx, mb;
-        int rc2 = make_tensor_map_2d(&mx, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, 128, BK, /*swizzle*/ false);
-        if (rc2 != GNNB_OK) return rc2;
-        rc2 = make_tensor_map_2d(&mb, Dt, 2, 128, (uint64_t)(terms * n), 256, 64, BK, true);
-        if (rc2 != GNNB_OK) return rc2;
-        const int btile = BK * 128 * 2;
-        const size_t smem_ta = ta_fixed() + (size_t)ta_nb(terms, btile) * terms * btile;
-        { static size_t hw_ = 0; if ((size_t)(smem_ta) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(linear_ta_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem_ta))); hw_ = (size_t)(smem_ta); } }
-        linear_ta_kernel<true><<<(unsigned)tiles, TA_THREADS, smem_ta, stream>>>(mx, mb, n, terms, 128, n, dW, lddw, p, (int)h);
-        GNNB_LAUNCH_CHECK();
-        return GNNB_OK;
-    }
-    int rt, splits;
-    plan_tiles(tiles, (n + BK - 1) / BK, &rt, &splits);
-    const int csize = cluster_size((tiles + rt - 1) / rt);
-    CUtensorMap map_x, map_b;
-    int rc = make_tensor_map_2d(&map_x, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, 128, BK, /*swizzle*/ false);
+    CUtensorMap mx, mb;
+    int rc = make_tensor_map_2d(&mx, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, 128, BK, /*swizzle*/ false);
     if (rc != GNNB_OK) return rc;
-    rc = make_tensor_map_2d(&map_b, Dt, 2, 128, (uint64_t)(terms * n), 256, 64, (uint32_t)(BK / csize), true);
+    rc = make_tensor_map_2d(&mb, Dt, 2, 128, (uint64_t)(terms * n), 256, 64, BK, true);
     if (rc != GNNB_OK) return rc;
-    const size_t smem = tc_smem_bytes(terms, BK * 128 * 2);
-    return launch_tc<true>(map_x, map_b, n, terms, 128, n, dW, lddw, h, p, partial, p, (int)h, tiles, smem, stream);
+    const int btile = BK * 128 * 2;
+    const size_t smem_ta = ta_fixed() + (size_t)ta_nb(terms, btile) * terms * btile;
+    { static size_t hw_ = 0; if (smem_ta > hw_) { GNNB_CUDA(cudaFuncSetAttribute(linear_ta_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ta)); hw_ = smem_ta; } }
+    linear_ta_kernel<true><<<(unsigned)tiles, TA_THREADS, smem_ta, stream>>>(mx, mb, n, terms, 128, n, dW, lddw, p, (int)h);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
 }
 
 }  // namespace gnnb
