@@ -112,7 +112,8 @@ def _declare(**work):
 def synth_genotypes(n, p, device, row0=0, p_total=None, seed=20240601, seed_freq=20240602, out=None):
     """int8 [n, p] block of the stateless synthetic genotype matrix."""
     p_total = p if p_total is None else p_total
-    X = out if out is not None else torch.empty((n, p), dtype=torch.int8, device=device)
+    # rows padded to 16 bytes, like every genotype matrix of this package (TMA needs 16-byte strides)
+    X = out if out is not None else torch.zeros((n, (p + 15) // 16 * 16), dtype=torch.int8, device=device)[:, :p]
     _need_cuda(X)
     with torch.cuda.device(X.device):
         _call("gnnb_synth_genotypes", _p(X), n, p, X.stride(0), row0, p_total, seed, seed_freq, _stream())
