@@ -49,6 +49,9 @@ def parse():
     ap.add_argument("--hidden", type=int, default=HIDDEN)
     ap.add_argument("--precision", default="auto")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--resident", choices=("packed", "int8"), default="packed",
+                    help="format of the genotypes kept in HBM for training: 2-bit packed (default; the projection kernels expand "
+                         "them on chip) or int8 codes")
     ap.add_argument("--e2e-format", choices=("packed", "int8"), default="packed",
                     help="host format of the genotypes in the end-to-end arm: 2-bit packed (default) or int8 codes")
     ap.add_argument("--cuda-graph", default="auto", choices=["auto", "on", "off"],
@@ -170,6 +173,8 @@ def run_ours(a):
         ew = g.edge_weight.float()
         g.edge_weight = ew                                           # float32 once, as get_args_tuple would per call
         ops.gcn_graph(g.edge_index, g.edge_weight, g.x.shape[0], True)
+        if a.resident == "packed":                                   # the graph is built; from here on only the projection reads x
+            g.x = ops.pack_2bit(g.x)
     torch.cuda.synchronize()
     setup_s = time.time() - t_setup
 
@@ -281,9 +286,9 @@ def run_ours(a):
     e2e = None
     if not a.no_e2e:
         host = []
-        packed = a.e2e_format == "packed"
+        packed = a.e2e_format == "packed" or a.resident == "packed"
         for g in batches:
-            src = ops.pack_2bit(g.x) if packed else g.x
+            src = g.x if g.x.dtype == torch.uint8 else (ops.pack_2bit(g.x) if packed else g.x)
             hx = torch.empty(src.shape, dtype=src.dtype).pin_memory()
             hx.copy_(src)
             del src
@@ -297,7 +302,7 @@ def run_ours(a):
             with torch.cuda.stream(copy_stream):
                 hx, hei, hew, hy = host[i]
                 x = hx.to(dev, non_blocking=True)
-                if packed:
+                if packed and a.resident != "packed":
                     x = ops.unpack_2bit(x, p)                             # expanded to int8 codes on the device
                 d = Data(x=x, edge_index=hei.to(dev, non_blocking=True), y=hy.to(dev, non_blocking=True))
                 d.edge_weight = hew.to(dev, non_blocking=True)
@@ -330,7 +335,8 @@ def run_ours(a):
             dist.all_reduce(moved)                                       # whole job: every rank copies its own subgraphs
         e2e = {"value": 1000.0 / ms_e2e, "unit": "epochs/s", "h2d_bytes_per_step": int(moved[0]),
                "d2h_bytes_per_step": int(moved[1]),
-               "host_format": "2-bit packed genotypes (4 codes per byte), expanded to int8 on the device" if packed else "int8 genotypes",
+               "host_format": ("2-bit packed genotypes (4 codes per byte), " + ("consumed packed by the projection kernels"
+                               if a.resident == "packed" else "expanded to int8 on the device")) if packed else "int8 genotypes",
                "note": "per epoch: every owned subgraph's genotypes + edge list + weights + phenotypes H2D from pinned "
                        "memory (prefetched one subgraph ahead on a copy stream), gcn_norm/CSR rebuilt per step, loss D2H per step"}
 
@@ -359,7 +365,7 @@ def run_ours(a):
                         "traffic": None}
         roofline["peak_source"] = "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)"
         try:    # DRAM bytes per launch of this kernel from the committed ncu capture (same shape as a training subgraph)
-            tr = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json"))).get(name)
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json"))).get(name if a.resident == "packed" or not name.startswith("gnnb_linear") else name + "@int8")
             if tr and tr["shape"][:2] == [per, p]:
                 roofline["traffic"] = tr["dram_bytes"]
                 roofline["traffic_source"] = "profiles/r01_traffic.json (" + tr["kernel"] + ", ncu --set full)"
@@ -368,7 +374,7 @@ def run_ours(a):
         if name.startswith("gnnb_linear"):
             roofline["note"] = ("the projection runs on the int8 tensor pipe (three 7-bit digits of the float operand, 3 x the "
                                 "algorithmic MACs issued); `achieved` counts the algorithmic 2*n*p*h against the measured bf16 peak; "
-                                "as an HBM stream it moves n*p int8 bytes per launch: "
+                                "as an HBM stream it moves the genotype matrix once per launch (n*p/4 bytes when 2-bit packed, n*p as int8): "
                                 f"{st['bytes'] / st['calls'] / (avg_ms * 1e-3) / 1e9:.0f} GB/s of {peaks.get('hbm_gbs', 6650.0):.0f}")
         roofline["avg_launch_ms"] = avg_ms
         roofline["share_of_step"] = st["ms"] / (ms_per_epoch * prof_steps)
@@ -384,10 +390,12 @@ def run_ours(a):
     line = {
         "metric": "train epochs/sec", "value": 1000.0 / ms_per_epoch, "unit": "epochs/s", "n_gpus": world, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": ms_per_epoch, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "f32 (int8 genotypes; marker projection on int8 tensor cores with the float operand quantised to 21 bits per feature)", "data": "synthetic",
+        "dtype": "f32 (genotype codes 2-bit packed in HBM, int8 on chip; marker projection on int8 tensor cores with the float operand quantised to 21 bits per feature)", "data": "synthetic",
         "config": {"workload": workload_name(a),
                    "parallelism": f"dp{world} (subgraphs sharded, flat-gradient all-reduce)",
                    "linear_precision": ops.config["linear_precision"], "cuda_graphs": bool(use_graphs),
+                   "resident_genotypes": "2-bit packed (12.5 GB at C5), expanded on chip by the projection kernels" if a.resident == "packed"
+                                         else "int8 codes (50 GB at C5)",
                    "l2": "inputs per epoch far exceed L2 (genotypes >= 0.78 GB per subgraph); no flush needed",
                    "setup_s": round(setup_s, 1), "final_train_loss": float(losses_host[-2]),
                    "final_test_loss": float(losses_host[-1])},

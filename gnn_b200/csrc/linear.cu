@@ -278,9 +278,9 @@ size_t linear_tc_workspace(int64_t n, int64_t p, int64_t h, int terms);
 // int8-limb implementation (linear_i8.cu), precision 4; shapes it does not take fall back to two bf16 terms
 bool linear_i8_supported(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, int64_t h);
 size_t linear_i8_workspace(int64_t n, int64_t p, int64_t h);
-int linear_i8_fwd(const int8_t* X, int64_t ldx, int64_t n, int64_t p, const float* W, int64_t ldw, int64_t h,
+int linear_i8_fwd(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p, const float* W, int64_t ldw, int64_t h,
                   float* H, int64_t ldh, void* ws, size_t ws_bytes, cudaStream_t stream);
-int linear_i8_bwd_w(const int8_t* X, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
+int linear_i8_bwd_w(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
                     float* dW, int64_t lddw, void* ws, size_t ws_bytes, cudaStream_t stream);
 
 int linear_simt_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* W, int64_t ldw, int64_t h,
@@ -358,14 +358,18 @@ int gnnb_linear_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t 
                     void* workspace, size_t workspace_bytes, void* stream_) {
     GNNB_ENTER();
     cudaStream_t stream = (cudaStream_t)stream_;
-    GNNB_REQUIRE(X && W && H && n >= 0 && p > 0 && h > 0 && ldx >= p && ldw >= p && ldh >= h, GNNB_E_BADARG, "linear_fwd: bad argument");
+    GNNB_REQUIRE(X && W && H && n >= 0 && p > 0 && h > 0 && ldx >= (x_is_i8 == 2 ? (p + 3) / 4 : p) && ldw >= p && ldh >= h, GNNB_E_BADARG, "linear_fwd: bad argument");
+    GNNB_REQUIRE(x_is_i8 >= 0 && x_is_i8 <= 2, GNNB_E_BADARG, "linear_fwd: x format must be 0 (float32), 1 (int8) or 2 (2-bit packed)");
     GNNB_REQUIRE(precision >= 0 && precision <= 4, GNNB_E_BADARG, "linear_fwd: precision must be 0..4");
     if (n == 0) return GNNB_OK;
     if (precision == 4) {
         if (linear_i8_supported(X, x_is_i8, ldx, n, p, h))
-            return linear_i8_fwd((const int8_t*)X, ldx, n, p, W, ldw, h, H, ldh, workspace, workspace_bytes, stream);
+            return linear_i8_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, workspace, workspace_bytes, stream);
         precision = 2;
     }
+    if (x_is_i8 == 2)
+        return fail(GNNB_E_UNSUPPORTED, "linear_fwd: 2-bit packed X needs precision 4, 16-byte aligned rows, n >= 128, p >= 128 and h <= 112 "
+                                        "(expand it with gnnb_unpack_2bit for other shapes)");
     if (precision > 0) return linear_tc_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, precision, workspace, workspace_bytes, stream);
     return linear_simt_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, workspace, workspace_bytes, stream);
 }
@@ -375,7 +379,8 @@ int gnnb_linear_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_
                       void* workspace, size_t workspace_bytes, void* stream_) {
     GNNB_ENTER();
     cudaStream_t stream = (cudaStream_t)stream_;
-    GNNB_REQUIRE(X && dH && dW && n >= 0 && p > 0 && h > 0 && ldx >= p && lddh >= h && lddw >= p, GNNB_E_BADARG, "linear_bwd_w: bad argument");
+    GNNB_REQUIRE(X && dH && dW && n >= 0 && p > 0 && h > 0 && ldx >= (x_is_i8 == 2 ? (p + 3) / 4 : p) && lddh >= h && lddw >= p, GNNB_E_BADARG, "linear_bwd_w: bad argument");
+    GNNB_REQUIRE(x_is_i8 >= 0 && x_is_i8 <= 2, GNNB_E_BADARG, "linear_bwd_w: x format must be 0 (float32), 1 (int8) or 2 (2-bit packed)");
     GNNB_REQUIRE(precision >= 0 && precision <= 4, GNNB_E_BADARG, "linear_bwd_w: precision must be 0..4");
     if (n == 0) {
         GNNB_CUDA(cudaMemset2DAsync(dW, lddw * sizeof(float), 0, p * sizeof(float), h, stream));
@@ -383,9 +388,12 @@ int gnnb_linear_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_
     }
     if (precision == 4) {
         if (linear_i8_supported(X, x_is_i8, ldx, n, p, h))
-            return linear_i8_bwd_w((const int8_t*)X, ldx, n, p, dH, lddh, h, dW, lddw, workspace, workspace_bytes, stream);
+            return linear_i8_bwd_w(X, x_is_i8, ldx, n, p, dH, lddh, h, dW, lddw, workspace, workspace_bytes, stream);
         precision = 2;
     }
+    if (x_is_i8 == 2)
+        return fail(GNNB_E_UNSUPPORTED, "linear_bwd_w: 2-bit packed X needs precision 4, 16-byte aligned rows, n >= 128, p >= 128 and h <= 112 "
+                                        "(expand it with gnnb_unpack_2bit for other shapes)");
     if (precision > 0)
         return linear_tc_bwd_w(X, x_is_i8, ldx, n, p, dH, lddh, h, dW, lddw, precision, workspace, workspace_bytes, stream);
     return linear_simt_bwd_w(X, x_is_i8, ldx, n, p, dH, lddh, h, dW, lddw, workspace, workspace_bytes, stream);

@@ -304,18 +304,215 @@ linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     if (warp == 2) tmem_dealloc_pair<512>(tmem_base);
 }
 
+// ---- the same GEMM with X as 2-BIT PACKED codes in HBM -----------------------------------------------------------------
+// Genotypes are 0/1/2: four codes per byte (gnnb_pack_2bit).  The X stream -- the only large one -- shrinks fourfold in
+// HBM, in L2 -> SM traffic and in the shared memory its ring needs.  TMA brings the packed tile [128 rows x 32 B]; four
+// converter warps per k-block (thread = row) expand it to the int8 [128 x 128 B] tile in the 128-byte-swizzled UMMA layout
+// (~1 ALU operation per code), fence.proxy.async, and arrive on the LEADER's `afull` barrier (8 arrivals: 4 warps x 2 CTAs);
+// the MMAs then read it exactly as the TMA-written tile of linear_i8_kernel.  The tile is the same for both directions
+// ([128 individuals x 128 markers]; K-major for the forward pass, MN-major for the weight gradient).
+#ifndef P2_PXS
+#define P2_PXS 8
+#endif
+#ifndef P2_AS
+#define P2_AS 4
+#endif
+#ifndef P2_BS
+#define P2_BS 5
+#endif
+constexpr int PXS = P2_PXS, AS = P2_AS, BS2 = P2_BS;     // PXS and AS even (two converter groups)
+constexpr int PX_BYTES = BM * (BKB / 4);                 // 4 KB packed tile
+constexpr int P2_THREADS = 128 + 256;
+
+struct Bars2 {
+    uint64_t pxfull[PXS], pxempty[PXS], afull[AS], aempty[AS], bfull[BS2], bempty[BS2], acc_full;
+    uint32_t tmem_ptr;
+};
+constexpr size_t SMEM2 = 1024 + (size_t)PXS * PX_BYTES + (size_t)AS * A_BYTES + (size_t)BS2 * B_BYTES + sizeof(Bars2) + 64;
+static_assert(SMEM2 <= 232448, "shared memory of linear_p2_kernel");
+
+// one packed word (16 codes) -> four words of four int8 codes: the four 2-bit planes, then a 4 x 4 byte transpose (prmt)
+__device__ __forceinline__ void expand16(uint32_t w, uint32_t (&o)[4]) {
+    const uint32_t A = w & 0x03030303u, B = (w >> 2) & 0x03030303u, C = (w >> 4) & 0x03030303u, D = (w >> 6) & 0x03030303u;
+    const uint32_t ab_lo = __byte_perm(A, B, 0x5140), cd_lo = __byte_perm(C, D, 0x5140);      // {A0,B0,A1,B1}, {C0,D0,C1,D1}
+    const uint32_t ab_hi = __byte_perm(A, B, 0x7362), cd_hi = __byte_perm(C, D, 0x7362);      // {A2,B2,A3,B3}, {C2,D2,C3,D3}
+    o[0] = __byte_perm(ab_lo, cd_lo, 0x5410);
+    o[1] = __byte_perm(ab_lo, cd_lo, 0x7632);
+    o[2] = __byte_perm(ab_hi, cd_hi, 0x5410);
+    o[3] = __byte_perm(ab_hi, cd_hi, 0x7632);
+}
+
 template <bool BWD>
+__global__ void __launch_bounds__(P2_THREADS, 1)
+linear_p2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b0,
+                 const __grid_constant__ CUtensorMap map_b1, int64_t k_total, const float* __restrict__ scale,
+                 float* __restrict__ out, int64_t ld_out, int64_t m_total, int h, int quad) {
+    extern __shared__ uint8_t smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t crank = cluster_ctarank();
+    const uint32_t rank = crank & 1, lead_rank = crank & ~1u, twin = crank >> 1;
+    const bool leader = rank == 0;
+    const uint16_t pair_mask = (uint16_t)(3u << lead_rank), all_mask = quad ? 15 : 3;
+    uint8_t* at = smem_raw + ((1024 - (smem_u32(smem_raw) & 1023)) & 1023);      // expanded A ring (swizzled: 1024-aligned)
+    uint8_t* bt = at + (size_t)AS * A_BYTES;                                   // digit ring
+    uint8_t* px = bt + (size_t)BS2 * B_BYTES;                                  // packed X ring
+    Bars2* bars = reinterpret_cast<Bars2*>(px + (size_t)PXS * PX_BYTES);
+    const int n_kb = (int)((k_total + BKB - 1) / BKB);
+    const int64_t m0 = ((int64_t)(blockIdx.x >> 1) * 2 + rank) * BM;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < PXS; ++s) { mbar_init(&bars->pxfull[s], 1); mbar_init(&bars->pxempty[s], 4); }
+        for (int s = 0; s < AS; ++s) { mbar_init(&bars->afull[s], 8); mbar_init(&bars->aempty[s], 1); }
+        for (int s = 0; s < BS2; ++s) { mbar_init(&bars->bfull[s], 2); mbar_init(&bars->bempty[s], quad ? 2 : 1); }
+        mbar_init(&bars->acc_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc_pair<512>(&bars->tmem_ptr);
+    tc_fence_before_sync();
+    cluster_sync_all();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = bars->tmem_ptr;
+
+    if (warp == 0) {
+        if (elect_one()) {                                             // TMA producer of the packed X ring (CTA-local)
+            prefetch_tensormap(&map_x);
+            for (int u = 0; u < n_kb; ++u) {
+                const int s = u % PXS;
+                mbar_wait(&bars->pxempty[s], ((u / PXS) & 1) ^ 1);
+                mbar_arrive_expect_tx(&bars->pxfull[s], PX_BYTES);
+                if (BWD) tma_load_2d(px + (size_t)s * PX_BYTES, &map_x, &bars->pxfull[s], (int32_t)(m0 / 4), u * BKB);   // 128 individuals x 32 B
+                else     tma_load_2d(px + (size_t)s * PX_BYTES, &map_x, &bars->pxfull[s], u * (BKB / 4), (int32_t)m0);
+            }
+        }
+    } else if (warp == 3) {
+        if (elect_one()) {                                             // TMA producer of the digit ring (as in linear_i8_kernel)
+            prefetch_tensormap(&map_b0);
+            prefetch_tensormap(&map_b1);
+            for (int u = 0; u < n_kb; ++u) {
+                const int s = u % BS2;
+                mbar_wait(&bars->bempty[s], ((u / BS2) & 1) ^ 1);
+                const uint32_t full_leader = mapa_u32(smem_u32(&bars->bfull[s]), lead_rank);
+                if (leader) mbar_arrive_expect_tx(&bars->bfull[s], 2 * B_BYTES);
+                else        mbar_arrive_cluster(full_leader);
+                uint8_t* b = bt + (size_t)s * B_BYTES;
+                if (quad) {
+                    const uint16_t mc = (uint16_t)((1u << rank) | (1u << (rank + 2)));
+                    tma_load_2d_pair_multicast(b + twin * (B0_HALF / 2), &map_b0, &bars->bfull[s], u * BKB,
+                                               (int32_t)(rank * (N0 / 2) + twin * (N0 / 4)), mc);
+                    tma_load_2d_pair_multicast(b + B0_HALF + twin * (B1_HALF / 2), &map_b1, &bars->bfull[s], u * BKB,
+                                               (int32_t)(N0 + rank * (N1 / 2) + twin * (N1 / 4)), mc);
+                } else {
+                    tma_load_2d_pair(b, &map_b0, full_leader, u * BKB, (int32_t)(rank * (N0 / 2)));
+                    tma_load_2d_pair(b + B0_HALF, &map_b1, full_leader, u * BKB, (int32_t)(N0 + rank * (N1 / 2)));
+                }
+            }
+        }
+    } else if (warp == 1 && leader) {
+        if (elect_one()) {                                             // MMA issuer (leader only)
+            constexpr uint32_t idesc0 = make_idesc(/*S32*/ 2, /*int8*/ 1, BWD ? 1 : 0, 0, 2 * BM, N0);
+            constexpr uint32_t idesc1 = make_idesc(/*S32*/ 2, /*int8*/ 1, BWD ? 1 : 0, 0, 2 * BM, N1);
+            for (int u = 0; u < n_kb; ++u) {
+                const int sa = u % AS, sb = u % BS2;
+                mbar_wait(&bars->afull[sa], (u / AS) & 1);             // both CTAs' converters have written their tiles
+                mbar_wait(&bars->bfull[sb], (u / BS2) & 1);
+                tc_fence_after_sync();
+                const uint32_t a_addr = smem_u32(at + (size_t)sa * A_BYTES);
+                const uint32_t b0_addr = smem_u32(bt + (size_t)sb * B_BYTES), b1_addr = b0_addr + B0_HALF;
+#pragma unroll
+                for (int k4 = 0; k4 < BKB / 32; ++k4) {
+                    const uint64_t da = BWD ? make_smem_desc(a_addr + k4 * 4096, 16384, 1024) : make_smem_desc(a_addr + k4 * 32, 16, 1024);
+                    const uint64_t db0 = make_smem_desc(b0_addr + k4 * 32, 16, 1024);
+                    const uint64_t db1 = make_smem_desc(b1_addr + k4 * 32, 16, 1024);
+                    const uint32_t acc = (u > 0 || k4 > 0) ? 1u : 0u;
+                    mma_i8_ss_pair(tmem_base, da, db0, idesc0, acc);
+                    mma_i8_ss_pair(tmem_base + ACC1_COL, da, db1, idesc1, acc);
+                }
+                tc_commit_pair(&bars->aempty[sa], pair_mask);
+                tc_commit_pair(&bars->bempty[sb], all_mask);
+            }
+            tc_commit_pair(&bars->acc_full, pair_mask);
+        }
+    } else if (warp >= 4) {
+        // ===================================================== converters: packed [128 x 32 B] -> int8 [128 x 128 B], swizzled
+        // two groups of four warps take the k-blocks alternately (a warp's chain of two barrier waits, the expansion, the proxy
+        // fence and the arrivals is longer than the tensor work of one k-block); thread = row of the tile
+        const int group = (warp - 4) >> 2, row = (threadIdx.x - 128) & 127;
+        const uint32_t afull_leader_base = mapa_u32(smem_u32(&bars->afull[0]), lead_rank);
+        const uint32_t row_off = (uint32_t)((row >> 3) * 1024 + (row & 7) * 128), sw = (uint32_t)(row & 7);
+        for (int u = group; u < n_kb; u += 2) {
+            const int sx = u % PXS, sa = u % AS;                       // PXS and AS are even: a slot always meets the same group
+            mbar_wait(&bars->pxfull[sx], (u / PXS) & 1);
+            mbar_wait(&bars->aempty[sa], ((u / AS) & 1) ^ 1);
+            uint32_t w[8];
+            const uint32_t src = smem_u32(px + (size_t)sx * PX_BYTES) + (uint32_t)(row * 32);
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(src));
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "r"(src + 16));
+            const uint32_t dst = smem_u32(at + (size_t)sa * A_BYTES) + row_off;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {                              // 16-byte chunk c of the row: 16 codes = one packed word
+                uint32_t o[4];
+                expand16(w[c], o);
+                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};"
+                             :: "r"(dst + (((uint32_t)c ^ sw) << 4)), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+            }
+            fence_proxy_async();                                       // generic-proxy stores -> visible to the tensor-core proxy
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive_cluster(afull_leader_base + (uint32_t)(sa * sizeof(uint64_t)));
+                mbar_arrive(&bars->pxempty[sx]);
+            }
+        }
+        if (warp < 8) {
+            // ================================================= epilogue (both CTAs): three digit sums -> one rounding
+            const int wq = warp & 3;
+            const int64_t m = m0 + 32 * wq + lane;
+            mbar_wait(&bars->acc_full, 0);
+            tc_fence_after_sync();
+            const uint32_t trow = tmem_base + ((uint32_t)(32 * wq) << 16);
+#pragma unroll 1
+            for (int c0 = 0; c0 < h; c0 += 32) {
+                uint32_t a0[32], a1[32], a2[32];
+                tmem_ld_32x32b_x32(trow + c0, a0);
+                tmem_ld_32x32b_x32(trow + HP + c0, a1);
+                tmem_ld_32x32b_x32(trow + ACC1_COL + c0, a2);
+                tmem_ld_wait();
+                if (m < m_total) {
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) {
+                        const int f = c0 + c;
+                        if (f < h) {
+                            const long long sum = (long long)(int)a0[c] + 128LL * (long long)(int)a1[c] + 16384LL * (long long)(int)a2[c];
+                            const float r = (float)((double)sum * (double)scale[f]);
+                            if (BWD) out[(int64_t)f * ld_out + m] = r;
+                            else     out[m * ld_out + f] = r;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before_sync();
+    cluster_sync_all();
+    if (warp == 2) tmem_dealloc_pair<512>(tmem_base);
+}
+
+template <bool BWD, bool PACKED>
 int launch_i8(const CUtensorMap& mx, const CUtensorMap& mb0, const CUtensorMap& mb1, int64_t k_total, const float* scale, float* out,
               int64_t ld_out, int64_t m_total, int h, cudaStream_t stream) {
     const int64_t tiles = (m_total + BM - 1) / BM, pairs = (tiles + 1) / 2;
-    static int quad = -1;
-    if (quad < 0) { const char* e = getenv("GNNB_LINEAR_QUAD"); quad = e ? atoi(e) : 1; }
+    static int quad = -1, ablate = 0;
+    if (quad < 0) {
+        const char* e = getenv("GNNB_LINEAR_QUAD");
+        quad = e ? atoi(e) : 1;
+        const char* a = getenv("GNNB_LINEAR_ABLATE");          // measurement only
+        ablate = a ? atoi(a) : 0;
+    }
     const int64_t groups = quad ? (pairs + 1) / 2 : pairs;
-    { static bool done = false; if (!done) { GNNB_CUDA(cudaFuncSetAttribute(linear_i8_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM)); done = true; } }
+    const size_t smem = PACKED ? SMEM2 : SMEM;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((quad ? 4 : 2) * groups));
-    cfg.blockDim = dim3(256);
-    cfg.dynamicSmemBytes = SMEM;
+    cfg.blockDim = dim3(PACKED ? P2_THREADS : 256);
+    cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -324,9 +521,13 @@ int launch_i8(const CUtensorMap& mx, const CUtensorMap& mb0, const CUtensorMap& 
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    static int ablate = -1;
-    if (ablate < 0) { const char* e = getenv("GNNB_LINEAR_ABLATE"); ablate = e ? atoi(e) : 0; }      // measurement only
-    GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_i8_kernel<BWD>, mx, mb0, mb1, k_total, scale, out, ld_out, m_total, h, quad, ablate));
+    if (PACKED) {
+        { static bool done = false; if (!done) { GNNB_CUDA(cudaFuncSetAttribute(linear_p2_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); done = true; } }
+        GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_p2_kernel<BWD>, mx, mb0, mb1, k_total, scale, out, ld_out, m_total, h, quad));
+    } else {
+        { static bool done = false; if (!done) { GNNB_CUDA(cudaFuncSetAttribute(linear_i8_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); done = true; } }
+        GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_i8_kernel<BWD>, mx, mb0, mb1, k_total, scale, out, ld_out, m_total, h, quad, ablate));
+    }
     return GNNB_OK;
 }
 }  // namespace
@@ -338,8 +539,9 @@ static uint32_t box_div() {          // quad mode fetches the digit half-tiles i
 }
 static size_t limb_bytes(int64_t k_len) { return align_up((size_t)LIMB_ROWS * align_up((size_t)k_len, 16), 1024); }
 
-bool linear_i8_supported(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, int64_t h) {
-    return x_is_i8 && (uintptr_t)X % 16 == 0 && ldx % 16 == 0 && h >= 1 && h <= HP && n >= 128 && p >= 128;
+// x_format: 1 = int8 codes (ldx in elements = bytes), 2 = 2-bit packed codes (ldx = bytes per packed row)
+bool linear_i8_supported(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p, int64_t h) {
+    return (x_format == 1 || x_format == 2) && (uintptr_t)X % 16 == 0 && ldx % 16 == 0 && h >= 1 && h <= HP && n >= 128 && p >= 128;
 }
 
 size_t linear_i8_workspace(int64_t n, int64_t p, int64_t h) {
@@ -348,7 +550,7 @@ size_t linear_i8_workspace(int64_t n, int64_t p, int64_t h) {
     return limb_bytes((int64_t)k_len) + 4096 + 2048;      // limbs + (amax, scale) + alignment slack
 }
 
-int linear_i8_fwd(const int8_t* X, int64_t ldx, int64_t n, int64_t p, const float* W, int64_t ldw, int64_t h,
+int linear_i8_fwd(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p, const float* W, int64_t ldw, int64_t h,
                   float* H, int64_t ldh, void* ws, size_t ws_bytes, cudaStream_t stream) {
     const size_t need = linear_i8_workspace(n, p, h);
     GNNB_REQUIRE(ws && ws_bytes >= need, GNNB_E_WORKSPACE, "linear_fwd: workspace %zu < %zu bytes", ws_bytes, need);
@@ -366,16 +568,18 @@ int linear_i8_fwd(const int8_t* X, int64_t ldx, int64_t n, int64_t p, const floa
         GNNB_LAUNCH_CHECK();
     }
     CUtensorMap mx, mb0, mb1;
-    int rc = make_tensor_map_2d(&mx, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, BKB, BM);
+    int rc = x_format == 2 ? make_tensor_map_2d(&mx, X, 1, (uint64_t)((p + 3) / 4), (uint64_t)n, (uint64_t)ldx, BKB / 4, BM, /*swizzle*/ false)
+                           : make_tensor_map_2d(&mx, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, BKB, BM);
     if (rc != GNNB_OK) return rc;
     rc = make_tensor_map_2d(&mb0, limbs, 1, (uint64_t)p, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N0 / 2 / box_div());
     if (rc != GNNB_OK) return rc;
     rc = make_tensor_map_2d(&mb1, limbs, 1, (uint64_t)p, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N1 / 2 / box_div());
     if (rc != GNNB_OK) return rc;
-    return launch_i8<false>(mx, mb0, mb1, p, scale, H, ldh, n, (int)h, stream);
+    if (x_format == 2) return launch_i8<false, true>(mx, mb0, mb1, p, scale, H, ldh, n, (int)h, stream);
+    return launch_i8<false, false>(mx, mb0, mb1, p, scale, H, ldh, n, (int)h, stream);
 }
 
-int linear_i8_bwd_w(const int8_t* X, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
+int linear_i8_bwd_w(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
                     float* dW, int64_t lddw, void* ws, size_t ws_bytes, cudaStream_t stream) {
     const size_t need = linear_i8_workspace(n, p, h);
     GNNB_REQUIRE(ws && ws_bytes >= need, GNNB_E_WORKSPACE, "linear_bwd_w: workspace %zu < %zu bytes", ws_bytes, need);
@@ -390,13 +594,16 @@ int linear_i8_bwd_w(const int8_t* X, int64_t ldx, int64_t n, int64_t p, const fl
     quantize_cols_kernel<<<dim3((unsigned)((ldl + 127) / 128), 4), 256, 0, stream>>>(dH, lddh, n, (int)h, amax_bits, limbs, ldl, scale);
     GNNB_LAUNCH_CHECK();
     CUtensorMap mx, mb0, mb1;
-    int rc = make_tensor_map_2d(&mx, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, 128, BKB);       // box: 128 markers x 128 individuals
+    // box: 128 markers (128 B, or 32 packed bytes) x 128 individuals
+    int rc = x_format == 2 ? make_tensor_map_2d(&mx, X, 1, (uint64_t)((p + 3) / 4), (uint64_t)n, (uint64_t)ldx, 32, BKB, /*swizzle*/ false)
+                           : make_tensor_map_2d(&mx, X, 1, (uint64_t)p, (uint64_t)n, (uint64_t)ldx, 128, BKB);
     if (rc != GNNB_OK) return rc;
     rc = make_tensor_map_2d(&mb0, limbs, 1, (uint64_t)n, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N0 / 2 / box_div());
     if (rc != GNNB_OK) return rc;
     rc = make_tensor_map_2d(&mb1, limbs, 1, (uint64_t)n, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N1 / 2 / box_div());
     if (rc != GNNB_OK) return rc;
-    return launch_i8<true>(mx, mb0, mb1, n, scale, dW, lddw, p, (int)h, stream);
+    if (x_format == 2) return launch_i8<true, true>(mx, mb0, mb1, n, scale, dW, lddw, p, (int)h, stream);
+    return launch_i8<true, false>(mx, mb0, mb1, n, scale, dW, lddw, p, (int)h, stream);
 }
 
 }  // namespace gnnb

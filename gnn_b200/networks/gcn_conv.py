@@ -5,7 +5,9 @@ parameters ``lin.weight [out, in]`` (Glorot uniform) and ``bias [out]`` (zeros),
 
 Forward and backward run as CUDA kernels from libgnn_b200.so:
   gcn_norm + CSR (once per edge list, cached)  -> graph.cu
-  H = x . W^T, dW = dH^T . x, dx = dH . W      -> linear.cu / linear_tc.cu   (x may be int8 genotypes)
+  H = x . W^T, dW = dH^T . x, dx = dH . W      -> linear_i8.cu / linear_tc.cu / linear.cu
+                                                  (x: float32, int8 genotype codes, or uint8 = 2-bit packed codes,
+                                                   four per byte as ops.pack_2bit writes them)
   out = A_hat H + b, dH = A_hat^T dOut         -> spmm.cu
 """
 import math
@@ -33,7 +35,7 @@ class _GCNConvFn(torch.autograd.Function):
         d_out = d_out.contiguous()
         d_bias = ops.colsum(d_out) if ctx.has_bias else None
         d_h = ops.spmm(g.rowptr_t, g.col_t, g.val_t, d_out, None, n=g.n, hub=g.hub_t)     # transposed CSR
-        d_w = ops.linear_bwd_w(x, d_h)
+        d_w = ops.linear_bwd_w(x, d_h, p=weight.shape[1])
         d_x = ops.linear_bwd_x(d_h, weight) if ctx.x_needs_grad else None
         return d_x, d_w, d_bias, None
 

@@ -441,44 +441,58 @@ def _precision(n, p, h, x_is_i8):
     return int(prec)
 
 
-def linear_fwd(X, W, precision=None):
-    """H = X . W^T with X int8 genotype codes or float32, W float32 [h, p]."""
-    _need_cuda(X, W)
-    x_is_i8 = X.dtype == torch.int8
-    if not x_is_i8 and X.dtype != torch.float32:
-        X = X.to(torch.float32)
+def _x_operand(X, p_packed):
+    """(tensor, x_format, p) of a projection input: float32 -> 0, int8 codes -> 1, uint8 = 2-bit packed codes -> 2
+    (then the marker count cannot be read off the tensor and comes from the weight's shape)."""
+    if X.dtype == torch.uint8:
+        if p_packed is None or X.shape[1] * 4 < p_packed:
+            raise _lib.GnnbError("2-bit packed genotypes: the row is shorter than the marker count")
+        fmt, p = 2, int(p_packed)
+    elif X.dtype == torch.int8:
+        fmt, p = 1, X.shape[1]
+    else:
+        if X.dtype != torch.float32:
+            X = X.to(torch.float32)
+        fmt, p = 0, X.shape[1]
     if X.stride(1) != 1:
         X = X.contiguous()
+    return X, fmt, p
+
+
+def linear_fwd(X, W, precision=None):
+    """H = X . W^T with X int8 genotype codes, 2-bit packed codes (uint8, see pack_2bit) or float32; W float32 [h, p]."""
+    _need_cuda(X, W)
     W = W.contiguous()
-    n, p = X.shape
     h = W.shape[0]
-    prec = _precision(n, p, h, x_is_i8) if precision is None else precision
+    X, fmt, p = _x_operand(X, W.shape[1])
+    if p != W.shape[1]:
+        raise _lib.GnnbError(f"linear_fwd: x has {p} columns, the weight {W.shape[1]}")
+    n = X.shape[0]
+    prec = _precision(n, p, h, fmt != 0) if precision is None else precision
     H = torch.empty((n, h), dtype=torch.float32, device=X.device)
     with torch.cuda.device(X.device):
         ws = _ws(_ws_bytes("gnnb_linear_workspace_bytes", n, p, h, prec), X.device)
-        _declare(flops=2.0 * n * p * h, bytes=float(n * p * X.element_size() + h * p * 4 + n * h * 4))
-        _call("gnnb_linear_fwd", _p(X), int(x_is_i8), X.stride(0), n, p, _p(W), W.stride(0), h,
+        _declare(flops=2.0 * n * p * h, bytes=float(n * X.shape[1] * X.element_size() + h * p * 4 + n * h * 4))
+        _call("gnnb_linear_fwd", _p(X), fmt, X.stride(0), n, p, _p(W), W.stride(0), h,
               _p(H), H.stride(0), prec, _p(ws), ws.numel(), _stream())
     return H
 
 
-def linear_bwd_w(X, dH, precision=None):
-    """dW [h, p] = dH^T . X"""
+def linear_bwd_w(X, dH, precision=None, p=None):
+    """dW [h, p] = dH^T . X  (``p``: marker count, needed when X is 2-bit packed)"""
     _need_cuda(X, dH)
-    x_is_i8 = X.dtype == torch.int8
-    if not x_is_i8 and X.dtype != torch.float32:
-        X = X.to(torch.float32)
-    if X.stride(1) != 1:
-        X = X.contiguous()
     dH = dH.contiguous()
-    n, p = X.shape
     h = dH.shape[1]
-    prec = _precision(n, p, h, x_is_i8) if precision is None else precision
+    X, fmt, p = _x_operand(X, p)
+    n = X.shape[0]
+    if dH.shape[0] != n:
+        raise _lib.GnnbError(f"linear_bwd_w: x has {n} rows, dH {dH.shape[0]}")
+    prec = _precision(n, p, h, fmt != 0) if precision is None else precision
     dW = torch.empty((h, p), dtype=torch.float32, device=X.device)
     with torch.cuda.device(X.device):
         ws = _ws(_ws_bytes("gnnb_linear_workspace_bytes", n, p, h, prec), X.device)
-        _declare(flops=2.0 * n * p * h, bytes=float(n * p * X.element_size() + h * p * 4 + n * h * 4))
-        _call("gnnb_linear_bwd_w", _p(X), int(x_is_i8), X.stride(0), n, p, _p(dH), dH.stride(0), h,
+        _declare(flops=2.0 * n * p * h, bytes=float(n * X.shape[1] * X.element_size() + h * p * 4 + n * h * 4))
+        _call("gnnb_linear_bwd_w", _p(X), fmt, X.stride(0), n, p, _p(dH), dH.stride(0), h,
               _p(dW), dW.stride(0), prec, _p(ws), ws.numel(), _stream())
     return dW
 

@@ -12,8 +12,9 @@ def l1_regularize(model, loss, l1_lambda):
 
 
 def _features(x):
-    # the reference calls x.float() (trainers/util.py:19); int8 genotype codes are consumed as they are
-    return x if x.dtype == torch.int8 else x.float()
+    # the reference calls x.float() (trainers/util.py:19); int8 genotype codes and 2-bit packed codes (uint8) are
+    # consumed as they are
+    return x if x.dtype in (torch.int8, torch.uint8) else x.float()
 
 
 def get_args_tuple(data):

@@ -307,3 +307,35 @@ def test_training_trajectory_golden(wheat, golden):
         pred_train = model(*get_args_tuple(batch)).detach().cpu().numpy()
         assert restate.pearson(pred_train, g[f"b{b}_pred_train"]) >= 0.9999
         assert rel_err(torch.from_numpy(pred_train), torch.from_numpy(g[f"b{b}_pred_train"])) < 1e-3
+
+
+@pytest.mark.parametrize("n,p,h", [(128, 128, 16), (479, 1279, 100), (1000, 4096, 100), (129, 200, 7), (3000, 5003, 32)])
+def test_linear_packed_genotypes(n, p, h):
+    """2-bit packed genotypes (uint8, four codes per byte) through the projection: the converter warps must hand the MMA
+    exactly the int8 tile, so the results are BIT-IDENTICAL to the int8 path (same exact integer sums, same rounding)."""
+    X = synth.genotypes(n, p, seed=3 * n + p)
+    buf = torch.zeros((n, (p + 15) // 16 * 16), dtype=torch.int8, device=DEV)
+    buf[:, :p] = torch.from_numpy(X).to(DEV)
+    Xd = buf[:, :p]
+    Xp = ops.pack_2bit(Xd)
+    assert Xp.dtype == torch.uint8 and Xp.shape == (n, ops.packed_stride(p))
+    g = torch.Generator(device="cpu").manual_seed(n)
+    W = (torch.randn(h, p, generator=g) * 0.05).to(DEV)
+    dH = torch.randn(n, h, generator=g).to(DEV)
+    assert torch.equal(ops.linear_fwd(Xp, W), ops.linear_fwd(Xd, W))
+    assert torch.equal(ops.linear_bwd_w(Xp, dH, p=p), ops.linear_bwd_w(Xd, dH))
+    # through the operator: same outputs and gradients with packed node features
+    ei = torch.stack([torch.arange(n, device=DEV), torch.roll(torch.arange(n, device=DEV), 1)])
+    torch.manual_seed(0)
+    conv = GCNConv(p, h).to(DEV)
+    out_a = conv(Xd, ei)
+    out_b = conv(Xp, ei)
+    assert torch.equal(out_a, out_b)
+    (out_b * dH).sum().backward()
+    gb = conv.lin.weight.grad.clone()
+    conv.zero_grad()
+    (conv(Xd, ei) * dH).sum().backward()
+    assert torch.equal(gb, conv.lin.weight.grad)
+    # shapes the packed kernel does not take are refused, not silently converted
+    with pytest.raises(Exception):
+        ops.linear_fwd(Xp, torch.randn(120, p, device=DEV))
