@@ -220,3 +220,19 @@ def test_ensemble_rows_sizes_property():
             for tr, te in rows:
                 assert len(tr) == round(0.5 * m) and len(set(tr.tolist())) == len(tr)
                 assert np.array_equal(te, np.arange(m, n))
+
+
+def test_pack_2bit_host_layout():
+    """Host packer of the PCIe / HBM genotype format: code j of a row in bits 2*(j%4) of byte j//4, rows padded to 16 bytes."""
+    rng = np.random.default_rng(0)
+    for n, p in ((1, 1), (3, 5), (7, 64), (5, 130)):
+        X = rng.integers(0, 4, size=(n, p)).astype(np.int8)
+        P = ops.pack_2bit_host(X)
+        assert P.dtype == np.uint8 and P.shape == (n, ops.packed_stride(p)) and ops.packed_stride(p) % 16 == 0
+        back = np.stack([(P[:, j // 4] >> (2 * (j % 4))) & 3 for j in range(p)], axis=1)
+        assert np.array_equal(back, X)
+        assert not P[:, (p + 3) // 4:].any()                       # padding bytes are zero
+        if p % 4:
+            assert not (P[:, p // 4] >> (2 * (p % 4))).any()       # padding codes inside the last byte are zero
+    with pytest.raises(ValueError):
+        ops.pack_2bit_host(np.array([[0, 4]], dtype=np.int8))
