@@ -368,7 +368,7 @@ int gnnb_linear_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t 
         precision = 2;
     }
     if (x_is_i8 == 2)
-        return fail(GNNB_E_UNSUPPORTED, "linear_fwd: 2-bit packed X needs precision 4, 16-byte aligned rows, n >= 128, p >= 128 and h <= 112 "
+        return fail(GNNB_E_UNSUPPORTED, "linear_fwd: 2-bit packed X needs precision 4, 16-byte aligned rows, n >= 128, p >= 128 and h <= 104 "
                                         "(expand it with gnnb_unpack_2bit for other shapes)");
     if (precision > 0) return linear_tc_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, precision, workspace, workspace_bytes, stream);
     return linear_simt_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, workspace, workspace_bytes, stream);
@@ -392,7 +392,7 @@ int gnnb_linear_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_
         precision = 2;
     }
     if (x_is_i8 == 2)
-        return fail(GNNB_E_UNSUPPORTED, "linear_bwd_w: 2-bit packed X needs precision 4, 16-byte aligned rows, n >= 128, p >= 128 and h <= 112 "
+        return fail(GNNB_E_UNSUPPORTED, "linear_bwd_w: 2-bit packed X needs precision 4, 16-byte aligned rows, n >= 128, p >= 128 and h <= 104 "
                                         "(expand it with gnnb_unpack_2bit for other shapes)");
     if (precision > 0)
         return linear_tc_bwd_w(X, x_is_i8, ldx, n, p, dH, lddh, h, dW, lddw, precision, workspace, workspace_bytes, stream);

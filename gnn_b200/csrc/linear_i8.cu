@@ -10,13 +10,13 @@
 // converter, no TMEM staging), and 21 bits relative to the row maximum beat the 16 bits of two bf16 terms.
 //
 // Kernel = the CTA-pair pipeline of knn_tc.cu (cta_group::2): a pair owns 256 rows of the M side, each CTA stages its
-// own 128-row A tile and HALF of the limb tile; the leader issues, per 128-byte k-block, 4 x [N = 224 (digits 0, 1) +
-// N = 128 (digit 2)].  The kernel is bound by the L2 -> SM operand stream, and the limb tile is the same for every pair:
+// own 128-row A tile and HALF of the limb tile; the leader issues, per 128-byte k-block, 4 x [N = 256 + N = 64] (the
+// three digit blocks at a stride of 104 rows, see "Digit layout" below).  The kernel is bound by the L2 -> SM operand stream, and the limb tile is the same for every pair:
 // clusters of 4 (two pairs, GNNB_LINEAR_QUAD, default on) fetch each limb half-tile once -- each of the two CTAs that
 // need it issues half of it as a TMA multicast to both -- and run the two pairs in lockstep per ring slot (the slot's
 // `empty` barrier collects the commits of both leaders).  Measured 0.240 -> 0.226 ms forward, 0.245 -> 0.224 backward.
-//   forward : M = individuals (A = X tile, K-major),             K = markers,     B = W limbs    [352, p]  K-major
-//   backward: M = markers     (A = X tile read MN-major),        K = individuals, B = dH^T limbs [352, n]  K-major
+//   forward : M = individuals (A = X tile, K-major),             K = markers,     B = W limbs    [320, p]  K-major
+//   backward: M = markers     (A = X tile read MN-major),        K = individuals, B = dH^T limbs [320, n]  K-major
 #include <math.h>
 
 #include "tc_common.cuh"
@@ -27,9 +27,24 @@ using namespace tc;
 
 namespace {
 constexpr int BM = 128, BKB = 128;                       // A tile: 128 rows (or 128 markers) x 128 bytes of K
-constexpr int HP = 112;                                  // rows per digit for digits 0 and 1 (h <= 112)
-constexpr int N0 = 2 * HP, N1 = 128;                     // the two MMAs of a k-step
-constexpr int LIMB_ROWS = N0 + N1;                       // 352 rows of the limb matrix: [0,112) d0, [112,224) d1, [224,352) d2
+// Digit layout.  An MMA costs ~45 + 0.4 N cycles on this pipe (scripts/ubench/mma_rate.cu), so the three digit blocks are
+// packed at a stride of 104 rows into 320 rows = one MMA of N = 256 plus one of N = 64 per k-step, whose accumulators are
+// adjacent TMEM columns (digit d of feature f = row / column d * 104 + f).  LI_COMPACT = 0 is the first layout (112-row
+// blocks for digits 0 and 1 in an N = 224 MMA, digit 2 alone in an N = 128 MMA: 352 rows).
+#ifndef LI_COMPACT
+#define LI_COMPACT 1
+#endif
+#if LI_COMPACT
+constexpr int HP = 104;                                  // rows per digit (h <= 104)
+constexpr int N0 = 256, N1 = 64;                         // the two MMAs of a k-step
+constexpr int D2_ROW = 2 * HP;                           // first row / accumulator column of digit 2
+#else
+constexpr int HP = 112;
+constexpr int N0 = 2 * HP, N1 = 128;
+constexpr int D2_ROW = N0;
+#endif
+constexpr int LIMB_ROWS = N0 + N1;                       // rows of the limb matrix
+constexpr int F_ROWS = LIMB_ROWS - D2_ROW;               // features slots the quantisers fill (padding rows are zeroed)
 constexpr int A_BYTES = BM * BKB, B0_HALF = (N0 / 2) * BKB, B1_HALF = (N1 / 2) * BKB;
 constexpr int B_BYTES = B0_HALF + B1_HALF;               // 22 KB: this CTA's half of the digit tile
 // Two rings with a producer thread each (X tiles from HBM, digit tiles multicast from L2), so that neither stream waits
@@ -43,7 +58,10 @@ constexpr int B_BYTES = B0_HALF + B1_HALF;               // 22 KB: this CTA's ha
 #define LI_BS 5
 #endif
 constexpr int XS = LI_XS, BS = LI_BS;
-constexpr int ACC1_COL = 256;                            // TMEM column of the digit-2 accumulator
+constexpr int ACC1_COL = 256;                            // TMEM column of the second MMA's accumulator
+constexpr int D2_COL = LI_COMPACT ? D2_ROW : ACC1_COL;   // TMEM column of digit 2, feature 0 (compact: N0 == ACC1_COL, so
+                                                         // accumulator columns and limb rows are numbered alike)
+static_assert(!LI_COMPACT || N0 == ACC1_COL, "the compact layout needs adjacent accumulators");
 
 struct Bars {
     uint64_t xfull[XS], xempty[XS], bfull[BS], bempty[BS], acc_full;
@@ -90,13 +108,13 @@ __global__ void col_absmax_kernel(const float* __restrict__ in, int64_t ld, int6
     atomicMax(&amax_bits[c], __float_as_uint(m));
 }
 
-// limbs[(digit rows), c] of W[f, c].  One thread = 16 consecutive columns of one limb-matrix row triple (f, 112 + f, 224 + f):
+// limbs[(digit rows), c] of W[f, c].  One thread = 16 consecutive columns of one limb-matrix row triple (f, HP + f, D2_ROW + f):
 // four float4 loads, three 16-byte stores.  Rows f >= h (padding of the MMA N dimension) and columns >= cols are zeroed here,
 // so the workspace needs no separate clear.
 __global__ void quantize_rows_kernel(const float* __restrict__ W, int64_t ldw, int h, int64_t cols, const unsigned* __restrict__ amax_bits,
                                      int8_t* __restrict__ limbs, int64_t ldl, float* __restrict__ scale) {
     const int64_t groups = ldl / 16;                     // ldl is a multiple of 16
-    const int64_t total = (int64_t)N1 * groups;          // f runs over 0..127: rows [0,112) carry digits 0/1, [0,128) digit 2
+    const int64_t total = (int64_t)F_ROWS * groups;      // f runs over the feature slots: digits 0/1 for f < HP, digit 2 for all
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int f = (int)(i / groups);
         const int64_t c0 = (i % groups) * 16;
@@ -128,7 +146,7 @@ __global__ void quantize_rows_kernel(const float* __restrict__ W, int64_t ldw, i
             *reinterpret_cast<uint4*>(limbs + (int64_t)f * ldl + c0) = *reinterpret_cast<const uint4*>(d[0]);
             *reinterpret_cast<uint4*>(limbs + (int64_t)(HP + f) * ldl + c0) = *reinterpret_cast<const uint4*>(d[1]);
         }
-        *reinterpret_cast<uint4*>(limbs + (int64_t)(N0 + f) * ldl + c0) = *reinterpret_cast<const uint4*>(d[2]);
+        *reinterpret_cast<uint4*>(limbs + (int64_t)(D2_ROW + f) * ldl + c0) = *reinterpret_cast<const uint4*>(d[2]);
     }
 }
 
@@ -148,6 +166,7 @@ __global__ void quantize_cols_kernel(const float* __restrict__ dH, int64_t ld, i
     const int quad = threadIdx.x & 31, fsub = threadIdx.x >> 5;
     for (int ff = fsub; ff < 32; ff += 8) {
         const int f = f0 + ff;
+        if (f >= F_ROWS) continue;
         const float a = f < h ? __uint_as_float(amax_bits[f]) : 0.f;
         const float inv = a > 0.f ? 1048576.0f / a : 0.f;
         __align__(4) int8_t d[3][4];
@@ -159,7 +178,7 @@ __global__ void quantize_cols_kernel(const float* __restrict__ dH, int64_t ld, i
                 *reinterpret_cast<uint32_t*>(limbs + (int64_t)f * ldl + col) = *reinterpret_cast<const uint32_t*>(d[0]);
                 *reinterpret_cast<uint32_t*>(limbs + (int64_t)(HP + f) * ldl + col) = *reinterpret_cast<const uint32_t*>(d[1]);
             }
-            *reinterpret_cast<uint32_t*>(limbs + (int64_t)(N0 + f) * ldl + col) = *reinterpret_cast<const uint32_t*>(d[2]);
+            *reinterpret_cast<uint32_t*>(limbs + (int64_t)(D2_ROW + f) * ldl + col) = *reinterpret_cast<const uint32_t*>(d[2]);
         }
         if (blockIdx.x == 0 && quad == 0 && f < h) scale[f] = a * (1.0f / 1048576.0f);
     }
@@ -172,7 +191,7 @@ linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                  const __grid_constant__ CUtensorMap map_b1, int64_t k_total, const float* __restrict__ scale,
                  float* __restrict__ out, int64_t ld_out, int64_t m_total, int h,
                  int quad,          // 1: clusters of 4 = two pairs; each digit half-tile is fetched once and multicast to both pairs
-                                    //    (map_b0 / map_b1 then have boxes of 56 / 32 rows instead of 112 / 64)
+                                    //    (map_b0 / map_b1 then have boxes of a quarter instead of a half of N0 / N1 rows)
                  int ablate) {      // measurement only (results invalid): 1 = no TMA loads, 2 = no MMAs
     extern __shared__ uint8_t smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -283,7 +302,7 @@ linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             uint32_t a0[32], a1[32], a2[32];
             tmem_ld_32x32b_x32(trow + c0, a0);
             tmem_ld_32x32b_x32(trow + HP + c0, a1);
-            tmem_ld_32x32b_x32(trow + ACC1_COL + c0, a2);
+            tmem_ld_32x32b_x32(trow + D2_COL + c0, a2);
             tmem_ld_wait();
             if (m < m_total) {
 #pragma unroll
@@ -474,7 +493,7 @@ linear_p2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 uint32_t a0[32], a1[32], a2[32];
                 tmem_ld_32x32b_x32(trow + c0, a0);
                 tmem_ld_32x32b_x32(trow + HP + c0, a1);
-                tmem_ld_32x32b_x32(trow + ACC1_COL + c0, a2);
+                tmem_ld_32x32b_x32(trow + D2_COL + c0, a2);
                 tmem_ld_wait();
                 if (m < m_total) {
 #pragma unroll
@@ -563,7 +582,7 @@ int linear_i8_fwd(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p
     row_absmax_kernel<<<dim3((unsigned)h, 16), 256, 0, stream>>>(W, ldw, p, amax_bits);
     GNNB_LAUNCH_CHECK();
     {
-        int64_t total = (int64_t)N1 * (ldl / 16), blocks = (total + 255) / 256, cap = (int64_t)sm_count() * 16;
+        int64_t total = (int64_t)F_ROWS * (ldl / 16), blocks = (total + 255) / 256, cap = (int64_t)sm_count() * 16;
         quantize_rows_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, stream>>>(W, ldw, (int)h, p, amax_bits, limbs, ldl, scale);
         GNNB_LAUNCH_CHECK();
     }

@@ -167,12 +167,12 @@ int gnnb_spmm_workspace_bytes(int64_t n_hub_tasks, int64_t F, size_t* bytes);
  *   bwd_x : dX [n, p] = dH [n, h] . W [h, p]                      (inner layers only)
  * X is float32 (x_is_i8 = 0), int8 genotype codes (x_is_i8 = 1; [0, 127] for precision 1..3, any int8 for 0 and 4), or
  * 2-BIT PACKED genotype codes as gnnb_pack_2bit writes them (x_is_i8 = 2; ldx = bytes per packed row, a multiple of 16;
- * precision 4 only, n >= 128, p >= 128, h <= 112): the kernels expand the packed tile to int8 on chip, so the matrix is
+ * precision 4 only, n >= 128, p >= 128, h <= 104): the kernels expand the packed tile to int8 on chip, so the matrix is
  * read from HBM at a quarter of the bytes; results are bit-identical to x_is_i8 = 1.
  * precision: 0 = fp32 CUDA-core tiles (exact reference arithmetic),
  *            1 / 2 / 3 = tcgen05 bf16 tensor-core tiles with the fp32 operand split into that many
  *            bf16 terms (3 ~ fp32-exact for integer-coded X; 1 = plain bf16 projection), fp32 accumulate;
- *            4 = int8 tensor cores (int8 X only, n >= 128, p >= 128, h <= 112; other shapes run as 2): the float
+ *            4 = int8 tensor cores (int8 X only, n >= 128, p >= 128, h <= 104; other shapes run as 2): the float
  *            operand is quantised per output feature to 21 bits and split into three int8 digits, the three
  *            exact int32 digit sums are combined as one 64-bit integer and rounded once (rel. error ~1e-6).
  */
