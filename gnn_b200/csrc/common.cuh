@@ -35,6 +35,21 @@ int  sm_count();
                                 cudaGetErrorString(_e), __FILE__, __LINE__);              \
     } while (0)
 
+// Opt a kernel in to `bytes` of dynamic shared memory.  The attribute belongs to the (function, DEVICE) pair, so the
+// high-water mark is kept per device ordinal: a process that drives several GPUs must set it on each of them.
+#define GNNB_MAX_DEVICES 64
+#define GNNB_SET_DYN_SMEM(kernel, bytes)                                                                     \
+    do {                                                                                                      \
+        static size_t hw_[GNNB_MAX_DEVICES] = {0};                                                            \
+        int dev_ = 0;                                                                                         \
+        GNNB_CUDA(cudaGetDevice(&dev_));                                                                      \
+        const bool tracked_ = dev_ >= 0 && dev_ < GNNB_MAX_DEVICES;                                           \
+        if (!tracked_ || (size_t)(bytes) > hw_[dev_]) {                                                       \
+            GNNB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes))); \
+            if (tracked_) hw_[dev_] = (size_t)(bytes);                                                        \
+        }                                                                                                     \
+    } while (0)
+
 #define GNNB_ENTER()                                        \
     do {                                                    \
         int _rc = ::gnnb::require_sm100();                  \

@@ -366,11 +366,11 @@ int gnnb_knn_i8(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q, 
             size_t smem = dp4a_smem_bytes(k);
             dim3 grid((unsigned)((n_q + TQ - 1) / TQ), (unsigned)n_splits);
             if (n_extra > 0) {
-                { static size_t hw_ = 0; if ((size_t)(smem) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_dp4a_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem))); hw_ = (size_t)(smem); } }
+                GNNB_SET_DYN_SMEM(knn_dp4a_kernel<true>, smem);
                 knn_dp4a_kernel<true><<<grid, 256, smem, stream>>>(Q, ldq, sq_q, n_q, q_off, K, ldk, sq_k, n_k, k_off, p,
                                                                    extra_q, extra_k, n_extra, k, n_splits, part_d2, part_idx, aligned4);
             } else {
-                { static size_t hw_ = 0; if ((size_t)(smem) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_dp4a_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem))); hw_ = (size_t)(smem); } }
+                GNNB_SET_DYN_SMEM(knn_dp4a_kernel<false>, smem);
                 knn_dp4a_kernel<false><<<grid, 256, smem, stream>>>(Q, ldq, sq_q, n_q, q_off, K, ldk, sq_k, n_k, k_off, p,
                                                                     extra_q, extra_k, n_extra, k, n_splits, part_d2, part_idx, aligned4);
             }
@@ -407,7 +407,7 @@ int gnnb_knn_f64(const double* Q, int64_t ldq, int64_t n_q, int64_t q_off,
     GNNB_REQUIRE(cv.ok(), GNNB_E_WORKSPACE, "knn_f64: workspace carve overflow");
     if (n_splits > 0) {
         size_t smem = (size_t)(2 * FQ * (FC + 1) + FQ * (FK + 1)) * sizeof(double) + (size_t)k * FQ * (sizeof(double) + sizeof(int));
-        { static size_t hw_ = 0; if (smem > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); hw_ = smem; } }
+        GNNB_SET_DYN_SMEM(knn_f64_kernel, smem);
         dim3 grid((unsigned)((n_q + FQ - 1) / FQ), (unsigned)n_splits);
         knn_f64_kernel<<<grid, 256, smem, stream>>>(Q, ldq, n_q, q_off, K, ldk, n_k, k_off, p, k, n_splits, part_d2, part_idx);
         GNNB_LAUNCH_CHECK();

@@ -521,11 +521,11 @@ int knn_tc_launch(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q
         cfg.attrs = attr;
         cfg.numAttrs = 1;
         if (extra) {
-            { static size_t hw_ = 0; if (smem > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_tc2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); hw_ = smem; } }
+            GNNB_SET_DYN_SMEM(knn_tc2_kernel<true>, smem);
             GNNB_CUDA(cudaLaunchKernelEx(&cfg, knn_tc2_kernel<true>, map_q, map_k, sq_q, n_q, q_off, sq_k, n_k, k_off, p, extra_q, extra_k,
                                          n_extra, k, n_splits, q_pairs, stages, part_d2, part_idx, use_quad, ablate));
         } else {
-            { static size_t hw_ = 0; if (smem > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_tc2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); hw_ = smem; } }
+            GNNB_SET_DYN_SMEM(knn_tc2_kernel<false>, smem);
             GNNB_CUDA(cudaLaunchKernelEx(&cfg, knn_tc2_kernel<false>, map_q, map_k, sq_q, n_q, q_off, sq_k, n_k, k_off, p, extra_q, extra_k,
                                          n_extra, k, n_splits, q_pairs, stages, part_d2, part_idx, use_quad, ablate));
         }
@@ -541,11 +541,11 @@ int knn_tc_launch(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q
     const int groups = (q_tiles + QG - 1) / QG;
     const unsigned grid = (unsigned)(groups * QG * n_splits);
     if (extra) {
-        { static size_t hw_ = 0; if ((size_t)(smem) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem))); hw_ = (size_t)(smem); } }
+        GNNB_SET_DYN_SMEM(knn_tc_kernel<true>, smem);
         knn_tc_kernel<true><<<grid, 256, smem, stream>>>(map_q, map_k, sq_q, n_q, q_off, sq_k, n_k, k_off, p, extra_q, extra_k,
                                                          n_extra, k, n_splits, q_tiles, stages, part_d2, part_idx);
     } else {
-        { static size_t hw_ = 0; if ((size_t)(smem) > hw_) { GNNB_CUDA(cudaFuncSetAttribute(knn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem))); hw_ = (size_t)(smem); } }
+        GNNB_SET_DYN_SMEM(knn_tc_kernel<false>, smem);
         knn_tc_kernel<false><<<grid, 256, smem, stream>>>(map_q, map_k, sq_q, n_q, q_off, sq_k, n_k, k_off, p, extra_q, extra_k,
                                                           n_extra, k, n_splits, q_tiles, stages, part_d2, part_idx);
     }

@@ -253,7 +253,7 @@ template <int MODE>
 static int launch_skinny(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M, int N, int K,
                          cudaStream_t stream) {
     const size_t smem = skinny_smem(MODE == 2 ? SK : K);
-    { static size_t hw_ = 0; if (smem > hw_) { GNNB_CUDA(cudaFuncSetAttribute(skinny_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); hw_ = smem; } }
+    GNNB_SET_DYN_SMEM(skinny_kernel<MODE>, smem);
     skinny_kernel<MODE><<<(unsigned)((M + SK - 1) / SK), 256, smem, stream>>>(A, lda, B, ldb, C, ldc, M, N, K);
     GNNB_LAUNCH_CHECK();
     return GNNB_OK;

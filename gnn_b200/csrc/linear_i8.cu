@@ -541,10 +541,10 @@ int launch_i8(const CUtensorMap& mx, const CUtensorMap& mb0, const CUtensorMap& 
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     if (PACKED) {
-        { static bool done = false; if (!done) { GNNB_CUDA(cudaFuncSetAttribute(linear_p2_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); done = true; } }
+        GNNB_SET_DYN_SMEM(linear_p2_kernel<BWD>, smem);
         GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_p2_kernel<BWD>, mx, mb0, mb1, k_total, scale, out, ld_out, m_total, h, quad));
     } else {
-        { static bool done = false; if (!done) { GNNB_CUDA(cudaFuncSetAttribute(linear_i8_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); done = true; } }
+        GNNB_SET_DYN_SMEM(linear_i8_kernel<BWD>, smem);
         GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_i8_kernel<BWD>, mx, mb0, mb1, k_total, scale, out, ld_out, m_total, h, quad, ablate));
     }
     return GNNB_OK;

@@ -327,7 +327,7 @@ int linear_tc_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
     if (rc != GNNB_OK) return rc;
     const int btile = (int)(h_pad * BK * 2);
     const size_t smem_ta = ta_fixed() + (size_t)ta_nb(terms, btile) * terms * btile;
-    { static size_t hw_ = 0; if (smem_ta > hw_) { GNNB_CUDA(cudaFuncSetAttribute(linear_ta_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ta)); hw_ = smem_ta; } }
+    GNNB_SET_DYN_SMEM(linear_ta_kernel<false>, smem_ta);
     linear_ta_kernel<false><<<(unsigned)tiles, TA_THREADS, smem_ta, stream>>>(mx, mb, p, terms, (int)h_pad, h_pad, H, ldh, n, (int)h);
     GNNB_LAUNCH_CHECK();
     return GNNB_OK;
@@ -354,7 +354,7 @@ int linear_tc_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t 
     if (rc != GNNB_OK) return rc;
     const int btile = BK * 128 * 2;
     const size_t smem_ta = ta_fixed() + (size_t)ta_nb(terms, btile) * terms * btile;
-    { static size_t hw_ = 0; if (smem_ta > hw_) { GNNB_CUDA(cudaFuncSetAttribute(linear_ta_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ta)); hw_ = smem_ta; } }
+    GNNB_SET_DYN_SMEM(linear_ta_kernel<true>, smem_ta);
     linear_ta_kernel<true><<<(unsigned)tiles, TA_THREADS, smem_ta, stream>>>(mx, mb, n, terms, 128, n, dW, lddw, p, (int)h);
     GNNB_LAUNCH_CHECK();
     return GNNB_OK;

@@ -617,6 +617,8 @@ int gnnb_colsum_static(const float* A, int64_t lda, int64_t n, int64_t F, float*
         cudaError_t e = cudaGetSymbolAddress((void**)&p, g_colsum_static_scratch);
         if (e != cudaSuccess || !p)
             return fail(GNNB_E_CUDA, "colsum_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+        // two host threads making their first call on one device at the same time both get here and both store the
+        // same address (a pointer-sized store of an identical value): harmless, so the table is not locked
         g_colsum_static_ptr[dev] = p;
     }
     float* partial = g_colsum_static_ptr[dev];

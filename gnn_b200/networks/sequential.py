@@ -55,7 +55,14 @@ class Sequential(torch.nn.Module):
         out = None
         for m, f, (ins, outs) in zip(self.nns, self.fns, self.descs):
             call = m if f is None else f
-            out = call(*[state[k] for k in ins if k not in absent])
+            vals = [state[k] for k in ins if k not in absent]
+            if isinstance(m, torch.nn.Linear) and vals and torch.is_tensor(vals[0]) and not vals[0].is_floating_point():
+                # the loaders keep genotypes as int8 codes where the reference has float32 (load.py:50); GCNConv reads the
+                # codes directly, a stock Linear in front of them (create_network_linear / _test) needs the float tensor
+                if vals[0].dtype != torch.int8:
+                    raise TypeError("2-bit packed genotypes feed GCNConv only; expand them (ops.unpack_2bit) for a Linear layer")
+                vals[0] = vals[0].float()
+            out = call(*vals)
             out = out if isinstance(out, tuple) else (out,)
             assert len(out) == len(outs)
             state.update(zip(outs, out))

@@ -3,6 +3,7 @@ streams, autograd bookkeeping.  Every function launches hand-written sm_100a ker
 libgnn_b200.so and raises if the library or a B200 is missing -- there is no fallback path.
 """
 import ctypes
+import weakref
 from collections import OrderedDict
 
 import torch
@@ -334,7 +335,7 @@ def build_edges(idx, d2, mode="connectivity", smoothing="laplacian", use_weights
 # --------------------------------------------------------------------------------------- K4
 class GcnGraph:
     """GCN-normalised adjacency in CSR, by target (forward) and by source (backward)."""
-    __slots__ = ("n", "nnz", "rowptr", "col", "val", "rowptr_t", "col_t", "val_t", "hub", "hub_t", "_keep")
+    __slots__ = ("n", "nnz", "rowptr", "col", "val", "rowptr_t", "col_t", "val_t", "hub", "hub_t", "nbytes")
 
     def agg_bytes(self, F, s=4):
         """Algorithmic bytes of one aggregation launch."""
@@ -342,22 +343,46 @@ class GcnGraph:
 
 
 _graph_cache = OrderedDict()
-_GRAPH_CACHE_MAX = 512
+_GRAPH_CACHE_MAX = 256                      # entries; the byte bound below is the one that matters for large graphs
+_GRAPH_CACHE_MAX_BYTES = 48 << 30
+
+
+def _graph_bytes(g):
+    total = 0
+    for name in ("rowptr", "col", "val", "rowptr_t", "col_t", "val_t"):
+        t = getattr(g, name)
+        total += t.numel() * t.element_size()
+    for plan in (g.hub, g.hub_t):
+        if plan is not None:
+            total += sum(t.numel() * t.element_size() for t in plan)
+    return total
+
+
+def _evict_dead(key):
+    _graph_cache.pop(key, None)
 
 
 def gcn_graph(edge_index, edge_weight, n, add_self_loops=True):
     """gcn_norm + CSR of PyG's GCNConv, built once per (edge list, weights) and cached:
-    the reference recomputes it on every forward (cached=False); the result is identical."""
+    the reference recomputes it on every forward (cached=False); the result is identical.
+
+    The cache is keyed on the IDENTITY (and version counter) of the two tensors and holds them only weakly: an entry
+    lives exactly as long as the tensors it was built from, so a temporary (``edge_weight.float()`` made per call) can
+    neither produce a stale hit through a reused address nor pin its CSR in device memory.  Callers that want hits pass
+    the same tensor objects again (trainers.util.get_args_tuple keeps the float32 weights on the Data object)."""
     _need_cuda(edge_index, edge_weight)
     if edge_index.dtype != torch.int64 or edge_index.dim() != 2 or edge_index.shape[0] != 2:
         raise _lib.GnnbError("edge_index must be int64 [2, E]")
-    key = (edge_index.data_ptr(), edge_index._version, edge_index.shape[1],
-           None if edge_weight is None else (edge_weight.data_ptr(), edge_weight._version, edge_weight.dtype),
+    key = (id(edge_index), edge_index._version, edge_index.shape[1],
+           None if edge_weight is None else (id(edge_weight), edge_weight._version),
            int(n), bool(add_self_loops))
     hit = _graph_cache.get(key)
     if hit is not None:
-        _graph_cache.move_to_end(key)
-        return hit
+        g, ei_ref, ew_ref = hit
+        if ei_ref() is edge_index and (edge_weight is None or (ew_ref is not None and ew_ref() is edge_weight)):
+            _graph_cache.move_to_end(key)
+            return g
+        del _graph_cache[key]                   # an id reused by another tensor before the weakref callback ran
     ei = edge_index.contiguous()
     ew = None if edge_weight is None else edge_weight.to(torch.float32).contiguous()
     E = ei.shape[1]
@@ -380,10 +405,13 @@ def gcn_graph(edge_index, edge_weight, n, add_self_loops=True):
               _p(ws), ws.numel(), _stream())
     g.hub = hub_plan(g.rowptr)              # hub rows cut into tasks (forward CSR and its transpose)
     g.hub_t = hub_plan(g.rowptr_t)
-    g._keep = (edge_index, edge_weight)     # keeps the keyed storage alive so its address cannot be reused
-    _graph_cache[key] = g
-    while len(_graph_cache) > _GRAPH_CACHE_MAX:
-        _graph_cache.popitem(last=False)
+    g.nbytes = _graph_bytes(g)
+    drop = lambda _ref, key=key: _evict_dead(key)       # noqa: E731 -- the entry dies with either tensor
+    _graph_cache[key] = (g, weakref.ref(edge_index, drop), None if edge_weight is None else weakref.ref(edge_weight, drop))
+    total = sum(v[0].nbytes for v in _graph_cache.values())
+    while len(_graph_cache) > 1 and (len(_graph_cache) > _GRAPH_CACHE_MAX or total > _GRAPH_CACHE_MAX_BYTES):
+        _, (old, _a, _b) = _graph_cache.popitem(last=False)
+        total -= old.nbytes
     return g
 
 

@@ -17,11 +17,24 @@ def _features(x):
     return x if x.dtype in (torch.int8, torch.uint8) else x.float()
 
 
+def _weights32(ew):
+    """``data.edge_weight.float()`` (trainers/util.py:19), converted once per weight tensor and kept ON that tensor:
+    the loaders hand out float64 weights, and a fresh float32 copy per call would defeat the gcn_norm / CSR cache
+    (ops.gcn_graph is keyed on tensor identity) and rebuild both CSRs on every forward."""
+    if ew.dtype == torch.float32:
+        return ew
+    memo = getattr(ew, "_gnnb_f32", None)
+    if memo is None or memo[0] != ew._version:
+        memo = (ew._version, ew.float())
+        ew._gnnb_f32 = memo
+    return memo[1]
+
+
 def get_args_tuple(data):
     """trainers/util.py:16-24: (x, edge_index, edge_weight) / (x, edge_index) / x."""
     if getattr(data, "edge_index", None) is not None:
         if getattr(data, "edge_weight", None) is not None:
-            return _features(data.x), data.edge_index, data.edge_weight.float()
+            return _features(data.x), data.edge_index, _weights32(data.edge_weight)
         return data.x, data.edge_index
     return data.x
 

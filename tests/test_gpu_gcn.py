@@ -72,6 +72,50 @@ def test_graph_cache_hits_same_tensors():
     assert ops.gcn_graph(ei, ew, 50, True) is not a
 
 
+def test_float64_weights_through_get_args_tuple_build_one_graph():
+    """The loaders hand out float64 edge weights and the trainers call get_args_tuple every epoch (plain.py:44): the float32
+    copy is made once per weight tensor, so consecutive forwards hit the gcn_norm / CSR cache, and an entry dies with
+    the tensors it was built from instead of pinning its CSR in device memory."""
+    import gc
+    from gnn_b200.data import Data
+    from gnn_b200.trainers.util import get_args_tuple
+    ops.clear_graph_cache()
+    ei, ew = random_graph(60, 400, 4)
+    d = Data(x=torch.randint(0, 3, (60, 16), dtype=torch.int8, device=DEV), edge_index=ei.to(DEV), y=torch.zeros(60, 1, device=DEV))
+    d.edge_weight = ew.double().to(DEV)
+    conv = GCNConv(16, 8).to(DEV)
+    outs = [conv(*get_args_tuple(d)) for _ in range(3)]
+    assert len(ops._graph_cache) == 1
+    assert torch.equal(outs[0], outs[2])
+    assert get_args_tuple(d)[2] is get_args_tuple(d)[2] and get_args_tuple(d)[2].dtype == torch.float32
+    d.edge_weight.mul_(0.5)                                   # in-place change: new float32 copy, new graph
+    assert not torch.equal(conv(*get_args_tuple(d)), outs[0])
+    before = len(ops._graph_cache)
+    tmp = conv(d.x, d.edge_index, d.edge_weight.float())     # a caller's own temporary: its entry dies with it
+    gc.collect()
+    assert len(ops._graph_cache) == before and tmp.shape == outs[0].shape
+    del d, tmp, outs
+    gc.collect()
+    assert len(ops._graph_cache) == 0
+
+
+def test_linear_first_factories_take_int8_genotypes():
+    """create_network_linear / create_network_test put a stock Linear on x (networks.py:130-134, 295-306); x is int8 here."""
+    n, p = 50, 24
+    x = torch.randint(0, 3, (n, p), dtype=torch.int8, device=DEV)
+    ei, _ = random_graph(n, 200, 5, weights=False)
+    ei = ei.to(DEV)
+    for factory, kw in ((nets.create_network_linear, {}), (nets.create_network_test, {"internal_size": 8, "dropout": 0.0})):
+        torch.manual_seed(0)
+        m = factory(p, 1, **kw).to(DEV)
+        out = m(x, ei)
+        assert out.shape == (n, 1) and rel_err(out, m(x.float(), ei)) < 1e-6
+        out.sum().backward()
+    ens = nets.create_ensemble_creator(nets.create_network_linear, nets.create_network_linear)(p, 1).to(DEV)
+    ens.nns[0].to(DEV)                                        # the sub-models are unregistered on purpose (networks.py:103)
+    assert ens(x, ei).shape == (n, 1)
+
+
 @pytest.mark.parametrize("F", [1, 3, 32, 100, 128, 132, 260])
 def test_spmm_against_dense(F):
     n = 300

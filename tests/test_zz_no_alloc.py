@@ -62,8 +62,11 @@ def test_static_scratch_matches_workspace_version_twice_in_a_row():
     out3 = torch.empty(512, dtype=torch.float32, device="cuda")
     colsum_static(wide, out3)
     assert torch.equal(out3, colsum_with_workspace(wide))
-    empty = torch.empty((0, 8), device="cuda")
-    out4 = torch.full((8,), 7.0, device="cuda")
+    # an empty input right after a call that filled every partial row of the same width: the sums must be zero, i.e. no
+    # partial the first call left in the shared array is read back
+    colsum_static(first, out1)
+    empty = torch.empty((0, 100), device="cuda")
+    out4 = torch.full((100,), 7.0, device="cuda")
     colsum_static(empty, out4)
     torch.cuda.synchronize()
     assert torch.count_nonzero(out4) == 0
