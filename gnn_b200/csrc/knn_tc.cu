@@ -22,6 +22,14 @@
 #include "knn_select.cuh"
 #include "tc_common.cuh"
 
+// Ablation switches (timing experiments that produce INVALID results) exist only in builds made with -DGNNB_ABLATION
+// (scripts/build_variant.sh); the product library has none.
+#ifdef GNNB_ABLATION
+#define KNN_ABLATE(bit) (ablate & (bit))
+#else
+#define KNN_ABLATE(bit) false
+#endif
+
 namespace gnnb {
 
 using namespace tc;
@@ -299,7 +307,7 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                int k, int n_splits, int q_pairs, int stages, double* __restrict__ part_d2, int32_t* __restrict__ part_idx,
                int quad,          // 1: clusters of 4 = two pairs with neighbouring query tiles and the same key range; each key
                                   //    half-tile is fetched once (half by each of the two CTAs that need it) and multicast to both
-               int ablate) {      // measurement only (results invalid): 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue work
+               int ablate) {      // -DGNNB_ABLATION builds only (results invalid): 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue work
     extern __shared__ uint8_t smem_raw[];
     const int warp = threadIdx.x >> 5;
     const uint32_t crank = cluster_ctarank();                   // 0..1, or 0..3 in quad mode
@@ -352,7 +360,7 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                     const uint32_t ph = (it / stages) & 1;
                     mbar_wait(&sm.empty[s], ph ^ 1);            // own slot freed by the pair's MMAs (multicast commit)
                     const uint32_t full_leader = mapa_u32(smem_u32(&sm.full[s]), lead_rank);
-                    if (ablate & 1) {
+                    if (KNN_ABLATE(1)) {
                         mbar_arrive_cluster(full_leader);
                         continue;
                     }
@@ -386,7 +394,7 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                     tc_fence_after_sync();
                     const uint32_t a_addr = smem_u32(sm.tiles + (size_t)s * STAGE2_BYTES);
                     const uint32_t b_addr = a_addr + A_BYTES;
-                    if (ablate & 2) {
+                    if (KNN_ABLATE(2)) {
                         for (uint32_t c = 0; c < (quad ? 4u : 2u); ++c) mbar_arrive_cluster(mapa_u32(smem_u32(&sm.empty[s]), c));
                         continue;
                     }
@@ -436,7 +444,7 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             named_bar_sync(1, EPI_THREADS);
             mbar_wait(&sm.tfull[b], tph);
             tc_fence_after_sync();
-            if (ablate & 4) {                                  // measurement only: no accumulator reads, no selection
+            if (KNN_ABLATE(4)) {                                  // measurement only: no accumulator reads, no selection
                 if (leader) mbar_arrive(&sm.tempty[b]);
                 else        mbar_arrive_cluster(mapa_u32(smem_u32(&sm.tempty[b]), lead_rank));
                 continue;
@@ -487,8 +495,10 @@ int knn_tc_launch(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q
     if (use_pair < 0) {
         const char* e = getenv("GNNB_KNN_PAIR");
         use_pair = e ? atoi(e) : 1;
-        const char* a = getenv("GNNB_KNN_ABLATE");             // measurement only: 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue
+#ifdef GNNB_ABLATION
+        const char* a = getenv("GNNB_KNN_ABLATE");             // measurement builds only: 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue
         ablate = a ? atoi(a) : 0;
+#endif
         const char* q = getenv("GNNB_KNN_QUAD");
         quad = q ? atoi(q) : -1;                               // -1: pick by shape
     }

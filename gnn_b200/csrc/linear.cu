@@ -275,13 +275,17 @@ int linear_tc_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
 int linear_tc_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
                     float* dW, int64_t lddw, int terms, void* ws, size_t ws_bytes, cudaStream_t stream);
 size_t linear_tc_workspace(int64_t n, int64_t p, int64_t h, int terms);
-// int8-limb implementation (linear_i8.cu), precision 4; shapes it does not take fall back to two bf16 terms
+// int8-digit implementation (linear_i8.cu), precision 4; shapes it does not take are REFUSED (GNNB_E_UNSUPPORTED), never
+// run at another precision behind the caller's back -- gnnb_linear_supported tells a caller beforehand
 bool linear_i8_supported(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, int64_t h);
 size_t linear_i8_workspace(int64_t n, int64_t p, int64_t h);
 int linear_i8_fwd(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p, const float* W, int64_t ldw, int64_t h,
                   float* H, int64_t ldh, void* ws, size_t ws_bytes, cudaStream_t stream);
 int linear_i8_bwd_w(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
                     float* dW, int64_t lddw, void* ws, size_t ws_bytes, cudaStream_t stream);
+int linear_i8_prepare_dh(int x_format, int64_t n, const float* dH, int64_t lddh, int64_t h, void* ws, size_t ws_bytes, cudaStream_t stream);
+int linear_i8_bwd_w_prepared(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p, int64_t h, float* dW, int64_t lddw,
+                             void* ws, size_t ws_bytes, cudaStream_t stream);
 
 int linear_simt_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, const float* W, int64_t ldw, int64_t h,
                     float* H, int64_t ldh, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
@@ -328,6 +332,14 @@ int linear_simt_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_
 
 using namespace gnnb;
 
+static int refuse_i8(const char* who, int x_format, int64_t n, int64_t p, int64_t h) {
+    return fail(GNNB_E_UNSUPPORTED,
+                "%s: precision 4 (int8 digits) takes int8 or 2-bit packed X with 16-byte aligned rows, n >= 128, p >= 128, h <= 104 and a "
+                "contraction short enough for int32 digit sums (got format %d, n = %lld, p = %lld, h = %lld); ask gnnb_linear_supported "
+                "and pick precision 3 (or expand packed X with gnnb_unpack_2bit) for other shapes",
+                who, x_format, (long long)n, (long long)p, (long long)h);
+}
+
 extern "C" {
 
 int gnnb_linear_workspace_bytes(int64_t n, int64_t p, int64_t h, int precision, size_t* bytes) {
@@ -363,13 +375,11 @@ int gnnb_linear_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t 
     GNNB_REQUIRE(precision >= 0 && precision <= 4, GNNB_E_BADARG, "linear_fwd: precision must be 0..4");
     if (n == 0) return GNNB_OK;
     if (precision == 4) {
-        if (linear_i8_supported(X, x_is_i8, ldx, n, p, h))
-            return linear_i8_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, workspace, workspace_bytes, stream);
-        precision = 2;
+        if (!linear_i8_supported(X, x_is_i8, ldx, n, p, h)) return refuse_i8("linear_fwd", x_is_i8, n, p, h);
+        return linear_i8_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, workspace, workspace_bytes, stream);
     }
     if (x_is_i8 == 2)
-        return fail(GNNB_E_UNSUPPORTED, "linear_fwd: 2-bit packed X needs precision 4, 16-byte aligned rows, n >= 128, p >= 128 and h <= 104 "
-                                        "(expand it with gnnb_unpack_2bit for other shapes)");
+        return fail(GNNB_E_UNSUPPORTED, "linear_fwd: 2-bit packed X runs at precision 4 only (expand it with gnnb_unpack_2bit otherwise)");
     if (precision > 0) return linear_tc_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, precision, workspace, workspace_bytes, stream);
     return linear_simt_fwd(X, x_is_i8, ldx, n, p, W, ldw, h, H, ldh, workspace, workspace_bytes, stream);
 }
@@ -387,16 +397,39 @@ int gnnb_linear_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_
         return GNNB_OK;
     }
     if (precision == 4) {
-        if (linear_i8_supported(X, x_is_i8, ldx, n, p, h))
-            return linear_i8_bwd_w(X, x_is_i8, ldx, n, p, dH, lddh, h, dW, lddw, workspace, workspace_bytes, stream);
-        precision = 2;
+        if (!linear_i8_supported(X, x_is_i8, ldx, n, p, h)) return refuse_i8("linear_bwd_w", x_is_i8, n, p, h);
+        return linear_i8_bwd_w(X, x_is_i8, ldx, n, p, dH, lddh, h, dW, lddw, workspace, workspace_bytes, stream);
     }
     if (x_is_i8 == 2)
-        return fail(GNNB_E_UNSUPPORTED, "linear_bwd_w: 2-bit packed X needs precision 4, 16-byte aligned rows, n >= 128, p >= 128 and h <= 104 "
-                                        "(expand it with gnnb_unpack_2bit for other shapes)");
+        return fail(GNNB_E_UNSUPPORTED, "linear_bwd_w: 2-bit packed X runs at precision 4 only (expand it with gnnb_unpack_2bit otherwise)");
     if (precision > 0)
         return linear_tc_bwd_w(X, x_is_i8, ldx, n, p, dH, lddh, h, dW, lddw, precision, workspace, workspace_bytes, stream);
     return linear_simt_bwd_w(X, x_is_i8, ldx, n, p, dH, lddh, h, dW, lddw, workspace, workspace_bytes, stream);
+}
+
+int gnnb_linear_supported(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, int64_t h, int precision) {
+    if (precision < 0 || precision > 4 || x_is_i8 < 0 || x_is_i8 > 2 || n < 0 || p <= 0 || h <= 0) return 0;
+    if (precision == 4) return linear_i8_supported(X, x_is_i8, ldx, n, p, h) ? 1 : 0;
+    if (x_is_i8 == 2) return 0;
+    if (precision == 0) return 1;
+    return x_is_i8 == 1 ? 1 : 0;                               // tcgen05 bf16 tiles read int8 codes; float32 X runs on the fp32 tiles
+}
+
+int gnnb_linear_prepare_dh(int x_is_i8, int64_t n, const float* dH, int64_t lddh, int64_t h,
+                           void* workspace, size_t workspace_bytes, void* stream_) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(dH && n >= 128 && h > 0 && h <= 104 && lddh >= h && (x_is_i8 == 1 || x_is_i8 == 2), GNNB_E_BADARG,
+                 "linear_prepare_dh: bad argument (int8 or packed X, n >= 128, h <= 104)");
+    return linear_i8_prepare_dh(x_is_i8, n, dH, lddh, h, workspace, workspace_bytes, (cudaStream_t)stream_);
+}
+
+int gnnb_linear_bwd_w_prepared(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, int64_t h,
+                               float* dW, int64_t lddw, void* workspace, size_t workspace_bytes, void* stream_) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(X && dW && n >= 128 && p > 0 && h > 0 && lddw >= p && ldx >= (x_is_i8 == 2 ? (p + 3) / 4 : p), GNNB_E_BADARG,
+                 "linear_bwd_w_prepared: bad argument");
+    if (!linear_i8_supported(X, x_is_i8, ldx, n, p < 128 ? 128 : p, h)) return refuse_i8("linear_bwd_w_prepared", x_is_i8, n, p, h);
+    return linear_i8_bwd_w_prepared(X, x_is_i8, ldx, n, p, h, dW, lddw, workspace, workspace_bytes, (cudaStream_t)stream_);
 }
 
 int gnnb_linear_bwd_x(const float* dH, int64_t lddh, int64_t n, int64_t h,

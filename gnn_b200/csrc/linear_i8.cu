@@ -1,13 +1,19 @@
 // K5 on the int8 tensor path (precision 4): H = X . W^T and dW = dH^T . X with X as int8 genotype codes.
 //
-// The float operand (W for the forward pass, dH for the weight gradient) is quantised per output feature to 21 bits and
-// split into three balanced base-128 digits ("limbs", each an int8 in [-64, 64]):
-//     w ~= s_f * (d0 + 128 d1 + 16384 d2),   s_f = max|w_f| / 2^20.
+// The float operand (W for the forward pass, dH for the weight gradient) is quantised per output feature to a fixed-point
+// integer q = round(w / s_f) and split into three balanced digits ("limbs", each an int8):
+//     24-bit form:  |q| <= 8 355 711,  q = d0 + 256 d1 + 65536 d2,  d in [-128, 127],  s_f = max|w_f| / 8 355 711
+//     21-bit form:  |q| <= 2^20,       q = d0 + 128 d1 + 16384 d2,  d in [-64, 64],    s_f = max|w_f| / 2^20
 // Three int8 MMAs (tcgen05 kind::i8, exact int32 accumulation) give the three digit sums; the epilogue combines them
 // as ONE exact 64-bit integer and rounds once: the result is the exact dot product of X with the quantised operand.
+// The form is chosen per call from the length K of the contraction and the largest code the X format admits, so that the
+// int32 digit sums cannot overflow: 24 bits when K * cmax * 128 < 2^31, else 21 bits when K * cmax * 64 < 2^31, else the
+// shape is refused (cmax = 3 for 2-bit packed X, 128 for int8 X).  24 bits relative to the feature's largest element is
+// the resolution of the float32 operand itself at that magnitude, i.e. the rounding the reference's own fp32 matmul
+// applies to its largest terms.  NaN / Inf in the float operand give NaN in every output of that feature.
 // Against the split-bf16 kernels of linear_tc.cu: the 8-bit pipe retires ~2.5x the MACs per clock of the bf16 pipe on
 // B200 (scripts/ubench/mma_rate.cu: 7080 vs 2850 MAC/clk/SM), X goes from TMA straight into the MMA (no int8 -> bf16
-// converter, no TMEM staging), and 21 bits relative to the row maximum beat the 16 bits of two bf16 terms.
+// converter, no TMEM staging), and three int8 digits beat the 16 bits of two bf16 terms.
 //
 // Kernel = the CTA-pair pipeline of knn_tc.cu (cta_group::2): a pair owns 256 rows of the M side, each CTA stages its
 // own 128-row A tile and HALF of the limb tile; the leader issues, per 128-byte k-block, 4 x [N = 256 + N = 64] (the
@@ -24,6 +30,14 @@
 namespace gnnb {
 
 using namespace tc;
+
+// Ablation switches (timing experiments that produce INVALID results) exist only in builds made with -DGNNB_ABLATION
+// (scripts/build_variant.sh); the product library has none.
+#ifdef GNNB_ABLATION
+#define LI_ABLATE(bit) (ablate & (bit))
+#else
+#define LI_ABLATE(bit) false
+#endif
 
 namespace {
 constexpr int BM = 128, BKB = 128;                       // A tile: 128 rows (or 128 markers) x 128 bytes of K
@@ -71,30 +85,46 @@ constexpr size_t SMEM = 1024 + (size_t)XS * A_BYTES + (size_t)BS * B_BYTES + siz
 static_assert(SMEM <= 232448, "shared memory of linear_i8_kernel");
 
 // ---- quantisation -----------------------------------------------------------------------------------------------------
+// SHIFT = 8: base-256 digits in [-128, 127] (24-bit form); SHIFT = 7: base-128 digits in [-64, 64] (21-bit form)
+constexpr float QMAX24 = 8355711.0f;                     // 127 * 65536 + 127 * 256 + 127: the top digit stays <= 127 after carries
+constexpr float QMAX21 = 1048576.0f;
+template <int SHIFT>
 __device__ __forceinline__ void digits3(float w, float inv_scale, int8_t& d0, int8_t& d1, int8_t& d2) {
-    int q = __float2int_rn(w * inv_scale);               // |q| <= 2^20
-    int t0 = ((q + 64) & 127) - 64;                      // balanced digit in [-64, 63]
-    int q1 = (q - t0) >> 7;
-    int t1 = ((q1 + 64) & 127) - 64;
-    int q2 = (q1 - t1) >> 7;                             // in [-64, 64]
+    constexpr int B = 1 << SHIFT, HALF = B >> 1;
+    int q = __float2int_rn(w * inv_scale);               // |q| <= QMAX
+    int t0 = ((q + HALF) & (B - 1)) - HALF;              // balanced digit
+    int q1 = (q - t0) >> SHIFT;
+    int t1 = ((q1 + HALF) & (B - 1)) - HALF;
+    int q2 = (q1 - t1) >> SHIFT;
     d0 = (int8_t)t0; d1 = (int8_t)t1; d2 = (int8_t)q2;
 }
+// (1 / scale, scale) of a feature whose largest magnitude has the bit pattern `bits`.  A non-finite maximum (NaN or Inf
+// somewhere in the feature) quantises everything to zero and makes the scale NaN: every output of the feature is NaN,
+// as it is (NaN or Inf) after the reference's fp32 matmul.
+__device__ __forceinline__ void feature_scale(unsigned bits, float qmax, float& inv, float& scale) {
+    const float a = __uint_as_float(bits);
+    if (bits >= 0x7F800000u) { inv = 0.f; scale = __uint_as_float(0x7FC00000u); return; }
+    inv = a > 0.f ? qmax / a : 0.f;
+    scale = a / qmax;
+}
 
-// amax_bits[r] = bits of max_c |in[r, c]|: grid (rows, chunks), one atomicMax per CTA (|x| >= 0 orders like its bit pattern)
+// amax_bits[r] = bits of max_c |in[r, c]|: grid (rows, chunks), one atomicMax per CTA.  The maximum is taken over the BIT
+// PATTERNS of |x|: for non-negative floats the integer order is the float order, +Inf sorts above every finite value and
+// every NaN above +Inf, so a NaN anywhere in the row survives the reduction (fmaxf would drop it).
 __global__ void row_absmax_kernel(const float* __restrict__ in, int64_t ld, int64_t cols, unsigned* __restrict__ amax_bits) {
     const float* row = in + (int64_t)blockIdx.x * ld;
     const int64_t per = (cols + gridDim.y - 1) / gridDim.y;
     const int64_t c0 = (int64_t)blockIdx.y * per, c1 = c0 + per < cols ? c0 + per : cols;
-    float m = 0.f;
-    for (int64_t c = c0 + threadIdx.x; c < c1; c += blockDim.x) m = fmaxf(m, fabsf(row[c]));
-    __shared__ float red[32];
-    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    unsigned m = 0;
+    for (int64_t c = c0 + threadIdx.x; c < c1; c += blockDim.x) m = max(m, __float_as_uint(row[c]) & 0x7FFFFFFFu);
+    __shared__ unsigned red[32];
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
     __syncthreads();
     if (threadIdx.x < 32) {
-        m = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
-        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-        if (threadIdx.x == 0) atomicMax(&amax_bits[blockIdx.x], __float_as_uint(m));
+        m = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0u;
+        for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (threadIdx.x == 0) atomicMax(&amax_bits[blockIdx.x], m);
     }
 }
 
@@ -103,14 +133,15 @@ __global__ void col_absmax_kernel(const float* __restrict__ in, int64_t ld, int6
     const int c = threadIdx.x;
     if (c >= cols) return;
     const int64_t r0 = (int64_t)blockIdx.x * 64, r1 = r0 + 64 < rows ? r0 + 64 : rows;
-    float m = 0.f;
-    for (int64_t r = r0; r < r1; ++r) m = fmaxf(m, fabsf(in[r * ld + c]));
-    atomicMax(&amax_bits[c], __float_as_uint(m));
+    unsigned m = 0;
+    for (int64_t r = r0; r < r1; ++r) m = max(m, __float_as_uint(in[r * ld + c]) & 0x7FFFFFFFu);
+    atomicMax(&amax_bits[c], m);
 }
 
 // limbs[(digit rows), c] of W[f, c].  One thread = 16 consecutive columns of one limb-matrix row triple (f, HP + f, D2_ROW + f):
 // four float4 loads, three 16-byte stores.  Rows f >= h (padding of the MMA N dimension) and columns >= cols are zeroed here,
 // so the workspace needs no separate clear.
+template <int SHIFT>
 __global__ void quantize_rows_kernel(const float* __restrict__ W, int64_t ldw, int h, int64_t cols, const unsigned* __restrict__ amax_bits,
                                      int8_t* __restrict__ limbs, int64_t ldl, float* __restrict__ scale) {
     const int64_t groups = ldl / 16;                     // ldl is a multiple of 16
@@ -120,8 +151,8 @@ __global__ void quantize_rows_kernel(const float* __restrict__ W, int64_t ldw, i
         const int64_t c0 = (i % groups) * 16;
         __align__(16) int8_t d[3][16];
         if (f < h) {
-            const float a = __uint_as_float(amax_bits[f]);
-            const float inv = a > 0.f ? 1048576.0f / a : 0.f;
+            float inv, sc;
+            feature_scale(amax_bits[f], SHIFT == 8 ? QMAX24 : QMAX21, inv, sc);
             const float* src = W + (int64_t)f * ldw + c0;
             const bool vec = (c0 + 16 <= cols) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0);
             float w[16];
@@ -136,8 +167,8 @@ __global__ void quantize_rows_kernel(const float* __restrict__ W, int64_t ldw, i
                 for (int q = 0; q < 16; ++q) w[q] = (c0 + q < cols) ? src[q] : 0.f;
             }
 #pragma unroll
-            for (int q = 0; q < 16; ++q) digits3(w[q], inv, d[0][q], d[1][q], d[2][q]);
-            if (c0 == 0) scale[f] = a * (1.0f / 1048576.0f);
+            for (int q = 0; q < 16; ++q) digits3<SHIFT>(w[q], inv, d[0][q], d[1][q], d[2][q]);
+            if (c0 == 0) scale[f] = sc;
         } else {
 #pragma unroll
             for (int q = 0; q < 16; ++q) d[0][q] = d[1][q] = d[2][q] = 0;
@@ -152,6 +183,7 @@ __global__ void quantize_rows_kernel(const float* __restrict__ W, int64_t ldw, i
 
 // limbs[(digit rows), r] of dH[r, f]: transposed through shared memory.  CTA = 128 rows x a quarter of the 128 limb-row
 // triples; a thread packs 4 consecutive rows of one triple into 32-bit stores (a warp writes 128 consecutive bytes).
+template <int SHIFT>
 __global__ void quantize_cols_kernel(const float* __restrict__ dH, int64_t ld, int64_t rows, int h, const unsigned* __restrict__ amax_bits,
                                      int8_t* __restrict__ limbs, int64_t ldl, float* __restrict__ scale) {
     __shared__ float tile[128][33];                      // [row][feature of this quarter]
@@ -167,11 +199,11 @@ __global__ void quantize_cols_kernel(const float* __restrict__ dH, int64_t ld, i
     for (int ff = fsub; ff < 32; ff += 8) {
         const int f = f0 + ff;
         if (f >= F_ROWS) continue;
-        const float a = f < h ? __uint_as_float(amax_bits[f]) : 0.f;
-        const float inv = a > 0.f ? 1048576.0f / a : 0.f;
+        float inv = 0.f, sc = 0.f;
+        if (f < h) feature_scale(amax_bits[f], SHIFT == 8 ? QMAX24 : QMAX21, inv, sc);
         __align__(4) int8_t d[3][4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) digits3(tile[4 * quad + q][ff], inv, d[0][q], d[1][q], d[2][q]);
+        for (int q = 0; q < 4; ++q) digits3<SHIFT>(tile[4 * quad + q][ff], inv, d[0][q], d[1][q], d[2][q]);
         const int64_t col = r0 + 4 * quad;               // ldl % 16 == 0 and r0 % 128 == 0: the 4-byte store stays inside the row
         if (col < ldl) {
             if (f < HP) {
@@ -180,7 +212,7 @@ __global__ void quantize_cols_kernel(const float* __restrict__ dH, int64_t ld, i
             }
             *reinterpret_cast<uint32_t*>(limbs + (int64_t)(D2_ROW + f) * ldl + col) = *reinterpret_cast<const uint32_t*>(d[2]);
         }
-        if (blockIdx.x == 0 && quad == 0 && f < h) scale[f] = a * (1.0f / 1048576.0f);
+        if (blockIdx.x == 0 && quad == 0 && f < h) scale[f] = sc;
     }
 }
 
@@ -192,7 +224,8 @@ linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                  float* __restrict__ out, int64_t ld_out, int64_t m_total, int h,
                  int quad,          // 1: clusters of 4 = two pairs; each digit half-tile is fetched once and multicast to both pairs
                                     //    (map_b0 / map_b1 then have boxes of a quarter instead of a half of N0 / N1 rows)
-                 int ablate) {      // measurement only (results invalid): 1 = no TMA loads, 2 = no MMAs
+                 int shift,         // log2 of the digit base: 8 (24-bit form) or 7 (21-bit form)
+                 int ablate) {      // -DGNNB_ABLATION builds only (results invalid): 1 = no TMA loads, 2 = no MMAs
     extern __shared__ uint8_t smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t crank = cluster_ctarank();                          // 0..1, or 0..3 in quad mode
@@ -225,7 +258,7 @@ linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 const int s = u % XS;
                 mbar_wait(&bars->xempty[s], ((u / XS) & 1) ^ 1);
                 const uint32_t full_leader = mapa_u32(smem_u32(&bars->xfull[s]), lead_rank);
-                if (ablate & 1) { mbar_arrive_cluster(full_leader); continue; }
+                if (LI_ABLATE(1)) { mbar_arrive_cluster(full_leader); continue; }
                 if (leader) mbar_arrive_expect_tx(&bars->xfull[s], 2 * A_BYTES);
                 else        mbar_arrive_cluster(full_leader);
                 uint8_t* a = xt + (size_t)s * A_BYTES;
@@ -241,7 +274,7 @@ linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 const int s = u % BS;
                 mbar_wait(&bars->bempty[s], ((u / BS) & 1) ^ 1);
                 const uint32_t full_leader = mapa_u32(smem_u32(&bars->bfull[s]), lead_rank);
-                if (ablate & 1) { mbar_arrive_cluster(full_leader); continue; }
+                if (LI_ABLATE(1)) { mbar_arrive_cluster(full_leader); continue; }
                 if (leader) mbar_arrive_expect_tx(&bars->bfull[s], 2 * B_BYTES);
                 else        mbar_arrive_cluster(full_leader);
                 uint8_t* b = bt + (size_t)s * B_BYTES;
@@ -269,7 +302,7 @@ linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 tc_fence_after_sync();
                 const uint32_t a_addr = smem_u32(xt + (size_t)sx * A_BYTES);
                 const uint32_t b0_addr = smem_u32(bt + (size_t)sb * B_BYTES), b1_addr = b0_addr + B0_HALF;
-                if (ablate & 2) {
+                if (LI_ABLATE(2)) {
                     for (uint32_t c = 0; c < 2u; ++c) mbar_arrive_cluster(mapa_u32(smem_u32(&bars->xempty[sx]), lead_rank + c));
                     for (uint32_t c = 0; c < (quad ? 4u : 2u); ++c) mbar_arrive_cluster(mapa_u32(smem_u32(&bars->bempty[sb]), c));
                     continue;
@@ -309,7 +342,7 @@ linear_i8_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 for (int c = 0; c < 32; ++c) {
                     const int f = c0 + c;
                     if (f < h) {
-                        const long long sum = (long long)(int)a0[c] + 128LL * (long long)(int)a1[c] + 16384LL * (long long)(int)a2[c];
+                        const long long sum = (long long)(int)a0[c] + ((long long)(int)a1[c] << shift) + ((long long)(int)a2[c] << (2 * shift));
                         const float r = (float)((double)sum * (double)scale[f]);
                         if (BWD) out[(int64_t)f * ld_out + m] = r;     // dW[f, marker]: a warp writes 32 consecutive markers
                         else     out[m * ld_out + f] = r;              // H[row, f]
@@ -365,7 +398,7 @@ template <bool BWD>
 __global__ void __launch_bounds__(P2_THREADS, 1)
 linear_p2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b0,
                  const __grid_constant__ CUtensorMap map_b1, int64_t k_total, const float* __restrict__ scale,
-                 float* __restrict__ out, int64_t ld_out, int64_t m_total, int h, int quad) {
+                 float* __restrict__ out, int64_t ld_out, int64_t m_total, int h, int quad, int shift) {
     extern __shared__ uint8_t smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t crank = cluster_ctarank();
@@ -500,7 +533,7 @@ linear_p2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     for (int c = 0; c < 32; ++c) {
                         const int f = c0 + c;
                         if (f < h) {
-                            const long long sum = (long long)(int)a0[c] + 128LL * (long long)(int)a1[c] + 16384LL * (long long)(int)a2[c];
+                            const long long sum = (long long)(int)a0[c] + ((long long)(int)a1[c] << shift) + ((long long)(int)a2[c] << (2 * shift));
                             const float r = (float)((double)sum * (double)scale[f]);
                             if (BWD) out[(int64_t)f * ld_out + m] = r;
                             else     out[m * ld_out + f] = r;
@@ -517,14 +550,16 @@ linear_p2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 
 template <bool BWD, bool PACKED>
 int launch_i8(const CUtensorMap& mx, const CUtensorMap& mb0, const CUtensorMap& mb1, int64_t k_total, const float* scale, float* out,
-              int64_t ld_out, int64_t m_total, int h, cudaStream_t stream) {
+              int64_t ld_out, int64_t m_total, int h, int shift, cudaStream_t stream) {
     const int64_t tiles = (m_total + BM - 1) / BM, pairs = (tiles + 1) / 2;
     static int quad = -1, ablate = 0;
     if (quad < 0) {
         const char* e = getenv("GNNB_LINEAR_QUAD");
         quad = e ? atoi(e) : 1;
-        const char* a = getenv("GNNB_LINEAR_ABLATE");          // measurement only
+#ifdef GNNB_ABLATION
+        const char* a = getenv("GNNB_LINEAR_ABLATE");          // measurement builds only
         ablate = a ? atoi(a) : 0;
+#endif
     }
     const int64_t groups = quad ? (pairs + 1) / 2 : pairs;
     const size_t smem = PACKED ? SMEM2 : SMEM;
@@ -542,10 +577,10 @@ int launch_i8(const CUtensorMap& mx, const CUtensorMap& mb0, const CUtensorMap& 
     cfg.numAttrs = 1;
     if (PACKED) {
         GNNB_SET_DYN_SMEM(linear_p2_kernel<BWD>, smem);
-        GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_p2_kernel<BWD>, mx, mb0, mb1, k_total, scale, out, ld_out, m_total, h, quad));
+        GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_p2_kernel<BWD>, mx, mb0, mb1, k_total, scale, out, ld_out, m_total, h, quad, shift));
     } else {
         GNNB_SET_DYN_SMEM(linear_i8_kernel<BWD>, smem);
-        GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_i8_kernel<BWD>, mx, mb0, mb1, k_total, scale, out, ld_out, m_total, h, quad, ablate));
+        GNNB_CUDA(cudaLaunchKernelEx(&cfg, linear_i8_kernel<BWD>, mx, mb0, mb1, k_total, scale, out, ld_out, m_total, h, quad, shift, ablate));
     }
     return GNNB_OK;
 }
@@ -558,9 +593,20 @@ static uint32_t box_div() {          // quad mode fetches the digit half-tiles i
 }
 static size_t limb_bytes(int64_t k_len) { return align_up((size_t)LIMB_ROWS * align_up((size_t)k_len, 16), 1024); }
 
-// x_format: 1 = int8 codes (ldx in elements = bytes), 2 = 2-bit packed codes (ldx = bytes per packed row)
+// log2 of the digit base for a contraction of length k_len, or 0 if the int32 digit sums could overflow in either form:
+// |sum| <= k_len * cmax * dmax with cmax = 3 (2-bit packed codes) or 128 (any int8) and dmax = 128 / 64 (24- / 21-bit form).
+static int digit_shift(int x_format, int64_t k_len) {
+    const int64_t cmax = x_format == 2 ? 3 : 128;
+    if (k_len * cmax * 128 < (1LL << 31)) return 8;
+    if (k_len * cmax * 64 < (1LL << 31)) return 7;
+    return 0;
+}
+
+// x_format: 1 = int8 codes (ldx in elements = bytes), 2 = 2-bit packed codes (ldx = bytes per packed row).
+// The contraction runs over p in the forward pass and over n in the weight gradient: both must be overflow-safe.
 bool linear_i8_supported(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p, int64_t h) {
-    return (x_format == 1 || x_format == 2) && (uintptr_t)X % 16 == 0 && ldx % 16 == 0 && h >= 1 && h <= HP && n >= 128 && p >= 128;
+    return (x_format == 1 || x_format == 2) && (uintptr_t)X % 16 == 0 && ldx % 16 == 0 && h >= 1 && h <= HP && n >= 128 && p >= 128 &&
+           digit_shift(x_format, p) != 0 && digit_shift(x_format, n) != 0;
 }
 
 size_t linear_i8_workspace(int64_t n, int64_t p, int64_t h) {
@@ -573,6 +619,8 @@ int linear_i8_fwd(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p
                   float* H, int64_t ldh, void* ws, size_t ws_bytes, cudaStream_t stream) {
     const size_t need = linear_i8_workspace(n, p, h);
     GNNB_REQUIRE(ws && ws_bytes >= need, GNNB_E_WORKSPACE, "linear_fwd: workspace %zu < %zu bytes", ws_bytes, need);
+    const int shift = digit_shift(x_format, p);
+    GNNB_REQUIRE(shift != 0, GNNB_E_UNSUPPORTED, "linear_fwd: %lld markers overflow the int32 digit sums", (long long)p);
     uint8_t* wsb = reinterpret_cast<uint8_t*>(align_up((size_t)(uintptr_t)ws, 1024));
     int8_t* limbs = reinterpret_cast<int8_t*>(wsb);
     const int64_t ldl = (int64_t)align_up((size_t)p, 16);
@@ -583,7 +631,9 @@ int linear_i8_fwd(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p
     GNNB_LAUNCH_CHECK();
     {
         int64_t total = (int64_t)F_ROWS * (ldl / 16), blocks = (total + 255) / 256, cap = (int64_t)sm_count() * 16;
-        quantize_rows_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, stream>>>(W, ldw, (int)h, p, amax_bits, limbs, ldl, scale);
+        const unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
+        if (shift == 8) quantize_rows_kernel<8><<<grid, 256, 0, stream>>>(W, ldw, (int)h, p, amax_bits, limbs, ldl, scale);
+        else            quantize_rows_kernel<7><<<grid, 256, 0, stream>>>(W, ldw, (int)h, p, amax_bits, limbs, ldl, scale);
         GNNB_LAUNCH_CHECK();
     }
     CUtensorMap mx, mb0, mb1;
@@ -594,14 +644,20 @@ int linear_i8_fwd(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p
     if (rc != GNNB_OK) return rc;
     rc = make_tensor_map_2d(&mb1, limbs, 1, (uint64_t)p, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N1 / 2 / box_div());
     if (rc != GNNB_OK) return rc;
-    if (x_format == 2) return launch_i8<false, true>(mx, mb0, mb1, p, scale, H, ldh, n, (int)h, stream);
-    return launch_i8<false, false>(mx, mb0, mb1, p, scale, H, ldh, n, (int)h, stream);
+    if (x_format == 2) return launch_i8<false, true>(mx, mb0, mb1, p, scale, H, ldh, n, (int)h, shift, stream);
+    return launch_i8<false, false>(mx, mb0, mb1, p, scale, H, ldh, n, (int)h, shift, stream);
 }
 
-int linear_i8_bwd_w(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
-                    float* dW, int64_t lddw, void* ws, size_t ws_bytes, cudaStream_t stream) {
-    const size_t need = linear_i8_workspace(n, p, h);
+// The weight gradient in two halves, so that a caller can split the markers into ranges (one GEMM launch per range, e.g.
+// to overlap the all-reduce of one range with the GEMM of the next) without quantising dH once per range:
+// linear_i8_prepare_dh fills the workspace with the digits and scales of dH^T, linear_i8_bwd_w_prepared runs the GEMM for
+// the markers X points at (any 16-byte aligned column range of the genotype matrix) against that workspace.
+int linear_i8_prepare_dh(int x_format, int64_t n, const float* dH, int64_t lddh, int64_t h, void* ws, size_t ws_bytes,
+                         cudaStream_t stream) {
+    const size_t need = linear_i8_workspace(n, 128, h);
     GNNB_REQUIRE(ws && ws_bytes >= need, GNNB_E_WORKSPACE, "linear_bwd_w: workspace %zu < %zu bytes", ws_bytes, need);
+    const int shift = digit_shift(x_format, n);
+    GNNB_REQUIRE(shift != 0, GNNB_E_UNSUPPORTED, "linear_bwd_w: %lld individuals overflow the int32 digit sums", (long long)n);
     uint8_t* wsb = reinterpret_cast<uint8_t*>(align_up((size_t)(uintptr_t)ws, 1024));
     int8_t* limbs = reinterpret_cast<int8_t*>(wsb);
     const int64_t ldl = (int64_t)align_up((size_t)n, 16);
@@ -610,8 +666,23 @@ int linear_i8_bwd_w(const void* X, int x_format, int64_t ldx, int64_t n, int64_t
     GNNB_CUDA(cudaMemsetAsync(amax_bits, 0, 512 * sizeof(unsigned), stream));
     col_absmax_kernel<<<(unsigned)((n + 63) / 64), 128, 0, stream>>>(dH, lddh, n, (int)h, amax_bits);
     GNNB_LAUNCH_CHECK();
-    quantize_cols_kernel<<<dim3((unsigned)((ldl + 127) / 128), 4), 256, 0, stream>>>(dH, lddh, n, (int)h, amax_bits, limbs, ldl, scale);
+    const dim3 grid((unsigned)((ldl + 127) / 128), 4);
+    if (shift == 8) quantize_cols_kernel<8><<<grid, 256, 0, stream>>>(dH, lddh, n, (int)h, amax_bits, limbs, ldl, scale);
+    else            quantize_cols_kernel<7><<<grid, 256, 0, stream>>>(dH, lddh, n, (int)h, amax_bits, limbs, ldl, scale);
     GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+int linear_i8_bwd_w_prepared(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p, int64_t h, float* dW, int64_t lddw,
+                             void* ws, size_t ws_bytes, cudaStream_t stream) {
+    const size_t need = linear_i8_workspace(n, 128, h);
+    GNNB_REQUIRE(ws && ws_bytes >= need, GNNB_E_WORKSPACE, "linear_bwd_w: workspace %zu < %zu bytes", ws_bytes, need);
+    const int shift = digit_shift(x_format, n);
+    GNNB_REQUIRE(shift != 0, GNNB_E_UNSUPPORTED, "linear_bwd_w: %lld individuals overflow the int32 digit sums", (long long)n);
+    uint8_t* wsb = reinterpret_cast<uint8_t*>(align_up((size_t)(uintptr_t)ws, 1024));
+    int8_t* limbs = reinterpret_cast<int8_t*>(wsb);
+    const int64_t ldl = (int64_t)align_up((size_t)n, 16);
+    float* scale = reinterpret_cast<float*>(reinterpret_cast<unsigned*>(wsb + limb_bytes(n)) + 512);
     CUtensorMap mx, mb0, mb1;
     // box: 128 markers (128 B, or 32 packed bytes) x 128 individuals
     int rc = x_format == 2 ? make_tensor_map_2d(&mx, X, 1, (uint64_t)((p + 3) / 4), (uint64_t)n, (uint64_t)ldx, 32, BKB, /*swizzle*/ false)
@@ -621,8 +692,17 @@ int linear_i8_bwd_w(const void* X, int x_format, int64_t ldx, int64_t n, int64_t
     if (rc != GNNB_OK) return rc;
     rc = make_tensor_map_2d(&mb1, limbs, 1, (uint64_t)n, (uint64_t)LIMB_ROWS, (uint64_t)ldl, BKB, N1 / 2 / box_div());
     if (rc != GNNB_OK) return rc;
-    if (x_format == 2) return launch_i8<true, true>(mx, mb0, mb1, n, scale, dW, lddw, p, (int)h, stream);
-    return launch_i8<true, false>(mx, mb0, mb1, n, scale, dW, lddw, p, (int)h, stream);
+    if (x_format == 2) return launch_i8<true, true>(mx, mb0, mb1, n, scale, dW, lddw, p, (int)h, shift, stream);
+    return launch_i8<true, false>(mx, mb0, mb1, n, scale, dW, lddw, p, (int)h, shift, stream);
+}
+
+int linear_i8_bwd_w(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
+                    float* dW, int64_t lddw, void* ws, size_t ws_bytes, cudaStream_t stream) {
+    const size_t need = linear_i8_workspace(n, p, h);
+    GNNB_REQUIRE(ws && ws_bytes >= need, GNNB_E_WORKSPACE, "linear_bwd_w: workspace %zu < %zu bytes", ws_bytes, need);
+    int rc = linear_i8_prepare_dh(x_format, n, dH, lddh, h, ws, ws_bytes, stream);
+    if (rc != GNNB_OK) return rc;
+    return linear_i8_bwd_w_prepared(X, x_format, ldx, n, p, h, dW, lddw, ws, ws_bytes, stream);
 }
 
 }  // namespace gnnb

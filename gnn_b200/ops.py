@@ -462,11 +462,19 @@ def spmm(rowptr, col, val, H, bias=None, n=None, hub=None, nnz=None):
 
 
 # --------------------------------------------------------------------------------------- K5
-def _precision(n, p, h, x_is_i8):
+def _precision(X, fmt, n, p, h):
+    """The projection path for this call.  ``config["linear_precision"]``: an explicit 0..4 is passed through (the library
+    refuses shapes that precision does not take); "auto" = int8 tensor cores with 24-bit fixed-point digits (4) for
+    integer genotypes wherever that kernel takes the shape, else three bf16 terms (3, ~fp32-exact on integer codes) for
+    int8 codes, exact fp32 tiles (0) for float features."""
     prec = config["linear_precision"]
-    if prec == "auto":          # int8 genotypes: int8 tensor cores, float operand as three 7-bit digits (rel. error ~1e-6;
-        return 4 if x_is_i8 else 0      # shapes that path does not take fall back to two bf16 terms); float x: fp32 tiles
-    return int(prec)
+    if fmt == 0:
+        return 0                          # float features (inner layers, scaled=True) always run on the exact fp32 tiles
+    if prec != "auto":
+        return int(prec)
+    if _lib.lib().gnnb_linear_supported(_p(X), fmt, X.stride(0), n, p, h, 4):
+        return 4
+    return 3 if fmt == 1 else 4           # packed X outside the int8 kernel's shapes: let the library refuse it loudly
 
 
 def _x_operand(X, p_packed):
@@ -496,7 +504,7 @@ def linear_fwd(X, W, precision=None):
     if p != W.shape[1]:
         raise _lib.GnnbError(f"linear_fwd: x has {p} columns, the weight {W.shape[1]}")
     n = X.shape[0]
-    prec = _precision(n, p, h, fmt != 0) if precision is None else precision
+    prec = _precision(X, fmt, n, p, h) if precision is None else precision
     H = torch.empty((n, h), dtype=torch.float32, device=X.device)
     with torch.cuda.device(X.device):
         ws = _ws(_ws_bytes("gnnb_linear_workspace_bytes", n, p, h, prec), X.device)
@@ -506,8 +514,9 @@ def linear_fwd(X, W, precision=None):
     return H
 
 
-def linear_bwd_w(X, dH, precision=None, p=None):
-    """dW [h, p] = dH^T . X  (``p``: marker count, needed when X is 2-bit packed)"""
+def linear_bwd_w(X, dH, precision=None, p=None, out=None):
+    """dW [h, p] = dH^T . X  (``p``: marker count, needed when X is 2-bit packed; ``out``: optional float32 [h, p] with unit
+    column stride to write into, e.g. the weight's slice of a flat gradient buffer)"""
     _need_cuda(X, dH)
     dH = dH.contiguous()
     h = dH.shape[1]
@@ -515,13 +524,63 @@ def linear_bwd_w(X, dH, precision=None, p=None):
     n = X.shape[0]
     if dH.shape[0] != n:
         raise _lib.GnnbError(f"linear_bwd_w: x has {n} rows, dH {dH.shape[0]}")
-    prec = _precision(n, p, h, fmt != 0) if precision is None else precision
-    dW = torch.empty((h, p), dtype=torch.float32, device=X.device)
+    prec = _precision(X, fmt, n, p, h) if precision is None else precision
+    dW = _grad_out(out, h, p, X.device)
     with torch.cuda.device(X.device):
         ws = _ws(_ws_bytes("gnnb_linear_workspace_bytes", n, p, h, prec), X.device)
         _declare(flops=2.0 * n * p * h, bytes=float(n * X.shape[1] * X.element_size() + h * p * 4 + n * h * 4))
         _call("gnnb_linear_bwd_w", _p(X), fmt, X.stride(0), n, p, _p(dH), dH.stride(0), h,
               _p(dW), dW.stride(0), prec, _p(ws), ws.numel(), _stream())
+    return dW
+
+
+def _grad_out(out, h, p, device):
+    if out is None:
+        return torch.empty((h, p), dtype=torch.float32, device=device)
+    if out.shape != (h, p) or out.dtype != torch.float32 or out.stride(1) != 1 or out.device != device:
+        raise _lib.GnnbError("linear_bwd_w: `out` must be a float32 [h, p] tensor with unit column stride on x's device")
+    return out
+
+
+def marker_ranges(p, n_ranges, fmt):
+    """Cut the markers into ``n_ranges`` ranges whose starts are 16-byte aligned in the genotype matrix (a multiple of 64
+    codes when packed, 16 when int8) and a multiple of 128 markers (one M tile of the weight-gradient kernel)."""
+    step = (p + n_ranges - 1) // n_ranges
+    step = (step + 127) // 128 * 128
+    return [(c0, min(p, c0 + step)) for c0 in range(0, p, step)]
+
+
+def linear_bwd_w_ranges(X, dH, ranges, p=None, out=None, after_range=None):
+    """dW = dH^T . X computed one marker range at a time from ONE quantisation of dH (gnnb_linear_prepare_dh +
+    gnnb_linear_bwd_w_prepared); ``after_range(c0, c1)`` is called after the kernels of each range have been enqueued --
+    the data-parallel step starts that range's all-reduce there, so it overlaps the next range's GEMM.  Same bits as
+    ``linear_bwd_w``.  Needs the int8-digit path (int8 or packed X); other inputs fall back to one ``linear_bwd_w``."""
+    _need_cuda(X, dH)
+    dH = dH.contiguous()
+    h = dH.shape[1]
+    X, fmt, p = _x_operand(X, p)
+    n = X.shape[0]
+    if (fmt == 0 or config["linear_precision"] not in ("auto", 4, "4")
+            or not _lib.lib().gnnb_linear_supported(_p(X), fmt, X.stride(0), n, p, h, 4)):
+        dW = linear_bwd_w(X, dH, p=p, out=out)
+        if after_range is not None:
+            after_range(0, p)
+        return dW
+    dW = _grad_out(out, h, p, X.device)
+    per_code = 4 if fmt == 2 else 1
+    with torch.cuda.device(X.device):
+        ws = _ws(_ws_bytes("gnnb_linear_workspace_bytes", n, p, h, 4), X.device)
+        _call("gnnb_linear_prepare_dh", fmt, n, _p(dH), dH.stride(0), h, _p(ws), ws.numel(), _stream())
+        for c0, c1 in ranges:
+            if c0 % (16 * per_code) != 0:
+                raise _lib.GnnbError("linear_bwd_w_ranges: range starts must be 16-byte aligned in the genotype matrix")
+            xs = ctypes.c_void_p(X.data_ptr() + c0 // per_code)
+            ds = ctypes.c_void_p(dW.data_ptr() + 4 * c0)
+            _declare(flops=2.0 * n * (c1 - c0) * h, bytes=float(n * (c1 - c0) // per_code + h * (c1 - c0) * 4))
+            _call("gnnb_linear_bwd_w_prepared", xs, fmt, X.stride(0), n, c1 - c0, h, ds, dW.stride(0),
+                  _p(ws), ws.numel(), _stream())
+            if after_range is not None:
+                after_range(c0, c1)
     return dW
 
 

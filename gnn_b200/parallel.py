@@ -182,3 +182,82 @@ def knn_sharded(X_local, row0, n_total, k, rank, world, extra_local=None):
         ops.knn_block(X_local, sq_local, row0, keys, sqk, int(offs[owner]), k, best_d2, best_idx, int(step > 0),
                       extra_local, ek)
     return best_idx, best_d2
+
+
+# ----------------------------------------------------------------------------------------------- CUDA-graphed steps
+def make_capturable(optimizer):
+    """True if ``optimizer.step()`` may be captured in a CUDA graph.  torch's Adam-family optimisers keep their step
+    counter on the host unless ``capturable`` is set; a captured host-side counter would silently freeze the bias
+    correction, so: groups that already say capturable=True are fine, an optimiser that has not stepped yet is switched
+    (the update rule is unchanged), anything else is refused."""
+    groups = getattr(optimizer, "param_groups", None)
+    if not groups or any("capturable" not in g for g in groups):
+        return False
+    if all(g["capturable"] for g in groups):
+        return True
+    if len(optimizer.state) > 0:
+        return False
+    for g in groups:
+        g["capturable"] = True
+    return True
+
+
+class GraphedStep:
+    """A fixed piece of device work -- typically one epoch body / optimiser step on one subgraph (ensemble2.py:51-88,
+    batches.py:34-61) -- that is run eagerly ``warmup`` times on a side stream, then captured into a CUDA graph and
+    replayed.  The ~100 small launches of a step on a 10^2..10^4-node subgraph are host-bound when issued one by one
+    ("small-graph regime"); a replay costs one launch.
+
+    ``fn`` must do the same device work on every call, must not synchronise with the host, and must leave its results in
+    tensors it returns (they belong to the graph's memory pool and are overwritten by the next replay -- copy what must
+    survive).  Every call performs the work exactly once, whether eager, capturing or replaying.  If capture fails the
+    object falls back to eager execution for good and keeps the reason in ``.error``."""
+
+    _side = {}
+
+    def __init__(self, fn, warmup=2, pool=None, enabled=True):
+        self.fn, self.warmup, self.pool = fn, max(1, int(warmup)), pool
+        self.enabled = bool(enabled)
+        self.calls, self.graph, self.out, self.error = 0, None, None, None
+
+    @classmethod
+    def side_stream(cls):
+        dev = torch.cuda.current_device()
+        s = cls._side.get(dev)
+        if s is None:
+            s = cls._side[dev] = torch.cuda.Stream()
+        return s
+
+    def _eager_on_side_stream(self):
+        cur, side = torch.cuda.current_stream(), self.side_stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            out = self.fn()
+        cur.wait_stream(side)
+        return out
+
+    def __call__(self):
+        self.calls += 1
+        if self.graph is not None:
+            self.graph.replay()
+            return self.out
+        if not self.enabled or self.error is not None:
+            return self.fn()
+        if self.calls <= self.warmup:
+            return self._eager_on_side_stream()         # allocator, autograd and NCCL warm-up outside capture
+        try:
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, pool=self.pool):
+                out = self.fn()
+            self.graph, self.out = graph, out
+        except Exception as exc:                        # noqa: BLE001 -- eager execution is always available
+            self.error = f"{type(exc).__name__}: {str(exc)[:300]}"
+            torch.cuda.synchronize()
+            return self.fn()
+        self.graph.replay()                             # capture records, replay executes: the step happens once
+        return self.out
+
+    @property
+    def captured(self):
+        return self.graph is not None

@@ -19,6 +19,7 @@ import torch
 from torch.nn import Identity
 
 from ..networks.networks import Ensemble
+from ..parallel import GraphedStep, make_capturable
 from .util import get_args_tuple, l1_regularize, pearson, save_csv, to_host
 
 
@@ -26,9 +27,46 @@ def _clone_state(model):
     return {k: v.detach().clone() for k, v in model.state_dict().items()}
 
 
+def _keep_state(model, into):
+    """Copy the current weights into the preallocated ``into`` (no allocation, no host work)."""
+    with torch.no_grad():
+        for k, v in model.state_dict().items():
+            into[k].copy_(v)
+
+
+class _Epoch:
+    """The epoch body of phase 1 (ensemble2.py:51-88) as one fixed piece of device work; its three scalars (train loss,
+    test loss, Pearson r of the test predictions) go to ``stats``."""
+
+    def __init__(self, model, optimizer, batch, loss_func, l1):
+        self.model, self.optimizer, self.loss_func, self.l1 = model, optimizer, loss_func, l1
+        self.args, self.test_args = get_args_tuple(batch), get_args_tuple(batch.test)
+        self.y, self.test_y = batch.y, batch.test.y
+        self.stats = torch.zeros(3, dtype=torch.float64, device=batch.y.device)
+
+    def __call__(self):
+        model = self.model
+        model.train()
+        self.optimizer.zero_grad(set_to_none=False)
+        out = model(*self.args)
+        model.eval()
+        with torch.no_grad():
+            out_test = model(*self.test_args)
+        loss = self.loss_func(out, self.y)
+        if self.l1 is not None:
+            loss = l1_regularize(model, loss, self.l1)
+        loss.backward()
+        self.optimizer.step()
+        with torch.no_grad():
+            self.stats[0] = loss.detach()
+            self.stats[1] = self.loss_func(out_test, self.test_y)
+            self.stats[2] = pearson(out_test, self.test_y)
+        return self.stats
+
+
 def train_ensemble2(model, optimizer, data, test_case="default", epochs=1000, aggregate_epochs=None,
                     max_no_improvement=-1, l1_lambda=0.01, use_l1_reg=False, save_loss=True,
-                    early_stopper=lambda _, __, ___: None, print_epochs=True, **_):
+                    early_stopper=lambda _, __, ___: None, print_epochs=True, cuda_graphs="auto", **_):
     if not torch.cuda.is_available():
         raise RuntimeError("gnn_b200 trainers need a CUDA device (no CPU fallback)")
     device = torch.device("cuda")
@@ -48,27 +86,20 @@ def train_ensemble2(model, optimizer, data, test_case="default", epochs=1000, ag
         no_improvement, least_loss = 0, 100000000
         losses, train_losses, corrs = [], [], []
         best_states.append(_clone_state(model))
-        args_tuple = get_args_tuple(batch)
-        test_tuple = get_args_tuple(batch.test)
+        for p in model.parameters():
+            if p.requires_grad and p.grad is None:
+                p.grad = torch.zeros_like(p)
+        graphs_on = (cuda_graphs is True or (cuda_graphs == "auto" and epochs > 3)) and make_capturable(optimizer)
+        step = GraphedStep(_Epoch(model, optimizer, batch, loss_func, l1_lambda if use_l1_reg else None),
+                           warmup=2, enabled=graphs_on)
         for epoch in range(epochs):
-            model.train()
-            optimizer.zero_grad()
-            out = model(*args_tuple)
-            model.eval()
-            out_test = model(*test_tuple)
-            loss = loss_func(out, batch.y)
-            if use_l1_reg:
-                loss = l1_regularize(model, loss, l1_lambda)
-            loss.backward()
-            optimizer.step()
-            with torch.no_grad():
-                tl, vl, r = to_host(loss, loss_func(out_test, batch.test.y), pearson(out_test, batch.test.y))
+            tl, vl, r = step().cpu().tolist()                  # the epoch's only device -> host copy
             train_losses.append(tl)
             losses.append(vl)
             corrs.append(r)
             if vl < least_loss:                                # ensemble2.py:92-95 saves the post-step weights
                 no_improvement, least_loss = 0, vl
-                best_states[i_batch] = _clone_state(model)
+                _keep_state(model, best_states[i_batch])
             else:
                 no_improvement += 1
             if vl < min_loss_so_far:

@@ -53,7 +53,7 @@ def distance_correlation(a, b, max_n=16384):
     a = a.detach().reshape(-1, 1).double()
     b = b.detach().reshape(-1, 1).double()
     if a.shape[0] > max_n:
-        return torch.tensor(float("nan"), device=a.device, dtype=torch.float64)
+        return torch.full((), float("nan"), device=a.device, dtype=torch.float64)      # no host copy: safe under graph capture
 
     def centred(v):
         d = (v - v.t()).abs()

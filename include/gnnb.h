@@ -167,15 +167,21 @@ int gnnb_spmm_workspace_bytes(int64_t n_hub_tasks, int64_t F, size_t* bytes);
  *   bwd_x : dX [n, p] = dH [n, h] . W [h, p]                      (inner layers only)
  * X is float32 (x_is_i8 = 0), int8 genotype codes (x_is_i8 = 1; [0, 127] for precision 1..3, any int8 for 0 and 4), or
  * 2-BIT PACKED genotype codes as gnnb_pack_2bit writes them (x_is_i8 = 2; ldx = bytes per packed row, a multiple of 16;
- * precision 4 only, n >= 128, p >= 128, h <= 104): the kernels expand the packed tile to int8 on chip, so the matrix is
- * read from HBM at a quarter of the bytes; results are bit-identical to x_is_i8 = 1.
+ * precision 4 only): the kernels expand the packed tile to int8 on chip, so the matrix is read from HBM at a quarter of
+ * the bytes; results are bit-identical to x_is_i8 = 1 wherever both formats use the 24-bit form below.
  * precision: 0 = fp32 CUDA-core tiles (exact reference arithmetic),
  *            1 / 2 / 3 = tcgen05 bf16 tensor-core tiles with the fp32 operand split into that many
  *            bf16 terms (3 ~ fp32-exact for integer-coded X; 1 = plain bf16 projection), fp32 accumulate;
- *            4 = int8 tensor cores (int8 X only, n >= 128, p >= 128, h <= 104; other shapes run as 2): the float
- *            operand is quantised per output feature to 21 bits and split into three int8 digits, the three
- *            exact int32 digit sums are combined as one 64-bit integer and rounded once (rel. error ~1e-6).
+ *            4 = int8 tensor cores (int8 or packed X, 16-byte aligned rows, n >= 128, p >= 128, h <= 104): the float
+ *            operand is quantised per output feature to a 24-bit fixed-point integer (relative to the feature's largest
+ *            magnitude) and split into three int8 digits; the three exact int32 digit sums are combined as one 64-bit
+ *            integer and rounded once (rel. error ~1e-7 per feature).  Contractions long enough to overflow an int32
+ *            digit sum use 21 bits (K * cmax * 128 >= 2^31, cmax = 3 for packed and 128 for int8 X) or are refused
+ *            (K * cmax * 64 >= 2^31).  NaN / Inf in the float operand make every output of that feature NaN.
+ * A precision is never changed behind the caller's back: a shape the requested precision does not take is refused with
+ * GNNB_E_UNSUPPORTED, and gnnb_linear_supported (1 / 0, no device work) says so beforehand.
  */
+int gnnb_linear_supported(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, int64_t h, int precision);
 int gnnb_linear_workspace_bytes(int64_t n, int64_t p, int64_t h, int precision, size_t* bytes);
 int gnnb_linear_fwd(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p,
                     const float* W, int64_t ldw, int64_t h, float* H, int64_t ldh, int precision,
@@ -185,6 +191,16 @@ int gnnb_linear_bwd_w(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_
                       void* workspace, size_t workspace_bytes, void* stream);
 int gnnb_linear_bwd_x(const float* dH, int64_t lddh, int64_t n, int64_t h,
                       const float* W, int64_t ldw, int64_t p, float* dX, int64_t lddx, void* stream);
+/* The precision-4 weight gradient in two halves, for callers that cut the markers into ranges -- one GEMM per range, so
+ * that the gradient all-reduce of one range (no reference counterpart) overlaps the GEMM of the next --
+ * without quantising dH once per range.  gnnb_linear_prepare_dh writes the digits and scales of dH [n, h] into the
+ * workspace (gnnb_linear_workspace_bytes(n, p, h, 4) bytes); gnnb_linear_bwd_w_prepared then computes
+ * dW[:, range] = dH^T . X[:, range] for the `p` markers X points at (a 16-byte aligned column offset into the int8 or
+ * packed matrix, same ldx) from that workspace.  Results equal gnnb_linear_bwd_w bit for bit. */
+int gnnb_linear_prepare_dh(int x_is_i8, int64_t n, const float* dH, int64_t lddh, int64_t h,
+                           void* workspace, size_t workspace_bytes, void* stream);
+int gnnb_linear_bwd_w_prepared(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, int64_t h,
+                               float* dW, int64_t lddw, void* workspace, size_t workspace_bytes, void* stream);
 /* db[f] = sum_i dOut[i, f]  -- the bias gradient of GCNConv; fixed summation order.
  * workspace: gnnb_colsum_workspace_bytes(F) bytes. */
 int gnnb_colsum_workspace_bytes(int64_t F, size_t* bytes);

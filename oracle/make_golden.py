@@ -22,8 +22,9 @@ Fixtures
   partition_small.npz  naive_partition(util.py:15-45) on small random neighbour streams
   wheat_features.npz   create_graph with scaled / include_self / hot (load.py:38-48, :57)
   wheat_ensemble.npz   the seeded-subsample loader (load_ensembles2.py:53-297): rows, labels, edges, feature digests
+  wheat_trainers.npz   trajectories of ``train`` (plain.py) and ``train_batches`` (batches.py), distance correlations
 
-``python -m oracle.make_golden features`` regenerates only the last two.
+``python -m oracle.make_golden features`` regenerates only wheat_features / wheat_ensemble, ``... trainers`` only the last.
 """
 import contextlib
 import io
@@ -193,14 +194,123 @@ def features_and_ensemble(ref, df):
     save("wheat_ensemble.npz", **ens)
 
 
+def trainers_golden(ref, df):
+    """wheat_trainers.npz: trajectories of the reference's ``train`` (plain.py:8-114) and ``train_batches``
+    (batches.py:7-81) through its own loader, and the distance-correlation values ``train`` reports."""
+    X = df.iloc[:, 1:].values
+    y = df["value"].values
+    H, EPOCHS, LR_ = 32, 5, 0.0020594745443455593
+    out = {"hidden": np.int64(H), "epochs": np.int64(EPOCHS), "lr": np.float64(LR_)}
+    cwd = os.getcwd()
+
+    def opt(model):
+        return torch.optim.Adam(model.parameters(), lr=LR_)
+
+    with tempfile.TemporaryDirectory() as tmp:
+        os.chdir(tmp)
+        try:
+            os.makedirs("output")
+            # ---- train: one training graph + test graph (batches=None), weights used (plain.py:38-41)
+            params = dict(num_neighbours=5, smoothing="laplacian", mode="distance", use_validation=False, split=0.8,
+                          use_weights=True, algorithm="euclidean")
+            with contextlib.redirect_stdout(io.StringIO()):
+                ds = ref.load.load_data(WHEAT_CSV, **params)
+            data = ds[0]
+            torch.manual_seed(0)
+            m_ref = ref.networks.create_network_two_no_conv_dropout(X.shape[1], 1, internal_size=H, dropout=0.0)
+            w0 = {k: v.clone().numpy() for k, v in m_ref.state_dict().items()}
+            buf = io.StringIO()
+            with contextlib.redirect_stdout(buf):
+                res = ref.plain.train(m_ref, opt(m_ref), data, epochs=EPOCHS, save_loss=False)["basics"]
+            printed = re.findall(r"Epoch: (\d+), Loss: ([-\d.]+), Test Loss: ([-\d.]+)", buf.getvalue())
+            assert len(printed) == EPOCHS
+            n = len(df)
+            tr_rows, te_rows = np.arange(0, int(n * 0.8)), np.arange(int(n * 0.8), n)      # split_dataset (util.py:76-84)
+            g = restate.create_graph(X[tr_rows], y[tr_rows], 5, "laplacian", True, True, "distance")
+            g_test = restate.create_graph(X[te_rows], y[te_rows], 5, "laplacian", True, True, "distance")
+            assert np.array_equal(data.edge_index.numpy(), g["edge_index"])
+            assert np.array_equal(data.test.edge_index.numpy(), g_test["edge_index"])
+            torch.manual_seed(0)
+            m = restate.make_model("create_network_two_no_conv_dropout", X.shape[1], 1, internal_size=H, dropout=0.0)
+            tl, vl, cors, dcors, out_test = restate.train_plain(m, opt(m), g, g_test, EPOCHS)
+            np.testing.assert_allclose(vl, res["losses"], rtol=1e-5)
+            np.testing.assert_allclose(cors, res["cors"], rtol=1e-6, atol=1e-7)
+            np.testing.assert_allclose(dcors, res["dcors"], rtol=1e-6, atol=1e-7)
+            for ep in range(EPOCHS):
+                assert abs(tl[ep] - float(printed[ep][1])) < 2e-5
+            out.update(plain_train_rows=tr_rows.astype(np.int32), plain_test_rows=te_rows.astype(np.int32),
+                       plain_train_loss=np.asarray(tl), plain_test_loss=np.asarray(res["losses"], dtype=np.float64),
+                       plain_cors=np.asarray(res["cors"], dtype=np.float64), plain_dcors=np.asarray(res["dcors"], dtype=np.float64),
+                       plain_pred_test=out_test.numpy())
+            for kk, v in w0.items():
+                out[f"plain__w0__{kk}"] = v
+
+            # ---- train_batches: three partitioned subgraphs, one step each per epoch, NO edge weights (batches.py:37)
+            params = dict(num_neighbours=5, smoothing="laplacian", mode="distance", use_validation=False, split=0.8,
+                          use_weights=True, algorithm="euclidean", batches=3,
+                          split_algorithm=ref.util.split_dataset_graph,
+                          split_algorithm_params={"partition": ref.util.naive_partition})
+            with contextlib.redirect_stdout(io.StringIO()):
+                ds = ref.load.load_data(WHEAT_CSV, **params)
+            data = [d for d in ds]
+            assert len(data) == 3
+            torch.manual_seed(1)
+            m_ref = ref.networks.create_network_two_no_conv_dropout(X.shape[1], 1, internal_size=H, dropout=0.0)
+            w0 = {k: v.clone().numpy() for k, v in m_ref.state_dict().items()}
+            buf = io.StringIO()
+            with contextlib.redirect_stdout(buf):
+                losses, last_epoch = ref.batches.train_batches(m_ref, opt(m_ref), data, epochs=EPOCHS, save_loss=False)
+            printed = re.findall(r"Epoch: (\d+):(\d+), Loss: ([-\d.]+), Test Loss: ([-\d.]+)", buf.getvalue())
+            assert len(printed) == 3 * EPOCHS and last_epoch == EPOCHS - 1
+            sizes = restate.split_sizes(n, 0.8, False, 0.1)
+            _, te, _ = restate.split_indices_graph(df, sizes, neighbours=5)
+            part = restate.split_indices_graph(df, 3, neighbours=5)
+            g_test = restate.create_graph(X[te], y[te], 5, "laplacian", True, True, "distance")
+            graphs = []
+            for b, rows in enumerate(part):
+                gb = restate.create_graph(X[rows], y[rows], 5, "laplacian", True, True, "distance")
+                assert np.array_equal(data[b].edge_index.numpy(), gb["edge_index"])
+                gb["test"] = g_test
+                graphs.append(gb)
+                out[f"batches_rows_{b}"] = np.asarray(rows, dtype=np.int32)
+            assert np.array_equal(data[0].test.edge_index.numpy(), g_test["edge_index"])
+            torch.manual_seed(1)
+            m = restate.make_model("create_network_two_no_conv_dropout", X.shape[1], 1, internal_size=H, dropout=0.0)
+            r_losses, r_train, steps, out_test = restate.train_batches(m, opt(m), graphs, EPOCHS)
+            np.testing.assert_allclose(r_losses, losses, rtol=1e-5)
+            for i, (a, c) in enumerate(steps):
+                assert abs(a - float(printed[i][2])) < 2e-5 and abs(c - float(printed[i][3])) < 2e-5, (i, a, c, printed[i])
+            out.update(batches_test_rows=np.asarray(te, dtype=np.int32), batches_losses=np.asarray(losses, dtype=np.float64),
+                       batches_train_losses=np.asarray(r_train), batches_steps=np.asarray(steps),
+                       batches_pred_test=out_test.numpy())
+            for kk, v in w0.items():
+                out[f"batches__w0__{kk}"] = v
+        finally:
+            os.chdir(cwd)
+    # distance correlation on its own: a few vectors with known structure
+    rng = np.random.default_rng(3)
+    a = rng.standard_normal(200)
+    cases = {"linear": (a, 2.0 * a + 1.0), "noise": (a, rng.standard_normal(200)), "square": (a, a * a),
+             "const": (a, np.ones(200))}
+    for name, (u, v) in cases.items():
+        out[f"dcor_{name}_a"], out[f"dcor_{name}_b"] = u, v
+        out[f"dcor_{name}"] = np.float64(restate.distance_correlation(u, v))
+    assert abs(out["dcor_linear"] - 1.0) < 1e-12 and out["dcor_const"] == 0.0
+    save("wheat_trainers.npz", **out)
+
+
 def main(argv=None):
     argv = sys.argv[1:] if argv is None else argv
     os.makedirs(GOLDEN, exist_ok=True)
     ref = ref_import.load(canonical_knn=True)
     df = wheat_frame()
+    if argv and argv[0] == "trainers":
+        trainers_golden(ref, df)
+        return 0
     features_and_ensemble(ref, df)
     if argv and argv[0] == "features":
         return 0
+    trainers_golden(ref, df)
     N = len(df)
     X = df.iloc[:, 1:].values
     y = df["value"].values

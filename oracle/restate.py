@@ -453,3 +453,66 @@ def pearson(a, b):
     b = b - b.mean()
     den = math.sqrt(float(a @ a) * float(b @ b))
     return float(a @ b) / den if den > 0 else float("nan")
+
+
+def distance_correlation(a, b):
+    """``dcor.distance_correlation(x, y)`` as gnn/trainers/plain.py:76-79 calls it (two 1-D float arrays of equal length).
+    The package (dcor, un-pinned in requirements.txt; absent from the image) computes the BIASED sample statistic of
+    Szekely, Rizzo and Bakirov (2007): pairwise distances a_ij = |x_i - x_j|, double centring
+    A_ij = a_ij - mean_i - mean_j + mean, dCov^2 = mean(A * B), dCor = sqrt(dCov^2 / sqrt(dVar_x^2 dVar_y^2)), and 0 when
+    either variance vanishes.  Restated from the published definition; the reference has no fixture for it."""
+    a = np.asarray(a, dtype=np.float64).reshape(-1)
+    b = np.asarray(b, dtype=np.float64).reshape(-1)
+
+    def centred(v):
+        d = np.abs(v[:, None] - v[None, :])
+        return d - d.mean(axis=0, keepdims=True) - d.mean(axis=1, keepdims=True) + d.mean()
+
+    A, B = centred(a), centred(b)
+    dcov2 = max(float((A * B).mean()), 0.0)
+    dvar = math.sqrt(float((A * A).mean()) * float((B * B).mean()))
+    return math.sqrt(dcov2 / dvar) if dvar > 0 else 0.0
+
+
+def train_plain(model, optimizer, graph, test, epochs):
+    """The loop of gnn/trainers/plain.py:35-100 (no ``range`` attribute, non-empty test graph): per epoch a train-mode
+    forward WITH edge weights, an eval-mode forward on the test graph, Pearson r (:71-74) and distance correlation
+    (:76-79) of the test predictions, MSE, backward, step.  Returns (train_losses, test_losses, cors, dcors, last test
+    predictions)."""
+    tl, vl, cors, dcors, out_test = [], [], [], [], None
+    yt = np.asarray(test["y"], dtype=np.float32).reshape(-1)
+    for _ in range(epochs):
+        a, c, out_test = epoch_step(model, optimizer, graph, test)
+        tl.append(a)
+        vl.append(c)
+        pred = out_test.numpy().reshape(-1)
+        cors.append(float(np.corrcoef(pred, yt)[0][1]))
+        dcors.append(distance_correlation(pred, yt))
+    return tl, vl, cors, dcors, out_test
+
+
+def train_batches(model, optimizer, graphs, epochs):
+    """The loop of gnn/trainers/batches.py:31-68: one optimiser step per subgraph, the model called WITHOUT edge
+    weights (:37, :44), per-epoch averages of the train and the test loss.  ``graphs`` = list of dicts with ``test``
+    nested.  Returns (test-loss averages, train-loss averages, per-step (train, test) pairs, last test predictions)."""
+    loss_func = torch.nn.MSELoss()
+    losses, train_losses, steps, out_test = [], [], [], None
+    for _ in range(epochs):
+        losses.append(0)
+        train_losses.append(0)
+        for g in graphs:
+            x, ei, _ = as_tensors(g)
+            xt, eit, _ = as_tensors(g["test"])
+            model.train()
+            optimizer.zero_grad()
+            out = model(x, ei)
+            model.eval()
+            out_test = model(xt, eit)
+            loss = loss_func(out, torch.as_tensor(g["y"], dtype=torch.float32))
+            loss.backward()
+            optimizer.step()
+            test_loss = float(loss_func(out_test, torch.as_tensor(g["test"]["y"], dtype=torch.float32)))
+            losses[-1] += test_loss / len(graphs)
+            train_losses[-1] += float(loss) / len(graphs)
+            steps.append((float(loss), test_loss))
+    return losses, train_losses, steps, out_test.detach()

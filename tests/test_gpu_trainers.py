@@ -95,3 +95,93 @@ def test_train_and_train_batches_run_and_learn(wheat_csv):
     opt = torch.optim.Adam(model.parameters(), lr=0.003)
     losses, epoch = train_batches(model, opt, [d for d in ds], epochs=5, save_loss=False, print_steps=False)
     assert epoch == 4 and len(losses) == 5 and all(np.isfinite(losses))
+
+
+def _golden_model(g, prefix, hidden):
+    model = nets.create_network_two_no_conv_dropout(1279, 1, internal_size=hidden, dropout=0.0)
+    model.load_state_dict({k.split("__w0__")[1]: torch.from_numpy(g[k]) for k in g.files if k.startswith(prefix + "__w0__")})
+    return model
+
+
+@pytest.mark.parametrize("graphs", [False, True])
+def test_train_against_the_reference_trajectory(wheat_csv, golden, graphs, capsys):
+    """gnn/trainers/plain.py:8-114 run by the reference on WHEAT (golden): per-epoch train / test losses, Pearson r and
+    distance correlation of the test predictions, eager and CUDA-graph replayed."""
+    from oracle import restate
+    g = golden("wheat_trainers.npz")
+    E, H, lr = int(g["epochs"]), int(g["hidden"]), float(g["lr"])
+    ds = load_data(wheat_csv, num_neighbours=5, smoothing="laplacian", mode="distance", use_validation=False, split=0.8,
+                   use_weights=True, algorithm="euclidean")
+    data = ds[0]
+    model = _golden_model(g, "plain", H)
+    res = train(model, torch.optim.Adam(model.parameters(), lr=lr), data, epochs=E, save_loss=False, cuda_graphs=graphs)["basics"]
+    np.testing.assert_allclose(res["losses"], g["plain_test_loss"], rtol=1e-4)
+    np.testing.assert_allclose(res["cors"], g["plain_cors"], atol=1e-4)
+    np.testing.assert_allclose(res["dcors"], g["plain_dcors"], atol=1e-4)
+    printed = [float(line.split("Loss: ")[1].split(",")[0]) for line in capsys.readouterr().out.splitlines() if line.startswith("Epoch:")]
+    np.testing.assert_allclose(printed, g["plain_train_loss"], rtol=1e-4, atol=1e-5)
+    model.eval()
+    from gnn_b200.trainers.util import get_args_tuple
+    pred = model(get_args_tuple(data.test)).detach().cpu().numpy()
+    # the golden predictions are those of the last epoch's PRE-step weights; one more step moves them very little
+    assert restate.pearson(pred, g["plain_pred_test"]) >= 0.999
+    assert res["epoch"] == E and res["model"] is model
+
+
+@pytest.mark.parametrize("graphs", [False, True])
+def test_train_batches_against_the_reference_trajectory(wheat_csv, golden, graphs, capsys):
+    """gnn/trainers/batches.py:7-81 run by the reference on three partitioned WHEAT subgraphs (golden): every step's train
+    and test loss (the model is called without edge weights, batches.py:37) and the per-epoch averages."""
+    g = golden("wheat_trainers.npz")
+    E, H, lr = int(g["epochs"]), int(g["hidden"]), float(g["lr"])
+    ds = load_data(wheat_csv, num_neighbours=5, smoothing="laplacian", mode="distance", use_validation=False, split=0.8,
+                   use_weights=True, algorithm="euclidean", batches=3, split_algorithm=split_dataset_graph,
+                   split_algorithm_params={"partition": naive_partition})
+    data = [d for d in ds]
+    assert len(data) == 3
+    model = _golden_model(g, "batches", H)
+    losses, epoch = train_batches(model, torch.optim.Adam(model.parameters(), lr=lr), data, epochs=E, save_loss=False,
+                                  cuda_graphs=graphs)
+    assert epoch == E - 1
+    np.testing.assert_allclose(losses, g["batches_losses"], rtol=1e-4)
+    rows = [line for line in capsys.readouterr().out.splitlines() if line.startswith("Epoch:")]
+    got = np.array([[float(r.split("Loss: ")[1].split(",")[0]), float(r.split("Test Loss: ")[1])] for r in rows])
+    np.testing.assert_allclose(got, g["batches_steps"], rtol=1e-4, atol=2e-5)
+    # early stopping: the rule of batches.py:69-76 on the same trajectory
+    model = _golden_model(g, "batches", H)
+    ref_losses = list(g["batches_losses"])
+    stale, best, stop = 0, 1e8, E - 1
+    for i, v in enumerate(ref_losses):
+        stale, best = (0, v) if v < best else (stale + 1, best)
+        if stale >= 1:
+            stop = i
+            break
+    _, epoch = train_batches(model, torch.optim.Adam(model.parameters(), lr=lr), data, epochs=E, save_loss=False,
+                             max_no_improvement=1, print_steps=False, cuda_graphs=graphs)
+    assert epoch == stop
+
+
+def test_distance_correlation_on_the_device(golden):
+    """trainers.util.distance_correlation (plain.py:76-79) against the oracle's restatement of dcor's V-statistic."""
+    from gnn_b200.trainers.util import distance_correlation
+    g = golden("wheat_trainers.npz")
+    for name in ("linear", "noise", "square", "const"):
+        a = torch.from_numpy(g[f"dcor_{name}_a"]).cuda()
+        b = torch.from_numpy(g[f"dcor_{name}_b"]).cuda()
+        assert abs(float(distance_correlation(a, b)) - float(g[f"dcor_{name}"])) < 1e-9, name
+
+
+def test_graphed_step_runs_each_call_once():
+    """parallel.GraphedStep: eager warm-up, capture + replay, and every call does the work exactly once."""
+    from gnn_b200.parallel import GraphedStep
+    acc = torch.zeros(3, device="cuda")
+
+    def body():
+        acc.add_(1.0)
+        return acc * 2.0
+
+    step = GraphedStep(body, warmup=2)
+    outs = [float(step()[0]) for _ in range(6)]
+    assert outs == [2.0, 4.0, 6.0, 8.0, 10.0, 12.0] and step.captured and step.error is None
+    off = GraphedStep(body, enabled=False)
+    assert float(off()[0]) == 14.0 and not off.captured

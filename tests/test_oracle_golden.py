@@ -226,3 +226,16 @@ def test_ensemble_loader_golden(wheat, golden, name, kw):
             assert np.array_equal(d["edge_index"], g[key + "_ei"]), key
             assert np.array_equal(d["edge_weight"], g[key + "_ew"]), key
             assert np.array_equal(d["y"], g[key + "_y"]) and digest(d["x"]) == g[key + "_xdigest"], key
+
+
+def test_distance_correlation_restatement(golden):
+    """restate.distance_correlation (dcor's biased V-statistic, plain.py:76-79): frozen values and the defining properties."""
+    from oracle import restate
+    g = golden("wheat_trainers.npz")
+    for name in ("linear", "noise", "square", "const"):
+        assert restate.distance_correlation(g[f"dcor_{name}_a"], g[f"dcor_{name}_b"]) == pytest.approx(float(g[f"dcor_{name}"]), abs=1e-12)
+    a = g["dcor_noise_a"]
+    assert restate.distance_correlation(a, -3.0 * a + 2.0) == pytest.approx(1.0, abs=1e-12)       # invariant under affine maps
+    assert 0.0 < float(g["dcor_noise"]) < 0.3 < float(g["dcor_square"]) < 1.0
+    assert restate.distance_correlation(a, g["dcor_noise_b"]) == pytest.approx(restate.distance_correlation(g["dcor_noise_b"], a), abs=1e-15)
+    assert np.all(np.isfinite(g["plain_dcors"])) and np.all((g["plain_dcors"] >= 0) & (g["plain_dcors"] <= 1))
