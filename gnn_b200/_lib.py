@@ -48,6 +48,7 @@ PROTOTYPES = {
     "gnnb_linear_bwd_w": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _i64, _i32, _vp, _sz, _vp]),
     "gnnb_linear_bwd_x": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _i64, _vp]),
     "gnnb_linear_supported": (_i32, [_vp, _i32, _i64, _i64, _i64, _i64, _i32]),
+    "gnnb_linear_bwd_w_wave_markers": (_i64, [_i32]),
     "gnnb_linear_prepare_dh": (_i32, [_i32, _i64, _vp, _i64, _i64, _vp, _sz, _vp]),
     "gnnb_linear_bwd_w_prepared": (_i32, [_vp, _i32, _i64, _i64, _i64, _i64, _vp, _i64, _vp, _sz, _vp]),
     "gnnb_colsum_workspace_bytes": (_i32, [_i64, _psz]),

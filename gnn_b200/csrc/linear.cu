@@ -283,6 +283,7 @@ int linear_i8_fwd(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p
                   float* H, int64_t ldh, void* ws, size_t ws_bytes, cudaStream_t stream);
 int linear_i8_bwd_w(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p, const float* dH, int64_t lddh, int64_t h,
                     float* dW, int64_t lddw, void* ws, size_t ws_bytes, cudaStream_t stream);
+int64_t linear_i8_bwd_w_wave_markers(int x_format);
 int linear_i8_prepare_dh(int x_format, int64_t n, const float* dH, int64_t lddh, int64_t h, void* ws, size_t ws_bytes, cudaStream_t stream);
 int linear_i8_bwd_w_prepared(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p, int64_t h, float* dW, int64_t lddw,
                              void* ws, size_t ws_bytes, cudaStream_t stream);
@@ -430,6 +431,11 @@ int gnnb_linear_bwd_w_prepared(const void* X, int x_is_i8, int64_t ldx, int64_t 
                  "linear_bwd_w_prepared: bad argument");
     if (!linear_i8_supported(X, x_is_i8, ldx, n, p < 128 ? 128 : p, h)) return refuse_i8("linear_bwd_w_prepared", x_is_i8, n, p, h);
     return linear_i8_bwd_w_prepared(X, x_is_i8, ldx, n, p, h, dW, lddw, workspace, workspace_bytes, (cudaStream_t)stream_);
+}
+
+int64_t gnnb_linear_bwd_w_wave_markers(int x_is_i8) {
+    if (require_sm100() != GNNB_OK || (x_is_i8 != 1 && x_is_i8 != 2)) return 0;
+    return linear_i8_bwd_w_wave_markers(x_is_i8);
 }
 
 int gnnb_linear_bwd_x(const float* dH, int64_t lddh, int64_t n, int64_t h,

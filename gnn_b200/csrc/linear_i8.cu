@@ -86,12 +86,17 @@ static_assert(SMEM <= 232448, "shared memory of linear_i8_kernel");
 
 // ---- quantisation -----------------------------------------------------------------------------------------------------
 // SHIFT = 8: base-256 digits in [-128, 127] (24-bit form); SHIFT = 7: base-128 digits in [-64, 64] (21-bit form)
-constexpr float QMAX24 = 8355711.0f;                     // 127 * 65536 + 127 * 256 + 127: the top digit stays <= 127 after carries
+// Largest |q| whose three balanced base-256 digits fit int8 is 127 * 65536 + 127 * 256 + 127 = 8 355 711.  w * (QMAX / amax)
+// is rounded twice in float32 and can land one unit above QMAX for the feature's largest element, so QMAX keeps a margin
+// below that bound and q is clamped to the bound: without either, the top digit of the maximum wrapped from 128 to -128.
+constexpr int   QLIM24 = 8355711;
+constexpr float QMAX24 = 8355000.0f;
 constexpr float QMAX21 = 1048576.0f;
 template <int SHIFT>
 __device__ __forceinline__ void digits3(float w, float inv_scale, int8_t& d0, int8_t& d1, int8_t& d2) {
     constexpr int B = 1 << SHIFT, HALF = B >> 1;
-    int q = __float2int_rn(w * inv_scale);               // |q| <= QMAX
+    int q = __float2int_rn(w * inv_scale);               // |q| <= QMAX up to float rounding
+    if (SHIFT == 8) q = max(-QLIM24, min(QLIM24, q));
     int t0 = ((q + HALF) & (B - 1)) - HALF;              // balanced digit
     int q1 = (q - t0) >> SHIFT;
     int t1 = ((q1 + HALF) & (B - 1)) - HALF;
@@ -607,6 +612,34 @@ static int digit_shift(int x_format, int64_t k_len) {
 bool linear_i8_supported(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p, int64_t h) {
     return (x_format == 1 || x_format == 2) && (uintptr_t)X % 16 == 0 && ldx % 16 == 0 && h >= 1 && h <= HP && n >= 128 && p >= 128 &&
            digit_shift(x_format, p) != 0 && digit_shift(x_format, n) != 0;
+}
+
+// Markers one full wave of the weight-gradient kernel covers on the current device: co-resident clusters x the markers a
+// cluster owns (4 or 2 M tiles of 128).  Cutting the markers at multiples of this costs no tensor-core time.
+int64_t linear_i8_bwd_w_wave_markers(int x_format) {
+    const int quad = (int)box_div() == 2 ? 1 : 0;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(quad ? 4 * 64 : 2 * 128);
+    cfg.blockDim = dim3(x_format == 2 ? P2_THREADS : 256);
+    cfg.dynamicSmemBytes = x_format == 2 ? SMEM2 : SMEM;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = quad ? 4 : 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int clusters = 0;
+    cudaError_t e;
+    if (x_format == 2) {
+        if (cudaFuncSetAttribute(linear_p2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM2) != cudaSuccess) return 0;
+        e = cudaOccupancyMaxActiveClusters(&clusters, linear_p2_kernel<true>, &cfg);
+    } else {
+        if (cudaFuncSetAttribute(linear_i8_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM) != cudaSuccess) return 0;
+        e = cudaOccupancyMaxActiveClusters(&clusters, linear_i8_kernel<true>, &cfg);
+    }
+    if (e != cudaSuccess || clusters <= 0) { cudaGetLastError(); return 0; }
+    return (int64_t)clusters * (quad ? 4 : 2) * BM;
 }
 
 size_t linear_i8_workspace(int64_t n, int64_t p, int64_t h) {

@@ -197,6 +197,9 @@ int gnnb_linear_bwd_x(const float* dH, int64_t lddh, int64_t n, int64_t h,
  * workspace (gnnb_linear_workspace_bytes(n, p, h, 4) bytes); gnnb_linear_bwd_w_prepared then computes
  * dW[:, range] = dH^T . X[:, range] for the `p` markers X points at (a 16-byte aligned column offset into the int8 or
  * packed matrix, same ldx) from that workspace.  Results equal gnnb_linear_bwd_w bit for bit. */
+/* Markers covered by one full wave of the precision-4 weight-gradient kernel on the current device (0 if unknown): ranges
+ * cut at multiples of it keep every SM busy.  Host-side query, no launch. */
+int64_t gnnb_linear_bwd_w_wave_markers(int x_is_i8);
 int gnnb_linear_prepare_dh(int x_is_i8, int64_t n, const float* dH, int64_t lddh, int64_t h,
                            void* workspace, size_t workspace_bytes, void* stream);
 int gnnb_linear_bwd_w_prepared(const void* X, int x_is_i8, int64_t ldx, int64_t n, int64_t p, int64_t h,
