@@ -19,10 +19,11 @@ from .. import ops
 
 class _GCNConvFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, graph):
+    def forward(ctx, x, weight, bias, graph, layer):
         h = ops.linear_fwd(x, weight)
         out = ops.spmm(graph.rowptr, graph.col, graph.val, h, bias, n=graph.n, hub=graph.hub)
         ctx.graph = graph
+        ctx.layer = layer
         ctx.has_bias = bias is not None
         ctx.x_needs_grad = x.is_floating_point() and x.requires_grad
         ctx.save_for_backward(x, weight)
@@ -33,11 +34,22 @@ class _GCNConvFn(torch.autograd.Function):
         x, weight = ctx.saved_tensors
         g = ctx.graph
         d_out = d_out.contiguous()
-        d_bias = ops.colsum(d_out) if ctx.has_bias else None
+        sink = getattr(ctx.layer, "grad_sink", None)
+        sunk = sink is not None and ctx.has_bias and weight.grad is not None and ctx.layer.bias.grad is not None
         d_h = ops.spmm(g.rowptr_t, g.col_t, g.val_t, d_out, None, n=g.n, hub=g.hub_t)     # transposed CSR
+        if sunk and not x.is_floating_point():
+            # data-parallel training (parallel.FlatGrads): dW and db go straight into the flat gradient buffer and their
+            # all-reduces start here; autograd gets None for both and has nothing to accumulate
+            sink.write(ctx.layer, x, d_h, d_out)
+            return None, None, None, None, None
+        d_bias = ops.colsum(d_out) if ctx.has_bias else None
         d_w = ops.linear_bwd_w(x, d_h, p=weight.shape[1])
         d_x = ops.linear_bwd_x(d_h, weight) if ctx.x_needs_grad else None
-        return d_x, d_w, d_bias, None
+        if sunk:        # float features: same contract (the sink's slices are overwritten, not accumulated into), plain kernels
+            weight.grad.copy_(d_w)
+            ctx.layer.bias.grad.copy_(d_bias)
+            return d_x, None, None, None, None
+        return d_x, d_w, d_bias, None, None
 
 
 class _Lin(torch.nn.Module):
@@ -66,6 +78,7 @@ class GCNConv(torch.nn.Module):
             raise NotImplementedError("only the improved=False, normalize=True GCNConv of the reference is implemented")
         self.in_channels, self.out_channels = in_channels, out_channels
         self.add_self_loops = add_self_loops
+        self.grad_sink = None           # set by parallel.FlatGrads: takes dW / db of this layer directly (see _GCNConvFn.backward)
         self.lin = _Lin(in_channels, out_channels)
         if bias:
             self.bias = torch.nn.Parameter(torch.zeros(out_channels))
@@ -82,7 +95,7 @@ class GCNConv(torch.nn.Module):
         if not x.is_cuda:
             raise RuntimeError("gnn_b200.GCNConv runs on CUDA tensors only (no CPU fallback)")
         graph = ops.gcn_graph(edge_index, edge_weight, x.shape[0], self.add_self_loops)
-        return _GCNConvFn.apply(x, self.lin.weight, self.bias, graph)
+        return _GCNConvFn.apply(x, self.lin.weight, self.bias, graph, self)
 
     def __repr__(self):
         return f"GCNConv({self.in_channels}, {self.out_channels})"

@@ -542,46 +542,72 @@ def _grad_out(out, h, p, device):
     return out
 
 
-def marker_ranges(p, n_ranges, fmt):
-    """Cut the markers into ``n_ranges`` ranges whose starts are 16-byte aligned in the genotype matrix (a multiple of 64
-    codes when packed, 16 when int8) and a multiple of 128 markers (one M tile of the weight-gradient kernel)."""
-    step = (p + n_ranges - 1) // n_ranges
-    step = (step + 127) // 128 * 128
+def marker_ranges(p, n_ranges=None, fmt=1, wave=0):
+    """Cut the markers into ranges whose starts are 16-byte aligned in the genotype matrix (a multiple of 64 codes when
+    packed, 16 when int8) and a multiple of 512 markers (the M tiles of one cluster of the weight-gradient kernel).
+    With ``wave`` (markers per full wave of clusters, ``bwd_w_wave_markers``) and no ``n_ranges`` every range but the
+    last is exactly one wave: cutting there costs no tensor-core time, cutting finer idles SMs at the end of each range."""
+    if n_ranges is None:
+        step = wave if wave > 0 else p
+    else:
+        step = (p + n_ranges - 1) // n_ranges
+    step = max(512, (step + 511) // 512 * 512)
     return [(c0, min(p, c0 + step)) for c0 in range(0, p, step)]
 
 
 def linear_bwd_w_ranges(X, dH, ranges, p=None, out=None, after_range=None):
     """dW = dH^T . X computed one marker range at a time from ONE quantisation of dH (gnnb_linear_prepare_dh +
     gnnb_linear_bwd_w_prepared); ``after_range(c0, c1)`` is called after the kernels of each range have been enqueued --
-    the data-parallel step starts that range's all-reduce there, so it overlaps the next range's GEMM.  Same bits as
-    ``linear_bwd_w``.  Needs the int8-digit path (int8 or packed X); other inputs fall back to one ``linear_bwd_w``."""
+    the data-parallel step starts that range's all-reduce there, so it overlaps the next range's GEMM.
+    ``out``: None, one float32 [h, p] tensor (the ranges are its column blocks), or a list with one contiguous
+    [h, c1 - c0] tensor per range.  Same bits as ``linear_bwd_w``.  Needs the int8-digit path (int8 or packed X); other
+    inputs fall back to one ``linear_bwd_w`` over all markers."""
     _need_cuda(X, dH)
     dH = dH.contiguous()
     h = dH.shape[1]
     X, fmt, p = _x_operand(X, p)
     n = X.shape[0]
+    per_range = isinstance(out, (list, tuple))
     if (fmt == 0 or config["linear_precision"] not in ("auto", 4, "4")
             or not _lib.lib().gnnb_linear_supported(_p(X), fmt, X.stride(0), n, p, h, 4)):
-        dW = linear_bwd_w(X, dH, p=p, out=out)
-        if after_range is not None:
-            after_range(0, p)
-        return dW
-    dW = _grad_out(out, h, p, X.device)
+        dW = linear_bwd_w(X, dH, p=p, out=None if per_range else out)
+        for i, (c0, c1) in enumerate(ranges):
+            if per_range:
+                out[i].copy_(dW[:, c0:c1])
+            if after_range is not None:
+                after_range(c0, c1)
+        return out if per_range else dW
+    dW = None if per_range else _grad_out(out, h, p, X.device)
     per_code = 4 if fmt == 2 else 1
     with torch.cuda.device(X.device):
         ws = _ws(_ws_bytes("gnnb_linear_workspace_bytes", n, p, h, 4), X.device)
         _call("gnnb_linear_prepare_dh", fmt, n, _p(dH), dH.stride(0), h, _p(ws), ws.numel(), _stream())
-        for c0, c1 in ranges:
+        for i, (c0, c1) in enumerate(ranges):
             if c0 % (16 * per_code) != 0:
                 raise _lib.GnnbError("linear_bwd_w_ranges: range starts must be 16-byte aligned in the genotype matrix")
             xs = ctypes.c_void_p(X.data_ptr() + c0 // per_code)
-            ds = ctypes.c_void_p(dW.data_ptr() + 4 * c0)
+            if per_range:
+                dst = _grad_out(out[i], h, c1 - c0, X.device)
+                ds, ldd = _p(dst), dst.stride(0)
+            else:
+                ds, ldd = ctypes.c_void_p(dW.data_ptr() + 4 * c0), dW.stride(0)
             _declare(flops=2.0 * n * (c1 - c0) * h, bytes=float(n * (c1 - c0) // per_code + h * (c1 - c0) * 4))
-            _call("gnnb_linear_bwd_w_prepared", xs, fmt, X.stride(0), n, c1 - c0, h, ds, dW.stride(0),
-                  _p(ws), ws.numel(), _stream())
+            _call("gnnb_linear_bwd_w_prepared", xs, fmt, X.stride(0), n, c1 - c0, h, ds, ldd, _p(ws), ws.numel(), _stream())
             if after_range is not None:
                 after_range(c0, c1)
-    return dW
+    return out if per_range else dW
+
+
+_wave_cache = {}
+
+
+def bwd_w_wave_markers(fmt, device):
+    """Markers one full wave of the weight-gradient kernel's clusters covers on ``device`` (0 if unknown)."""
+    key = (fmt, device.index)
+    if key not in _wave_cache:
+        with torch.cuda.device(device):
+            _wave_cache[key] = int(_lib.lib().gnnb_linear_bwd_w_wave_markers(fmt))
+    return _wave_cache[key]
 
 
 def linear_bwd_x(dH, W):
@@ -598,11 +624,14 @@ def linear_bwd_x(dH, W):
     return dX
 
 
-def colsum(A):
+def colsum(A, out=None):
     _need_cuda(A)
     A = A.contiguous()
     n, F = A.shape
-    out = torch.empty(F, dtype=torch.float32, device=A.device)
+    if out is None:
+        out = torch.empty(F, dtype=torch.float32, device=A.device)
+    elif out.shape != (F,) or out.dtype != torch.float32 or not out.is_contiguous():
+        raise _lib.GnnbError("colsum: `out` must be a contiguous float32 [F] tensor")
     with torch.cuda.device(A.device):
         ws = _ws(_ws_bytes("gnnb_colsum_workspace_bytes", F), A.device)
         _call("gnnb_colsum", _p(A), A.stride(0), n, F, _p(out), _p(ws), ws.numel(), _stream())

@@ -45,10 +45,22 @@ def row_shard(n_rows, rank, world, align=128):
 
 
 class FlatGrads:
-    """All gradients of a model as views into one contiguous fp32 buffer -> a single all-reduce per step."""
+    """All gradients of a model as views into one contiguous fp32 buffer.
 
-    def __init__(self, params):
-        self.params = [p for p in params if p.requires_grad]
+    The marker projection of the first GCN layer owns almost all of it (h x p floats, 20 MB at C5).  Given that layer
+    (``sink_layer``: a GCNConv fed with integer genotypes), its weight and bias come FIRST in the buffer and the layer gets
+    a *gradient sink*: its backward writes dW and db straight into their slices -- no zero-fill of and no accumulate pass
+    over 20 MB per step -- and, on several GPUs, starts the all-reduce of every finished marker range while the GEMM of
+    the next range runs (``ops.linear_bwd_w_ranges``).  Everything else is the small tail.  Without a sink layer the
+    buffer is zeroed and reduced in one piece."""
+
+    def __init__(self, params, sink_layer=None, world=1, group=None):
+        params = [p for p in params if p.requires_grad]
+        head = []
+        if sink_layer is not None and getattr(sink_layer, "bias", None) is not None:
+            head = [sink_layer.lin.weight, sink_layer.bias]
+            params = head + [p for p in params if all(p is not q for q in head)]
+        self.params = params
         total = sum(p.numel() for p in self.params)
         dev = self.params[0].device
         self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
@@ -56,14 +68,91 @@ class FlatGrads:
         for p in self.params:
             p.grad = self.flat[off:off + p.numel()].view_as(p)
             off += p.numel()
+        self.world, self.group, self.pending, self._stage = int(world), group, [], {}
+        self.has_sink = bool(head)
+        self.range_markers = None           # markers per all-reduce range; None = one full wave of the weight-gradient kernel
+        if head:
+            self.w_numel = head[0].numel()
+            self.tail = self.flat[self.w_numel + head[1].numel():]      # what autograd still accumulates into
+            sink_layer.grad_sink = self
 
+    # ---- called by the sink layer's backward (networks/gcn_conv.py) -------------------------------------------------
+    def write(self, layer, x, d_h, d_out):
+        """dW = d_h^T x and db = colsum(d_out) of the sink layer, written in place; all-reduces started range by range."""
+        from . import ops
+        w, b = layer.lin.weight, layer.bias
+        ops.colsum(d_out, out=b.grad)
+        many = self.world > 1
+        if many:                 # db and the tail are final here: every other layer's backward ran before this one
+            self._start(self.flat[self.w_numel:])
+        h, p = w.shape
+        fmt = 2 if x.dtype == torch.uint8 else 1
+        wave = self.range_markers or ops.bwd_w_wave_markers(fmt, x.device)
+        ranges = ops.marker_ranges(p, None, fmt, wave=wave) if many else [(0, p)]
+        if many and len(ranges) > 1:
+            # a marker range is a column block of dW [h, p] -- not contiguous, and a collective wants one piece of memory:
+            # the GEMM of a range writes into its own contiguous staging block, the all-reduce runs on that block while
+            # the next range is computed, and finish() copies the averaged block into the gradient (one pass over dW)
+            outs = [self._staging(h, r) for r in ranges]
+
+            def after(c0, c1):
+                self._start(self._stage[(h, c0, c1)], back=(w.grad, c0, c1))
+            ops.linear_bwd_w_ranges(x, d_h, ranges, p=p, out=outs, after_range=after)
+        else:
+            ops.linear_bwd_w_ranges(x, d_h, ranges, p=p, out=w.grad)
+            if many:
+                self._start(self.flat[:self.w_numel])
+
+    def _staging(self, h, r):
+        key = (h, r[0], r[1])
+        buf = self._stage.get(key)
+        if buf is None:
+            buf = self._stage[key] = torch.empty((h, r[1] - r[0]), dtype=torch.float32, device=self.flat.device)
+        return buf
+
+    def _start(self, buf, back=None):
+        avg = dist.get_backend(self.group) == "nccl"             # gloo has no AVG: sum, then divide in finish()
+        work = dist.all_reduce(buf, op=dist.ReduceOp.AVG if avg else dist.ReduceOp.SUM, group=self.group, async_op=True)
+        self.pending.append((work, buf, back, avg))
+
+    def finish(self):
+        """Wait for every all-reduce started by ``write`` and copy staged ranges into the gradient."""
+        for work, buf, back, avg in self.pending:
+            work.wait()
+            if not avg:
+                buf.div_(self.world)
+            if back is not None:
+                grad, c0, c1 = back
+                grad[:, c0:c1].copy_(buf)
+        self.pending = []
+
+    # ---- per step ----------------------------------------------------------------------------------------------------
     def zero(self):
-        self.flat.zero_()
+        if self.has_sink:
+            self.tail.zero_()                    # the sink layer's slices are overwritten, never accumulated into
+        else:
+            self.flat.zero_()
 
     def allreduce_mean(self, world, group=None):
-        if world > 1:
+        if world <= 1:
+            return
+        if self.pending:                         # the sink started everything during the backward pass
+            self.finish()
+            return
+        if dist.get_backend(group) == "nccl":
+            dist.all_reduce(self.flat, op=dist.ReduceOp.AVG, group=group)
+        else:
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
             self.flat.div_(world)
+
+
+def first_genotype_layer(model):
+    """The GCNConv that reads the genotype matrix (the first module of the reference's GCN factories), or None."""
+    from .networks.gcn_conv import GCNConv
+    nns = getattr(model, "nns", None)
+    if nns is not None and len(nns) > 0 and isinstance(nns[0], GCNConv):
+        return nns[0]
+    return None
 
 
 def broadcast_parameters(model, src=0):
@@ -127,9 +216,12 @@ def sharded_eval(model, data, rank, world, args_of):
         return model(*args)
     x, edge_index = args[0], args[1]
     edge_weight = args[2] if len(args) > 2 else None
-    n = x.shape[0]
+    shard = getattr(data, "x_shard", None)               # create_graph_sharded: x holds this rank's rows only
+    n = data.y.shape[0] if shard is not None else x.shape[0]
     lo, hi = row_shard(n, rank, world)
-    cur = x[lo:hi]
+    if shard is not None and tuple(shard) != (lo, hi):
+        raise ValueError(f"sharded_eval: x holds rows {tuple(shard)}, this rank evaluates rows {(lo, hi)}")
+    cur = x if shard is not None else x[lo:hi]
     for m, f in zip(model.nns, model.fns):
         if f is not None:
             cur = f(cur)
@@ -182,6 +274,149 @@ def knn_sharded(X_local, row0, n_total, k, rank, world, extra_local=None):
         ops.knn_block(X_local, sq_local, row0, keys, sqk, int(offs[owner]), k, best_d2, best_idx, int(step > 0),
                       extra_local, ek)
     return best_idx, best_d2
+
+
+# ----------------------------------------------------------------------------------------------- sharded graph build
+def shard_sizes(n_local, rank, world, device):
+    """(sizes, offsets) of the row shards of all ranks, as Python lists."""
+    sizes = torch.zeros(world, dtype=torch.int64, device=device)
+    sizes[rank] = n_local
+    if world > 1:
+        dist.all_reduce(sizes)
+    offs = torch.cumsum(sizes, 0) - sizes
+    return [int(v) for v in sizes.tolist()], [int(v) for v in offs.tolist()]
+
+
+def ring_pass(local, sizes, rank, world, fold, make_buffers):
+    """Pass every rank's block once round the ring (rank r sends to r + 1, receives from r - 1), double-buffered:
+    ``fold(owner, tensors)`` is called for the block of every owner, starting with the rank's own, while the next block
+    is already in flight (the transfers run on the backend's stream, the fold on the current one).
+    ``local``: tuple of tensors of this rank's block; ``make_buffers(n_rows)``: a matching tuple of empty tensors."""
+    cur, owner = tuple(local), rank
+    spare = [None, None]
+    for s in range(world):
+        reqs, nxt, nxt_owner = [], None, None
+        if s + 1 < world:
+            nxt_owner = (rank - s - 1) % world
+            slot = s & 1
+            if spare[slot] is None or spare[slot][0].shape[0] != sizes[nxt_owner]:
+                spare[slot] = tuple(make_buffers(sizes[nxt_owner]))
+            nxt = spare[slot]
+            ops_ = [dist.P2POp(dist.isend, t, (rank + 1) % world) for t in cur]
+            ops_ += [dist.P2POp(dist.irecv, t, (rank - 1) % world) for t in nxt]
+            reqs = dist.batch_isend_irecv(ops_)
+        fold(owner, cur)
+        for r in reqs:
+            r.wait()
+        if nxt is not None:
+            cur, owner = nxt, nxt_owner
+
+
+def knn_ring(X_local, row0, n_total, k, rank, world, extra_local=None, impl=None):
+    """Row-sharded kNN graph build with the key blocks passed round a ring: rank r owns the query rows
+    [row0, row0 + n_local); in step s it folds the block that started s ranks behind it into its running lists
+    (gnnb_knn_i8, merge = 1) while the next block arrives.  No neighbour list is ever reduced across ranks, and the lists
+    are bit-identical to ``ops.knn`` on the whole matrix for any number of ranks.
+    The received blocks land in this GPU's own memory before any kernel reads them.
+    Returns (idx int32 [n_local, k] of GLOBAL row ids, d2 float64 [n_local, k])."""
+    from . import ops
+    dev = X_local.device
+    n_local, p = X_local.shape
+    ld = X_local.stride(0)
+    sq_local = ops.row_sqnorm(X_local)
+    best_d2 = torch.empty((n_local, k), dtype=torch.float64, device=dev)
+    best_idx = torch.empty((n_local, k), dtype=torch.int32, device=dev)
+    n_extra = 0 if extra_local is None else extra_local.shape[1]
+    sizes, offs = shard_sizes(n_local, rank, world, dev)
+    assert sum(sizes) == n_total and offs[rank] == row0
+    qb = ops.config["knn_query_block"]
+    state = {"first": True}
+
+    def fold(owner, block):
+        keys = block[0][:, :p]
+        ek = block[2] if n_extra else None
+        for q0 in range(0, n_local, qb):
+            q1 = min(n_local, q0 + qb)
+            ops.knn_block(X_local[q0:q1], sq_local[q0:q1], row0 + q0, keys, block[1], offs[owner], k,
+                          best_d2[q0:q1], best_idx[q0:q1], 0 if state["first"] else 1,
+                          None if n_extra == 0 else extra_local[q0:q1], ek, impl)
+        state["first"] = False
+
+    def make_buffers(rows):
+        out = [torch.empty((rows, ld), dtype=torch.int8, device=dev), torch.empty(rows, dtype=torch.int64, device=dev)]
+        if n_extra:
+            out.append(torch.empty((rows, n_extra), dtype=torch.float64, device=dev))
+        return out
+
+    local = [X_local.as_strided((n_local, ld), (ld, 1)), sq_local]      # the padded storage: receivers keep the 16-byte row stride
+    if n_extra:
+        local.append(extra_local.contiguous())
+    ring_pass(local, sizes, rank, world, fold, make_buffers)
+    return best_idx, best_d2
+
+
+def allgather_shards(local, sizes, rank, world):
+    """Concatenate per-rank row shards of unequal length (``sizes``) on every rank."""
+    if world == 1:
+        return local
+    per = max(sizes)
+    pad = torch.zeros((per,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    pad[:local.shape[0]] = local
+    out = torch.empty((world * per,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(out, pad)
+    return torch.cat([out[r * per:r * per + sizes[r]] for r in range(world)])
+
+
+def fetch_rows(store_local, sizes, offs, wanted, rank, world):
+    """Rows ``wanted`` (global ids, any order, repeats allowed) of a row-sharded matrix, as one [len(wanted), ld] tensor in
+    the order asked for: one all-to-all of the requested ids, one all-to-all of the rows (df.iloc[batch_nodes] of
+    util.py:68 when the frame is spread over the GPUs).  ``store_local``: this rank's shard [sizes[rank], ld]."""
+    dev = store_local.device
+    wanted = torch.as_tensor(wanted, dtype=torch.int64, device=dev)
+    if world == 1:
+        return store_local[wanted]
+    uniq, inverse = torch.unique(wanted, sorted=True, return_inverse=True)
+    bounds = torch.tensor(offs[1:] + [offs[-1] + sizes[-1]], dtype=torch.int64, device=dev)
+    owner = torch.searchsorted(bounds, uniq, right=True)
+    ask = torch.bincount(owner, minlength=world)
+    give = torch.empty_like(ask)
+    dist.all_to_all_single(give, ask)
+    ask_l, give_l = [int(v) for v in ask.tolist()], [int(v) for v in give.tolist()]
+    ids = torch.empty(sum(give_l), dtype=torch.int64, device=dev)
+    dist.all_to_all_single(ids, uniq, output_split_sizes=give_l, input_split_sizes=ask_l)
+    rows_out = store_local[ids - offs[rank]]
+    rows_in = torch.empty((int(uniq.numel()), store_local.shape[1]), dtype=store_local.dtype, device=dev)
+    dist.all_to_all_single(rows_in, rows_out, output_split_sizes=ask_l, input_split_sizes=give_l)
+    return rows_in[inverse]
+
+
+def create_graph_sharded(X_shard, y_all, n_neighbors, rank, world, smoothing="laplacian", use_weights=False,
+                         mode="connectivity", remove_mean=True):
+    """``create_graph`` (load.py:21-81) for ONE graph whose node rows are sharded over the ranks by ``row_shard``: the
+    O(n^2 p) neighbour search runs as a ring over the shards, the k x n neighbour lists (12 bytes per entry) are
+    all-gathered, and every rank runs the O(n k) similarity / symmetrisation / Laplacian pass on the full lists -- the same
+    bytes a reverse-edge exchange would move, no distributed sort, and an edge list that is bit-identical to the one-GPU
+    build by construction (the global d_max and max L are then local reductions).  Returns a Data whose ``x`` holds this
+    rank's rows only (``x_shard = (lo, hi)``), as ``sharded_eval`` wants it."""
+    import numpy as np
+    from . import ops
+    from .data import Data
+    n = int(len(y_all))
+    lo, hi = row_shard(n, rank, world)
+    assert X_shard.shape[0] == hi - lo
+    idx_l, d2_l = knn_ring(X_shard, lo, n, n_neighbors, rank, world)
+    sizes = [row_shard(n, r, world)[1] - row_shard(n, r, world)[0] for r in range(world)]
+    idx, d2 = allgather_shards(idx_l, sizes, rank, world), allgather_shards(d2_l, sizes, rank, world)
+    ei, ew = ops.build_edges(idx, d2, mode=mode, smoothing=smoothing, use_weights=use_weights)
+    yv = np.asarray(y_all, dtype=np.float64)
+    if remove_mean:
+        yv = yv - yv.mean()
+    y = torch.from_numpy(yv.astype(np.float32).reshape(-1, 1)).to(X_shard.device)
+    data = Data(x=X_shard, y=y, edge_index=ei)
+    if use_weights:
+        data.edge_weight = ew
+    data.x_shard = (lo, hi)
+    return data
 
 
 # ----------------------------------------------------------------------------------------------- CUDA-graphed steps

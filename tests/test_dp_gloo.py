@@ -84,3 +84,43 @@ def test_row_shard_covers_everything():
             assert spans[0][0] == 0 and spans[-1][1] == n
             assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
             assert all((lo % 128 == 0) for lo, _ in spans if lo < n)
+
+
+def _exchange_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    parallel.init_distributed(backend="gloo")
+    total, ld = 11, 16
+    full = (torch.arange(total * ld, dtype=torch.int32) % 127).to(torch.int8).reshape(total, ld)
+    cut = [0, 4, 7, 11][:world + 1] if world == 3 else [0, 7, 11]
+    lo, hi = cut[rank], cut[rank + 1]
+    local = full[lo:hi].clone()
+    sizes, offs = parallel.shard_sizes(hi - lo, rank, world, torch.device("cpu"))
+    assert sizes == [b - a for a, b in zip(cut, cut[1:])] and offs == cut[:-1]
+    # ring: every owner's block is folded exactly once, own block first, with the right contents
+    seen = []
+
+    def fold(owner, block):
+        assert torch.equal(block[0], full[cut[owner]:cut[owner + 1]]) and int(block[1][0]) == owner
+        seen.append(owner)
+
+    tag = torch.full((hi - lo,), rank, dtype=torch.int64)
+    parallel.ring_pass((local, tag), sizes, rank, world, fold,
+                       lambda rows: (torch.empty((rows, ld), dtype=torch.int8), torch.empty(rows, dtype=torch.int64)))
+    assert seen == [(rank - s) % world for s in range(world)]
+    # shards of unequal length -> the whole matrix on every rank
+    assert torch.equal(parallel.allgather_shards(local, sizes, rank, world), full)
+    # rows by global id, any order, repeats, rows of both owners
+    wanted = [10, 0, 3, 3, 8, 6, 7, 1] if rank == 0 else [2, 9, 2, 5]
+    got = parallel.fetch_rows(local, sizes, offs, wanted, rank, world)
+    assert torch.equal(got, full[torch.tensor(wanted)])
+    dist.barrier()
+    if rank == 0:
+        open(out, "w").write("ok")
+    dist.destroy_process_group()
+
+
+def test_ring_allgather_and_row_exchange_two_ranks(tmp_path):
+    out = str(tmp_path / "ok")
+    mp.spawn(_exchange_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    assert open(out).read() == "ok"

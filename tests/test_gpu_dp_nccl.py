@@ -1,0 +1,92 @@
+"""Two NCCL ranks on two GPUs: the data-parallel step with the gradient sink (range-wise overlapped all-reduce), the
+row-sharded evaluation and the row-sharded neighbour search, each against its single-GPU counterpart.  Skipped on a box
+with fewer than two GPUs (run it with ``gpurun --gpus 2``)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _make(rank_seed, n, p, dev):
+    from gnn_b200 import ops
+    from gnn_b200.data import GenotypeTable
+    from gnn_b200.loaders.load import create_graph
+    X = ops.synth_genotypes(n, p, dev, row0=1000 * rank_seed, p_total=p)
+    y = np.random.default_rng(rank_seed).standard_normal(n)
+    return create_graph(GenotypeTable(X, y), n_neighbors=6, smoothing="laplacian", use_weights=True, mode="distance",
+                        algorithm="euclidean")
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    import torch.distributed as dist
+    from gnn_b200 import ops, parallel
+    from gnn_b200.networks import networks as nets
+    from gnn_b200.trainers.util import get_args_tuple
+    parallel.init_distributed()
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    n, p, h = 700, 2048, 32
+    graphs = [_make(s, n, p, dev) for s in range(4)]                 # every rank can build every subgraph (oracle below)
+    for g in graphs:
+        g.x = ops.pack_2bit(g.x)
+    torch.manual_seed(0)
+    model = nets.create_network_two_no_conv_dropout(p, 1, internal_size=h, dropout=0.0).to(dev)
+    ref = nets.create_network_two_no_conv_dropout(p, 1, internal_size=h, dropout=0.0).to(dev)
+    parallel.broadcast_parameters(model)
+    ref.load_state_dict(model.state_dict())
+    flat = parallel.FlatGrads(model.parameters(), sink_layer=parallel.first_genotype_layer(model), world=world)
+    flat.range_markers = 512                                          # four ranges at p = 2048: staged, overlapped reduces
+    opt = torch.optim.Adam(model.parameters(), lr=1e-2)
+    opt_ref = torch.optim.Adam(ref.parameters(), lr=1e-2)
+    lf = torch.nn.MSELoss()
+    mine = parallel.owned(len(graphs), rank, world)
+    for step, b in enumerate(mine):
+        parallel.dp_step(model, flat, opt, graphs[b], world, lf, get_args_tuple)
+        opt_ref.zero_grad()
+        for r in range(world):                                        # gradient averaging over the step's subgraphs
+            g = graphs[step * world + r]
+            (lf(ref(*get_args_tuple(g)), g.y) / world).backward()
+        for (k, a), (_, c) in zip(model.named_parameters(), ref.named_parameters()):
+            err = float((a.grad - c.grad).abs().max() / c.grad.abs().max().clamp_min(1e-30))
+            assert err < 1e-5, (step, k, err)
+        opt_ref.step()
+    for a, c in zip(model.parameters(), ref.parameters()):
+        assert float((a - c).abs().max()) < 1e-5
+    # row-sharded evaluation == the unsharded model, bit for bit
+    test = graphs[3]
+    whole = parallel.sharded_eval(model, test, 0, 1, get_args_tuple)
+    shard = parallel.sharded_eval(model, test, rank, world, get_args_tuple)
+    assert torch.equal(whole, shard)
+    # row-sharded neighbour search == one GPU, bit for bit
+    N = 1500
+    X = ops.synth_genotypes(N, p, dev, row0=7, p_total=p)
+    lo, hi = (0, 800) if rank == 0 else (800, N)
+    idx, d2 = parallel.knn_sharded(X[lo:hi], lo, N, 8, rank, world)
+    idx1, d21 = ops.knn(X, 8)
+    assert torch.equal(idx, idx1[lo:hi]) and torch.equal(d2, d21[lo:hi])
+    torch.cuda.synchronize()
+    dist.barrier()
+    if rank == 0:
+        open(out, "w").write("ok")
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_nccl_ranks(tmp_path):
+    out = str(tmp_path / "ok")
+    mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    assert open(out).read() == "ok"

@@ -216,8 +216,8 @@ def test_linear_int8_limb_path(n, p, h):
 def test_linear_int8_digits_with_outliers_inside_a_feature(spread):
     """The fixed-point scale is per output feature, so what matters is the spread INSIDE a feature: a few rows of dH (hub
     nodes) or a few markers of W far above the rest.  24 bits relative to the feature's maximum keep every output within
-    the path's 1e-4 of float64 (max-abs over max-abs per feature, the metric of every other test here), and no worse than
-    the exact-fp32 tiles (precision 0) do on the same inputs."""
+    the path's 1e-4 of float64 (max-abs over max-abs per feature, the metric of every other test here) and within 1e-5 of
+    what the exact-fp32 tiles (precision 0) reach on the same inputs."""
     n, p, h = 2048, 4096, 100
     X = torch.from_numpy(synth.genotypes(n, p, seed=11)).to(DEV)
     g = torch.Generator(device="cpu").manual_seed(int(spread))
@@ -235,11 +235,10 @@ def test_linear_int8_digits_with_outliers_inside_a_feature(spread):
         ef, eb = rel_err(fwd[:, f], ref_f[:, f]), rel_err(bwd[f], ref_b[f])
         worst = max(worst, ef, eb)
         assert ef < 1e-4 and eb < 1e-4, (f, ef, eb)
-        assert ef < 4 * rel_err(fwd0[:, f], ref_f[:, f]) + 1e-6 and eb < 4 * rel_err(bwd0[f], ref_b[f]) + 1e-6, f
-    assert worst < 2e-5, worst
-    # elements far BELOW the maximum keep their absolute resolution max * 2^-23: the typical (non-outlier) outputs
-    typical = ref_f.abs().median()
-    assert float((fwd.double() - ref_f).abs().max()) < 1e-4 * float(typical) * max(1.0, spread / 1e3)
+        assert ef < rel_err(fwd0[:, f], ref_f[:, f]) + 1e-5 and eb < rel_err(bwd0[f], ref_b[f]) + 1e-5, f
+    # measured 2.6e-6 .. 3.8e-6 whatever the spread: the error is 2^-24 of the feature's maximum per element, so it is
+    # constant relative to the feature's largest outputs (relative to its TYPICAL outputs it grows like max / rms)
+    assert worst < 1e-5, worst
 
 
 def test_linear_int8_digit_sums_cannot_overflow():
@@ -300,16 +299,56 @@ def test_weight_gradient_by_marker_ranges_and_into_a_given_buffer():
     assert ops.linear_bwd_w(X, dH, out=view) is view and torch.equal(view, want) and float(flat[0]) == 9.0
     for x, fmt in ((X, 1), (Xp, 2)):
         ranges = ops.marker_ranges(p, 4, fmt)
+        assert ops.marker_ranges(p, None, fmt, wave=1024) == [(c, min(p, c + 1024)) for c in range(0, p, 1024)]
         assert ranges[0][0] == 0 and ranges[-1][1] == p and all(a[1] == b[0] for a, b in zip(ranges, ranges[1:]))
         seen = []
         view.fill_(-1.0)
         got = ops.linear_bwd_w_ranges(x, dH, ranges, p=p, out=view, after_range=lambda c0, c1: seen.append((c0, c1)))
         assert seen == ranges and torch.equal(got, want)
+        outs = [torch.empty((h, c1 - c0), device=DEV) for c0, c1 in ranges]      # one contiguous block per range
+        ops.linear_bwd_w_ranges(x, dH, ranges, p=p, out=outs)
+        assert torch.equal(torch.cat(outs, dim=1), want)
+    assert ops.bwd_w_wave_markers(2, X.device) % 512 == 0 and ops.bwd_w_wave_markers(2, X.device) >= 512 * 16
     # float features take the fallback: one plain call, one callback
     seen = []
     xf = torch.randn(n, 64, device=DEV)
     assert rel_err(ops.linear_bwd_w_ranges(xf, dH, [(0, 64)], after_range=lambda a, b: seen.append((a, b))),
                    dH.double().t() @ xf.double()) < 1e-5 and seen == [(0, 64)]
+
+
+@pytest.mark.parametrize("packed", [False, True])
+def test_gradient_sink_writes_the_first_layer_gradients_in_place(packed):
+    """parallel.FlatGrads with a sink layer: the first GCNConv's backward writes dW / db into the flat buffer itself (no
+    zero-fill, no accumulate pass); two steps in a row give the bits of plain autograd, i.e. nothing stale is added."""
+    from gnn_b200 import parallel
+    n, p, h = 600, 1024, 32
+    X = torch.from_numpy(synth.genotypes(n, p, seed=4)).to(DEV)
+    x = ops.pack_2bit(X) if packed else X
+    ei, ew = random_graph(n, 5000, 6)
+    ei, ew = ei.to(DEV), ew.to(DEV)
+    y = torch.randn(n, 1, device=DEV)
+    torch.manual_seed(0)
+    plain = nets.create_network_two_no_conv_dropout(p, 1, internal_size=h, dropout=0.0).to(DEV)
+    sunk = nets.create_network_two_no_conv_dropout(p, 1, internal_size=h, dropout=0.0).to(DEV)
+    sunk.load_state_dict(plain.state_dict())
+    layer = parallel.first_genotype_layer(sunk)
+    assert layer is sunk.nns[0]
+    flat = parallel.FlatGrads(sunk.parameters(), sink_layer=layer)
+    assert flat.has_sink and flat.params[0] is layer.lin.weight and flat.params[1] is layer.bias
+    flat.flat.fill_(123.0)                                   # stale contents everywhere: the step must not see them
+    for step in range(2):
+        plain.zero_grad()
+        torch.nn.functional.mse_loss(plain(x, ei, ew), y).backward()
+        flat.zero()
+        torch.nn.functional.mse_loss(sunk(x, ei, ew), y).backward()
+        flat.allreduce_mean(1)
+        for (k, a), (_, b) in zip(plain.named_parameters(), sunk.named_parameters()):
+            assert torch.equal(a.grad, b.grad), (step, k)
+            assert b.grad.data_ptr() >= flat.flat.data_ptr() and b.grad.data_ptr() < flat.flat.data_ptr() + 4 * flat.flat.numel()
+    # float features through the same layer keep the contract (overwrite, not accumulate)
+    flat.zero()
+    torch.nn.functional.mse_loss(sunk(X.float(), ei, ew), y).backward()
+    assert rel_err(layer.lin.weight.grad, plain.nns[0].lin.weight.grad) < 1e-5
 
 
 @pytest.mark.parametrize("F", [4, 100, 256])
