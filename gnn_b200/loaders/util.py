@@ -50,6 +50,14 @@ def _sizes(n_rows, batches):
     return [int(b) for b in batches]
 
 
+def partition_order(idx):
+    """Nodes in the order ``naive_partition`` meets them: by first occurrence in the neighbour stream (the flattened
+    canonical lists).  Device scatter-min (gnnb_first_occurrence), one D2H copy of n int64, host argsort."""
+    first_pos = ops.first_occurrence(idx).cpu().numpy()
+    seen = np.nonzero(first_pos != np.iinfo(np.int64).max)[0]
+    return seen[np.argsort(first_pos[seen], kind="stable")]
+
+
 def split_indices_graph(table, batches, neighbours=5):
     """Row indices of every batch of ``split_dataset_graph`` for a device-resident table."""
     n = len(table)
@@ -58,10 +66,7 @@ def split_indices_graph(table, batches, neighbours=5):
     if order is None:       # the reference rebuilds this graph for every split of the same frame (load.py:203, :238)
         extra = torch.from_numpy(np.array(table.value, dtype=np.float64).reshape(-1, 1))
         idx, _ = ops.knn(table.markers, neighbours, extra=extra)
-        first_pos = ops.first_occurrence(idx).cpu().numpy()      # device scatter-min, then one D2H of n int64
-        seen = np.nonzero(first_pos != np.iinfo(np.int64).max)[0]
-        order = seen[np.argsort(first_pos[seen], kind="stable")]
-        cache[neighbours] = order
+        order = cache[neighbours] = partition_order(idx)
     return ops.partition_walk(order, n, _sizes(n, batches))
 
 

@@ -72,11 +72,14 @@ class Profiler:
     def __init__(self):
         self.records = []            # (name, work_dict, start_event, end_event)
 
-    def summary(self):
+    def summary(self, by_shape=False):
+        """name -> totals; with ``by_shape`` the key is ``name[shape]`` for calls that declared one (projection, aggregation,
+        neighbour search), so that e.g. the 50 000-wide tensor-core projection and the 100-wide inner products are apart."""
         torch.cuda.synchronize()
         out = {}
         for name, work, e0, e1 in self.records:
-            slot = out.setdefault(name, {"calls": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
+            key = f"{name}[{work['shape']}]" if by_shape and "shape" in work else name
+            slot = out.setdefault(key, {"calls": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
             slot["calls"] += 1
             slot["ms"] += e0.elapsed_time(e1)
             slot["flops"] += work.get("flops", 0.0)
@@ -214,7 +217,7 @@ def knn_block(Q, sq_q, q_off, K, sq_k, k_off, k, best_d2, best_idx, merge, extra
     with torch.cuda.device(Q.device):
         nbytes = _ws_bytes("gnnb_knn_workspace_bytes", Q.shape[0], K.shape[0], Q.shape[1], k, impl)
         ws = _ws(nbytes, Q.device)
-        _declare(flops=2.0 * Q.shape[0] * K.shape[0] * Q.shape[1])
+        _declare(flops=2.0 * Q.shape[0] * K.shape[0] * Q.shape[1], shape=f"{Q.shape[0]}x{K.shape[0]}x{Q.shape[1]}")
         _call("gnnb_knn_i8", _p(Q), Q.stride(0), _p(sq_q), Q.shape[0], q_off,
               _p(K), K.stride(0), _p(sq_k), K.shape[0], k_off, Q.shape[1],
               _p(extra_q), _p(extra_k), n_extra, k, _p(best_d2), _p(best_idx), int(merge), impl,
@@ -448,7 +451,8 @@ def spmm(rowptr, col, val, H, bias=None, n=None, hub=None, nnz=None):
     out = torch.empty((n, H.shape[1]), dtype=torch.float32, device=H.device)
     nnz = int(col.numel()) if nnz is None else int(nnz)
     F = int(H.shape[1])
-    _declare(bytes=float(nnz * (F * 4 + 8) + n * F * 4 + (n + 1) * 4 + n * 4 + F * 4))    # AGG_BYTES, SURVEY.md 8d
+    _declare(bytes=float(nnz * (F * 4 + 8) + n * F * 4 + (n + 1) * 4 + n * 4 + F * 4),     # AGG_BYTES, SURVEY.md 8d
+             shape=f"n{n},nnz{nnz},F{F}")
     with torch.cuda.device(H.device):
         if hub is not None:
             nt = hub[0].numel()
@@ -508,7 +512,8 @@ def linear_fwd(X, W, precision=None):
     H = torch.empty((n, h), dtype=torch.float32, device=X.device)
     with torch.cuda.device(X.device):
         ws = _ws(_ws_bytes("gnnb_linear_workspace_bytes", n, p, h, prec), X.device)
-        _declare(flops=2.0 * n * p * h, bytes=float(n * X.shape[1] * X.element_size() + h * p * 4 + n * h * 4))
+        _declare(flops=2.0 * n * p * h, bytes=float(n * X.shape[1] * X.element_size() + h * p * 4 + n * h * 4),
+                 shape=f"{n}x{p}x{h},fmt{fmt},prec{prec}")
         _call("gnnb_linear_fwd", _p(X), fmt, X.stride(0), n, p, _p(W), W.stride(0), h,
               _p(H), H.stride(0), prec, _p(ws), ws.numel(), _stream())
     return H
@@ -528,7 +533,8 @@ def linear_bwd_w(X, dH, precision=None, p=None, out=None):
     dW = _grad_out(out, h, p, X.device)
     with torch.cuda.device(X.device):
         ws = _ws(_ws_bytes("gnnb_linear_workspace_bytes", n, p, h, prec), X.device)
-        _declare(flops=2.0 * n * p * h, bytes=float(n * X.shape[1] * X.element_size() + h * p * 4 + n * h * 4))
+        _declare(flops=2.0 * n * p * h, bytes=float(n * X.shape[1] * X.element_size() + h * p * 4 + n * h * 4),
+                 shape=f"{n}x{p}x{h},fmt{fmt},prec{prec}")
         _call("gnnb_linear_bwd_w", _p(X), fmt, X.stride(0), n, p, _p(dH), dH.stride(0), h,
               _p(dW), dW.stride(0), prec, _p(ws), ws.numel(), _stream())
     return dW
@@ -591,7 +597,8 @@ def linear_bwd_w_ranges(X, dH, ranges, p=None, out=None, after_range=None):
                 ds, ldd = _p(dst), dst.stride(0)
             else:
                 ds, ldd = ctypes.c_void_p(dW.data_ptr() + 4 * c0), dW.stride(0)
-            _declare(flops=2.0 * n * (c1 - c0) * h, bytes=float(n * (c1 - c0) // per_code + h * (c1 - c0) * 4))
+            _declare(flops=2.0 * n * (c1 - c0) * h, bytes=float(n * (c1 - c0) // per_code + h * (c1 - c0) * 4),
+                     shape=f"{n}x{c1 - c0}x{h},fmt{fmt},prec4")
             _call("gnnb_linear_bwd_w_prepared", xs, fmt, X.stride(0), n, c1 - c0, h, ds, ldd, _p(ws), ws.numel(), _stream())
             if after_range is not None:
                 after_range(c0, c1)
@@ -618,7 +625,7 @@ def linear_bwd_x(dH, W):
     n, h = dH.shape
     p = W.shape[1]
     dX = torch.empty((n, p), dtype=torch.float32, device=dH.device)
-    _declare(flops=2.0 * n * p * h)
+    _declare(flops=2.0 * n * p * h, shape=f"{n}x{p}x{h}")
     with torch.cuda.device(dH.device):
         _call("gnnb_linear_bwd_x", _p(dH), dH.stride(0), n, h, _p(W), W.stride(0), p, _p(dX), dX.stride(0), _stream())
     return dX

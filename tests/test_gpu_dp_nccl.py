@@ -78,6 +78,30 @@ def _worker(rank, world, port, out):
     idx, d2 = parallel.knn_sharded(X[lo:hi], lo, N, 8, rank, world)
     idx1, d21 = ops.knn(X, 8)
     assert torch.equal(idx, idx1[lo:hi]) and torch.equal(d2, d21[lo:hi])
+    # the same search with the key blocks passed round a ring (double-buffered isend / irecv), with a phenotype column
+    extra = torch.from_numpy(np.random.default_rng(1).standard_normal((N, 1))).to(dev)
+    idx_r, d2_r = parallel.knn_ring(X[lo:hi], lo, N, 8, rank, world, extra_local=extra[lo:hi])
+    idx_e, d2_e = ops.knn(X, 8, extra=extra)
+    assert torch.equal(idx_r, idx_e[lo:hi]) and torch.equal(d2_r, d2_e[lo:hi])
+    # rows by global id from the sharded matrix
+    sizes, offs = parallel.shard_sizes(hi - lo, rank, world, dev)
+    wanted = torch.randperm(N, generator=torch.Generator().manual_seed(rank))[:300]
+    store = X.as_strided((N, X.stride(0)), (X.stride(0), 1))
+    got = parallel.fetch_rows(store[lo:hi], sizes, offs, wanted, rank, world)
+    assert torch.equal(got, store[wanted.to(dev)])
+    # one graph built from row shards: same edge list as on one GPU, and the sharded evaluation accepts the shard
+    from gnn_b200.data import GenotypeTable
+    from gnn_b200.loaders.load import create_graph
+    yv = np.random.default_rng(2).standard_normal(N)
+    one = create_graph(GenotypeTable(X, yv), n_neighbors=6, smoothing="laplacian", use_weights=True, mode="distance")
+    slo, shi = parallel.row_shard(N, rank, world)
+    shd = parallel.create_graph_sharded(X[slo:shi], yv, 6, rank, world, use_weights=True, mode="distance")
+    assert torch.equal(shd.edge_index, one.edge_index) and torch.equal(shd.edge_weight, one.edge_weight)
+    assert torch.equal(shd.y, one.y) and shd.x_shard == (slo, shi)
+    big = nets.create_network_two_no_conv_dropout(p, 1, internal_size=h, dropout=0.0).to(dev)
+    parallel.broadcast_parameters(big)
+    assert torch.equal(parallel.sharded_eval(big, shd, rank, world, get_args_tuple),
+                       parallel.sharded_eval(big, one, 0, 1, get_args_tuple))
     torch.cuda.synchronize()
     dist.barrier()
     if rank == 0:
