@@ -452,7 +452,7 @@ def spmm(rowptr, col, val, H, bias=None, n=None, hub=None, nnz=None):
     nnz = int(col.numel()) if nnz is None else int(nnz)
     F = int(H.shape[1])
     _declare(bytes=float(nnz * (F * 4 + 8) + n * F * 4 + (n + 1) * 4 + n * 4 + F * 4),     # AGG_BYTES, SURVEY.md 8d
-             shape=f"n{n},nnz{nnz},F{F}")
+             shape=f"n{n},F{F}")
     with torch.cuda.device(H.device):
         if hub is not None:
             nt = hub[0].numel()
