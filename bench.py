@@ -58,6 +58,8 @@ def parse():
     ap.add_argument("--partition", choices=("graph", "contiguous"), default="graph",
                     help="graph: split_dataset_graph + naive_partition over the global kNN graph (the shipped configuration); "
                          "contiguous: split_dataset row slices (no global graph)")
+    ap.add_argument("--dp-cut", default="last_wave", choices=["last_wave", "every_wave", "none"],
+                    help="where the first-layer weight gradient is cut for the overlapped all-reduce (parallel.FlatGrads._ranges)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-agg-hbm", action="store_true", help="skip the aggregation measurement on the whole-frame graph")
     ap.add_argument("--cuda-graph", default="auto", choices=["auto", "on", "off"],
@@ -349,6 +351,7 @@ def run_ours(a):
     model = nets.create_network_two_no_conv_dropout(p, 1, internal_size=a.hidden, dropout=DROPOUT).to(dev)
     parallel.broadcast_parameters(model)
     flat = parallel.FlatGrads(model.parameters(), sink_layer=parallel.first_genotype_layer(model), world=world)
+    flat.cut = a.dp_cut
     opt = torch.optim.Adam(model.parameters(), lr=LR, fused=True, capturable=True)   # the update rule of main.py:318, one kernel
     loss_func = torch.nn.MSELoss()
     agg_hbm = None
@@ -542,7 +545,7 @@ def run_ours(a):
                    "optimizer_steps_per_epoch": steps_per_epoch, "subgraphs_per_s": B * 1000.0 / ms_per_epoch,
                    "update_rule": (f"one Adam step per {world} subgraph(s): the gradients of the ranks' subgraphs are averaged, so an epoch "
                                    f"takes {steps_per_epoch} optimiser steps here and {B} at dp1 / in the reference's train_batches"),
-                   "linear_precision": ops.config["linear_precision"], "cuda_graphs": bool(graphs_ok),
+                   "linear_precision": ops.config["linear_precision"], "cuda_graphs": bool(graphs_ok), "dp_cut": a.dp_cut,
                    "cuda_graph_errors": graph_errors,
                    "resident_genotypes": "2-bit packed (12.5 GB at C5), expanded on chip by the projection kernels",
                    "l2": "inputs per epoch far exceed L2 (genotypes >= 0.19 GB per subgraph, 64 subgraphs); no flush needed",

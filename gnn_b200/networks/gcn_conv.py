@@ -36,18 +36,28 @@ class _GCNConvFn(torch.autograd.Function):
         d_out = d_out.contiguous()
         sink = getattr(ctx.layer, "grad_sink", None)
         sunk = sink is not None and ctx.has_bias and weight.grad is not None and ctx.layer.bias.grad is not None
+        # the bias gradient (column sums of dOut) and the aggregation of dOut are independent and each fills only part of
+        # the GPU: they run side by side, and so do the weight and the input gradient of an inner layer
+        bias_job = None
+        if ctx.has_bias:
+            into = ctx.layer.bias.grad if sunk else None
+            bias_job = ops.Fork(lambda: ops.colsum(d_out, out=into), reads=(d_out, into))
         d_h = ops.spmm(g.rowptr_t, g.col_t, g.val_t, d_out, None, n=g.n, hub=g.hub_t)     # transposed CSR
         if sunk and not x.is_floating_point():
             # data-parallel training (parallel.FlatGrads): dW and db go straight into the flat gradient buffer and their
             # all-reduces start here; autograd gets None for both and has nothing to accumulate
-            sink.write(ctx.layer, x, d_h, d_out)
+            bias_job.join()
+            sink.write(ctx.layer, x, d_h)
             return None, None, None, None, None
-        d_bias = ops.colsum(d_out) if ctx.has_bias else None
-        d_w = ops.linear_bwd_w(x, d_h, p=weight.shape[1])
-        d_x = ops.linear_bwd_x(d_h, weight) if ctx.x_needs_grad else None
+        if ctx.x_needs_grad:
+            w_job = ops.Fork(lambda: ops.linear_bwd_w(x, d_h, p=weight.shape[1]), reads=(x, d_h), slot=1)
+            d_x = ops.linear_bwd_x(d_h, weight)
+            d_w = w_job.join()
+        else:
+            d_w, d_x = ops.linear_bwd_w(x, d_h, p=weight.shape[1]), None
+        d_bias = bias_job.join() if bias_job is not None else None
         if sunk:        # float features: same contract (the sink's slices are overwritten, not accumulated into), plain kernels
             weight.grad.copy_(d_w)
-            ctx.layer.bias.grad.copy_(d_bias)
             return d_x, None, None, None, None
         return d_x, d_w, d_bias, None, None
 

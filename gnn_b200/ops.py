@@ -679,3 +679,42 @@ def partition_walk(order, n_nodes, sizes, taken=None):
         res.append(out[pos:pos + int(ln)].copy())
         pos += int(ln)
     return res
+
+
+# --------------------------------------------------------------------------------------- independent work side by side
+_side_streams = {}
+
+
+class Fork:
+    """Run an independent piece of a backward pass on a side stream while the main stream carries on (e.g. the bias
+    gradient's column sums next to the aggregation of the same dOut: each fills a fraction of the GPU).  Usage:
+
+        job = Fork(lambda: colsum(d_out), reads=(d_out,))     # enqueued on the side stream, after everything so far
+        d_h = spmm(...)                                        # main stream, concurrently
+        d_bias = job.join()                                    # main stream waits; the result is safe to use on it
+
+    Works eagerly and under CUDA-graph capture (the fork and join become graph edges).  ``slot`` picks one of a few side
+    streams per device so that two forks can be in flight at once."""
+
+    def __init__(self, fn, reads=(), slot=0):
+        self.main = torch.cuda.current_stream()
+        dev = self.main.device_index
+        key = (dev, slot)
+        side = _side_streams.get(key)
+        if side is None:
+            side = _side_streams[key] = torch.cuda.Stream(device=dev)
+        self.side = side
+        side.wait_stream(self.main)
+        with torch.cuda.stream(side):
+            self.out = fn()
+        for t in reads:
+            if t is not None:
+                t.record_stream(side)
+
+    def join(self):
+        self.main.wait_stream(self.side)
+        outs = self.out if isinstance(self.out, (tuple, list)) else (self.out,)
+        for t in outs:
+            if torch.is_tensor(t):
+                t.record_stream(self.main)
+        return self.out

@@ -70,25 +70,25 @@ class FlatGrads:
             off += p.numel()
         self.world, self.group, self.pending, self._stage = int(world), group, [], {}
         self.has_sink = bool(head)
-        self.range_markers = None           # markers per all-reduce range; None = one full wave of the weight-gradient kernel
+        self.range_markers = None           # markers per wave of the weight-gradient kernel; None = ask the library
+        self.cut = "last_wave"              # see _ranges
         if head:
             self.w_numel = head[0].numel()
             self.tail = self.flat[self.w_numel + head[1].numel():]      # what autograd still accumulates into
             sink_layer.grad_sink = self
 
     # ---- called by the sink layer's backward (networks/gcn_conv.py) -------------------------------------------------
-    def write(self, layer, x, d_h, d_out):
-        """dW = d_h^T x and db = colsum(d_out) of the sink layer, written in place; all-reduces started range by range."""
+    def write(self, layer, x, d_h):
+        """dW = d_h^T x of the sink layer written in place (the layer's backward has already put db into ``bias.grad``);
+        all-reduces started range by range."""
         from . import ops
-        w, b = layer.lin.weight, layer.bias
-        ops.colsum(d_out, out=b.grad)
+        w = layer.lin.weight
         many = self.world > 1
         if many:                 # db and the tail are final here: every other layer's backward ran before this one
             self._start(self.flat[self.w_numel:])
         h, p = w.shape
         fmt = 2 if x.dtype == torch.uint8 else 1
-        wave = self.range_markers or ops.bwd_w_wave_markers(fmt, x.device)
-        ranges = ops.marker_ranges(p, None, fmt, wave=wave) if many else [(0, p)]
+        ranges = self._ranges(p, fmt, x.device) if many else [(0, p)]
         if many and len(ranges) > 1:
             # a marker range is a column block of dW [h, p] -- not contiguous, and a collective wants one piece of memory:
             # the GEMM of a range writes into its own contiguous staging block, the all-reduce runs on that block while
@@ -102,6 +102,21 @@ class FlatGrads:
             ops.linear_bwd_w_ranges(x, d_h, ranges, p=p, out=w.grad)
             if many:
                 self._start(self.flat[:self.w_numel])
+
+    def _ranges(self, p, fmt, device):
+        """Where the markers are cut for the overlapped all-reduce.  The weight-gradient GEMM runs in waves of clusters
+        (``ops.bwd_w_wave_markers`` markers each); a cut costs a launch, a pipeline fill and a drain (~10 us), and what stays
+        exposed in any case is the all-reduce of the LAST range.  ``cut``: "last_wave" (default) = all full waves but the
+        last one | the rest: one cut, the first all-reduce hides behind the last wave; "every_wave" = one range per wave;
+        "none" = one GEMM, one all-reduce after it."""
+        from . import ops
+        wave = self.range_markers or ops.bwd_w_wave_markers(fmt, device)
+        if self.cut == "none" or wave <= 0 or p <= wave:
+            return [(0, p)]
+        per_wave = ops.marker_ranges(p, None, fmt, wave=wave)
+        if self.cut == "every_wave" or len(per_wave) <= 2:
+            return per_wave
+        return [(0, per_wave[-1][0]), per_wave[-1]]
 
     def _staging(self, h, r):
         key = (h, r[0], r[1])

@@ -49,7 +49,7 @@ def _worker(rank, world, port, out):
     parallel.broadcast_parameters(model)
     ref.load_state_dict(model.state_dict())
     flat = parallel.FlatGrads(model.parameters(), sink_layer=parallel.first_genotype_layer(model), world=world)
-    flat.range_markers = 512                                          # four ranges at p = 2048: staged, overlapped reduces
+    flat.range_markers, flat.cut = 512, "every_wave"                  # four ranges at p = 2048: staged, overlapped reduces
     opt = torch.optim.Adam(model.parameters(), lr=1e-2)
     opt_ref = torch.optim.Adam(ref.parameters(), lr=1e-2)
     lf = torch.nn.MSELoss()
