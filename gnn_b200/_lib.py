@@ -31,6 +31,7 @@ PROTOTYPES = {
     "gnnb_knn_f64": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _i64, _i64, _i64, _i32, _vp, _vp, _i32, _vp, _sz, _vp]),
     "gnnb_knn_insert_self": (_i32, [_vp, _vp, _i64, _i32, _i64, _vp]),
     "gnnb_unpack_2bit": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _vp]),
+    "gnnb_base3_to_2bit": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _vp, _vp]),
     "gnnb_pack_2bit": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _vp, _vp]),
     "gnnb_scale_columns_i8": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _vp, _i64, _vp]),
     "gnnb_graph_workspace_bytes": (_i32, [_i64, _i32, _psz]),

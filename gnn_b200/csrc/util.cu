@@ -452,6 +452,67 @@ __global__ void __launch_bounds__(256) colsum_final_kernel(const float* __restri
     if (lane == 0) out[f] = s;
 }
 
+
+// ------------------------------------------------------------------------------------ base-3 host / PCIe format
+// Genotypes are 0 / 1 / 2, so five of them fit one byte (3^5 = 243): value = c0 + 3 c1 + 9 c2 + 27 c3 + 81 c4.  That is the
+// densest byte-aligned form (1.6 bits per code against 2) and what crosses PCIe when the genotypes live on the host; on the
+// device it is re-coded once into the 2-bit form the projection kernels read.  One thread = 16 input bytes = 80 codes =
+// 20 output bytes; the byte -> ten-bit table sits in shared memory.  HBM-bound: 0.2 B read + 0.25 B written per code.
+__global__ void __launch_bounds__(256)
+base3_to_2bit_kernel(const uint8_t* __restrict__ in, int64_t ldi, int64_t n, int64_t p, uint8_t* __restrict__ out, int64_t ldo,
+                     int32_t* __restrict__ bad_flag) {
+    __shared__ uint16_t lut[256];
+    {
+        const int b = threadIdx.x;                         // blockDim.x == 256
+        int v = b, bits = 0;
+        for (int d = 0; d < 5; ++d) { bits |= (v % 3) << (2 * d); v /= 3; }
+        lut[b] = b < 243 ? (uint16_t)bits : (uint16_t)0xFFFF;
+    }
+    __syncthreads();
+    const int64_t groups = (p + 79) / 80, total = n * groups;
+    const int64_t in_bytes = (p + 4) / 5, out_bytes = (p + 3) / 4;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / groups, g = i % groups;
+        const uint8_t* src = in + r * ldi + g * 16;
+        uint8_t b[16];
+        if ((g + 1) * 16 <= ldi && ((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
+            *reinterpret_cast<uint4*>(b) = *reinterpret_cast<const uint4*>(src);
+        } else {
+#pragma unroll
+            for (int q = 0; q < 16; ++q) b[q] = (g * 16 + q < in_bytes) ? src[q] : 0;
+        }
+        unsigned long long c[4];
+        bool bad = false;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const unsigned l0 = lut[b[4 * q]], l1 = lut[b[4 * q + 1]], l2 = lut[b[4 * q + 2]], l3 = lut[b[4 * q + 3]];
+            bad |= ((l0 | l1 | l2 | l3) & 0x8000u) != 0;
+            c[q] = (unsigned long long)(l0 & 1023u) | ((unsigned long long)(l1 & 1023u) << 10) | ((unsigned long long)(l2 & 1023u) << 20) |
+                   ((unsigned long long)(l3 & 1023u) << 30);
+        }
+        if (bad && bad_flag) *bad_flag = 1;
+        uint32_t w[5];
+        w[0] = (uint32_t)c[0];
+        w[1] = (uint32_t)(c[0] >> 32) | (uint32_t)(c[1] << 8);
+        w[2] = (uint32_t)(c[1] >> 24) | (uint32_t)(c[2] << 16);
+        w[3] = (uint32_t)(c[2] >> 16) | (uint32_t)(c[3] << 24);
+        w[4] = (uint32_t)(c[3] >> 8);
+        uint8_t* dst = out + r * ldo + g * 20;
+        if ((g + 1) * 20 <= out_bytes && ((reinterpret_cast<uintptr_t>(dst) & 3) == 0)) {
+#pragma unroll
+            for (int q = 0; q < 5; ++q) reinterpret_cast<uint32_t*>(dst)[q] = w[q];
+        } else {
+            // last group of a row: only the bytes that hold codes; codes past p inside the last byte are cleared
+            for (int q = 0; q < 20 && g * 20 + q < out_bytes; ++q) {
+                uint8_t v = (uint8_t)(w[q >> 2] >> (8 * (q & 3)));
+                const int64_t first = (g * 20 + q) * 4;
+                if (first + 4 > p) v &= (uint8_t)((1u << (2 * (p - first))) - 1u);
+                dst[q] = v;
+            }
+        }
+    }
+}
+
 }  // namespace gnnb
 
 using namespace gnnb;
@@ -538,6 +599,18 @@ int gnnb_pack_2bit(const int8_t* X, int64_t ldx, int64_t n, int64_t p, uint8_t* 
     int64_t blocks = (n * ((p + 3) / 4) + 255) / 256;
     int64_t cap = (int64_t)sm_count() * 32;
     pack_2bit_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(X, ldx, n, p, out, ldo, bad_flag);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+int gnnb_base3_to_2bit(const uint8_t* P3, int64_t ldi, int64_t n, int64_t p, uint8_t* out, int64_t ldo, int32_t* bad_flag,
+                       void* stream) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(P3 && out && n >= 0 && p > 0 && ldi >= (p + 4) / 5 && ldo >= (p + 3) / 4, GNNB_E_BADARG, "base3_to_2bit: bad argument");
+    if (n == 0) return GNNB_OK;
+    int64_t blocks = (n * ((p + 79) / 80) + 255) / 256;
+    int64_t cap = (int64_t)sm_count() * 32;
+    base3_to_2bit_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(P3, ldi, n, p, out, ldo, bad_flag);
     GNNB_LAUNCH_CHECK();
     return GNNB_OK;
 }

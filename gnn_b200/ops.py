@@ -3,6 +3,7 @@ streams, autograd bookkeeping.  Every function launches hand-written sm_100a ker
 libgnn_b200.so and raises if the library or a B200 is missing -- there is no fallback path.
 """
 import ctypes
+import os
 import weakref
 from collections import OrderedDict
 
@@ -15,6 +16,7 @@ config = {
     "linear_precision": "auto",
     "knn_impl": 0,              # 0 = pick, 1 = dp4a tiles, 2 = tcgen05 int8 tiles
     "knn_query_block": 1 << 18,
+    "fork": os.environ.get("GNNB_FORK", "1") != "0",    # independent pieces of a backward pass on side streams (ops.Fork)
 }
 
 _launches = 0                   # C-ABI calls that enqueue kernels (bench.py reports it)
@@ -182,6 +184,44 @@ def pack_2bit(X):
         _call("gnnb_pack_2bit", _p(X), X.stride(0), n, p, _p(out), out.stride(0), _p(bad), _stream())
     if int(bad.item()):
         raise ValueError("2-bit packing needs genotype codes in 0..3")
+    return out
+
+
+def base3_stride(p):
+    """Row stride in bytes of base-3 packed markers: five codes per byte, padded to 16 bytes."""
+    return ((p + 4) // 5 + 15) // 16 * 16
+
+
+def pack_base3(X):
+    """int8 codes 0..2 on the GPU -> base-3 packed uint8 [n, base3_stride(p)] (five codes per byte: the host / PCIe form).
+    Set-up only (index arithmetic in torch); raises if a code is outside 0..2 (synchronises)."""
+    _rows_ok(X)
+    n, p = X.shape
+    if n and (int(X.min()) < 0 or int(X.max()) > 2):
+        raise ValueError("base-3 packing needs genotype codes in 0..2")
+    q = (p + 4) // 5
+    out = torch.zeros((n, base3_stride(p)), dtype=torch.uint8, device=X.device)
+    weights = torch.tensor([1, 3, 9, 27, 81], dtype=torch.int32, device=X.device)
+    for r0 in range(0, n, 8192):
+        blk = torch.zeros((min(n, r0 + 8192) - r0, q * 5), dtype=torch.int32, device=X.device)
+        blk[:, :p] = X[r0:r0 + 8192]
+        out[r0:r0 + 8192, :q] = (blk.view(-1, q, 5) * weights).sum(dim=2).to(torch.uint8)
+    return out
+
+
+def unpack_base3(P3, p, out=None):
+    """base-3 packed markers on the GPU -> 2-bit packed uint8 [n, packed_stride(p)] (what the projection kernels read)."""
+    _need_cuda(P3)
+    if P3.dtype != torch.uint8 or P3.dim() != 2 or P3.stride(1) != 1:
+        raise _lib.GnnbError("base-3 packed markers must be a 2-D uint8 tensor with unit column stride")
+    n = P3.shape[0]
+    if out is None:
+        out = torch.empty((n, packed_stride(p)), dtype=torch.uint8, device=P3.device)
+        if packed_stride(p) > (p + 3) // 4:
+            out[:, (p + 3) // 4:] = 0
+    with torch.cuda.device(P3.device):
+        _declare(bytes=float(n * ((p + 4) // 5) + n * ((p + 3) // 4)))
+        _call("gnnb_base3_to_2bit", _p(P3), P3.stride(0), n, p, _p(out), out.stride(0), None, _stream())
     return out
 
 
@@ -697,6 +737,9 @@ class Fork:
     streams per device so that two forks can be in flight at once."""
 
     def __init__(self, fn, reads=(), slot=0):
+        if not config["fork"]:                                   # A/B switch: run in line on the main stream
+            self.side, self.out = None, fn()
+            return
         self.main = torch.cuda.current_stream()
         dev = self.main.device_index
         key = (dev, slot)
@@ -712,6 +755,8 @@ class Fork:
                 t.record_stream(side)
 
     def join(self):
+        if self.side is None:
+            return self.out
         self.main.wait_stream(self.side)
         outs = self.out if isinstance(self.out, (tuple, list)) else (self.out,)
         for t in outs:

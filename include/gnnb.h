@@ -60,6 +60,13 @@ int gnnb_i8_to_f32(const int8_t* X, int64_t ldx, int64_t n, int64_t p, float* ou
 int gnnb_unpack_2bit(const uint8_t* P, int64_t ldp, int64_t n, int64_t p, int8_t* out, int64_t ldo, void* stream);
 int gnnb_pack_2bit(const int8_t* X, int64_t ldx, int64_t n, int64_t p, uint8_t* out, int64_t ldo, int32_t* bad_flag,
                    void* stream);
+/* Base-3 marker packing -- the densest byte-aligned host / PCIe form of 0/1/2 genotypes: five codes per byte,
+ * value = c0 + 3 c1 + 9 c2 + 27 c3 + 81 c4 (bytes 243..255 are invalid and set *bad_flag).  gnnb_base3_to_2bit re-codes
+ * such rows (ldi bytes apart, >= ceil(p / 5)) into the 2-bit form of gnnb_pack_2bit (ldo bytes apart, >= ceil(p / 4);
+ * bits past the last code of a row are zero) that the projection kernels read.  No reference counterpart (the reference
+ * keeps markers as float64 in a DataFrame, load.py:182-187). */
+int gnnb_base3_to_2bit(const uint8_t* P3, int64_t ldi, int64_t n, int64_t p, uint8_t* out, int64_t ldo, int32_t* bad_flag,
+                       void* stream);
 /* `scaled=True` (load.py:45-48; load_ensembles2.py:150-157): per column x -= mean, x /= std (ddof 1), NaN -> 0, with
  * pandas' arithmetic (exact mean; two-pass variance summed in numpy's pairwise order), so the float64 output equals
  * `df_x.values` of the reference bit for bit on integer-coded markers.  out64 feeds gnnb_knn_f64, out32 is `x`

@@ -50,3 +50,24 @@ def test_pack_unpack_2bit_round_trip(n, p):
         ops.pack_2bit(torch.full((2, 8), 5, dtype=torch.int8, device="cuda"))
     with pytest.raises(ValueError):
         ops.pack_2bit_host(np.full((2, 8), -1, dtype=np.int8))
+
+
+@pytest.mark.parametrize("n,p", [(3, 1), (5, 79), (4, 80), (7, 81), (33, 5003), (64, 50000), (300, 1279)])
+def test_base3_host_format_recodes_to_the_2bit_form(n, p):
+    """Five 0/1/2 codes per byte across PCIe, re-coded on the device into the 2-bit form the projection kernels read: equal,
+    byte for byte (padding included), to packing the int8 codes directly."""
+    X = torch.from_numpy(synth.genotypes(n, p, seed=n * 1000 + p)).cuda()
+    P3 = ops.pack_base3(X)
+    assert P3.shape == (n, ops.base3_stride(p)) and int(P3.max()) <= 242
+    # the host side of the format, restated in numpy
+    Xh = X.cpu().numpy().astype(np.int64)
+    q = (p + 4) // 5
+    padded = np.zeros((n, q * 5), dtype=np.int64)
+    padded[:, :p] = Xh
+    want = (padded.reshape(n, q, 5) * np.array([1, 3, 9, 27, 81])).sum(axis=2)
+    assert np.array_equal(P3[:, :q].cpu().numpy(), want)
+    got = ops.unpack_base3(P3, p)
+    assert torch.equal(got, ops.pack_2bit(X))
+    assert torch.equal(ops.unpack_2bit(got, p), X)
+    with pytest.raises(ValueError):
+        ops.pack_base3(torch.full((2, 7), 3, dtype=torch.int8, device="cuda"))
