@@ -54,7 +54,7 @@ class FlatGrads:
     the next range runs (``ops.linear_bwd_w_ranges``).  Everything else is the small tail.  Without a sink layer the
     buffer is zeroed and reduced in one piece."""
 
-    def __init__(self, params, sink_layer=None, world=1, group=None):
+    def __init__(self, params, sink_layer=None, world=1, group=None, nvls=True):
         params = [p for p in params if p.requires_grad]
         head = []
         if sink_layer is not None and getattr(sink_layer, "bias", None) is not None:
@@ -63,7 +63,11 @@ class FlatGrads:
         self.params = params
         total = sum(p.numel() for p in self.params)
         dev = self.params[0].device
-        self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.nvls, self.nvls_error = None, None
+        if int(world) > 1 and nvls and dev.type == "cuda" and dist.is_initialized() and dist.get_backend(group) == "nccl":
+            self._try_symmetric(total, dev, int(world), group)
+        if self.nvls is None:
+            self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
         off = 0
         for p in self.params:
             p.grad = self.flat[off:off + p.numel()].view_as(p)
@@ -77,13 +81,44 @@ class FlatGrads:
             self.tail = self.flat[self.w_numel + head[1].numel():]      # what autograd still accumulates into
             sink_layer.grad_sink = self
 
+    # ---- averaging through the NVSwitch -------------------------------------------------------------------------------
+    def _try_symmetric(self, total, dev, world, group):
+        """Put the flat buffer into ONE symmetric allocation mapped through a multicast object on all ranks, so that the
+        step's gradient averaging is a single pass of our own multimem kernel (csrc/comm.cu: the switch adds the replicas in
+        flight) between two cross-GPU barriers, instead of a library all-reduce.  Falls back to NCCL (reason kept in
+        ``nvls_error``) where symmetric memory or multicast is unavailable.  Collective: every rank must construct it."""
+        try:
+            import torch.distributed._symmetric_memory as symm
+            pg = dist.group.WORLD if group is None else group
+            padded = (total + 4 * world - 1) // (4 * world) * (4 * world)
+            buf = symm.empty(padded, dtype=torch.float32, device=dev)
+            handle = symm.rendezvous(buf, pg.group_name)
+            ok = torch.tensor([1 if (handle.has_multicast_support and int(handle.multicast_ptr) != 0) else 0], device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            if not int(ok):
+                raise RuntimeError("no multicast support for symmetric memory on this box")
+            buf.zero_()
+            self.nvls = (handle, buf, int(handle.multicast_ptr), padded, dist.get_rank(group))
+            self.flat = buf[:total]
+        except Exception as exc:                                  # noqa: BLE001 -- NCCL is always available
+            self.nvls, self.nvls_error = None, f"{type(exc).__name__}: {str(exc)[:200]}"
+
+    def _nvls_mean(self):
+        import ctypes
+        from . import ops
+        handle, buf, mc_ptr, padded, rank = self.nvls
+        handle.barrier(channel=0)                                 # every rank's gradients are written
+        with torch.cuda.device(buf.device):
+            ops._call("gnnb_allreduce_mean_multimem", ctypes.c_void_p(mc_ptr), padded, rank, self.world, 0, ops._stream())
+        handle.barrier(channel=1)                                 # every slice has been delivered everywhere
+
     # ---- called by the sink layer's backward (networks/gcn_conv.py) -------------------------------------------------
     def write(self, layer, x, d_h):
         """dW = d_h^T x of the sink layer written in place (the layer's backward has already put db into ``bias.grad``);
         all-reduces started range by range."""
         from . import ops
         w = layer.lin.weight
-        many = self.world > 1
+        many = self.world > 1 and self.nvls is None               # NVLS path: one pass over the whole buffer after the backward
         if many:                 # db and the tail are final here: every other layer's backward ran before this one
             self._start(self.flat[self.w_numel:])
         h, p = w.shape
@@ -150,6 +185,9 @@ class FlatGrads:
 
     def allreduce_mean(self, world, group=None):
         if world <= 1:
+            return
+        if self.nvls is not None:
+            self._nvls_mean()
             return
         if self.pending:                         # the sink started everything during the backward pass
             self.finish()
@@ -325,6 +363,22 @@ def ring_pass(local, sizes, rank, world, fold, make_buffers):
             r.wait()
         if nxt is not None:
             cur, owner = nxt, nxt_owner
+
+
+def warm_up_collectives(rank, world, device):
+    """Create the communicator and its point-to-point / all-to-all connections before anything is timed: NCCL builds them
+    lazily on first use (seconds at 8 ranks), which would otherwise be charged to the first section that communicates."""
+    if world == 1:
+        return
+    t = torch.zeros(world * 4, dtype=torch.float32, device=device)
+    dist.all_reduce(t)
+    out = torch.empty(world * world * 4, dtype=torch.float32, device=device)
+    dist.all_gather_into_tensor(out, t)
+    dist.all_to_all_single(torch.empty_like(t), t)
+    ring_pass((t,), [t.shape[0]] * world, rank, world, lambda owner, block: None,
+              lambda rows: (torch.empty(rows, dtype=torch.float32, device=device),))
+    torch.cuda.synchronize()
+    dist.barrier()
 
 
 def knn_ring(X_local, row0, n_total, k, rank, world, extra_local=None, impl=None):

@@ -226,6 +226,15 @@ int gnnb_colsum(const float* A, int64_t lda, int64_t n, int64_t F, float* out,
 #define GNNB_COLSUM_STATIC_MAX_F 512
 int gnnb_colsum_static(const float* A, int64_t lda, int64_t n, int64_t F, float* out, void* stream);
 
+/* ---- K9: gradient averaging across the GPUs of one box (no reference counterpart: the reference has no distributed
+ *      code) --------------------------------------------------------------------------------------- */
+/* In-place mean over `world` replicas of a float32 buffer through the NVSwitch: rank r pulls the sum of its 1/world slice
+ * with multimem.ld_reduce, scales it and pushes it to every replica with multimem.st.  `multicast_ptr` is the MULTICAST
+ * address of one symmetric allocation (16-byte aligned, n_floats % 4 == 0) mapped on all ranks.  The call only enqueues
+ * this rank's kernel: the caller must put a cross-GPU barrier before it (every rank's contribution is written) and after
+ * it (every slice has been delivered).  max_ctas > 0 bounds the grid (to run beside another kernel); 0 = one CTA per SM. */
+int gnnb_allreduce_mean_multimem(void* multicast_ptr, int64_t n_floats, int rank, int world, int max_ctas, void* stream);
+
 /* ---- subsampling -------------------------------------------------------------------------- */
 /* first_pos[v] = min{ e : S[e] == v } (INT64_MAX when v never occurs), S = the neighbour column of
  * the kNN edge list in row-major order, i.e. idx flattened -- the parallel half of

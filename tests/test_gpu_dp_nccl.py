@@ -48,7 +48,7 @@ def _worker(rank, world, port, out):
     ref = nets.create_network_two_no_conv_dropout(p, 1, internal_size=h, dropout=0.0).to(dev)
     parallel.broadcast_parameters(model)
     ref.load_state_dict(model.state_dict())
-    flat = parallel.FlatGrads(model.parameters(), sink_layer=parallel.first_genotype_layer(model), world=world)
+    flat = parallel.FlatGrads(model.parameters(), sink_layer=parallel.first_genotype_layer(model), world=world, nvls=False)
     flat.range_markers, flat.cut = 512, "every_wave"                  # four ranges at p = 2048: staged, overlapped reduces
     opt = torch.optim.Adam(model.parameters(), lr=1e-2)
     opt_ref = torch.optim.Adam(ref.parameters(), lr=1e-2)
@@ -66,6 +66,38 @@ def _worker(rank, world, port, out):
         opt_ref.step()
     for a, c in zip(model.parameters(), ref.parameters()):
         assert float((a - c).abs().max()) < 1e-5
+    # gradient averaging through the NVSwitch (our multimem kernel over a symmetric flat buffer) against NCCL's all-reduce
+    torch.manual_seed(1)
+    m2 = nets.create_network_two_no_conv_dropout(p, 1, internal_size=h, dropout=0.0).to(dev)
+    f2 = parallel.FlatGrads(m2.parameters(), sink_layer=parallel.first_genotype_layer(m2), world=world)
+    assert f2.nvls is not None, f2.nvls_error
+    for trial in range(3):
+        vals = torch.randn(f2.flat.numel(), device=dev, generator=torch.Generator(device=dev).manual_seed(10 * trial + rank))
+        f2.flat.copy_(vals)
+        want = vals.clone()
+        dist.all_reduce(want, op=dist.ReduceOp.AVG)
+        f2.allreduce_mean(world)
+        assert float((f2.flat - want).abs().max()) <= 1e-6 * float(want.abs().max())
+        both = [torch.empty_like(f2.flat) for _ in range(world)]
+        dist.all_gather(both, f2.flat.contiguous())
+        assert torch.equal(both[0], both[1])                      # replicas hold the same bits
+    # ... and a whole data-parallel step on that path (sink writes dW in place, one NVLS pass after the backward)
+    ref2 = nets.create_network_two_no_conv_dropout(p, 1, internal_size=h, dropout=0.0).to(dev)
+    parallel.broadcast_parameters(m2)
+    ref2.load_state_dict(m2.state_dict())
+    opt2 = torch.optim.Adam(m2.parameters(), lr=1e-2)
+    for step, b in enumerate(mine):
+        parallel.dp_step(m2, f2, opt2, graphs[b], world, lf, get_args_tuple)
+        ref2.zero_grad()
+        for r in range(world):
+            g = graphs[step * world + r]
+            (lf(ref2(*get_args_tuple(g)), g.y) / world).backward()
+        for (k, a), (_, c) in zip(m2.named_parameters(), ref2.named_parameters()):
+            err = float((a.grad - c.grad).abs().max() / c.grad.abs().max().clamp_min(1e-30))
+            assert err < 1e-5, ("nvls", step, k, err)
+        with torch.no_grad():
+            for a, c in zip(m2.parameters(), ref2.parameters()):
+                c.copy_(a)
     # row-sharded evaluation == the unsharded model, bit for bit
     test = graphs[3]
     whole = parallel.sharded_eval(model, test, 0, 1, get_args_tuple)
