@@ -60,8 +60,9 @@ def parse():
                          "contiguous: split_dataset row slices (no global graph)")
     ap.add_argument("--dp-cut", default="last_wave", choices=["last_wave", "every_wave", "none"],
                     help="where the first-layer weight gradient is cut for the overlapped all-reduce (parallel.FlatGrads._ranges)")
-    ap.add_argument("--allreduce", default="nvls", choices=["nvls", "nccl"],
-                    help="gradient averaging: our multimem kernel through the NVSwitch (falls back to NCCL where unavailable) or NCCL")
+    ap.add_argument("--allreduce", default="auto", choices=["auto", "p2p", "nvls", "nccl"],
+                    help="gradient averaging: our kernels over a symmetric flat buffer (p2p: NVLink loads / stores; nvls: multimem "
+                         "through the NVSwitch; both fall back to NCCL where symmetric memory is unavailable) or NCCL's all-reduce")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-agg-hbm", action="store_true", help="skip the aggregation measurement on the whole-frame graph")
     ap.add_argument("--cuda-graph", default="auto", choices=["auto", "on", "off"],
@@ -355,7 +356,7 @@ def run_ours(a):
     model = nets.create_network_two_no_conv_dropout(p, 1, internal_size=a.hidden, dropout=DROPOUT).to(dev)
     parallel.broadcast_parameters(model)
     flat = parallel.FlatGrads(model.parameters(), sink_layer=parallel.first_genotype_layer(model), world=world,
-                              nvls=a.allreduce == "nvls")
+                              averaging=a.allreduce)
     flat.cut = a.dp_cut
     opt = torch.optim.Adam(model.parameters(), lr=LR, fused=True, capturable=True)   # the update rule of main.py:318, one kernel
     loss_func = torch.nn.MSELoss()
@@ -554,7 +555,7 @@ def run_ours(a):
                    "update_rule": (f"one Adam step per {world} subgraph(s): the gradients of the ranks' subgraphs are averaged, so an epoch "
                                    f"takes {steps_per_epoch} optimiser steps here and {B} at dp1 / in the reference's train_batches"),
                    "linear_precision": ops.config["linear_precision"], "cuda_graphs": bool(graphs_ok), "dp_cut": a.dp_cut,
-                   "gradient_averaging": ("multimem (NVLS) kernel over a symmetric flat buffer" if flat.nvls is not None else
+                   "gradient_averaging": (f"own {flat.averaging} kernel over a symmetric flat buffer (csrc/comm.cu)" if flat.nvls is not None else
                                           "NCCL all-reduce" + (f" (NVLS path unavailable: {flat.nvls_error})" if flat.nvls_error else "")) if world > 1 else "single GPU",
                    "cuda_graph_errors": graph_errors,
                    "resident_genotypes": "2-bit packed (12.5 GB at C5), expanded on chip by the projection kernels",

@@ -56,6 +56,7 @@ PROTOTYPES = {
     "gnnb_colsum": (_i32, [_vp, _i64, _i64, _i64, _vp, _vp, _sz, _vp]),
     "gnnb_colsum_static": (_i32, [_vp, _i64, _i64, _i64, _vp, _vp]),
     "gnnb_allreduce_mean_multimem": (_i32, [_vp, _i64, _i32, _i32, _i32, _vp]),
+    "gnnb_allreduce_mean_p2p": (_i32, [_vp, _i64, _i32, _i32, _i32, _vp]),
     "gnnb_first_occurrence": (_i32, [_vp, _i64, _i64, _vp, _vp]),
     "gnnb_partition_walk_host": (_i64, [_vp, _i64, _i64, _vp, _i64, _vp, _vp, _vp]),
 }

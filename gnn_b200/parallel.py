@@ -54,7 +54,7 @@ class FlatGrads:
     the next range runs (``ops.linear_bwd_w_ranges``).  Everything else is the small tail.  Without a sink layer the
     buffer is zeroed and reduced in one piece."""
 
-    def __init__(self, params, sink_layer=None, world=1, group=None, nvls=True):
+    def __init__(self, params, sink_layer=None, world=1, group=None, averaging="auto"):
         params = [p for p in params if p.requires_grad]
         head = []
         if sink_layer is not None and getattr(sink_layer, "bias", None) is not None:
@@ -64,7 +64,9 @@ class FlatGrads:
         total = sum(p.numel() for p in self.params)
         dev = self.params[0].device
         self.nvls, self.nvls_error = None, None
-        if int(world) > 1 and nvls and dev.type == "cuda" and dist.is_initialized() and dist.get_backend(group) == "nccl":
+        self.averaging = "p2p" if averaging == "auto" else averaging      # "p2p" | "nvls" (both: our kernels, symmetric memory) | "nccl"
+        if (int(world) > 1 and self.averaging in ("p2p", "nvls") and dev.type == "cuda" and dist.is_initialized()
+                and dist.get_backend(group) == "nccl"):
             self._try_symmetric(total, dev, int(world), group)
         if self.nvls is None:
             self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
@@ -83,22 +85,32 @@ class FlatGrads:
 
     # ---- averaging through the NVSwitch -------------------------------------------------------------------------------
     def _try_symmetric(self, total, dev, world, group):
-        """Put the flat buffer into ONE symmetric allocation mapped through a multicast object on all ranks, so that the
-        step's gradient averaging is a single pass of our own multimem kernel (csrc/comm.cu: the switch adds the replicas in
-        flight) between two cross-GPU barriers, instead of a library all-reduce.  Falls back to NCCL (reason kept in
-        ``nvls_error``) where symmetric memory or multicast is unavailable.  Collective: every rank must construct it."""
+        """Put the flat buffer into ONE symmetric allocation (every rank maps every replica, plus a multicast object over
+        all of them), so that the step's gradient averaging is a single pass of our own kernel (csrc/comm.cu) between two
+        cross-GPU barriers instead of a library all-reduce: "p2p" reads and writes the replicas over NVLink directly,
+        "nvls" lets the switch add them in flight (multimem).  Falls back to NCCL (reason kept in ``nvls_error``) where
+        symmetric memory is unavailable.  Collective: every rank must construct it."""
         try:
             import torch.distributed._symmetric_memory as symm
             pg = dist.group.WORLD if group is None else group
             padded = (total + 4 * world - 1) // (4 * world) * (4 * world)
             buf = symm.empty(padded, dtype=torch.float32, device=dev)
             handle = symm.rendezvous(buf, pg.group_name)
-            ok = torch.tensor([1 if (handle.has_multicast_support and int(handle.multicast_ptr) != 0) else 0], device=dev)
+            usable = len(handle.buffer_ptrs) == world and all(int(p) != 0 for p in handle.buffer_ptrs)
+            if self.averaging == "nvls":
+                usable = usable and bool(handle.has_multicast_support) and int(handle.multicast_ptr) != 0
+            ok = torch.tensor([1 if usable else 0], device=dev)
             dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
             if not int(ok):
-                raise RuntimeError("no multicast support for symmetric memory on this box")
+                raise RuntimeError("symmetric memory (peer mappings / multicast) is not usable on this box")
             buf.zero_()
-            self.nvls = (handle, buf, int(handle.multicast_ptr), padded, dist.get_rank(group))
+            off = int(getattr(handle, "offset", 0) or 0)
+            import ctypes
+            peers = (ctypes.c_uint64 * world)(*[int(p) + off for p in handle.buffer_ptrs])
+            if int(peers[dist.get_rank(group)]) != buf.data_ptr():
+                raise RuntimeError("symmetric buffer: the local mapping is not where the tensor lives")
+            mc = int(handle.multicast_ptr) + off if handle.has_multicast_support else 0
+            self.nvls = (handle, buf, mc, padded, dist.get_rank(group), peers)
             self.flat = buf[:total]
         except Exception as exc:                                  # noqa: BLE001 -- NCCL is always available
             self.nvls, self.nvls_error = None, f"{type(exc).__name__}: {str(exc)[:200]}"
@@ -106,10 +118,13 @@ class FlatGrads:
     def _nvls_mean(self):
         import ctypes
         from . import ops
-        handle, buf, mc_ptr, padded, rank = self.nvls
+        handle, buf, mc_ptr, padded, rank, peers = self.nvls
         handle.barrier(channel=0)                                 # every rank's gradients are written
         with torch.cuda.device(buf.device):
-            ops._call("gnnb_allreduce_mean_multimem", ctypes.c_void_p(mc_ptr), padded, rank, self.world, 0, ops._stream())
+            if self.averaging == "nvls":
+                ops._call("gnnb_allreduce_mean_multimem", ctypes.c_void_p(mc_ptr), padded, rank, self.world, 0, ops._stream())
+            else:
+                ops._call("gnnb_allreduce_mean_p2p", peers, padded, rank, self.world, 0, ops._stream())
         handle.barrier(channel=1)                                 # every slice has been delivered everywhere
 
     # ---- called by the sink layer's backward (networks/gcn_conv.py) -------------------------------------------------

@@ -234,6 +234,11 @@ int gnnb_colsum_static(const float* A, int64_t lda, int64_t n, int64_t F, float*
  * this rank's kernel: the caller must put a cross-GPU barrier before it (every rank's contribution is written) and after
  * it (every slice has been delivered).  max_ctas > 0 bounds the grid (to run beside another kernel); 0 = one CTA per SM. */
 int gnnb_allreduce_mean_multimem(void* multicast_ptr, int64_t n_floats, int rank, int world, int max_ctas, void* stream);
+/* The same mean over plain peer memory (NVLink loads / stores, no multicast object): peer_ptrs_host is a HOST array of the
+ * `world` device addresses of the replicas as mapped in THIS process (16-byte aligned; entry `rank` is the local one).
+ * Rank r reads its slice from every replica, adds in rank order, and writes the mean into every replica: all replicas
+ * end up with the same bits.  Same barrier contract as above.  world in {1, 2, 4, 8}. */
+int gnnb_allreduce_mean_p2p(const uint64_t* peer_ptrs_host, int64_t n_floats, int rank, int world, int max_ctas, void* stream);
 
 /* ---- subsampling -------------------------------------------------------------------------- */
 /* first_pos[v] = min{ e : S[e] == v } (INT64_MAX when v never occurs), S = the neighbour column of

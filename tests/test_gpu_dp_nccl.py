@@ -48,7 +48,7 @@ def _worker(rank, world, port, out):
     ref = nets.create_network_two_no_conv_dropout(p, 1, internal_size=h, dropout=0.0).to(dev)
     parallel.broadcast_parameters(model)
     ref.load_state_dict(model.state_dict())
-    flat = parallel.FlatGrads(model.parameters(), sink_layer=parallel.first_genotype_layer(model), world=world, nvls=False)
+    flat = parallel.FlatGrads(model.parameters(), sink_layer=parallel.first_genotype_layer(model), world=world, averaging="nccl")
     flat.range_markers, flat.cut = 512, "every_wave"                  # four ranges at p = 2048: staged, overlapped reduces
     opt = torch.optim.Adam(model.parameters(), lr=1e-2)
     opt_ref = torch.optim.Adam(ref.parameters(), lr=1e-2)
@@ -66,21 +66,23 @@ def _worker(rank, world, port, out):
         opt_ref.step()
     for a, c in zip(model.parameters(), ref.parameters()):
         assert float((a - c).abs().max()) < 1e-5
-    # gradient averaging through the NVSwitch (our multimem kernel over a symmetric flat buffer) against NCCL's all-reduce
-    torch.manual_seed(1)
-    m2 = nets.create_network_two_no_conv_dropout(p, 1, internal_size=h, dropout=0.0).to(dev)
-    f2 = parallel.FlatGrads(m2.parameters(), sink_layer=parallel.first_genotype_layer(m2), world=world)
-    assert f2.nvls is not None, f2.nvls_error
-    for trial in range(3):
-        vals = torch.randn(f2.flat.numel(), device=dev, generator=torch.Generator(device=dev).manual_seed(10 * trial + rank))
-        f2.flat.copy_(vals)
-        want = vals.clone()
-        dist.all_reduce(want, op=dist.ReduceOp.AVG)
-        f2.allreduce_mean(world)
-        assert float((f2.flat - want).abs().max()) <= 1e-6 * float(want.abs().max())
-        both = [torch.empty_like(f2.flat) for _ in range(world)]
-        dist.all_gather(both, f2.flat.contiguous())
-        assert torch.equal(both[0], both[1])                      # replicas hold the same bits
+    # gradient averaging by our own kernels over a symmetric flat buffer (NVLink peer loads / stores, and multimem through
+    # the NVSwitch) against NCCL's all-reduce; all replicas must end up with the same bits
+    for mode in ("nvls", "p2p"):
+        torch.manual_seed(1)
+        m2 = nets.create_network_two_no_conv_dropout(p, 1, internal_size=h, dropout=0.0).to(dev)
+        f2 = parallel.FlatGrads(m2.parameters(), sink_layer=parallel.first_genotype_layer(m2), world=world, averaging=mode)
+        assert f2.nvls is not None and f2.averaging == mode, f2.nvls_error
+        for trial in range(3):
+            vals = torch.randn(f2.flat.numel(), device=dev, generator=torch.Generator(device=dev).manual_seed(10 * trial + rank))
+            f2.flat.copy_(vals)
+            want = vals.clone()
+            dist.all_reduce(want, op=dist.ReduceOp.AVG)
+            f2.allreduce_mean(world)
+            assert float((f2.flat - want).abs().max()) <= 1e-6 * float(want.abs().max()), mode
+            both = [torch.empty_like(f2.flat) for _ in range(world)]
+            dist.all_gather(both, f2.flat.contiguous())
+            assert torch.equal(both[0], both[1]), mode            # replicas hold the same bits
     # ... and a whole data-parallel step on that path (sink writes dW in place, one NVLS pass after the backward)
     ref2 = nets.create_network_two_no_conv_dropout(p, 1, internal_size=h, dropout=0.0).to(dev)
     parallel.broadcast_parameters(m2)
