@@ -63,6 +63,7 @@ def parse():
     ap.add_argument("--allreduce", default="auto", choices=["auto", "p2p", "nvls", "nccl"],
                     help="gradient averaging: our kernels over a symmetric flat buffer (p2p: NVLink loads / stores; nvls: multimem "
                          "through the NVSwitch; both fall back to NCCL where symmetric memory is unavailable) or NCCL's all-reduce")
+    ap.add_argument("--epochs-per-step", type=int, default=0, help="0 = as many as make the timed region ~1 s (default); N = exactly N")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-agg-hbm", action="store_true", help="skip the aggregation measurement on the whole-frame graph")
     ap.add_argument("--cuda-graph", default="auto", choices=["auto", "on", "off"],
@@ -415,7 +416,7 @@ def run_ours(a):
     if a.cuda_graph == "on" and not graphs_ok:
         raise RuntimeError(f"CUDA-graph capture failed: {graph_errors}")
     probe_ms, _ = timed(epoch, 1)
-    epochs_per_step = max(1, int(math.ceil(1000.0 / max(1e-3, probe_ms * a.steps))))       # timed region >= ~1 s at every N
+    epochs_per_step = a.epochs_per_step or max(1, int(math.ceil(1000.0 / max(1e-3, probe_ms * a.steps))))   # timed region >= ~1 s at every N
 
     def step():
         out = None
