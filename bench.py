@@ -450,7 +450,8 @@ def run_ours(a):
             hx = torch.empty(x3.shape, dtype=x3.dtype).pin_memory()
             hx.copy_(x3)
             del x3
-            host.append((hx, g.edge_index.cpu().pin_memory(), g.edge_weight.cpu().pin_memory(), g.y.cpu().pin_memory()))
+            # node ids fit 32 bits: the edge list crosses PCIe as int32 and is widened to the int64 the operator takes on the device
+            host.append((hx, g.edge_index.to(torch.int32).cpu().pin_memory(), g.edge_weight.cpu().pin_memory(), g.y.cpu().pin_memory()))
         copy_stream = torch.cuda.Stream()
         main_stream = torch.cuda.current_stream(dev)
 
@@ -473,6 +474,7 @@ def run_ours(a):
                 nxt = stage(i + 1) if i + 1 < len(host) else None        # prefetch the next subgraph while this one trains
                 torch.cuda.current_stream().wait_event(ev)
                 d.x = ops.unpack_base3(d.x, p)                            # re-coded on the device into the form the projection reads
+                d.edge_index = d.edge_index.long()
                 loss = parallel.dp_step(model, flat, opt, d, world, loss_func, get_args_tuple)
                 out.append(float(loss))                                   # D2H read of the step's result
             out_test = parallel.sharded_eval(model, test, rank, world, get_args_tuple)
@@ -488,7 +490,7 @@ def run_ours(a):
         e2e = {"value": 1000.0 / ms_e2e, "unit": "epochs/s", "h2d_bytes_per_step": int(moved[0]),
                "d2h_bytes_per_step": int(moved[1]), "h2d_gbs_achieved": float(moved[0]) / (ms_e2e * 1e-3) / 1e9,
                "host_format": "base-3 packed genotypes (5 codes per byte) re-coded on the device to the 2-bit form the projection kernels read",
-               "note": "per epoch: every owned subgraph's genotypes + edge list + weights + phenotypes H2D from pinned "
+               "note": "per epoch: every owned subgraph's genotypes (base-3) + edge list (int32) + weights (float32) + phenotypes H2D from pinned "
                        "memory (prefetched one subgraph ahead on a copy stream), gcn_norm/CSR rebuilt per step, loss D2H per step"}
 
     # ---- graph-build record: the neighbour searches of the set-up, per shape (CUDA events around every gnnb_knn_i8 call)
