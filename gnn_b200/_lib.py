@@ -55,6 +55,10 @@ PROTOTYPES = {
     "gnnb_colsum_workspace_bytes": (_i32, [_i64, _psz]),
     "gnnb_colsum": (_i32, [_vp, _i64, _i64, _i64, _vp, _vp, _sz, _vp]),
     "gnnb_colsum_static": (_i32, [_vp, _i64, _i64, _i64, _vp, _vp]),
+    "gnnb_head_supported": (_i32, [_i64, _i64]),
+    "gnnb_head_workspace_bytes": (_i32, [_i64, _i64, _i64, _psz]),
+    "gnnb_head_fwd": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _vp]),
+    "gnnb_head_bwd": (_i32, [_vp, _i64, _vp, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _sz, _vp]),
     "gnnb_allreduce_mean_multimem": (_i32, [_vp, _i64, _i32, _i32, _i32, _vp]),
     "gnnb_allreduce_mean_p2p": (_i32, [_vp, _i64, _i32, _i32, _i32, _vp]),
     "gnnb_first_occurrence": (_i32, [_vp, _i64, _i64, _vp, _vp]),

@@ -1,0 +1,228 @@
+// K8: the dense head of the GCN factories, Linear(h -> out) with a handful of outputs (out = 1 in every shipped
+// configuration, gnn/networks/networks.py:273-274; gnn/main.py:438).  torch runs it as four library launches per step
+// (gemv forward, gemv + gemm-k1 + split-K reduce backward) plus a reduction for the bias; here it is one kernel each way.
+// Both are single passes over the [n, h] activations (HBM / L2 bound, ~6 MB at the C5 subgraph): a warp owns a row, a lane
+// a float4 of it; the weight rows live in shared memory.
+//   forward : out[r, o] = sum_c A[r, c] W[o, c] + b[o]
+//   backward: dA[r, c] = sum_o dOut[r, o] W[o, c];  dW[o, c] = sum_r dOut[r, o] A[r, c];  db[o] = sum_r dOut[r, o]
+// dW / db are accumulated per lane over the warp's rows, summed over the CTA's warps in warp order, written as one partial
+// per CTA, and the CTA that finishes last adds the partials in CTA order: the grid is a function of (n, device) only, so
+// the result is reproducible.
+#include "common.cuh"
+
+namespace gnnb {
+
+constexpr int HEAD_WARPS = 8, HEAD_THREADS = HEAD_WARPS * 32;
+
+template <int O, int T>
+__global__ void __launch_bounds__(HEAD_THREADS)
+head_fwd_kernel(const float* __restrict__ A, int64_t lda, int64_t n, int h, const float* __restrict__ W, int64_t ldw,
+                const float* __restrict__ bias, float* __restrict__ out, int64_t ldo) {
+    __shared__ __align__(16) float w_s[O * T * 128];
+    for (int i = threadIdx.x; i < O * T * 128; i += HEAD_THREADS) {
+        const int o = i / (T * 128), c = i % (T * 128);
+        w_s[i] = c < h ? W[(int64_t)o * ldw + c] : 0.f;
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool vec = (lda % 4 == 0) && ((reinterpret_cast<uintptr_t>(A) & 15) == 0);
+    for (int64_t r = (int64_t)blockIdx.x * HEAD_WARPS + warp; r < n; r += (int64_t)gridDim.x * HEAD_WARPS) {
+        const float* row = A + r * lda;
+        float acc[O];
+#pragma unroll
+        for (int o = 0; o < O; ++o) acc[o] = 0.f;
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const int c = t * 128 + lane * 4;
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c + 3 < h && vec) a = *reinterpret_cast<const float4*>(row + c);
+            else {
+                if (c < h) a.x = row[c];
+                if (c + 1 < h) a.y = row[c + 1];
+                if (c + 2 < h) a.z = row[c + 2];
+                if (c + 3 < h) a.w = row[c + 3];
+            }
+#pragma unroll
+            for (int o = 0; o < O; ++o) {
+                const float4 w = *reinterpret_cast<const float4*>(w_s + (o * T + t) * 128 + lane * 4);
+                acc[o] = fmaf(a.x, w.x, fmaf(a.y, w.y, fmaf(a.z, w.z, fmaf(a.w, w.w, acc[o]))));
+            }
+        }
+#pragma unroll
+        for (int o = 0; o < O; ++o)
+            for (int s = 16; s > 0; s >>= 1) acc[o] += __shfl_xor_sync(0xffffffffu, acc[o], s);
+        if (lane == 0) {
+#pragma unroll
+            for (int o = 0; o < O; ++o) out[r * ldo + o] = acc[o] + (bias ? bias[o] : 0.f);
+        }
+    }
+}
+
+// partial layout per CTA: [O][T * 128] weight-gradient columns, then [O] bias gradients
+template <int O, int T>
+__global__ void __launch_bounds__(HEAD_THREADS)
+head_bwd_kernel(const float* __restrict__ dOut, int64_t lddo, const float* __restrict__ A, int64_t lda, int64_t n, int h,
+                const float* __restrict__ W, int64_t ldw, float* __restrict__ dA, int64_t ldda,
+                float* __restrict__ dW, int64_t lddw, float* __restrict__ db, float* __restrict__ partial, unsigned* __restrict__ ticket) {
+    constexpr int PER = O * T * 128 + O;
+    __shared__ __align__(16) float w_s[O * T * 128];
+    __shared__ __align__(16) float red[HEAD_WARPS][PER];
+    __shared__ bool last;
+    for (int i = threadIdx.x; i < O * T * 128; i += HEAD_THREADS) {
+        const int o = i / (T * 128), c = i % (T * 128);
+        w_s[i] = c < h ? W[(int64_t)o * ldw + c] : 0.f;
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool vec_a = (lda % 4 == 0) && ((reinterpret_cast<uintptr_t>(A) & 15) == 0);
+    const bool vec_d = dA && (ldda % 4 == 0) && ((reinterpret_cast<uintptr_t>(dA) & 15) == 0);
+    float4 gw[O * T];
+    float gb[O];
+#pragma unroll
+    for (int i = 0; i < O * T; ++i) gw[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int o = 0; o < O; ++o) gb[o] = 0.f;
+    for (int64_t r = (int64_t)blockIdx.x * HEAD_WARPS + warp; r < n; r += (int64_t)gridDim.x * HEAD_WARPS) {
+        float g[O];
+#pragma unroll
+        for (int o = 0; o < O; ++o) { g[o] = dOut[r * lddo + o]; gb[o] += g[o]; }
+        const float* row = A + r * lda;
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const int c = t * 128 + lane * 4;
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c + 3 < h && vec_a) a = *reinterpret_cast<const float4*>(row + c);
+            else {
+                if (c < h) a.x = row[c];
+                if (c + 1 < h) a.y = row[c + 1];
+                if (c + 2 < h) a.z = row[c + 2];
+                if (c + 3 < h) a.w = row[c + 3];
+            }
+            float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int o = 0; o < O; ++o) {
+                const float4 w = *reinterpret_cast<const float4*>(w_s + (o * T + t) * 128 + lane * 4);
+                d.x = fmaf(g[o], w.x, d.x); d.y = fmaf(g[o], w.y, d.y); d.z = fmaf(g[o], w.z, d.z); d.w = fmaf(g[o], w.w, d.w);
+                float4& q = gw[o * T + t];
+                q.x = fmaf(g[o], a.x, q.x); q.y = fmaf(g[o], a.y, q.y); q.z = fmaf(g[o], a.z, q.z); q.w = fmaf(g[o], a.w, q.w);
+            }
+            if (dA) {
+                float* drow = dA + r * ldda;
+                if (c + 3 < h && vec_d) *reinterpret_cast<float4*>(drow + c) = d;
+                else {
+                    if (c < h) drow[c] = d.x;
+                    if (c + 1 < h) drow[c + 1] = d.y;
+                    if (c + 2 < h) drow[c + 2] = d.z;
+                    if (c + 3 < h) drow[c + 3] = d.w;
+                }
+            }
+        }
+    }
+    // warp partials -> shared memory -> one partial per CTA (warps added in warp order)
+#pragma unroll
+    for (int i = 0; i < O * T; ++i) *reinterpret_cast<float4*>(&red[warp][i * 128 + lane * 4]) = gw[i];
+    if (lane == 0) {
+#pragma unroll
+        for (int o = 0; o < O; ++o) red[warp][O * T * 128 + o] = gb[o];
+    }
+    __syncthreads();
+    float* mine = partial + (int64_t)blockIdx.x * PER;
+    for (int i = threadIdx.x; i < PER; i += HEAD_THREADS) {
+        float s = red[0][i];
+#pragma unroll
+        for (int w = 1; w < HEAD_WARPS; ++w) s += red[w][i];
+        mine[i] = s;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    for (int i = threadIdx.x; i < PER; i += HEAD_THREADS) {        // the last CTA: partials in CTA order
+        float s = 0.f;
+        for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(partial + (int64_t)b * PER + i);
+        if (i < O * T * 128) {
+            const int o = i / (T * 128), c = i % (T * 128);
+            if (c < h) dW[(int64_t)o * lddw + c] = s;
+        } else if (db) {
+            db[i - O * T * 128] = s;
+        }
+    }
+    if (threadIdx.x == 0) *ticket = 0;                             // ready for the next call
+}
+
+static int head_grid(int64_t n) {
+    int64_t blocks = (n + HEAD_WARPS * 4 - 1) / (HEAD_WARPS * 4);      // ~4 rows per warp at least
+    const int64_t cap = (int64_t)sm_count() * 4;
+    if (blocks > cap) blocks = cap;
+    return (int)(blocks < 1 ? 1 : blocks);
+}
+static int head_t(int64_t h) { return h <= 128 ? 1 : h <= 256 ? 2 : h <= 512 ? 4 : h <= 1024 ? 8 : 0; }
+static bool head_ok(int64_t h, int64_t o) { const int t = head_t(h); return t > 0 && o >= 1 && o <= 4 && o * t <= 8; }
+
+#define HEAD_DISPATCH(O_, T_, CALL)                                      \
+    if (o == O_ && t == T_) { CALL(O_, T_); launched = true; }
+#define HEAD_ALL(CALL)                                                   \
+    HEAD_DISPATCH(1, 1, CALL) HEAD_DISPATCH(1, 2, CALL) HEAD_DISPATCH(1, 4, CALL) HEAD_DISPATCH(1, 8, CALL) \
+    HEAD_DISPATCH(2, 1, CALL) HEAD_DISPATCH(2, 2, CALL) HEAD_DISPATCH(2, 4, CALL)                             \
+    HEAD_DISPATCH(3, 1, CALL) HEAD_DISPATCH(3, 2, CALL) HEAD_DISPATCH(4, 1, CALL) HEAD_DISPATCH(4, 2, CALL)
+
+}  // namespace gnnb
+
+using namespace gnnb;
+
+extern "C" {
+
+int gnnb_head_supported(int64_t h, int64_t out) { return head_ok(h, out) ? 1 : 0; }
+
+int gnnb_head_workspace_bytes(int64_t n, int64_t h, int64_t out, size_t* bytes) {
+    GNNB_REQUIRE(bytes && n >= 0 && head_ok(h, out), GNNB_E_BADARG, "head_workspace_bytes: bad argument (out <= 4, h <= 1024, out * ceil(h / 128) <= 8)");
+    const int t = head_t(h);
+    *bytes = 256 + (size_t)sm_count() * 4 * (size_t)(out * t * 128 + out) * sizeof(float);
+    return GNNB_OK;
+}
+
+int gnnb_head_fwd(const float* A, int64_t lda, int64_t n, int64_t h, const float* W, int64_t ldw, int64_t out_features,
+                  const float* bias, float* out, int64_t ldo, void* stream) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(A && W && out && n >= 0 && lda >= h && ldw >= h && ldo >= out_features, GNNB_E_BADARG, "head_fwd: bad argument");
+    GNNB_REQUIRE(head_ok(h, out_features), GNNB_E_UNSUPPORTED, "head_fwd: out <= 4, h <= 1024 and out * ceil(h / 128) <= 8 (got h = %lld, out = %lld)",
+                 (long long)h, (long long)out_features);
+    if (n == 0) return GNNB_OK;
+    const int o = (int)out_features, t = head_t(h), grid = head_grid(n);
+    bool launched = false;
+#define CALL_FWD(O_, T_) head_fwd_kernel<O_, T_><<<grid, HEAD_THREADS, 0, (cudaStream_t)stream>>>(A, lda, n, (int)h, W, ldw, bias, out, ldo)
+    HEAD_ALL(CALL_FWD)
+#undef CALL_FWD
+    GNNB_REQUIRE(launched, GNNB_E_UNSUPPORTED, "head_fwd: shape not instantiated");
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+int gnnb_head_bwd(const float* dOut, int64_t lddo, const float* A, int64_t lda, int64_t n, int64_t h, const float* W, int64_t ldw,
+                  int64_t out_features, float* dA, int64_t ldda, float* dW, int64_t lddw, float* db,
+                  void* workspace, size_t workspace_bytes, void* stream) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(dOut && A && W && dW && n >= 0 && lda >= h && ldw >= h && lddw >= h && lddo >= out_features && (!dA || ldda >= h), GNNB_E_BADARG,
+                 "head_bwd: bad argument");
+    GNNB_REQUIRE(head_ok(h, out_features), GNNB_E_UNSUPPORTED, "head_bwd: out <= 4, h <= 1024 and out * ceil(h / 128) <= 8 (got h = %lld, out = %lld)",
+                 (long long)h, (long long)out_features);
+    size_t need = 0;
+    int rc = gnnb_head_workspace_bytes(n, h, out_features, &need);
+    if (rc != GNNB_OK) return rc;
+    GNNB_REQUIRE(workspace && workspace_bytes >= need, GNNB_E_WORKSPACE, "head_bwd: workspace %zu < %zu bytes", workspace_bytes, need);
+    unsigned* ticket = reinterpret_cast<unsigned*>(align_up((size_t)(uintptr_t)workspace, 256));
+    float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(ticket) + 128);
+    GNNB_CUDA(cudaMemsetAsync(ticket, 0, sizeof(unsigned), (cudaStream_t)stream));
+    const int o = (int)out_features, t = head_t(h), grid = n == 0 ? 1 : head_grid(n);
+    bool launched = false;
+#define CALL_BWD(O_, T_) head_bwd_kernel<O_, T_><<<grid, HEAD_THREADS, 0, (cudaStream_t)stream>>>(dOut, lddo, A, lda, n, (int)h, W, ldw, dA, ldda, dW, lddw, db, partial, ticket)
+    HEAD_ALL(CALL_BWD)
+#undef CALL_BWD
+    GNNB_REQUIRE(launched, GNNB_E_UNSUPPORTED, "head_bwd: shape not instantiated");
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+}  // extern "C"

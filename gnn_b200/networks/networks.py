@@ -3,9 +3,10 @@ SURVEY.md 2.1 #3) and ``Ensemble``.  Same names, arguments and module order, so 
 The CNN / dense / k-hop factories of that file are outside the hot path and are not provided.
 """
 import torch
-from torch.nn import Dropout, Linear, ReLU
+from torch.nn import Dropout, ReLU
 
 from .gcn_conv import GCNConv
+from .head import Linear            # torch.nn.Linear whose few-output case runs on our kernels (same parameters and keys)
 from .sequential import Sequential
 
 _ARGS = 'x, edge_index, edge_weights?'

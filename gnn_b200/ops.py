@@ -685,6 +685,41 @@ def colsum(A, out=None):
     return out
 
 
+# --------------------------------------------------------------------------------------- K8: dense head
+def head_supported(h, out):
+    return bool(_lib.lib().gnnb_head_supported(int(h), int(out)))
+
+
+def head_fwd(A, W, bias=None):
+    """out = A . W^T + bias for a Linear(h -> out) with a handful of outputs (see include/gnnb.h)."""
+    _need_cuda(A, W)
+    A = A if (A.dtype == torch.float32 and A.stride(1) == 1) else A.float().contiguous()
+    W = W.contiguous()
+    n, h = A.shape
+    out = torch.empty((n, W.shape[0]), dtype=torch.float32, device=A.device)
+    with torch.cuda.device(A.device):
+        _call("gnnb_head_fwd", _p(A), A.stride(0), n, h, _p(W), W.stride(0), W.shape[0], _p(bias), _p(out), out.stride(0), _stream())
+    return out
+
+
+def head_bwd(d_out, A, W, need_dA=True, need_db=True):
+    """(dA or None, dW, db or None) of ``head_fwd``."""
+    _need_cuda(d_out, A, W)
+    A = A if (A.dtype == torch.float32 and A.stride(1) == 1) else A.float().contiguous()
+    d_out = d_out.contiguous()
+    W = W.contiguous()
+    n, h = A.shape
+    o = W.shape[0]
+    dA = torch.empty((n, h), dtype=torch.float32, device=A.device) if need_dA else None
+    dW = torch.empty((o, h), dtype=torch.float32, device=A.device)
+    db = torch.empty(o, dtype=torch.float32, device=A.device) if need_db else None
+    with torch.cuda.device(A.device):
+        ws = _ws(_ws_bytes("gnnb_head_workspace_bytes", n, h, o), A.device)
+        _call("gnnb_head_bwd", _p(d_out), d_out.stride(0), _p(A), A.stride(0), n, h, _p(W), W.stride(0), o,
+              _p(dA), h, _p(dW), h, _p(db), _p(ws), ws.numel(), _stream())
+    return dA, dW, db
+
+
 # --------------------------------------------------------------------------------------- subsampling
 def first_occurrence(idx):
     """first_pos[v] = first position of node v in the flattened neighbour lists."""

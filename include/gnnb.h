@@ -226,6 +226,21 @@ int gnnb_colsum(const float* A, int64_t lda, int64_t n, int64_t F, float* out,
 #define GNNB_COLSUM_STATIC_MAX_F 512
 int gnnb_colsum_static(const float* A, int64_t lda, int64_t n, int64_t F, float* out, void* stream);
 
+/* ---- K8: the dense head -------------------------------------------------------------------------------------------- */
+/* Replaces torch.nn.Linear(h, out) at the end of the GCN factories (gnn/networks/networks.py:273-274 and the other
+ * factories; out = 1 in every shipped configuration, gnn/main.py:438) and its autograd, for a handful of outputs:
+ *   fwd: out[r, o] = sum_c A[r, c] W[o, c] + bias[o]                       (bias may be NULL)
+ *   bwd: dA[r, c] = sum_o dOut[r, o] W[o, c]  (dA may be NULL);  dW[o, c] = sum_r dOut[r, o] A[r, c];  db[o] = sum_r dOut[r, o]
+ * float32, row-major; out <= 4, h <= 1024 and out * ceil(h / 128) <= 8 (gnnb_head_supported says so, 1 / 0); the sums over
+ * rows are taken in a fixed order (reproducible).  Workspace: gnnb_head_workspace_bytes. */
+int gnnb_head_supported(int64_t h, int64_t out);
+int gnnb_head_workspace_bytes(int64_t n, int64_t h, int64_t out, size_t* bytes);
+int gnnb_head_fwd(const float* A, int64_t lda, int64_t n, int64_t h, const float* W, int64_t ldw, int64_t out_features,
+                  const float* bias, float* out, int64_t ldo, void* stream);
+int gnnb_head_bwd(const float* dOut, int64_t lddo, const float* A, int64_t lda, int64_t n, int64_t h, const float* W, int64_t ldw,
+                  int64_t out_features, float* dA, int64_t ldda, float* dW, int64_t lddw, float* db,
+                  void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- K9: gradient averaging across the GPUs of one box (no reference counterpart: the reference has no distributed
  *      code) --------------------------------------------------------------------------------------- */
 /* In-place mean over `world` replicas of a float32 buffer through the NVSwitch: rank r pulls the sum of its 1/world slice

@@ -351,6 +351,47 @@ def test_gradient_sink_writes_the_first_layer_gradients_in_place(packed):
     assert rel_err(layer.lin.weight.grad, plain.nns[0].lin.weight.grad) < 1e-5
 
 
+@pytest.mark.parametrize("n,h,o", [(15625, 100, 1), (1000, 100, 3), (77, 128, 4), (500, 300, 1), (64, 1024, 1), (10, 7, 2), (1, 100, 1)])
+def test_head_linear_kernels_against_torch(n, h, o):
+    """networks.head.Linear (the dense head of every GCN factory): one kernel forward, one backward, against torch's own
+    Linear on the same parameters -- outputs and all three gradients, a strided input, reproducible sums."""
+    from gnn_b200.networks.head import Linear
+    torch.manual_seed(n + h)
+    mine = Linear(h, o).to(DEV)
+    ref = torch.nn.Linear(h, o).to(DEV)
+    ref.load_state_dict(mine.state_dict())
+    assert ops.head_supported(h, o)
+    base = torch.randn(n, h + 4, device=DEV)
+    x1 = base[:, :h].clone().requires_grad_(True)
+    x2 = base[:, :h].clone().requires_grad_(True)
+    wgt = torch.randn(n, o, device=DEV)
+    y1, y2 = mine(x1), ref(x2)
+    assert rel_err(y1, y2) < 1e-5
+    (y1 * wgt).sum().backward()
+    (y2 * wgt).sum().backward()
+    assert rel_err(x1.grad, x2.grad) < 1e-5
+    assert rel_err(mine.weight.grad, ref.weight.grad) < 1e-5 and rel_err(mine.bias.grad, ref.bias.grad) < 1e-5
+    # strided rows (a column slice of a wider matrix), no input gradient, same bits on a second run
+    g1 = mine.weight.grad.clone()
+    mine.zero_grad()
+    (mine(base[:, :h]) * wgt).sum().backward()
+    assert torch.equal(mine.weight.grad, g1)
+    no_bias = Linear(h, o, bias=False).to(DEV)
+    assert rel_err(no_bias(base[:, :h]), base[:, :h] @ no_bias.weight.t()) < 1e-5
+
+
+def test_head_linear_falls_back_outside_its_shapes():
+    from gnn_b200.networks.head import Linear
+    for h, o in ((2000, 1), (100, 8), (600, 3)):
+        assert not ops.head_supported(h, o)
+        m = Linear(h, o).to(DEV)
+        x = torch.randn(33, h, device=DEV)
+        assert rel_err(m(x), torch.nn.functional.linear(x, m.weight, m.bias)) < 1e-6
+    m = Linear(100, 1).to(DEV)
+    assert m(torch.randn(4, 5, 100, device=DEV)).shape == (4, 5, 1)           # 3-D input: torch's path
+    assert Linear(100, 1)(torch.randn(6, 100)).shape == (6, 1)                 # CPU tensors: torch's path
+
+
 @pytest.mark.parametrize("F", [4, 100, 256])
 def test_spmm_hub_rows_planned_and_unplanned(F):
     """A graph with hubs (rows of 300 .. 5000 entries): the planned path (tasks + last-arriver reduction) and the
