@@ -118,10 +118,20 @@ __device__ __forceinline__ void feature_scale(unsigned bits, float qmax, float& 
 // every NaN above +Inf, so a NaN anywhere in the row survives the reduction (fmaxf would drop it).
 __global__ void row_absmax_kernel(const float* __restrict__ in, int64_t ld, int64_t cols, unsigned* __restrict__ amax_bits) {
     const float* row = in + (int64_t)blockIdx.x * ld;
-    const int64_t per = (cols + gridDim.y - 1) / gridDim.y;
-    const int64_t c0 = (int64_t)blockIdx.y * per, c1 = c0 + per < cols ? c0 + per : cols;
+    const int64_t per = ((cols + gridDim.y - 1) / gridDim.y + 3) / 4 * 4;          // chunk starts stay 16-byte aligned
+    const int64_t c0 = (int64_t)blockIdx.y * per < cols ? (int64_t)blockIdx.y * per : cols, c1 = c0 + per < cols ? c0 + per : cols;
     unsigned m = 0;
-    for (int64_t c = c0 + threadIdx.x; c < c1; c += blockDim.x) m = max(m, __float_as_uint(row[c]) & 0x7FFFFFFFu);
+    if ((((reinterpret_cast<uintptr_t>(row) | (uintptr_t)(c0 * 4)) & 15) == 0) {        // 128-bit loads over the aligned body
+        const int64_t n4 = (c1 - c0) / 4;
+        const uint4* v = reinterpret_cast<const uint4*>(row + c0);
+        for (int64_t i = threadIdx.x; i < n4; i += blockDim.x) {
+            const uint4 q = v[i];
+            m = max(max(m, q.x & 0x7FFFFFFFu), max(max(q.y & 0x7FFFFFFFu, q.z & 0x7FFFFFFFu), q.w & 0x7FFFFFFFu));
+        }
+        for (int64_t c = c0 + 4 * n4 + threadIdx.x; c < c1; c += blockDim.x) m = max(m, __float_as_uint(row[c]) & 0x7FFFFFFFu);
+    } else {
+        for (int64_t c = c0 + threadIdx.x; c < c1; c += blockDim.x) m = max(m, __float_as_uint(row[c]) & 0x7FFFFFFFu);
+    }
     __shared__ unsigned red[32];
     for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
