@@ -65,8 +65,9 @@ head_bwd_kernel(const float* __restrict__ dOut, int64_t lddo, const float* __res
                 const float* __restrict__ W, int64_t ldw, float* __restrict__ dA, int64_t ldda,
                 float* __restrict__ dW, int64_t lddw, float* __restrict__ db, float* __restrict__ partial, unsigned* __restrict__ ticket) {
     constexpr int PER = O * T * 128 + O;
+    constexpr int PER_S = (PER + 3) / 4 * 4;                        // rows of `red` stay 16-byte aligned for the float4 stores
     __shared__ __align__(16) float w_s[O * T * 128];
-    __shared__ __align__(16) float red[HEAD_WARPS][PER];
+    __shared__ __align__(16) float red[HEAD_WARPS][PER_S];
     __shared__ bool last;
     for (int i = threadIdx.x; i < O * T * 128; i += HEAD_THREADS) {
         const int o = i / (T * 128), c = i % (T * 128);

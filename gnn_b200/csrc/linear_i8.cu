@@ -121,7 +121,7 @@ __global__ void row_absmax_kernel(const float* __restrict__ in, int64_t ld, int6
     const int64_t per = ((cols + gridDim.y - 1) / gridDim.y + 3) / 4 * 4;          // chunk starts stay 16-byte aligned
     const int64_t c0 = (int64_t)blockIdx.y * per < cols ? (int64_t)blockIdx.y * per : cols, c1 = c0 + per < cols ? c0 + per : cols;
     unsigned m = 0;
-    if ((((reinterpret_cast<uintptr_t>(row) | (uintptr_t)(c0 * 4)) & 15) == 0) {        // 128-bit loads over the aligned body
+    if (((reinterpret_cast<uintptr_t>(row) | (uintptr_t)(c0 * 4)) & 15) == 0) {        // 128-bit loads over the aligned body
         const int64_t n4 = (c1 - c0) / 4;
         const uint4* v = reinterpret_cast<const uint4*>(row + c0);
         for (int64_t i = threadIdx.x; i < n4; i += blockDim.x) {
