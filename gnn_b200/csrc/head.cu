@@ -26,34 +26,47 @@ head_fwd_kernel(const float* __restrict__ A, int64_t lda, int64_t n, int h, cons
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool vec = (lda % 4 == 0) && ((reinterpret_cast<uintptr_t>(A) & 15) == 0);
-    for (int64_t r = (int64_t)blockIdx.x * HEAD_WARPS + warp; r < n; r += (int64_t)gridDim.x * HEAD_WARPS) {
-        const float* row = A + r * lda;
-        float acc[O];
+    constexpr int R = 4;                                            // rows in flight per warp (one load each: latency-bound otherwise)
+    const int64_t warps = (int64_t)gridDim.x * HEAD_WARPS;
+    for (int64_t r0 = ((int64_t)blockIdx.x * HEAD_WARPS + warp) * R; r0 < n; r0 += warps * R) {
+        float4 a[R][T];
 #pragma unroll
-        for (int o = 0; o < O; ++o) acc[o] = 0.f;
+        for (int q = 0; q < R; ++q)
 #pragma unroll
-        for (int t = 0; t < T; ++t) {
-            const int c = t * 128 + lane * 4;
-            float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (c + 3 < h && vec) a = *reinterpret_cast<const float4*>(row + c);
-            else {
-                if (c < h) a.x = row[c];
-                if (c + 1 < h) a.y = row[c + 1];
-                if (c + 2 < h) a.z = row[c + 2];
-                if (c + 3 < h) a.w = row[c + 3];
+            for (int t = 0; t < T; ++t) {
+                const int c = t * 128 + lane * 4;
+                const int64_t r = r0 + q;
+                a[q][t] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (r < n) {
+                    const float* row = A + r * lda;
+                    if (c + 3 < h && vec) a[q][t] = *reinterpret_cast<const float4*>(row + c);
+                    else {
+                        if (c < h) a[q][t].x = row[c];
+                        if (c + 1 < h) a[q][t].y = row[c + 1];
+                        if (c + 2 < h) a[q][t].z = row[c + 2];
+                        if (c + 3 < h) a[q][t].w = row[c + 3];
+                    }
+                }
             }
 #pragma unroll
-            for (int o = 0; o < O; ++o) {
-                const float4 w = *reinterpret_cast<const float4*>(w_s + (o * T + t) * 128 + lane * 4);
-                acc[o] = fmaf(a.x, w.x, fmaf(a.y, w.y, fmaf(a.z, w.z, fmaf(a.w, w.w, acc[o]))));
+        for (int q = 0; q < R; ++q) {
+            float acc[O];
+#pragma unroll
+            for (int o = 0; o < O; ++o) acc[o] = 0.f;
+#pragma unroll
+            for (int t = 0; t < T; ++t)
+#pragma unroll
+                for (int o = 0; o < O; ++o) {
+                    const float4 w = *reinterpret_cast<const float4*>(w_s + (o * T + t) * 128 + lane * 4);
+                    acc[o] = fmaf(a[q][t].x, w.x, fmaf(a[q][t].y, w.y, fmaf(a[q][t].z, w.z, fmaf(a[q][t].w, w.w, acc[o]))));
+                }
+#pragma unroll
+            for (int o = 0; o < O; ++o)
+                for (int sft = 16; sft > 0; sft >>= 1) acc[o] += __shfl_xor_sync(0xffffffffu, acc[o], sft);
+            if (lane == 0 && r0 + q < n) {
+#pragma unroll
+                for (int o = 0; o < O; ++o) out[(r0 + q) * ldo + o] = acc[o] + (bias ? bias[o] : 0.f);
             }
-        }
-#pragma unroll
-        for (int o = 0; o < O; ++o)
-            for (int s = 16; s > 0; s >>= 1) acc[o] += __shfl_xor_sync(0xffffffffu, acc[o], s);
-        if (lane == 0) {
-#pragma unroll
-            for (int o = 0; o < O; ++o) out[r * ldo + o] = acc[o] + (bias ? bias[o] : 0.f);
         }
     }
 }
@@ -83,38 +96,59 @@ head_bwd_kernel(const float* __restrict__ dOut, int64_t lddo, const float* __res
     for (int i = 0; i < O * T; ++i) gw[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int o = 0; o < O; ++o) gb[o] = 0.f;
-    for (int64_t r = (int64_t)blockIdx.x * HEAD_WARPS + warp; r < n; r += (int64_t)gridDim.x * HEAD_WARPS) {
-        float g[O];
+    constexpr int R = 2;                                            // rows in flight per warp
+    const int64_t warps = (int64_t)gridDim.x * HEAD_WARPS;
+    for (int64_t r0 = ((int64_t)blockIdx.x * HEAD_WARPS + warp) * R; r0 < n; r0 += warps * R) {
+        float g[R][O];
+        float4 a[R][T];
 #pragma unroll
-        for (int o = 0; o < O; ++o) { g[o] = dOut[r * lddo + o]; gb[o] += g[o]; }
-        const float* row = A + r * lda;
+        for (int q = 0; q < R; ++q) {
+            const int64_t r = r0 + q;
 #pragma unroll
-        for (int t = 0; t < T; ++t) {
-            const int c = t * 128 + lane * 4;
-            float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (c + 3 < h && vec_a) a = *reinterpret_cast<const float4*>(row + c);
-            else {
-                if (c < h) a.x = row[c];
-                if (c + 1 < h) a.y = row[c + 1];
-                if (c + 2 < h) a.z = row[c + 2];
-                if (c + 3 < h) a.w = row[c + 3];
+            for (int o = 0; o < O; ++o) g[q][o] = r < n ? dOut[r * lddo + o] : 0.f;
+#pragma unroll
+            for (int t = 0; t < T; ++t) {
+                const int c = t * 128 + lane * 4;
+                a[q][t] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (r < n) {
+                    const float* row = A + r * lda;
+                    if (c + 3 < h && vec_a) a[q][t] = *reinterpret_cast<const float4*>(row + c);
+                    else {
+                        if (c < h) a[q][t].x = row[c];
+                        if (c + 1 < h) a[q][t].y = row[c + 1];
+                        if (c + 2 < h) a[q][t].z = row[c + 2];
+                        if (c + 3 < h) a[q][t].w = row[c + 3];
+                    }
+                }
             }
-            float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
 #pragma unroll
-            for (int o = 0; o < O; ++o) {
-                const float4 w = *reinterpret_cast<const float4*>(w_s + (o * T + t) * 128 + lane * 4);
-                d.x = fmaf(g[o], w.x, d.x); d.y = fmaf(g[o], w.y, d.y); d.z = fmaf(g[o], w.z, d.z); d.w = fmaf(g[o], w.w, d.w);
-                float4& q = gw[o * T + t];
-                q.x = fmaf(g[o], a.x, q.x); q.y = fmaf(g[o], a.y, q.y); q.z = fmaf(g[o], a.z, q.z); q.w = fmaf(g[o], a.w, q.w);
-            }
-            if (dA) {
-                float* drow = dA + r * ldda;
-                if (c + 3 < h && vec_d) *reinterpret_cast<float4*>(drow + c) = d;
-                else {
-                    if (c < h) drow[c] = d.x;
-                    if (c + 1 < h) drow[c + 1] = d.y;
-                    if (c + 2 < h) drow[c + 2] = d.z;
-                    if (c + 3 < h) drow[c + 3] = d.w;
+        for (int q = 0; q < R; ++q) {
+            const int64_t r = r0 + q;
+#pragma unroll
+            for (int o = 0; o < O; ++o) gb[o] += g[q][o];
+#pragma unroll
+            for (int t = 0; t < T; ++t) {
+                const int c = t * 128 + lane * 4;
+                float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int o = 0; o < O; ++o) {
+                    const float4 w = *reinterpret_cast<const float4*>(w_s + (o * T + t) * 128 + lane * 4);
+                    const float go = g[q][o];
+                    d.x = fmaf(go, w.x, d.x); d.y = fmaf(go, w.y, d.y); d.z = fmaf(go, w.z, d.z); d.w = fmaf(go, w.w, d.w);
+                    float4& acc = gw[o * T + t];
+                    acc.x = fmaf(go, a[q][t].x, acc.x); acc.y = fmaf(go, a[q][t].y, acc.y);
+                    acc.z = fmaf(go, a[q][t].z, acc.z); acc.w = fmaf(go, a[q][t].w, acc.w);
+                }
+                if (dA && r < n) {
+                    float* drow = dA + r * ldda;
+                    if (c + 3 < h && vec_d) *reinterpret_cast<float4*>(drow + c) = d;
+                    else {
+                        if (c < h) drow[c] = d.x;
+                        if (c + 1 < h) drow[c + 1] = d.y;
+                        if (c + 2 < h) drow[c + 2] = d.z;
+                        if (c + 3 < h) drow[c + 3] = d.w;
+                    }
                 }
             }
         }
@@ -140,14 +174,18 @@ head_bwd_kernel(const float* __restrict__ dOut, int64_t lddo, const float* __res
     __syncthreads();
     if (!last) return;
     __threadfence();
-    for (int i = threadIdx.x; i < PER; i += HEAD_THREADS) {        // the last CTA: partials in CTA order
-        float s = 0.f;
-        for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(partial + (int64_t)b * PER + i);
-        if (i < O * T * 128) {
-            const int o = i / (T * 128), c = i % (T * 128);
-            if (c < h) dW[(int64_t)o * lddw + c] = s;
-        } else if (db) {
-            db[i - O * T * 128] = s;
+    // the last CTA: a warp per output element, lanes stride over the CTAs' partials, then a fixed shuffle tree
+    for (int i = warp; i < PER; i += HEAD_WARPS) {
+        float sacc = 0.f;
+        for (unsigned b = lane; b < gridDim.x; b += 32) sacc += __ldcg(partial + (int64_t)b * PER + i);
+        for (int sft = 16; sft > 0; sft >>= 1) sacc += __shfl_xor_sync(0xffffffffu, sacc, sft);
+        if (lane == 0) {
+            if (i < O * T * 128) {
+                const int o = i / (T * 128), c = i % (T * 128);
+                if (c < h) dW[(int64_t)o * lddw + c] = sacc;
+            } else if (db) {
+                db[i - O * T * 128] = sacc;
+            }
         }
     }
     if (threadIdx.x == 0) *ticket = 0;                             // ready for the next call
@@ -155,7 +193,7 @@ head_bwd_kernel(const float* __restrict__ dOut, int64_t lddo, const float* __res
 
 static int head_grid(int64_t n) {
     int64_t blocks = (n + HEAD_WARPS * 4 - 1) / (HEAD_WARPS * 4);      // ~4 rows per warp at least
-    const int64_t cap = (int64_t)sm_count() * 4;
+    const int64_t cap = (int64_t)sm_count() * 2;
     if (blocks > cap) blocks = cap;
     return (int)(blocks < 1 ? 1 : blocks);
 }
@@ -180,7 +218,7 @@ int gnnb_head_supported(int64_t h, int64_t out) { return head_ok(h, out) ? 1 : 0
 int gnnb_head_workspace_bytes(int64_t n, int64_t h, int64_t out, size_t* bytes) {
     GNNB_REQUIRE(bytes && n >= 0 && head_ok(h, out), GNNB_E_BADARG, "head_workspace_bytes: bad argument (out <= 4, h <= 1024, out * ceil(h / 128) <= 8)");
     const int t = head_t(h);
-    *bytes = 256 + (size_t)sm_count() * 4 * (size_t)(out * t * 128 + out) * sizeof(float);
+    *bytes = 256 + (size_t)sm_count() * 2 * (size_t)(out * t * 128 + out) * sizeof(float);
     return GNNB_OK;
 }
 
