@@ -174,17 +174,25 @@ head_bwd_kernel(const float* __restrict__ dOut, int64_t lddo, const float* __res
     __syncthreads();
     if (!last) return;
     __threadfence();
-    // the last CTA: a warp per output element, lanes stride over the CTAs' partials, then a fixed shuffle tree
-    for (int i = warp; i < PER; i += HEAD_WARPS) {
+    // the last CTA: thread = (output element, half of the CTAs); consecutive threads read consecutive floats of a partial
+    // (coalesced: one SM must pull every partial, so the number of L2 sectors it requests is what this tail costs); each
+    // half is added in CTA order, then the two halves in half order -- a fixed tree
+    float* halves = &red[0][0];                                    // [2][128] of the staging area, free again by now
+    for (int base = 0; base < PER; base += 128) {
+        const int i = base + (threadIdx.x & 127), half = threadIdx.x >> 7;
         float sacc = 0.f;
-        for (unsigned b = lane; b < gridDim.x; b += 32) sacc += __ldcg(partial + (int64_t)b * PER + i);
-        for (int sft = 16; sft > 0; sft >>= 1) sacc += __shfl_xor_sync(0xffffffffu, sacc, sft);
-        if (lane == 0) {
+        if (i < PER)
+            for (unsigned b = half; b < gridDim.x; b += 2) sacc += __ldcg(partial + (int64_t)b * PER + i);
+        __syncthreads();
+        halves[half * 128 + (threadIdx.x & 127)] = sacc;
+        __syncthreads();
+        if (half == 0 && i < PER) {
+            const float total = halves[threadIdx.x & 127] + halves[128 + (threadIdx.x & 127)];
             if (i < O * T * 128) {
                 const int o = i / (T * 128), c = i % (T * 128);
-                if (c < h) dW[(int64_t)o * lddw + c] = sacc;
+                if (c < h) dW[(int64_t)o * lddw + c] = total;
             } else if (db) {
-                db[i - O * T * 128] = sacc;
+                db[i - O * T * 128] = total;
             }
         }
     }
