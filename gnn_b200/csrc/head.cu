@@ -96,7 +96,7 @@ head_bwd_kernel(const float* __restrict__ dOut, int64_t lddo, const float* __res
     for (int i = 0; i < O * T; ++i) gw[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int o = 0; o < O; ++o) gb[o] = 0.f;
-    constexpr int R = 2;                                            // rows in flight per warp
+    constexpr int R = (O * T <= 2) ? 4 : 2;                         // rows in flight per warp
     const int64_t warps = (int64_t)gridDim.x * HEAD_WARPS;
     for (int64_t r0 = ((int64_t)blockIdx.x * HEAD_WARPS + warp) * R; r0 < n; r0 += warps * R) {
         float g[R][O];
@@ -181,8 +181,10 @@ head_bwd_kernel(const float* __restrict__ dOut, int64_t lddo, const float* __res
     for (int base = 0; base < PER; base += 128) {
         const int i = base + (threadIdx.x & 127), half = threadIdx.x >> 7;
         float sacc = 0.f;
-        if (i < PER)
-            for (unsigned b = half; b < gridDim.x; b += 2) sacc += __ldcg(partial + (int64_t)b * PER + i);
+        if (i < PER) {
+#pragma unroll 16
+            for (unsigned b = half; b < gridDim.x; b += 2) sacc += __ldcg(partial + (int64_t)b * PER + i);      // 16 loads in flight
+        }
         __syncthreads();
         halves[half * 128 + (threadIdx.x & 127)] = sacc;
         __syncthreads();
@@ -201,7 +203,7 @@ head_bwd_kernel(const float* __restrict__ dOut, int64_t lddo, const float* __res
 
 static int head_grid(int64_t n) {
     int64_t blocks = (n + HEAD_WARPS * 4 - 1) / (HEAD_WARPS * 4);      // ~4 rows per warp at least
-    const int64_t cap = (int64_t)sm_count() * 2;
+    const int64_t cap = (int64_t)sm_count();                            // one partial per SM: the tail of the backward pass reads them all
     if (blocks > cap) blocks = cap;
     return (int)(blocks < 1 ? 1 : blocks);
 }

@@ -5,14 +5,19 @@ import torch
 from gnn_b200 import ops
 n, h, o = 15625, 100, 1
 A = torch.randn(n, h, device="cuda"); W = torch.randn(o, h, device="cuda"); b = torch.randn(o, device="cuda"); dO = torch.randn(n, o, device="cuda")
-def t(fn, it=200):
-    for _ in range(10): fn()
+def t(fn, it=50):
+    """device time per call: `it` calls captured in one CUDA graph (no host launch cost), replayed 5 times"""
+    for _ in range(3): fn()
     torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(it): fn()
+    g.replay(); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(it): fn()
+    for _ in range(5): g.replay()
     e1.record(); torch.cuda.synchronize()
-    return e0.elapsed_time(e1) / it * 1e3
+    return e0.elapsed_time(e1) / (5 * it) * 1e3
 def torch_bwd():
     return dO @ W, dO.t() @ A, dO.sum(0)
 print(f"head_fwd {t(lambda: ops.head_fwd(A, W, b)):.1f} us | torch linear {t(lambda: torch.nn.functional.linear(A, W, b)):.1f} us")
