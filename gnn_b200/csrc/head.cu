@@ -96,7 +96,7 @@ head_bwd_kernel(const float* __restrict__ dOut, int64_t lddo, const float* __res
     for (int i = 0; i < O * T; ++i) gw[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int o = 0; o < O; ++o) gb[o] = 0.f;
-    constexpr int R = (O * T <= 2) ? 4 : 2;                         // rows in flight per warp
+    constexpr int R = 2;                                            // rows in flight per warp
     const int64_t warps = (int64_t)gridDim.x * HEAD_WARPS;
     for (int64_t r0 = ((int64_t)blockIdx.x * HEAD_WARPS + warp) * R; r0 < n; r0 += warps * R) {
         float g[R][O];
@@ -203,7 +203,7 @@ head_bwd_kernel(const float* __restrict__ dOut, int64_t lddo, const float* __res
 
 static int head_grid(int64_t n) {
     int64_t blocks = (n + HEAD_WARPS * 4 - 1) / (HEAD_WARPS * 4);      // ~4 rows per warp at least
-    const int64_t cap = (int64_t)sm_count();                            // one partial per SM: the tail of the backward pass reads them all
+    const int64_t cap = (int64_t)sm_count() * 4;                        // 32 warps per SM: the row loop is latency-bound
     if (blocks > cap) blocks = cap;
     return (int)(blocks < 1 ? 1 : blocks);
 }
@@ -228,7 +228,7 @@ int gnnb_head_supported(int64_t h, int64_t out) { return head_ok(h, out) ? 1 : 0
 int gnnb_head_workspace_bytes(int64_t n, int64_t h, int64_t out, size_t* bytes) {
     GNNB_REQUIRE(bytes && n >= 0 && head_ok(h, out), GNNB_E_BADARG, "head_workspace_bytes: bad argument (out <= 4, h <= 1024, out * ceil(h / 128) <= 8)");
     const int t = head_t(h);
-    *bytes = 256 + (size_t)sm_count() * 2 * (size_t)(out * t * 128 + out) * sizeof(float);
+    *bytes = 256 + (size_t)sm_count() * 4 * (size_t)(out * t * 128 + out) * sizeof(float);
     return GNNB_OK;
 }
 
