@@ -64,6 +64,8 @@ def parse():
                     help="gradient averaging: our kernels over a symmetric flat buffer (p2p: NVLink loads / stores; nvls: multimem "
                          "through the NVSwitch; both fall back to NCCL where symmetric memory is unavailable) or NCCL's all-reduce")
     ap.add_argument("--epochs-per-step", type=int, default=0, help="0 = as many as make the timed region ~1 s (default); N = exactly N")
+    ap.add_argument("--optimizer", default="own", choices=["own", "torch"],
+                    help="Adam as gnn_b200.optim.Adam (csrc/adam.cu) or torch.optim.Adam(fused, capturable): same update rule")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-agg-hbm", action="store_true", help="skip the aggregation measurement on the whole-frame graph")
     ap.add_argument("--cuda-graph", default="auto", choices=["auto", "on", "off"],
@@ -382,7 +384,11 @@ def run_ours(a):
     flat = parallel.FlatGrads(model.parameters(), sink_layer=parallel.first_genotype_layer(model), world=world,
                               averaging=a.allreduce)
     flat.cut = a.dp_cut
-    opt = torch.optim.Adam(model.parameters(), lr=LR, fused=True, capturable=True)   # the update rule of main.py:318, one kernel
+    if a.optimizer == "own":
+        from gnn_b200.optim import Adam
+        opt = Adam(model.parameters(), lr=LR)                        # the update rule of main.py:318, one launch over the whole grid
+    else:
+        opt = torch.optim.Adam(model.parameters(), lr=LR, fused=True, capturable=True)
     loss_func = torch.nn.MSELoss()
     agg_hbm = None
     if "frame_lists" in info:
@@ -587,6 +593,7 @@ def run_ours(a):
                    "update_rule": (f"one Adam step per {world} subgraph(s): the gradients of the ranks' subgraphs are averaged, so an epoch "
                                    f"takes {steps_per_epoch} optimiser steps here and {B} at dp1 / in the reference's train_batches"),
                    "linear_precision": ops.config["linear_precision"], "cuda_graphs": bool(graphs_ok), "dp_cut": a.dp_cut,
+                   "optimizer": "gnn_b200.optim.Adam (csrc/adam.cu)" if a.optimizer == "own" else "torch.optim.Adam(fused=True, capturable=True)",
                    "gradient_averaging": (f"own {flat.averaging} kernel over a symmetric flat buffer (csrc/comm.cu)" if flat.nvls is not None else
                                           "NCCL all-reduce" + (f" (NVLS path unavailable: {flat.nvls_error})" if flat.nvls_error else "")) if world > 1 else "single GPU",
                    "cuda_graph_errors": graph_errors,

@@ -241,6 +241,13 @@ int gnnb_head_bwd(const float* dOut, int64_t lddo, const float* A, int64_t lda, 
                   int64_t out_features, float* dA, int64_t ldda, float* dW, int64_t lddw, float* db,
                   void* workspace, size_t workspace_bytes, void* stream);
 
+/* Replaces torch.optim.Adam(lr).step() (gnn/main.py:318: no weight decay, no amsgrad) for up to 8 float32 tensors in one
+ * launch: m = m + (g - m)(1 - b1); v = b2 v + (1 - b2) g^2; p -= (lr / (1 - b1^t)) m / (sqrt(v) / sqrt(1 - b2^t) + eps).
+ * The five arrays are HOST arrays of `count` device pointers / element counts; `step` is a DEVICE float32 holding the step
+ * count t of THIS update (the caller increments it before the call), so the update can be captured in a CUDA graph. */
+int gnnb_adam_step(int count, float* const* params, const float* const* grads, float* const* exp_avg, float* const* exp_avg_sq,
+                   const int64_t* numel, const float* step, float lr, float beta1, float beta2, float eps, void* stream);
+
 /* ---- K9: gradient averaging across the GPUs of one box (no reference counterpart: the reference has no distributed
  *      code) --------------------------------------------------------------------------------------- */
 /* In-place mean over `world` replicas of a float32 buffer through the NVSwitch: rank r pulls the sum of its 1/world slice
