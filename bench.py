@@ -66,6 +66,8 @@ def parse():
     ap.add_argument("--epochs-per-step", type=int, default=0, help="0 = as many as make the timed region ~1 s (default); N = exactly N")
     ap.add_argument("--optimizer", default="own", choices=["own", "torch"],
                     help="Adam as gnn_b200.optim.Adam (csrc/adam.cu) or torch.optim.Adam(fused, capturable): same update rule")
+    ap.add_argument("--overlap-eval", type=int, default=0, help="1: the eval forward of epoch e runs on a second stream, on a weight "
+                    "snapshot, beside the first steps of epoch e + 1")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-agg-hbm", action="store_true", help="skip the aggregation measurement on the whole-frame graph")
     ap.add_argument("--cuda-graph", default="auto", choices=["auto", "on", "off"],
@@ -405,8 +407,22 @@ def run_ours(a):
     pool = torch.cuda.graph_pool_handle() if use_graphs else None
     steps_g = [parallel.GraphedStep(lambda g=g: parallel.dp_step(model, flat, opt, g, world, loss_func, get_args_tuple),
                                     warmup=2, pool=pool, enabled=use_graphs) for g in batches]
-    eval_g = parallel.GraphedStep(lambda: loss_func(parallel.sharded_eval(model, test, rank, world, get_args_tuple), test.y),
-                                  warmup=2, pool=pool, enabled=use_graphs)
+    # The eval forward of an epoch only reads the epoch's final weights: with --overlap-eval it runs on a second stream, on a
+    # snapshot of the weights, while the next epoch's training steps already run (same results; the timed region still ends
+    # after the last eval).  Off: the eval forward runs in line, after the epoch's last step.
+    overlap = bool(a.overlap_eval)
+    eval_model = model
+    eval_stream = torch.cuda.Stream() if overlap else None
+    if overlap:
+        eval_model = nets.create_network_two_no_conv_dropout(p, 1, internal_size=a.hidden, dropout=DROPOUT).to(dev)
+        eval_model.load_state_dict(model.state_dict())
+        for q in eval_model.parameters():
+            q.requires_grad_(False)
+    eval_src = [p for p in model.parameters()]
+    eval_dst = [p for p in eval_model.parameters()]
+    eval_g = parallel.GraphedStep(lambda: loss_func(parallel.sharded_eval(eval_model, test, rank, world, get_args_tuple), test.y),
+                                  warmup=2, pool=None if overlap else pool, enabled=use_graphs)
+    pending = {"test_loss": None}
 
     def epoch(eager=False):
         losses = []
@@ -414,9 +430,23 @@ def run_ours(a):
             losses.append(parallel.dp_step(model, flat, opt, g, world, loss_func, get_args_tuple) if eager else s())
         if eager:
             test_loss = loss_func(parallel.sharded_eval(model, test, rank, world, get_args_tuple), test.y)
+        elif overlap:
+            main = torch.cuda.current_stream()
+            main.wait_stream(eval_stream)                    # the previous eval has read the snapshot
+            with torch.no_grad():
+                torch._foreach_copy_(eval_dst, eval_src)
+            eval_stream.wait_stream(main)
+            with torch.cuda.stream(eval_stream):
+                pending["test_loss"] = eval_g()
+            return torch.stack([v.reshape(()) for v in losses])
         else:
             test_loss = eval_g()
         return torch.stack([v.reshape(()) for v in losses] + [test_loss.reshape(())])
+
+    def drain():
+        """Everything the epochs started has finished on the main stream (the overlapped eval of the last epoch included)."""
+        if overlap:
+            torch.cuda.current_stream().wait_stream(eval_stream)
 
     def timed(fn, steps):
         barrier()
@@ -425,6 +455,7 @@ def run_ours(a):
         last = None
         for _ in range(steps):
             last = fn()
+        drain()
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -468,6 +499,8 @@ def run_ours(a):
     prof = ops.profiler.summary(by_shape=True)
     ops.profiler = None
     launches = launches_per_epoch * a.steps * epochs_per_step if graphs_ok else ops.launches() - launches0 - launches_per_epoch
+    if overlap and pending["test_loss"] is not None:
+        last = torch.cat([last.reshape(-1), pending["test_loss"].reshape(1)])
     losses_host = last.cpu().numpy()
 
     # ---- end to end: host buffers -> device every step, loss back to the host every step
@@ -592,7 +625,7 @@ def run_ours(a):
                    "optimizer_steps_per_epoch": steps_per_epoch, "subgraphs_per_s": B * 1000.0 / ms_per_epoch,
                    "update_rule": (f"one Adam step per {world} subgraph(s): the gradients of the ranks' subgraphs are averaged, so an epoch "
                                    f"takes {steps_per_epoch} optimiser steps here and {B} at dp1 / in the reference's train_batches"),
-                   "linear_precision": ops.config["linear_precision"], "cuda_graphs": bool(graphs_ok), "dp_cut": a.dp_cut,
+                   "linear_precision": ops.config["linear_precision"], "cuda_graphs": bool(graphs_ok), "dp_cut": a.dp_cut, "overlap_eval": overlap,
                    "optimizer": "gnn_b200.optim.Adam (csrc/adam.cu)" if a.optimizer == "own" else "torch.optim.Adam(fused=True, capturable=True)",
                    "gradient_averaging": (f"own {flat.averaging} kernel over a symmetric flat buffer (csrc/comm.cu)" if flat.nvls is not None else
                                           "NCCL all-reduce" + (f" (NVLS path unavailable: {flat.nvls_error})" if flat.nvls_error else "")) if world > 1 else "single GPU",
