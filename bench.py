@@ -66,7 +66,7 @@ def parse():
     ap.add_argument("--epochs-per-step", type=int, default=0, help="0 = as many as make the timed region ~1 s (default); N = exactly N")
     ap.add_argument("--optimizer", default="own", choices=["own", "torch"],
                     help="Adam as gnn_b200.optim.Adam (csrc/adam.cu) or torch.optim.Adam(fused, capturable): same update rule")
-    ap.add_argument("--overlap-eval", type=int, default=0, help="1: the eval forward of epoch e runs on a second stream, on a weight "
+    ap.add_argument("--overlap-eval", type=int, default=1, help="1 (default): the eval forward of epoch e runs on a second stream, on a weight "
                     "snapshot, beside the first steps of epoch e + 1")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-agg-hbm", action="store_true", help="skip the aggregation measurement on the whole-frame graph")
