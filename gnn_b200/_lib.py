@@ -28,6 +28,9 @@ PROTOTYPES = {
     "gnnb_knn_workspace_bytes": (_i32, [_i64, _i64, _i64, _i32, _i32, _psz]),
     "gnnb_knn_i8": (_i32, [_vp, _i64, _vp, _i64, _i64, _vp, _i64, _vp, _i64, _i64, _i64, _vp, _vp, _i32,
                            _i32, _vp, _vp, _i32, _i32, _vp, _sz, _vp]),
+    "gnnb_pack_fp4": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _vp, _vp]),
+    "gnnb_knn_fp4": (_i32, [_vp, _i64, _vp, _i64, _i64, _vp, _i64, _vp, _i64, _i64, _i64, _vp, _vp, _i32,
+                            _i32, _vp, _vp, _i32, _vp, _sz, _vp]),
     "gnnb_knn_f64": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _i64, _i64, _i64, _i32, _vp, _vp, _i32, _vp, _sz, _vp]),
     "gnnb_knn_insert_self": (_i32, [_vp, _vp, _i64, _i32, _i64, _vp]),
     "gnnb_unpack_2bit": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _vp]),

@@ -299,7 +299,7 @@ int knn_pick_splits(int64_t n_q, int64_t n_k, int tile_q, int tile_k) {
 int knn_tc_launch(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q, int64_t q_off,
                   const int8_t* K, int64_t ldk, const int64_t* sq_k, int64_t n_k, int64_t k_off, int64_t p,
                   const double* extra_q, const double* extra_k, int n_extra, int k, int n_splits,
-                  double* part_d2, int32_t* part_idx, cudaStream_t stream);
+                  double* part_d2, int32_t* part_idx, cudaStream_t stream, int fp4 = 0);
 bool knn_tc_supported(int64_t ldq, int64_t ldk, const void* Q, const void* K, int k);
 int knn_tc_splits(int64_t n_q, int64_t n_k);
 
@@ -376,6 +376,46 @@ int gnnb_knn_i8(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q, 
             }
             GNNB_LAUNCH_CHECK();
         }
+    }
+    knn_merge_kernel<<<(unsigned)((n_q + 127) / 128), 128, 0, stream>>>(part_d2, part_idx, n_splits, n_q, k, best_d2, best_idx,
+                                                                        merge, tmp_d2, tmp_idx);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+// The same search with both operands as e2m1-packed codes (gnnb_pack_fp4) on the FP4 tensor path (tcgen05 kind::mxf4).
+int gnnb_knn_fp4(const uint8_t* Q4, int64_t ldq, const int64_t* sq_q, int64_t n_q, int64_t q_off,
+                 const uint8_t* K4, int64_t ldk, const int64_t* sq_k, int64_t n_k, int64_t k_off,
+                 int64_t p,
+                 const double* extra_q, const double* extra_k, int n_extra,
+                 int k, double* best_d2, int32_t* best_idx, int merge,
+                 void* workspace, size_t workspace_bytes, void* stream_) {
+    GNNB_ENTER();
+    cudaStream_t stream = (cudaStream_t)stream_;
+    GNNB_REQUIRE(Q4 && K4 && sq_q && sq_k && best_d2 && best_idx, GNNB_E_BADARG, "knn_fp4: null pointer");
+    GNNB_REQUIRE(n_q >= 0 && n_k >= 0 && p > 0 && ldq >= (p + 1) / 2 && ldk >= (p + 1) / 2, GNNB_E_BADARG, "knn_fp4: bad shape");
+    GNNB_REQUIRE(k > 0 && k <= GNNB_KNN_MAX_K, GNNB_E_UNSUPPORTED, "knn_fp4: k = %d outside 1..%d", k, GNNB_KNN_MAX_K);
+    GNNB_REQUIRE(n_extra >= 0 && n_extra <= KNN_MAX_EXTRA, GNNB_E_UNSUPPORTED, "knn_fp4: at most %d float columns", KNN_MAX_EXTRA);
+    GNNB_REQUIRE(n_extra == 0 || (extra_q && extra_k), GNNB_E_BADARG, "knn_fp4: extra columns missing");
+    GNNB_REQUIRE(p <= 4000000, GNNB_E_UNSUPPORTED, "knn_fp4: p = %lld: the f32 dot product of 0/1/2 codes is exact up to 4 p < 2^24", (long long)p);
+    GNNB_REQUIRE(q_off + n_q < 2147483647LL && k_off + n_k < 2147483647LL, GNNB_E_UNSUPPORTED, "knn_fp4: indices exceed int32");
+    GNNB_REQUIRE(knn_tc_supported(ldq, ldk, Q4, K4, k), GNNB_E_UNSUPPORTED, "knn_fp4: needs 16-byte aligned packed rows (ld %% 16 == 0) and k <= 64");
+    if (n_q == 0) return GNNB_OK;
+    size_t need = 0;
+    gnnb_knn_workspace_bytes(n_q, n_k, p, k, 2, &need);
+    GNNB_REQUIRE(workspace && workspace_bytes >= need, GNNB_E_WORKSPACE, "knn_fp4: workspace %zu < %zu bytes", workspace_bytes, need);
+    const int n_splits = n_k == 0 ? 0 : knn_tc_splits(n_q, n_k);
+    Carver cv(workspace, workspace_bytes);
+    size_t per = (size_t)n_q * k;
+    double* part_d2 = cv.take<double>(per * (n_splits > 0 ? n_splits : 1));
+    int32_t* part_idx = cv.take<int32_t>(per * (n_splits > 0 ? n_splits : 1));
+    double* tmp_d2 = cv.take<double>(per);
+    int32_t* tmp_idx = cv.take<int32_t>(per);
+    GNNB_REQUIRE(cv.ok(), GNNB_E_WORKSPACE, "knn_fp4: workspace carve overflow");
+    if (n_splits > 0) {
+        int rc = knn_tc_launch(reinterpret_cast<const int8_t*>(Q4), ldq, sq_q, n_q, q_off, reinterpret_cast<const int8_t*>(K4), ldk, sq_k,
+                               n_k, k_off, p, extra_q, extra_k, n_extra, k, n_splits, part_d2, part_idx, stream, /*fp4*/ 1);
+        if (rc != GNNB_OK) return rc;
     }
     knn_merge_kernel<<<(unsigned)((n_q + 127) / 128), 128, 0, stream>>>(part_d2, part_idx, n_splits, n_q, k, best_d2, best_idx,
                                                                         merge, tmp_d2, tmp_idx);

@@ -79,12 +79,12 @@ __device__ inline Smem carve(uint8_t* raw, int stages, int k, bool extra) {
 
 // One accumulator tile (this thread's row x 256 key columns): distances, one compare per column, rare insertions.
 // Exact integer path (no float side columns): RowSelectorU64; otherwise the float64 RowSelector.
-template <bool HAS_EXTRA>
+template <bool HAS_EXTRA, int TN = BN, bool FP4 = false>
 __device__ __forceinline__ void scan_accumulator(uint32_t taddr_row, bool valid, long long sqq, const long long* __restrict__ sqk_b,
                                                  const double* __restrict__ ek_b, const double* eq_r, int n_extra, int ncols,
                                                  int64_t gi, int64_t gk0, RowSelector& sel, long long& thr_ll, RowSelectorU64& selu) {
 #pragma unroll 1
-    for (int chunk = 0; chunk < BN / 32; ++chunk) {
+    for (int chunk = 0; chunk < TN / 32; ++chunk) {
         uint32_t v[32];
         tmem_ld_32x32b_x32(taddr_row + chunk * 32, v);
         tmem_ld_wait();
@@ -92,7 +92,9 @@ __device__ __forceinline__ void scan_accumulator(uint32_t taddr_row, bool valid,
 #pragma unroll
             for (int c = 0; c < 32; ++c) {
                 const int col = chunk * 32 + c;
-                const long long di = sqq + sqk_b[col] - 2LL * (long long)(int)v[c];
+                // int8 tiles accumulate in s32; fp4 tiles in f32, where the dot product of 0/1/2 codes is an exact integer < 2^24
+                const long long dot = FP4 ? (long long)__uint_as_float(v[c]) : (long long)(int)v[c];
+                const long long di = sqq + sqk_b[col] - 2LL * dot;
                 if (HAS_EXTRA) {
                     if (di <= thr_ll && col < ncols) {
                         const int64_t gj = gk0 + col;
@@ -271,6 +273,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__
 // (distance + selection, one thread per query row) is the one-CTA epilogue unchanged.
 namespace {
 constexpr int B_HALF_BYTES = (BN / 2) * BKB, STAGE2_BYTES = A_BYTES + B_HALF_BYTES;
+constexpr int FP4_TN = 224;                               // key-tile width of the fp4 kernel: 2 x 224 accumulator + 64 scale columns of TMEM
 constexpr int QGP = 8;                                    // query-tile PAIRS per raster group (even: a quad = two pairs of one split)
 
 __host__ __device__ inline size_t smem_bytes2(int stages, int k, bool extra) {
@@ -298,7 +301,12 @@ __device__ inline Smem carve2(uint8_t* raw, int stages, int k, bool extra) {
 }
 }  // namespace
 
-template <bool HAS_EXTRA>
+// FP4 = true: the operands are e2m1-packed genotype codes (two per byte, gnnb_pack_fp4) and the tiles run on
+// tcgen05.mma kind::mxf4 -- K = 64 codes per instruction instead of 32, so a 128-byte k-block covers 256 markers and both
+// the tensor time and every byte stream halve.  Block scale factors are mandatory for that kind: a constant 2^0 (ue8m0
+// 0x7F) fills the tensor-memory columns behind the accumulators, which is why the key tile is TN = 224 wide there
+// (2 x 224 accumulator columns + 64 scale columns = 512).  Products and sums of 0/1/2 codes are exact in f32.
+template <bool HAS_EXTRA, int TN, bool FP4>
 __global__ void __launch_bounds__(256, 1)
 knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                const int64_t* __restrict__ sq_q, int64_t n_q, int64_t q_off,
@@ -326,10 +334,11 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
     const int q_tile = 2 * q_pair + (int)rank;                  // may be one past the last tile: TMA zero-fills, rows are skipped
 
     Smem sm = carve2(smem_raw, stages, k, HAS_EXTRA);
-    const int64_t n_ktiles = (n_k + BN - 1) / BN;
+    const int64_t n_ktiles = (n_k + TN - 1) / TN;
     const int64_t kt_begin = n_ktiles * split / n_splits;
     const int64_t kt_end = n_ktiles * (split + 1) / n_splits;
-    const int n_kb = (int)((p + BKB - 1) / BKB);
+    const int n_kb = (int)((p + BKB - 1) / BKB);                  // p = bytes per operand row (markers, or markers / 2 when FP4)
+    constexpr int TB_HALF = (TN / 2) * BKB, TSTAGE = A_BYTES + TB_HALF;   // this CTA's half of the key tile; one ring slot
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < stages; ++s) {
@@ -347,6 +356,23 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
     cluster_sync_all();                                         // barriers and TMEM of both CTAs exist from here on
     tc_fence_after_sync();
     const uint32_t tmem_base = *sm.tmem_ptr;
+    if (FP4) {
+        // kind::mxf4 multiplies every 32-code block by a ue8m0 scale factor read from tensor memory: all of them are 2^0.
+        // Warps 4-7 of both CTAs fill columns [2 TN, 2 TN + 64) of their 128 lanes with 0x7F bytes; the MMAs read the A
+        // scales from the first 32 of those columns and the B scales from the last 32, whatever the layout inside them.
+        if (warp >= 4) {
+            uint32_t ones[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) ones[i] = 0x7F7F7F7Fu;
+            const uint32_t lanes = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16);
+            tmem_st_32x32b_x32(lanes + 2 * TN, ones);
+            tmem_st_32x32b_x32(lanes + 2 * TN + 32, ones);
+            tmem_st_wait();
+        }
+        tc_fence_before_sync();
+        cluster_sync_all();                                     // the leader's MMAs read the scales of both CTAs
+        tc_fence_after_sync();
+    }
 
     if (warp == 0) {
         // ===================================================== TMA producer (both CTAs)
@@ -364,35 +390,36 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                         mbar_arrive_cluster(full_leader);
                         continue;
                     }
-                    if (leader) mbar_arrive_expect_tx(&sm.full[s], 2 * STAGE2_BYTES);
+                    if (leader) mbar_arrive_expect_tx(&sm.full[s], 2 * TSTAGE);
                     else        mbar_arrive_cluster(full_leader);
-                    uint8_t* a = sm.tiles + (size_t)s * STAGE2_BYTES;
+                    uint8_t* a = sm.tiles + (size_t)s * TSTAGE;
                     tma_load_2d_pair(a, &map_q, full_leader, kb * BKB, q_tile * BM);
                     if (quad)
-                        tma_load_2d_pair_multicast(a + A_BYTES + twin * (B_HALF_BYTES / 2), &map_k, &sm.full[s], kb * BKB,
-                                                   (int32_t)(kt * BN + rank * (BN / 2) + twin * (BN / 4)),
+                        tma_load_2d_pair_multicast(a + A_BYTES + twin * (TB_HALF / 2), &map_k, &sm.full[s], kb * BKB,
+                                                   (int32_t)(kt * TN + rank * (TN / 2) + twin * (TN / 4)),
                                                    (uint16_t)((1u << rank) | (1u << (rank + 2))));
                     else
-                        tma_load_2d_pair(a + A_BYTES, &map_k, full_leader, kb * BKB, (int32_t)(kt * BN + rank * (BN / 2)));
+                        tma_load_2d_pair(a + A_BYTES, &map_k, full_leader, kb * BKB, (int32_t)(kt * TN + rank * (TN / 2)));
                 }
             }
         }
     } else if (warp == 1 && leader) {
         // ===================================================== MMA issuer (one thread of the leader CTA)
         if (elect_one()) {
-            constexpr uint32_t idesc = make_idesc(/*S32*/ 2, /*int8*/ 1, 0, 0, 2 * BM, BN);
+            constexpr uint32_t idesc = FP4 ? make_idesc_mxf4(2 * BM, TN) : make_idesc(/*S32*/ 2, /*int8*/ 1, 0, 0, 2 * BM, TN);
+            const uint32_t tsf = tmem_base + 2 * TN;              // FP4: 64 columns of constant scale factors (see below)
             uint32_t it = 0, tile = 0;
             for (int64_t kt = kt_begin; kt < kt_end; ++kt, ++tile) {
                 const uint32_t b = tile & 1, tph = (tile >> 1) & 1;
                 mbar_wait(&sm.tempty[b], tph ^ 1);              // both epilogues have drained this accumulator
                 tc_fence_after_sync();
-                const uint32_t d_tmem = tmem_base + b * BN;
+                const uint32_t d_tmem = tmem_base + b * TN;
                 for (int kb = 0; kb < n_kb; ++kb, ++it) {
                     const int s = it % stages;
                     const uint32_t ph = (it / stages) & 1;
                     mbar_wait(&sm.full[s], ph);                 // the bytes of both CTAs have landed
                     tc_fence_after_sync();
-                    const uint32_t a_addr = smem_u32(sm.tiles + (size_t)s * STAGE2_BYTES);
+                    const uint32_t a_addr = smem_u32(sm.tiles + (size_t)s * TSTAGE);
                     const uint32_t b_addr = a_addr + A_BYTES;
                     if (KNN_ABLATE(2)) {
                         for (uint32_t c = 0; c < (quad ? 4u : 2u); ++c) mbar_arrive_cluster(mapa_u32(smem_u32(&sm.empty[s]), c));
@@ -402,7 +429,8 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                     for (int k4 = 0; k4 < BKB / 32; ++k4) {
                         const uint64_t da = make_smem_desc(a_addr + k4 * 32, 16, 1024);
                         const uint64_t db = make_smem_desc(b_addr + k4 * 32, 16, 1024);
-                        mma_i8_ss_pair(d_tmem, da, db, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+                        if (FP4) mma_mxf4_ss_pair(d_tmem, da, db, idesc, tsf, tsf + 32, (kb > 0 || k4 > 0) ? 1u : 0u);
+                        else     mma_i8_ss_pair(d_tmem, da, db, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
                     }
                     // (releasing slots two at a time to halve the commits was measured: 9.3 -> 10.9 ms, the loads need the slot early)
                     tc_commit_pair(&sm.empty[s], all_mask);     // frees the slot in both CTAs (and tells the twin pair in quad mode)
@@ -431,11 +459,11 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         uint32_t tile = 0;
         for (int64_t kt = kt_begin; kt < kt_end; ++kt, ++tile) {
             const uint32_t b = tile & 1, tph = (tile >> 1) & 1;
-            const int64_t k0 = kt * BN;
-            long long* sqk_b = sm.sqk + b * BN;
-            double* ek_b = sm.ek + (size_t)b * BN * KNN_MAX_EXTRA;
+            const int64_t k0 = kt * TN;
+            long long* sqk_b = sm.sqk + b * TN;
+            double* ek_b = sm.ek + (size_t)b * TN * KNN_MAX_EXTRA;
 #pragma unroll
-            for (int t = e; t < BN; t += EPI_THREADS) {
+            for (int t = e; t < TN; t += EPI_THREADS) {
                 const int64_t gk = k0 + t;
                 sqk_b[t] = (gk < n_k) ? sq_k[gk] : 0;
                 if (HAS_EXTRA)
@@ -449,8 +477,8 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                 else        mbar_arrive_cluster(mapa_u32(smem_u32(&sm.tempty[b]), lead_rank));
                 continue;
             }
-            const int ncols = (int)((n_k - k0) < BN ? (n_k - k0) : BN);
-            scan_accumulator<HAS_EXTRA>(tmem_base + ((uint32_t)(32 * wq) << 16) + b * BN, valid, sqq, sqk_b, ek_b, eq_r, n_extra,
+            const int ncols = (int)((n_k - k0) < TN ? (n_k - k0) : TN);
+            scan_accumulator<HAS_EXTRA, TN, FP4>(tmem_base + ((uint32_t)(32 * wq) << 16) + b * TN, valid, sqq, sqk_b, ek_b, eq_r, n_extra,
                                         ncols, gi, k_off + k0, sel, thr_ll, selu);
             tc_fence_before_sync();
             if (leader) mbar_arrive(&sm.tempty[b]);
@@ -476,7 +504,7 @@ bool knn_tc_supported(int64_t ldq, int64_t ldk, const void* Q, const void* K, in
 }
 
 int knn_tc_splits(int64_t n_q, int64_t n_k) {
-    int64_t q_tiles = (n_q + BM - 1) / BM, k_tiles = (n_k + BN - 1) / BN;
+    int64_t q_tiles = (n_q + BM - 1) / BM, k_tiles = (n_k + BN - 1) / BN;      // (the fp4 kernel has a few more, narrower key tiles: s <= k_tiles holds for it too)
     int64_t s;
     if (q_tiles >= QG) s = 8;                                   // ~QG x 8 = 144 co-resident CTAs share 18 Q tiles and 8 K ranges
     else s = (sm_count() + q_tiles - 1) / q_tiles;
@@ -489,7 +517,8 @@ int knn_tc_splits(int64_t n_q, int64_t n_k) {
 int knn_tc_launch(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q, int64_t q_off,
                   const int8_t* K, int64_t ldk, const int64_t* sq_k, int64_t n_k, int64_t k_off, int64_t p,
                   const double* extra_q, const double* extra_k, int n_extra, int k, int n_splits,
-                  double* part_d2, int32_t* part_idx, cudaStream_t stream) {
+                  double* part_d2, int32_t* part_idx, cudaStream_t stream, int fp4) {
+    // fp4 != 0: Q and K are e2m1-packed rows (gnnb_pack_fp4), ldq / ldk in bytes; p stays the marker count
     const int q_tiles = (int)((n_q + BM - 1) / BM);
     static int use_pair = -1, ablate = 0, quad = 1;
     if (use_pair < 0) {
@@ -506,12 +535,16 @@ int knn_tc_launch(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q
     // quads pay off on long K loops (15625 x 50000: 9.8 -> 9.3 ms); on short ones the lockstep of the two pairs costs more
     // than the shared key tile saves (65536 x 8192: 60 -> 65 ms)
     const int use_quad = quad >= 0 ? quad : (p >= 16384 ? 1 : 0);
+    if (fp4 && !(use_pair && q_tiles >= 2))
+        return fail(GNNB_E_UNSUPPORTED, "knn_fp4: needs at least 129 query rows (CTA-pair kernel)");
     if (use_pair && q_tiles >= 2) {
-        // CTA pairs: 256 queries x 256 keys per pair, each CTA stages its 128 queries and one half of the key tile
+        // CTA pairs: 256 queries x 256 (fp4: 224) keys per pair, each CTA stages its 128 queries and one half of the key tile
+        const int tn = fp4 ? FP4_TN : BN;
+        const int64_t k_bytes = fp4 ? (p + 1) / 2 : p;            // bytes of one operand row = extent of the contraction in memory
         CUtensorMap map_q, map_k;
-        int rc = make_tensor_map_2d(&map_q, Q, 1, (uint64_t)p, (uint64_t)n_q, (uint64_t)ldq, BKB, BM);
+        int rc = make_tensor_map_2d(&map_q, Q, 1, (uint64_t)k_bytes, (uint64_t)n_q, (uint64_t)ldq, BKB, BM);
         if (rc != GNNB_OK) return rc;
-        rc = make_tensor_map_2d(&map_k, K, 1, (uint64_t)p, (uint64_t)n_k, (uint64_t)ldk, BKB, use_quad ? BN / 4 : BN / 2);
+        rc = make_tensor_map_2d(&map_k, K, 1, (uint64_t)k_bytes, (uint64_t)n_k, (uint64_t)ldk, BKB, use_quad ? tn / 4 : tn / 2);
         if (rc != GNNB_OK) return rc;
         int stages = MAX_STAGES;
         while (stages > 2 && smem_bytes2(stages, k, extra) > 232448) --stages;
@@ -530,15 +563,20 @@ int knn_tc_launch(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q
         attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
         cfg.numAttrs = 1;
-        if (extra) {
-            GNNB_SET_DYN_SMEM(knn_tc2_kernel<true>, smem);
-            GNNB_CUDA(cudaLaunchKernelEx(&cfg, knn_tc2_kernel<true>, map_q, map_k, sq_q, n_q, q_off, sq_k, n_k, k_off, p, extra_q, extra_k,
-                                         n_extra, k, n_splits, q_pairs, stages, part_d2, part_idx, use_quad, ablate));
+#define KNN_LAUNCH2(EXTRA_, TN_, FP4_)                                                                                              \
+    do {                                                                                                                           \
+        GNNB_SET_DYN_SMEM((knn_tc2_kernel<EXTRA_, TN_, FP4_>), smem);                                                              \
+        GNNB_CUDA(cudaLaunchKernelEx(&cfg, knn_tc2_kernel<EXTRA_, TN_, FP4_>, map_q, map_k, sq_q, n_q, q_off, sq_k, n_k, k_off, k_bytes, \
+                                     extra_q, extra_k, n_extra, k, n_splits, q_pairs, stages, part_d2, part_idx, use_quad, ablate)); \
+    } while (0)
+        if (fp4) {
+            if (extra) KNN_LAUNCH2(true, FP4_TN, true);
+            else       KNN_LAUNCH2(false, FP4_TN, true);
         } else {
-            GNNB_SET_DYN_SMEM(knn_tc2_kernel<false>, smem);
-            GNNB_CUDA(cudaLaunchKernelEx(&cfg, knn_tc2_kernel<false>, map_q, map_k, sq_q, n_q, q_off, sq_k, n_k, k_off, p, extra_q, extra_k,
-                                         n_extra, k, n_splits, q_pairs, stages, part_d2, part_idx, use_quad, ablate));
+            if (extra) KNN_LAUNCH2(true, BN, false);
+            else       KNN_LAUNCH2(false, BN, false);
         }
+#undef KNN_LAUNCH2
         return GNNB_OK;
     }
     CUtensorMap map_q, map_k;

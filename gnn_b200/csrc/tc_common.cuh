@@ -182,6 +182,20 @@ __device__ __forceinline__ void mma_i8_ss_pair(uint32_t tmem_d, uint64_t desc_a,
         : "memory");
 }
 
+// CTA-pair MMA on e2m1 (FP4) operands, kind::mxf4: K = 64 four-bit elements (32 bytes) per instruction, f32 accumulators,
+// one ue8m0 scale factor per 32 elements of every A row / B row read from tensor memory at tsfa / tsfb (block32).
+__device__ __forceinline__ void mma_mxf4_ss_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t tsfa,
+                                                 uint32_t tsfb, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::mxf4.block_scale.block32 [%0], %1, %2, %3, [%5], [%6], p;\n\t"
+        "}\n"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(tsfa), "r"(tsfb)
+        : "memory");
+}
+
 // D[tmem] (+)= A[smem desc] * B[smem desc], issued by ONE thread
 __device__ __forceinline__ void mma_i8_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
@@ -273,6 +287,12 @@ __host__ __device__ constexpr uint32_t make_idesc(uint32_t c_format, uint32_t ab
                                                   uint32_t m, uint32_t n) {
     return (c_format << 4) | (ab_format << 7) | (ab_format << 10) | (a_mn_major << 15) | (b_mn_major << 16) | ((n >> 3) << 17) |
            ((m >> 4) << 24);
+}
+
+// Instruction descriptor of the block-scaled kinds (kind::mxf4 here): a_format [7,10) and b_format [10,13) = 1 (E2M1), both
+// operands K-major, n >> 3 at [17,23), scale format bit 23 = 1 (UE8M0), m >> 4 at [24,29), scale-factor ids 0, K = 64 (bit 31 = 0).
+__host__ __device__ constexpr uint32_t make_idesc_mxf4(uint32_t m, uint32_t n) {
+    return (1u << 7) | (1u << 10) | ((n >> 3) << 17) | (1u << 23) | ((m >> 4) << 24);
 }
 
 // ------------------------------------------------------------------------------------------ host: tensor maps

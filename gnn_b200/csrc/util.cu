@@ -513,6 +513,36 @@ base3_to_2bit_kernel(const uint8_t* __restrict__ in, int64_t ldi, int64_t n, int
     }
 }
 
+
+// ------------------------------------------------------------------------------------ e2m1 (FP4) operand form of the search
+// 0 / 1 / 2 are exact e2m1 values (nibbles 0b0000, 0b0010, 0b0100 = code << 1); two codes per byte, code 2 j in the low
+// nibble.  The FP4 tensor path of the neighbour search (kind::mxf4, twice the int8 rate) reads this form.  One thread = 16
+// codes = 8 output bytes; HBM-bound (1 B read + 0.5 B written per code).  Padding bytes up to ldo are zeroed (0.0).
+__global__ void pack_fp4_kernel(const int8_t* __restrict__ X, int64_t ldx, int64_t n, int64_t p, uint8_t* __restrict__ out, int64_t ldo,
+                                int32_t* __restrict__ bad_flag) {
+    const int64_t groups = ldo / 8, total = n * groups;                // ldo is a multiple of 16
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / groups, c0 = (i % groups) * 16;
+        const int8_t* src = X + r * ldx + c0;
+        int8_t c[16];
+        if (c0 + 16 <= p && ((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
+            *reinterpret_cast<uint4*>(c) = *reinterpret_cast<const uint4*>(src);
+        } else {
+#pragma unroll
+            for (int q = 0; q < 16; ++q) c[q] = (c0 + q < p) ? src[q] : (int8_t)0;
+        }
+        unsigned long long w = 0;
+        bool bad = false;
+#pragma unroll
+        for (int q = 0; q < 16; ++q) {
+            bad |= (c[q] < 0) | (c[q] > 2);
+            w |= (unsigned long long)((c[q] & 3) << 1) << (4 * q);
+        }
+        if (bad && bad_flag) *bad_flag = 1;
+        *reinterpret_cast<unsigned long long*>(out + r * ldo + c0 / 2) = w;
+    }
+}
+
 }  // namespace gnnb
 
 using namespace gnnb;
@@ -611,6 +641,18 @@ int gnnb_base3_to_2bit(const uint8_t* P3, int64_t ldi, int64_t n, int64_t p, uin
     int64_t blocks = (n * ((p + 79) / 80) + 255) / 256;
     int64_t cap = (int64_t)sm_count() * 32;
     base3_to_2bit_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(P3, ldi, n, p, out, ldo, bad_flag);
+    GNNB_LAUNCH_CHECK();
+    return GNNB_OK;
+}
+
+int gnnb_pack_fp4(const int8_t* X, int64_t ldx, int64_t n, int64_t p, uint8_t* out, int64_t ldo, int32_t* bad_flag, void* stream) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(X && out && n >= 0 && p > 0 && ldx >= p && ldo >= (p + 1) / 2 && ldo % 16 == 0 && (uintptr_t)out % 16 == 0, GNNB_E_BADARG,
+                 "pack_fp4: bad argument (ldo must be a multiple of 16 bytes >= ceil(p / 2))");
+    if (n == 0) return GNNB_OK;
+    int64_t blocks = (n * (ldo / 8) + 255) / 256;
+    int64_t cap = (int64_t)sm_count() * 32;
+    pack_fp4_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(X, ldx, n, p, out, ldo, bad_flag);
     GNNB_LAUNCH_CHECK();
     return GNNB_OK;
 }

@@ -14,7 +14,8 @@ from . import _lib
 # knobs: 0 = CUDA-core reference tiles, 1..3 = tcgen05 with that many bf16 terms, "auto"
 config = {
     "linear_precision": "auto",
-    "knn_impl": 0,              # 0 = pick, 1 = dp4a tiles, 2 = tcgen05 int8 tiles
+    "knn_impl": 0,              # 0 = pick, 1 = dp4a tiles, 2 = tcgen05 int8 tiles, 3 = tcgen05 FP4 tiles (codes 0..2)
+    "knn_fp4": os.environ.get("GNNB_KNN_FP4", "1") != "0",      # "pick" prefers the FP4 tiles where they apply
     "knn_query_block": 1 << 18,
     "fork": os.environ.get("GNNB_FORK", "1") != "0",    # independent pieces of a backward pass on side streams (ops.Fork)
 }
@@ -264,6 +265,42 @@ def knn_block(Q, sq_q, q_off, K, sq_k, k_off, k, best_d2, best_idx, merge, extra
               _p(ws), ws.numel(), _stream())
 
 
+def fp4_stride(p):
+    """Row stride in bytes of e2m1-packed markers: two codes per byte, padded to 16 bytes."""
+    return ((p + 1) // 2 + 15) // 16 * 16
+
+
+def pack_fp4(X):
+    """int8 codes 0..2 -> e2m1-packed uint8 [n, fp4_stride(p)] (the operand form of the FP4 neighbour search), or None if a
+    code is outside 0..2 (one host read of a flag)."""
+    _rows_ok(X)
+    n, p = X.shape
+    out = torch.empty((n, fp4_stride(p)), dtype=torch.uint8, device=X.device)
+    bad = torch.zeros(1, dtype=torch.int32, device=X.device)
+    with torch.cuda.device(X.device):
+        _declare(bytes=float(n * p + n * fp4_stride(p)))
+        _call("gnnb_pack_fp4", _p(X), X.stride(0), n, p, _p(out), out.stride(0), _p(bad), _stream())
+    return None if int(bad.item()) else out
+
+
+def knn_block_fp4(Q4, sq_q, q_off, K4, sq_k, k_off, p, k, best_d2, best_idx, merge, extra_q=None, extra_k=None):
+    """``knn_block`` on e2m1-packed operands (``pack_fp4``): tcgen05 kind::mxf4 tiles, bit-identical lists."""
+    _need_cuda(Q4, K4, best_d2, best_idx)
+    n_extra = 0 if extra_q is None else extra_q.shape[1]
+    with torch.cuda.device(Q4.device):
+        nbytes = _ws_bytes("gnnb_knn_workspace_bytes", Q4.shape[0], K4.shape[0], p, k, 2)
+        ws = _ws(nbytes, Q4.device)
+        _declare(flops=2.0 * Q4.shape[0] * K4.shape[0] * p, shape=f"{Q4.shape[0]}x{K4.shape[0]}x{p},fp4")
+        _call("gnnb_knn_fp4", _p(Q4), Q4.stride(0), _p(sq_q), Q4.shape[0], q_off,
+              _p(K4), K4.stride(0), _p(sq_k), K4.shape[0], k_off, p,
+              _p(extra_q), _p(extra_k), n_extra, k, _p(best_d2), _p(best_idx), int(merge), _p(ws), ws.numel(), _stream())
+
+
+def fp4_worthwhile(n_q, p):
+    """The FP4 search needs the CTA-pair kernel (>= 129 query rows) and pays for its packing pass on long rows."""
+    return n_q >= 256 and p >= 512
+
+
 def knn(X, k, extra=None, impl=None):
     """Canonical k nearest neighbours of every row of int8 X (sklearn call at load.py:52-59, util.py:52-57).
 
@@ -280,10 +317,19 @@ def knn(X, k, extra=None, impl=None):
     best_d2 = torch.empty((n, k), dtype=torch.float64, device=X.device)
     best_idx = torch.empty((n, k), dtype=torch.int32, device=X.device)
     qb = config["knn_query_block"]
+    impl = config["knn_impl"] if impl is None else impl
+    X4 = None
+    if impl == 3 or (impl == 0 and config["knn_fp4"] and fp4_worthwhile(n, X.shape[1])):
+        X4 = pack_fp4(X)                                   # None when a code is outside 0..2: the int8 tiles take any code
+        if X4 is None and impl == 3:
+            raise _lib.GnnbError("knn impl 3 (FP4 tensor path) needs genotype codes in 0..2")
     for q0 in range(0, n, qb):
         q1 = min(n, q0 + qb)
-        knn_block(X[q0:q1], sq[q0:q1], q0, X, sq, 0, k, best_d2[q0:q1], best_idx[q0:q1], 0,
-                  None if extra is None else extra[q0:q1], extra, impl)
+        eq = None if extra is None else extra[q0:q1]
+        if X4 is not None and q1 - q0 >= 129:
+            knn_block_fp4(X4[q0:q1], sq[q0:q1], q0, X4, sq, 0, X.shape[1], k, best_d2[q0:q1], best_idx[q0:q1], 0, eq, extra)
+        else:
+            knn_block(X[q0:q1], sq[q0:q1], q0, X, sq, 0, k, best_d2[q0:q1], best_idx[q0:q1], 0, eq, extra, 0 if impl == 3 else impl)
     return best_idx, best_d2
 
 

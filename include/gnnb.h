@@ -98,6 +98,18 @@ int gnnb_knn_i8(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q, 
                 int k, double* best_d2, int32_t* best_idx, int merge, int impl,
                 void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same search on the FP4 tensor path (tcgen05 kind::mxf4: twice the int8 rate, half the operand bytes) for genotype
+ * codes 0 / 1 / 2: Q4 / K4 are e2m1-packed rows as gnnb_pack_fp4 writes them (two codes per byte; ldq / ldk in BYTES, multiples
+ * of 16), sq_q / sq_k the squared norms of the int8 codes (gnnb_row_sqnorm_i8).  Products and f32 sums of such codes are
+ * exact (4 p < 2^24), so the lists are bit-identical to gnnb_knn_i8.  Needs n_q >= 129.  Workspace: gnnb_knn_workspace_bytes(.., impl 2). */
+int gnnb_pack_fp4(const int8_t* X, int64_t ldx, int64_t n, int64_t p, uint8_t* out, int64_t ldo, int32_t* bad_flag, void* stream);
+int gnnb_knn_fp4(const uint8_t* Q4, int64_t ldq, const int64_t* sq_q, int64_t n_q, int64_t q_off,
+                 const uint8_t* K4, int64_t ldk, const int64_t* sq_k, int64_t n_k, int64_t k_off,
+                 int64_t p,
+                 const double* extra_q, const double* extra_k, int n_extra,
+                 int k, double* best_d2, int32_t* best_idx, int merge,
+                 void* workspace, size_t workspace_bytes, void* stream);
+
 /* Same contract for float64 features (the `scaled` / transformed markers of load.py:45-48, load_ensembles2.py:150-157):
  * d2 = sum_c fl(fl(q_c - k_c)^2) accumulated left to right in float64 (bit-identical to the oracle).  CUDA-core tiles. */
 int gnnb_knn_f64(const double* Q, int64_t ldq, int64_t n_q, int64_t q_off,
