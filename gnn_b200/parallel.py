@@ -417,25 +417,45 @@ def knn_ring(X_local, row0, n_total, k, rank, world, extra_local=None, impl=None
     sizes, offs = shard_sizes(n_local, rank, world, dev)
     assert sum(sizes) == n_total and offs[rank] == row0
     qb = ops.config["knn_query_block"]
+    qb = -(-n_local // max(1, -(-n_local // qb)))         # equal query blocks: none of them tiny (the FP4 kernel wants >= 129 rows)
     state = {"first": True}
+    # codes 0 / 1 / 2 on every rank: the blocks travel and are searched in their e2m1-packed form (half the bytes on the
+    # links, FP4 tensor tiles); otherwise as int8 codes
+    X4 = None
+    if impl in (None, 0, 3) and ops.config["knn_fp4"] and ops.fp4_worthwhile(n_local, p):
+        X4 = ops.pack_fp4(X_local)
+        if world > 1:
+            ok = torch.tensor([0 if X4 is None else 1], device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if not int(ok):
+                X4 = None
+    if X4 is not None and min(sizes) < 129:
+        X4 = None
 
     def fold(owner, block):
-        keys = block[0][:, :p]
         ek = block[2] if n_extra else None
         for q0 in range(0, n_local, qb):
             q1 = min(n_local, q0 + qb)
-            ops.knn_block(X_local[q0:q1], sq_local[q0:q1], row0 + q0, keys, block[1], offs[owner], k,
-                          best_d2[q0:q1], best_idx[q0:q1], 0 if state["first"] else 1,
-                          None if n_extra == 0 else extra_local[q0:q1], ek, impl)
+            eq = None if n_extra == 0 else extra_local[q0:q1]
+            if X4 is not None:
+                ops.knn_block_fp4(X4[q0:q1], sq_local[q0:q1], row0 + q0, block[0], block[1], offs[owner], p, k,
+                                  best_d2[q0:q1], best_idx[q0:q1], 0 if state["first"] else 1, eq, ek)
+            else:
+                ops.knn_block(X_local[q0:q1], sq_local[q0:q1], row0 + q0, block[0][:, :p], block[1], offs[owner], k,
+                              best_d2[q0:q1], best_idx[q0:q1], 0 if state["first"] else 1, eq, ek, impl)
         state["first"] = False
 
+    width = X4.shape[1] if X4 is not None else ld
+
     def make_buffers(rows):
-        out = [torch.empty((rows, ld), dtype=torch.int8, device=dev), torch.empty(rows, dtype=torch.int64, device=dev)]
+        out = [torch.empty((rows, width), dtype=torch.uint8 if X4 is not None else torch.int8, device=dev),
+               torch.empty(rows, dtype=torch.int64, device=dev)]
         if n_extra:
             out.append(torch.empty((rows, n_extra), dtype=torch.float64, device=dev))
         return out
 
-    local = [X_local.as_strided((n_local, ld), (ld, 1)), sq_local]      # the padded storage: receivers keep the 16-byte row stride
+    # the padded storage travels: receivers keep the 16-byte row stride TMA needs
+    local = [X4 if X4 is not None else X_local.as_strided((n_local, ld), (ld, 1)), sq_local]
     if n_extra:
         local.append(extra_local.contiguous())
     ring_pass(local, sizes, rank, world, fold, make_buffers)

@@ -164,3 +164,39 @@ def test_row_sharded_entry_point_single_rank():
     a_i, a_d = parallel.knn_sharded(X, 0, 900, 12, 0, 1)
     b_i, b_d = ops.knn(X, 12)
     assert torch.equal(a_i, b_i) and torch.equal(a_d, b_d)
+
+
+@pytest.mark.parametrize("n,p,k", [(300, 600, 5), (1000, 4096, 10), (3534, 5003, 10), (2000, 20001, 32), (129, 512, 3)])
+def test_fp4_tensor_path_equals_int8_tensor_path(n, p, k):
+    """Genotype codes 0 / 1 / 2 are exact e2m1 values and their dot products exact in f32, so the search on the FP4 tensor
+    path (tcgen05 kind::mxf4 with constant block scales, key tiles of 224) returns the int8 path's lists bit for bit --
+    with a float64 side column too, folding key blocks into running lists too."""
+    X = ops.synth_genotypes(n, p, "cuda", row0=3)
+    a_i, a_d = ops.knn(X, k, impl=2)
+    b_i, b_d = ops.knn(X, k, impl=3)
+    assert torch.equal(a_i, b_i) and torch.equal(a_d, b_d)
+    extra = torch.randn(n, 1, device="cuda", dtype=torch.float64)
+    a_i, a_d = ops.knn(X, k, extra=extra, impl=2)
+    b_i, b_d = ops.knn(X, k, extra=extra, impl=3)
+    assert torch.equal(a_i, b_i) and torch.equal(a_d, b_d)
+    # streaming: two key blocks folded one after the other
+    X4, sq = ops.pack_fp4(X), ops.row_sqnorm(X)
+    assert X4 is not None and X4.shape == (n, ops.fp4_stride(p))
+    d2 = torch.empty((n, k), dtype=torch.float64, device="cuda")
+    idx = torch.empty((n, k), dtype=torch.int32, device="cuda")
+    cut = (n // 2 + 15) // 16 * 16
+    ops.knn_block_fp4(X4, sq, 0, X4[cut:], sq[cut:], cut, p, k, d2, idx, 0)
+    ops.knn_block_fp4(X4, sq, 0, X4[:cut], sq[:cut], 0, p, k, d2, idx, 1)
+    want_i, want_d = ops.knn(X, k, impl=2)
+    assert torch.equal(idx, want_i) and torch.equal(d2, want_d)
+
+
+def test_fp4_tensor_path_is_refused_for_other_codes():
+    X = torch.randint(0, 4, (300, 600), dtype=torch.int8, device="cuda")            # a code 3 somewhere
+    X[5, 7] = 3
+    assert ops.pack_fp4(X) is None
+    with pytest.raises(Exception, match="codes in 0..2"):
+        ops.knn(X, 4, impl=3)
+    a = ops.knn(X, 4)                                                                # "pick" falls back to the int8 tiles
+    b = ops.knn(X, 4, impl=1)
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
