@@ -295,9 +295,9 @@ def kernel_table(prof, peaks, steps):
         if name in ("gnnb_linear_fwd", "gnnb_linear_bwd_w", "gnnb_linear_bwd_w_prepared", "gnnb_linear_bwd_x") and st["flops"]:
             rec.update(bound="tensor", achieved=st["flops"] / (st["ms"] * 1e-3) / 1e12, unit="TFLOP/s",
                        peak=peaks.get("bf16_tflops_sustained", 1400.0))
-        elif name == "gnnb_knn_i8" and st["flops"]:
-            rec.update(bound="tensor", achieved=st["flops"] / (st["ms"] * 1e-3) / 1e12, unit="TOP/s (int8)",
-                       peak=2.0 * peaks.get("bf16_tflops", 1650.0))
+        elif name in ("gnnb_knn_i8", "gnnb_knn_fp4") and st["flops"]:
+            rec.update(bound="tensor", achieved=st["flops"] / (st["ms"] * 1e-3) / 1e12, unit="TOP/s",
+                       peak=(4.0 if name == "gnnb_knn_fp4" else 2.0) * peaks.get("bf16_tflops", 1650.0))
         elif name == "gnnb_spmm" and st["bytes"]:
             rec.update(bound="hbm", achieved=st["bytes"] / (st["ms"] * 1e-3) / 1e9, unit="GB/s (algorithmic AGG_BYTES)",
                        peak=peaks.get("hbm_gbs", 6650.0))
@@ -378,7 +378,7 @@ def run_ours(a):
     t_setup = time.time()
     ops.profiler = ops.Profiler()
     batches, test, info = build_workload(a, rank, world, dev)
-    knn_prof = {k2: v for k2, v in ops.profiler.summary(by_shape=True).items() if k2.startswith("gnnb_knn_i8")}
+    knn_prof = {k2: v for k2, v in ops.profiler.summary(by_shape=True).items() if k2.startswith("gnnb_knn_")}
     ops.profiler = None
     torch.manual_seed(0)
     model = nets.create_network_two_no_conv_dropout(p, 1, internal_size=a.hidden, dropout=DROPOUT).to(dev)
@@ -563,11 +563,13 @@ def run_ours(a):
 
     # ---- graph-build record: the neighbour searches of the set-up, per shape (CUDA events around every gnnb_knn_i8 call)
     graph_build = {"setup_sections_s": info.get("setup"), "partition": a.partition, "knn": []}
-    int8_peak = 2.0 * peaks.get("bf16_tflops", 1650.0)
+    bf16_peak = peaks.get("bf16_tflops", 1650.0)
     for key, st in sorted(knn_prof.items(), key=lambda kv: -kv[1]["ms"]):
         tops = st["flops"] / (st["ms"] * 1e-3) / 1e12
+        fp4 = key.startswith("gnnb_knn_fp4")
         graph_build["knn"].append({"call": key, "calls": st["calls"], "avg_ms": st["ms"] / st["calls"], "total_ms": st["ms"],
-                                   "tops_int8": tops, "frac_of_2x_bf16_peak": tops / int8_peak})
+                                   "tops": tops, "tensor_path": "fp4 (kind::mxf4)" if fp4 else "int8 (kind::i8)",
+                                   "frac_of_2x_bf16_peak": tops / (2.0 * bf16_peak), "frac_of_4x_bf16_peak": tops / (4.0 * bf16_peak)})
     gb = torch.tensor([info.get("setup", {}).get("global_knn_s", 0.0)], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(gb, op=dist.ReduceOp.MAX)
@@ -575,7 +577,8 @@ def run_ours(a):
     if float(gb) > 0:
         graph_build["global_knn_tops_whole_job"] = 2.0 * N * N * p / float(gb) / 1e12
         graph_build["global_knn_note"] = ("one kNN graph over all individuals, phenotype column included (float64 side column: "
-                                          "the selection runs on the float64 path), key blocks passed round a ring of the ranks")
+                                          "the selection runs on the float64 path), key blocks passed round a ring of the ranks; "
+                                          "operands e2m1-packed, FP4 tensor tiles (exact for 0/1/2 codes)")
     if rank != 0:
         return None
 
