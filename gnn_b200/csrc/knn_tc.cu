@@ -273,18 +273,22 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__
 // (distance + selection, one thread per query row) is the one-CTA epilogue unchanged.
 namespace {
 constexpr int B_HALF_BYTES = (BN / 2) * BKB, STAGE2_BYTES = A_BYTES + B_HALF_BYTES;
+#ifndef KNN_FP4_NT
+#define KNN_FP4_NT 2
+#endif
+constexpr int FP4_NT = KNN_FP4_NT;                        // key tiles per pass of the FP4 kernel (see knn_tc2_kernel)
 constexpr int FP4_TN = 224;                               // key-tile width of the fp4 kernel: 2 x 224 accumulator + 64 scale columns of TMEM
 constexpr int QGP = 8;                                    // query-tile PAIRS per raster group (even: a quad = two pairs of one split)
 
-__host__ __device__ inline size_t smem_bytes2(int stages, int k, bool extra) {
-    return 1024 + (size_t)stages * STAGE2_BYTES + 128 + 2 * BN * sizeof(long long) +
+__host__ __device__ inline size_t smem_bytes2(int stages, int k, bool extra, int stage_bytes = STAGE2_BYTES) {
+    return 1024 + (size_t)stages * stage_bytes + 128 + 2 * BN * sizeof(long long) +
            (extra ? 2 * BN * KNN_MAX_EXTRA * sizeof(double) : 0) + (size_t)k * BM * (sizeof(double) + sizeof(int));
 }
-__device__ inline Smem carve2(uint8_t* raw, int stages, int k, bool extra) {
+__device__ inline Smem carve2(uint8_t* raw, int stages, int k, bool extra, int stage_bytes = STAGE2_BYTES) {
     Smem s;
     uint8_t* base = raw + ((1024 - (smem_u32(raw) & 1023)) & 1023);
     s.tiles = base;
-    uint8_t* p = base + (size_t)stages * STAGE2_BYTES;
+    uint8_t* p = base + (size_t)stages * stage_bytes;
     s.full = reinterpret_cast<uint64_t*>(p);
     s.empty = s.full + MAX_STAGES;
     s.tfull = s.empty + MAX_STAGES;
@@ -306,7 +310,12 @@ __device__ inline Smem carve2(uint8_t* raw, int stages, int k, bool extra) {
 // the tensor time and every byte stream halve.  Block scale factors are mandatory for that kind: a constant 2^0 (ue8m0
 // 0x7F) fills the tensor-memory columns behind the accumulators, which is why the key tile is TN = 224 wide there
 // (2 x 224 accumulator columns + 64 scale columns = 512).  Products and sums of 0/1/2 codes are exact in f32.
-template <bool HAS_EXTRA, int TN, bool FP4>
+// NT = key tiles per pass over the query tile's k-blocks.  NT = 1: the two accumulators double-buffer (the epilogue of
+// tile j overlaps the MMAs of tile j + 1).  NT = 2 (the FP4 kernel): both accumulators are filled in ONE pass -- every
+// query k-block is fetched once for two key tiles and 8 MMAs share a commit -- because at twice the tensor rate the kernel
+// is bound by the L2 -> SM operand stream (ncu: tensor pipe 49 % active with NT = 1), of which the query tile is 70 %;
+// the price is that the epilogue of a tile pair no longer overlaps tensor work.
+template <bool HAS_EXTRA, int TN, bool FP4, int NT>
 __global__ void __launch_bounds__(256, 1)
 knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                const int64_t* __restrict__ sq_q, int64_t n_q, int64_t q_off,
@@ -333,12 +342,12 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
     if ((quad ? (q_pair & ~1) : q_pair) >= q_pairs) return;
     const int q_tile = 2 * q_pair + (int)rank;                  // may be one past the last tile: TMA zero-fills, rows are skipped
 
-    Smem sm = carve2(smem_raw, stages, k, HAS_EXTRA);
+    constexpr int TB_HALF = (TN / 2) * BKB, TSTAGE = A_BYTES + NT * TB_HALF;   // this CTA's half of NT key tiles; one ring slot
+    Smem sm = carve2(smem_raw, stages, k, HAS_EXTRA, NT == 1 ? STAGE2_BYTES : TSTAGE);
     const int64_t n_ktiles = (n_k + TN - 1) / TN;
     const int64_t kt_begin = n_ktiles * split / n_splits;
     const int64_t kt_end = n_ktiles * (split + 1) / n_splits;
     const int n_kb = (int)((p + BKB - 1) / BKB);                  // p = bytes per operand row (markers, or markers / 2 when FP4)
-    constexpr int TB_HALF = (TN / 2) * BKB, TSTAGE = A_BYTES + TB_HALF;   // this CTA's half of the key tile; one ring slot
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < stages; ++s) {
@@ -380,7 +389,7 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             prefetch_tensormap(&map_q);
             prefetch_tensormap(&map_k);
             uint32_t it = 0;
-            for (int64_t kt = kt_begin; kt < kt_end; ++kt) {
+            for (int64_t kt = kt_begin; kt < kt_end; kt += NT) {
                 for (int kb = 0; kb < n_kb; ++kb, ++it) {
                     const int s = it % stages;
                     const uint32_t ph = (it / stages) & 1;
@@ -394,12 +403,16 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                     else        mbar_arrive_cluster(full_leader);
                     uint8_t* a = sm.tiles + (size_t)s * TSTAGE;
                     tma_load_2d_pair(a, &map_q, full_leader, kb * BKB, q_tile * BM);
-                    if (quad)
-                        tma_load_2d_pair_multicast(a + A_BYTES + twin * (TB_HALF / 2), &map_k, &sm.full[s], kb * BKB,
-                                                   (int32_t)(kt * TN + rank * (TN / 2) + twin * (TN / 4)),
-                                                   (uint16_t)((1u << rank) | (1u << (rank + 2))));
-                    else
-                        tma_load_2d_pair(a + A_BYTES, &map_k, full_leader, kb * BKB, (int32_t)(kt * TN + rank * (TN / 2)));
+#pragma unroll
+                    for (int t = 0; t < NT; ++t) {              // (a key tile past the end reads as zeros and is skipped by the epilogue)
+                        uint8_t* bdst = a + A_BYTES + t * TB_HALF;
+                        if (quad)
+                            tma_load_2d_pair_multicast(bdst + twin * (TB_HALF / 2), &map_k, &sm.full[s], kb * BKB,
+                                                       (int32_t)((kt + t) * TN + rank * (TN / 2) + twin * (TN / 4)),
+                                                       (uint16_t)((1u << rank) | (1u << (rank + 2))));
+                        else
+                            tma_load_2d_pair(bdst, &map_k, full_leader, kb * BKB, (int32_t)((kt + t) * TN + rank * (TN / 2)));
+                    }
                 }
             }
         }
@@ -409,9 +422,10 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             constexpr uint32_t idesc = FP4 ? make_idesc_mxf4(2 * BM, TN) : make_idesc(/*S32*/ 2, /*int8*/ 1, 0, 0, 2 * BM, TN);
             const uint32_t tsf = tmem_base + 2 * TN;              // FP4: 64 columns of constant scale factors (see below)
             uint32_t it = 0, tile = 0;
-            for (int64_t kt = kt_begin; kt < kt_end; ++kt, ++tile) {
-                const uint32_t b = tile & 1, tph = (tile >> 1) & 1;
-                mbar_wait(&sm.tempty[b], tph ^ 1);              // both epilogues have drained this accumulator
+            for (int64_t kt = kt_begin; kt < kt_end; kt += NT, ++tile) {
+                // NT = 1: accumulator b = tile parity; NT = 2: both accumulators belong to this pass (barrier pair 0 only)
+                const uint32_t b = NT == 1 ? (tile & 1) : 0u, tph = NT == 1 ? ((tile >> 1) & 1) : (tile & 1);
+                mbar_wait(&sm.tempty[b], tph ^ 1);              // both epilogues have drained the accumulator(s)
                 tc_fence_after_sync();
                 const uint32_t d_tmem = tmem_base + b * TN;
                 for (int kb = 0; kb < n_kb; ++kb, ++it) {
@@ -426,16 +440,19 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                         continue;
                     }
 #pragma unroll
-                    for (int k4 = 0; k4 < BKB / 32; ++k4) {
-                        const uint64_t da = make_smem_desc(a_addr + k4 * 32, 16, 1024);
-                        const uint64_t db = make_smem_desc(b_addr + k4 * 32, 16, 1024);
-                        if (FP4) mma_mxf4_ss_pair(d_tmem, da, db, idesc, tsf, tsf + 32, (kb > 0 || k4 > 0) ? 1u : 0u);
-                        else     mma_i8_ss_pair(d_tmem, da, db, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+                    for (int t = 0; t < NT; ++t) {
+#pragma unroll
+                        for (int k4 = 0; k4 < BKB / 32; ++k4) {
+                            const uint64_t da = make_smem_desc(a_addr + k4 * 32, 16, 1024);
+                            const uint64_t db = make_smem_desc(b_addr + t * TB_HALF + k4 * 32, 16, 1024);
+                            if (FP4) mma_mxf4_ss_pair(d_tmem + t * TN, da, db, idesc, tsf, tsf + 32, (kb > 0 || k4 > 0) ? 1u : 0u);
+                            else     mma_i8_ss_pair(d_tmem + t * TN, da, db, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+                        }
                     }
                     // (releasing slots two at a time to halve the commits was measured: 9.3 -> 10.9 ms, the loads need the slot early)
                     tc_commit_pair(&sm.empty[s], all_mask);     // frees the slot in both CTAs (and tells the twin pair in quad mode)
                 }
-                tc_commit_pair(&sm.tfull[b], pair_mask);        // accumulator complete, both epilogues may read
+                tc_commit_pair(&sm.tfull[b], pair_mask);        // accumulator(s) complete, both epilogues may read
             }
         }
     } else if (warp >= 4) {
@@ -457,17 +474,19 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                 for (int c = 0; c < n_extra; ++c) eq_r[c] = extra_q[row * n_extra + c];
         }
         uint32_t tile = 0;
-        for (int64_t kt = kt_begin; kt < kt_end; ++kt, ++tile) {
-            const uint32_t b = tile & 1, tph = (tile >> 1) & 1;
-            const int64_t k0 = kt * TN;
-            long long* sqk_b = sm.sqk + b * TN;
-            double* ek_b = sm.ek + (size_t)b * TN * KNN_MAX_EXTRA;
+        for (int64_t kt = kt_begin; kt < kt_end; kt += NT, ++tile) {
+            const uint32_t b = NT == 1 ? (tile & 1) : 0u, tph = NT == 1 ? ((tile >> 1) & 1) : (tile & 1);
 #pragma unroll
-            for (int t = e; t < TN; t += EPI_THREADS) {
-                const int64_t gk = k0 + t;
-                sqk_b[t] = (gk < n_k) ? sq_k[gk] : 0;
-                if (HAS_EXTRA)
-                    for (int c = 0; c < n_extra; ++c) ek_b[t * KNN_MAX_EXTRA + c] = (gk < n_k) ? extra_k[gk * n_extra + c] : 0.0;
+            for (int u = 0; u < NT; ++u) {                      // squared norms (and side columns) of the pass's key rows
+                const int64_t k0 = (kt + u) * TN;
+                long long* sqk_b = sm.sqk + (b + u) * TN;
+                double* ek_b = sm.ek + (size_t)(b + u) * TN * KNN_MAX_EXTRA;
+                for (int t = e; t < TN; t += EPI_THREADS) {
+                    const int64_t gk = k0 + t;
+                    sqk_b[t] = (gk < n_k) ? sq_k[gk] : 0;
+                    if (HAS_EXTRA)
+                        for (int c = 0; c < n_extra; ++c) ek_b[t * KNN_MAX_EXTRA + c] = (gk < n_k) ? extra_k[gk * n_extra + c] : 0.0;
+                }
             }
             named_bar_sync(1, EPI_THREADS);
             mbar_wait(&sm.tfull[b], tph);
@@ -477,9 +496,15 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                 else        mbar_arrive_cluster(mapa_u32(smem_u32(&sm.tempty[b]), lead_rank));
                 continue;
             }
-            const int ncols = (int)((n_k - k0) < TN ? (n_k - k0) : TN);
-            scan_accumulator<HAS_EXTRA, TN, FP4>(tmem_base + ((uint32_t)(32 * wq) << 16) + b * TN, valid, sqq, sqk_b, ek_b, eq_r, n_extra,
-                                        ncols, gi, k_off + k0, sel, thr_ll, selu);
+#pragma unroll
+            for (int u = 0; u < NT; ++u) {
+                const int64_t k0 = (kt + u) * TN;
+                if (k0 >= n_k || kt + u >= kt_end) break;       // the odd tile of the last pass
+                const int ncols = (int)((n_k - k0) < TN ? (n_k - k0) : TN);
+                scan_accumulator<HAS_EXTRA, TN, FP4>(tmem_base + ((uint32_t)(32 * wq) << 16) + (b + u) * TN, valid, sqq,
+                                                     sm.sqk + (b + u) * TN, sm.ek + (size_t)(b + u) * TN * KNN_MAX_EXTRA, eq_r, n_extra,
+                                                     ncols, gi, k_off + k0, sel, thr_ll, selu);
+            }
             tc_fence_before_sync();
             if (leader) mbar_arrive(&sm.tempty[b]);
             else        mbar_arrive_cluster(mapa_u32(smem_u32(&sm.tempty[b]), lead_rank));
@@ -546,9 +571,10 @@ int knn_tc_launch(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q
         if (rc != GNNB_OK) return rc;
         rc = make_tensor_map_2d(&map_k, K, 1, (uint64_t)k_bytes, (uint64_t)n_k, (uint64_t)ldk, BKB, use_quad ? tn / 4 : tn / 2);
         if (rc != GNNB_OK) return rc;
+        const int stage_bytes = (fp4 && FP4_NT > 1) ? A_BYTES + FP4_NT * (FP4_TN / 2) * BKB : STAGE2_BYTES;
         int stages = MAX_STAGES;
-        while (stages > 2 && smem_bytes2(stages, k, extra) > 232448) --stages;
-        const size_t smem = smem_bytes2(stages, k, extra);
+        while (stages > 2 && smem_bytes2(stages, k, extra, stage_bytes) > 232448) --stages;
+        const size_t smem = smem_bytes2(stages, k, extra, stage_bytes);
         const int q_pairs = (q_tiles + 1) / 2;
         const int groups = (q_pairs + QGP - 1) / QGP;
         cudaLaunchConfig_t cfg = {};
@@ -565,8 +591,8 @@ int knn_tc_launch(const int8_t* Q, int64_t ldq, const int64_t* sq_q, int64_t n_q
         cfg.numAttrs = 1;
 #define KNN_LAUNCH2(EXTRA_, TN_, FP4_)                                                                                              \
     do {                                                                                                                           \
-        GNNB_SET_DYN_SMEM((knn_tc2_kernel<EXTRA_, TN_, FP4_>), smem);                                                              \
-        GNNB_CUDA(cudaLaunchKernelEx(&cfg, knn_tc2_kernel<EXTRA_, TN_, FP4_>, map_q, map_k, sq_q, n_q, q_off, sq_k, n_k, k_off, k_bytes, \
+        GNNB_SET_DYN_SMEM((knn_tc2_kernel<EXTRA_, TN_, FP4_, (FP4_ ? FP4_NT : 1)>), smem);                                         \
+        GNNB_CUDA(cudaLaunchKernelEx(&cfg, knn_tc2_kernel<EXTRA_, TN_, FP4_, (FP4_ ? FP4_NT : 1)>, map_q, map_k, sq_q, n_q, q_off, sq_k, n_k, k_off, k_bytes, \
                                      extra_q, extra_k, n_extra, k, n_splits, q_pairs, stages, part_d2, part_idx, use_quad, ablate)); \
     } while (0)
         if (fp4) {
