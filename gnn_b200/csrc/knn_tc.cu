@@ -476,6 +476,7 @@ knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         uint32_t tile = 0;
         for (int64_t kt = kt_begin; kt < kt_end; kt += NT, ++tile) {
             const uint32_t b = NT == 1 ? (tile & 1) : 0u, tph = NT == 1 ? ((tile >> 1) & 1) : (tile & 1);
+            if (NT > 1) named_bar_sync(1, EPI_THREADS);         // both norm buffers are reused every pass: wait for the slowest reader
 #pragma unroll
             for (int u = 0; u < NT; ++u) {                      // squared norms (and side columns) of the pass's key rows
                 const int64_t k0 = (kt + u) * TN;
