@@ -274,7 +274,7 @@ knn_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__
 namespace {
 constexpr int B_HALF_BYTES = (BN / 2) * BKB, STAGE2_BYTES = A_BYTES + B_HALF_BYTES;
 #ifndef KNN_FP4_NT
-#define KNN_FP4_NT 2
+#define KNN_FP4_NT 1       // measured at 15 625 x 50 000, k = 32: 1 -> 6.95 ms, 2 -> 10.4 ms (see knn_tc2_kernel)
 #endif
 constexpr int FP4_NT = KNN_FP4_NT;                        // key tiles per pass of the FP4 kernel (see knn_tc2_kernel)
 constexpr int FP4_TN = 224;                               // key-tile width of the fp4 kernel: 2 x 224 accumulator + 64 scale columns of TMEM
@@ -311,10 +311,12 @@ __device__ inline Smem carve2(uint8_t* raw, int stages, int k, bool extra, int s
 // 0x7F) fills the tensor-memory columns behind the accumulators, which is why the key tile is TN = 224 wide there
 // (2 x 224 accumulator columns + 64 scale columns = 512).  Products and sums of 0/1/2 codes are exact in f32.
 // NT = key tiles per pass over the query tile's k-blocks.  NT = 1: the two accumulators double-buffer (the epilogue of
-// tile j overlaps the MMAs of tile j + 1).  NT = 2 (the FP4 kernel): both accumulators are filled in ONE pass -- every
-// query k-block is fetched once for two key tiles and 8 MMAs share a commit -- because at twice the tensor rate the kernel
-// is bound by the L2 -> SM operand stream (ncu: tensor pipe 49 % active with NT = 1), of which the query tile is 70 %;
-// the price is that the epilogue of a tile pair no longer overlaps tensor work.
+// tile j overlaps the MMAs of tile j + 1).  NT = 2: both accumulators are filled in ONE pass -- every query k-block is
+// fetched once for two key tiles and 8 MMAs share a commit.  It was built for the FP4 kernel, which at twice the tensor
+// rate is bound by the L2 -> SM operand stream (ncu: tensor pipe 49 % active), 70 % of it the query tile; but the epilogue
+// of a tile pair then no longer overlaps tensor work, and the selection's insertions (a whole warp pays ~150 cycles
+// whenever one of its 32 rows inserts, ~160 times per row and key split) cost more than the saved loads:
+// 15 625 x 50 000, k = 32: 6.95 ms with NT = 1, 10.4 ms with NT = 2.  NT = 1 is what ships.
 template <bool HAS_EXTRA, int TN, bool FP4, int NT>
 __global__ void __launch_bounds__(256, 1)
 knn_tc2_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
