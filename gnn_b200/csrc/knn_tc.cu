@@ -534,8 +534,18 @@ bool knn_tc_supported(int64_t ldq, int64_t ldk, const void* Q, const void* K, in
 int knn_tc_splits(int64_t n_q, int64_t n_k) {
     int64_t q_tiles = (n_q + BM - 1) / BM, k_tiles = (n_k + BN - 1) / BN;      // (the fp4 kernel has a few more, narrower key tiles: s <= k_tiles holds for it too)
     int64_t s;
-    if (q_tiles >= QG) s = 8;                                   // ~QG x 8 = 144 co-resident CTAs share 18 Q tiles and 8 K ranges
-    else s = (sm_count() + q_tiles - 1) / q_tiles;
+    static int forced = -1;                                     // GNNB_KNN_SPLITS: tuning knob (any value gives the same lists)
+    if (forced < 0) { const char* e = getenv("GNNB_KNN_SPLITS"); forced = e ? atoi(e) : 0; }
+    // Every key split keeps its own list per query row, and every list pays its own warm-up of insertions (a whole warp
+    // stalls ~150 cycles whenever one of its rows inserts), so fewer splits are cheaper -- as long as one wave of CTA pairs
+    // fills the GPU (66 pairs = 33 co-resident clusters of four).  Measured, FP4 kernel, ms at splits = 1 / 2 / 4 / 8:
+    // 15 625 rows 5.26 / 5.39 / 5.94 / 6.97; 3 534 rows 0.99 / 0.55 / 0.34 / 0.41; 1 814 rows - / 0.18 / 0.14 / 0.12.  From a few
+    // waves on, 8 splits win again (90 000 rows: 190 / 181 / - / 178) because a group of 8 query pairs x 8 key ranges keeps
+    // its operands in L2.
+    const int64_t q_pairs = (q_tiles + 1) / 2, wave = 66;
+    if (forced > 0) s = forced;
+    else if (q_pairs >= 2 * wave) s = 8;
+    else s = (wave + q_pairs / 2) / q_pairs;                    // round(66 / q_pairs)
     if (s > KNN_MAX_SPLITS) s = KNN_MAX_SPLITS;
     if (s > k_tiles) s = k_tiles;
     if (s < 1) s = 1;
