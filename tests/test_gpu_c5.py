@@ -2,7 +2,7 @@
 15 625 individuals x 50 000 SNPs, the 180 000-node test graph, k = 32, hidden 100.
 
 What runs here is what the benchmark runs -- the 2-bit packed projection in clusters of four (linear_p2_kernel), the
-tcgen05 quad-cluster neighbour search with the 5-slot ring (knn_tc2_kernel), the planned aggregation with hub rows of
+tcgen05 quad-cluster neighbour search (knn_tc2_kernel, int8 tiles and the FP4 tiles the graph build uses), the planned aggregation with hub rows of
 tens of thousands of entries -- compared with independent float64 / exact-integer arithmetic on the same inputs and,
 for the whole training step, with the oracle's torch-CPU restatement (oracle.restate.epoch_step, ensemble2.py:51-88).
 Bars as everywhere: bit-exact indices and integer distances, 1e-4 relative for fp32 activations / gradients (the
@@ -123,6 +123,8 @@ def test_tensor_core_knn_at_the_subgraph_shape(sub):
     assert torch.equal(d2[rows], bd)
     idx1, d1 = ops.knn(X, K, impl=1)                                        # CUDA-core dp4a tiles on the full matrix
     assert torch.equal(idx2, idx1) and torch.equal(d2, d1)
+    idx4, d4 = ops.knn(X, K, impl=3)                                        # FP4 tensor tiles: what the bench's graph build runs
+    assert torch.equal(idx2, idx4) and torch.equal(d2, d4)
     # size-independent properties: ascending (d2, j), no self, all slots filled
     assert bool((d2[:, 1:] >= d2[:, :-1]).all())
     tie = d2[:, 1:] == d2[:, :-1]
@@ -137,6 +139,8 @@ def test_tensor_core_knn_at_the_test_graph_shape(big):
     bi, bd = brute_force_lists(big, ops.row_sqnorm(big), rows, K)
     assert torch.equal(idx[rows], bi) and torch.equal(d2[rows], bd)
     assert bool((d2[:, 1:] >= d2[:, :-1]).all()) and bool((idx >= 0).all())
+    idx4, d4 = ops.knn(big, K, impl=3)                                      # FP4 tensor tiles on all 180 000 rows
+    assert torch.equal(idx, idx4) and torch.equal(d2, d4)
 
 
 # ------------------------------------------------------------------------------------------------- (c) aggregation
