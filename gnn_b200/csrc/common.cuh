@@ -95,4 +95,15 @@ __device__ __forceinline__ unsigned long long splitmix64_dev(unsigned long long 
     return z ^ (z >> 31);
 }
 
+// (d0, d1) = (a0 * b0 + d0, a1 * b1 + d1), each lane one IEEE fp32 fma (round to nearest even) -- fma.rn.f32x2, SASS FFMA2.
+// With a0 == a1 the assembler uses the broadcast-scalar form, so no packing moves are spent on the shared factor.
+__device__ __forceinline__ void ffma2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
+    unsigned long long d, a, b;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(d0), "f"(d1));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(a0), "f"(a1));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(b) : "f"(b0), "f"(b1));
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(d));
+}
+
 }  // namespace gnnb

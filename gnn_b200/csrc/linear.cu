@@ -113,25 +113,82 @@ static int launch_gemm(const AT* A, int64_t sam, int64_t sak, const float* B, in
 // Inner layers (h x h weights, float activations): both small dimensions fit one CTA tile, so the generic 64x64x16 kernel
 // spends its time on tile overhead (29 / 25 / 34+14 us for 15625 x 100 x 100 -- 11 % of a C5 epoch).  Here a CTA keeps BOTH
 // operands of a 128-deep product in shared memory and every thread owns an 8 x 8 block of the 128 x 128 output tile
-// (64 FMAs per 4 128-bit shared loads), fp32 FMA in ascending k like the generic kernel.
+// (32 packed FMAs = 64 fp32 FMAs per 4 128-bit shared loads), fp32 FMA in ascending k like the generic kernel.
+// Measured (CUDA graph replays, B200): 15 625 x 100 x 100 forward 14.0 us, dX 12.6, dW 20.1 incl. the chunk sum (cuBLAS through
+// torch: 13.5 / 13.2 / 49.0); 180 000 rows 118 / 118 / 181 us (126 / 130 / 300).  Half of a CTA's time is the latency of
+// filling its tiles and writing its rows, the other half the shared-memory reads of the product (16 floats per 64 FMAs).
 //   MODE 0  C[m, n] = sum_k A[m, k] * W[n, k]      forward      (K, N <= 128; CTA = 128 rows m)
 //   MODE 1  C[m, n] = sum_k A[m, k] * W[k, n]      dX           (K, N <= 128; CTA = 128 rows m)
 //   MODE 2  P[c][i, j] = sum_{m in chunk c} A[m, i] * B[m, j]   weight gradient partials (I, J <= 128; chunk = 128 rows),
 //           summed over chunks in ascending order by splitk_reduce_kernel
 constexpr int SK = 128, SK_LD = SK + 4;
 
-template <int MODE>
+// 128-bit tile loaders of the VEC instances (all leading dimensions, widths and base addresses multiples of four floats):
+// a thread issues its (up to) 16 loads before the first store, so a tile costs ONE round trip to L2 / HBM instead of the
+// eight of the scalar path -- the kernel spent more time waiting for its tiles than multiplying them.
+// dst[k][r] = src[(row0 + r) * ld + k] for r < 128 (zero where row0 + r >= rows), k < kdim.  A warp takes 16 rows x 2 quads of
+// k: full 32-byte sectors on the global side, and the four transposing stores of a quad hit 32 different banks.
+__device__ __forceinline__ void skinny_load_transposed(float* __restrict__ dst, const float* __restrict__ src, int64_t ld,
+                                                       int64_t row0, int64_t rows, int kdim, int tid) {
+    const int lane = tid & 31, r = (tid >> 5) * 16 + (lane & 15), kq0 = lane >> 4;
+    const int64_t m = row0 + r;
+    const bool row_ok = m < rows;
+    const float* p = src + m * ld;
+    float4 v[16];
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+        const int k = (q * 2 + kq0) * 4;
+        v[q] = (row_ok && k < kdim) ? __ldg(reinterpret_cast<const float4*>(p + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+        const int k = (q * 2 + kq0) * 4;
+        if (k < kdim) {
+            dst[(k + 0) * SK_LD + r] = v[q].x;
+            dst[(k + 1) * SK_LD + r] = v[q].y;
+            dst[(k + 2) * SK_LD + r] = v[q].z;
+            dst[(k + 3) * SK_LD + r] = v[q].w;
+        }
+    }
+}
+// dst[k][c] = src[(row0 + k) * ld + c] for k < krows (zero where row0 + k >= rows or c >= cols), c < 128.
+__device__ __forceinline__ void skinny_load_straight(float* __restrict__ dst, const float* __restrict__ src, int64_t ld,
+                                                     int64_t row0, int64_t rows, int cols, int krows, int tid) {
+    float4 v[16];
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+        const int f = tid + q * 256, k = f >> 5, c = (f & 31) * 4;
+        v[q] = (k < krows && row0 + k < rows && c < cols) ? __ldg(reinterpret_cast<const float4*>(src + (row0 + k) * ld + c))
+                                                          : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+        const int f = tid + q * 256, k = f >> 5, c = (f & 31) * 4;
+        if (k < krows) *reinterpret_cast<float4*>(dst + k * SK_LD + c) = v[q];
+    }
+}
+
+template <int MODE, bool VEC>
 __global__ void __launch_bounds__(256, 2)
 skinny_kernel(const float* __restrict__ A, int64_t lda, const float* __restrict__ B, int64_t ldb,
               float* __restrict__ C, int64_t ldc, int64_t M, int N, int K) {
-    extern __shared__ float sk_smem[];
+    extern __shared__ __align__(16) float sk_smem[];
     const int kdim = MODE == 2 ? SK : K;                       // depth of the product held in shared memory
     float* As = sk_smem;                                       // [kdim][SK_LD]: As[k][row of the output tile]
     float* Bs = sk_smem + (size_t)kdim * SK_LD;                // [kdim][SK_LD]: Bs[k][column of the output tile]
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
     const int64_t m0 = (int64_t)blockIdx.x * SK;
-    // Loads are issued in batches of 8 per thread before the first store, so that their latencies overlap.
-    if (MODE == 2) {
+    if (VEC) {
+        if (MODE == 2) {
+            skinny_load_straight(As, A, lda, m0, M, N, SK, tid);
+            skinny_load_straight(Bs, B, ldb, m0, M, K, SK, tid);
+        } else {
+            skinny_load_transposed(As, A, lda, m0, M, kdim, tid);
+            if (MODE == 0) skinny_load_transposed(Bs, B, ldb, 0, N, kdim, tid);        // W[n, k] -> Bs[k][n]
+            else           skinny_load_straight(Bs, B, ldb, 0, kdim, N, kdim, tid);    // W[k, n] -> Bs[k][n]
+        }
+    } else if (MODE == 2) {
+        // scalar path: loads are issued in batches of 8 per thread before the first store, so that their latencies overlap
         // A[m, i] and B[m, j] are already k-major (k = m): straight copies, zero padding past the matrices
         for (int e0 = tid; e0 < SK * SK; e0 += 256 * 8) {
             float va[8], vb[8];
@@ -197,12 +254,30 @@ skinny_kernel(const float* __restrict__ A, int64_t lda, const float* __restrict_
         const float4 b1 = *reinterpret_cast<const float4*>(Bs + k * SK_LD + 64 + tx * 4);
         const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
         const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+        // packed FMA (fma.rn.f32x2 -> FFMA2 with a broadcast scalar): the three-register scalar FFMA issues every other cycle
+        // per scheduler on this part, FFMA2 does two of them in the same slot; each lane is the same IEEE fma as fmaf
 #pragma unroll
         for (int i = 0; i < 8; ++i)
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+            for (int j = 0; j < 8; j += 2) ffma2(acc[i][j], acc[i][j + 1], a[i], a[i], b[j], b[j + 1]);
     }
-    if (MODE == 2) {
+    if (VEC) {
+        // rows of the output (or of the chunk's partial) are multiples of four floats wide and 16-byte aligned
+        float* out = MODE == 2 ? C + (int64_t)blockIdx.x * N * K : C + m0 * ldc;
+        const int64_t ldo = MODE == 2 ? K : ldc;
+        const int64_t row_lim = MODE == 2 ? N : M - m0;
+        const int col_lim = MODE == 2 ? K : N;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int r = (i < 4 ? 0 : 60) + ty * 4 + i;
+            if (r < row_lim) {
+                if (tx * 4 < col_lim)
+                    *reinterpret_cast<float4*>(out + r * ldo + tx * 4) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+                if (64 + tx * 4 < col_lim)
+                    *reinterpret_cast<float4*>(out + r * ldo + 64 + tx * 4) = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
+            }
+        }
+    } else if (MODE == 2) {
         // partial [N (= I) rows][K (= J) columns], dense, one per chunk
         float* P = C + (int64_t)blockIdx.x * N * K;
 #pragma unroll
@@ -253,8 +328,18 @@ template <int MODE>
 static int launch_skinny(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M, int N, int K,
                          cudaStream_t stream) {
     const size_t smem = skinny_smem(MODE == 2 ? SK : K);
-    GNNB_SET_DYN_SMEM(skinny_kernel<MODE>, smem);
-    skinny_kernel<MODE><<<(unsigned)((M + SK - 1) / SK), 256, smem, stream>>>(A, lda, B, ldb, C, ldc, M, N, K);
+    const unsigned grid = (unsigned)((M + SK - 1) / SK);
+    // 128-bit loads and stores when every row of every operand starts on a 16-byte boundary and is a multiple of four floats wide
+    // (MODE 2 writes dense [N, K] partials into the workspace: ldc is not used there)
+    const bool vec = ((lda | ldb | (MODE == 2 ? 0 : ldc) | N | K) & 3) == 0 &&
+                     (((uintptr_t)A | (uintptr_t)B | (uintptr_t)C) & 15) == 0;
+    if (vec) {
+        GNNB_SET_DYN_SMEM((skinny_kernel<MODE, true>), smem);
+        skinny_kernel<MODE, true><<<grid, 256, smem, stream>>>(A, lda, B, ldb, C, ldc, M, N, K);
+    } else {
+        GNNB_SET_DYN_SMEM((skinny_kernel<MODE, false>), smem);
+        skinny_kernel<MODE, false><<<grid, 256, smem, stream>>>(A, lda, B, ldb, C, ldc, M, N, K);
+    }
     GNNB_LAUNCH_CHECK();
     return GNNB_OK;
 }

@@ -6,7 +6,7 @@ import subprocess
 import sys
 
 LIB = "gnn_b200/lib/libgnn_b200.so"
-COLS = ["UTCIMMA", "UTCHMMA", "UTCOMMA", "UTMALDG", "LDTM", "STTM", "UTCBAR", "HMMA", "LDG.E.128", "LDGMC"]
+COLS = ["UTCIMMA", "UTCHMMA", "UTCOMMA", "UTMALDG", "LDTM", "STTM", "UTCBAR", "HMMA", "FFMA2", "LDG.E.128", "LDGMC"]
 
 
 def main():
@@ -28,9 +28,10 @@ def main():
     mangled = list(counts)
     dem = subprocess.run(["c++filt"], input="\n".join(mangled), capture_output=True, text=True).stdout.splitlines()
     for a, b in zip(mangled, dem):
-        names[a] = re.sub(r"\(.*$", "", b).replace("void ", "")
+        b = b.replace("(anonymous namespace)::", "").replace("void ", "")
+        names[a] = re.sub(r"\((?!anonymous).*$", "", b)
     print("# cuobjdump -sass " + LIB + ", occurrences per kernel (UTCIMMA/UTCHMMA/UTCOMMA = tcgen05.mma kind::i8 / "
-          "kind::f16 / kind::mxf4 block-scaled, UTMALDG = TMA load, LDTM/STTM = tcgen05.ld/st, HMMA = legacy mma.sync, "
+          "kind::f16 / kind::mxf4 block-scaled, UTMALDG = TMA load, LDTM/STTM = tcgen05.ld/st, HMMA = legacy mma.sync, FFMA2 = packed fp32 fma (fma.rn.f32x2), "
           "LDGMC = multimem.ld_reduce)")
     print("kernel," + ",".join(COLS))
     for k in sorted(counts, key=lambda k: names[k]):
