@@ -384,7 +384,7 @@ def run_ours(a):
     model = nets.create_network_two_no_conv_dropout(p, 1, internal_size=a.hidden, dropout=DROPOUT).to(dev)
     parallel.broadcast_parameters(model)
     flat = parallel.FlatGrads(model.parameters(), sink_layer=parallel.first_genotype_layer(model), world=world,
-                              averaging=a.allreduce)
+                              averaging=a.allreduce, model=model)     # every layer writes its gradients in place
     flat.cut = a.dp_cut
     if a.optimizer == "own":
         from gnn_b200.optim import Adam

@@ -35,7 +35,14 @@ class _GCNConvFn(torch.autograd.Function):
         g = ctx.graph
         d_out = d_out.contiguous()
         sink = getattr(ctx.layer, "grad_sink", None)
-        sunk = sink is not None and ctx.has_bias and weight.grad is not None and ctx.layer.bias.grad is not None
+        # parallel.FlatGrads: this layer's dW / db are written straight into their slices of the flat gradient buffer.  The
+        # first layer has the sink itself (it also starts the all-reduces); other layers are marked ``grad_inplace`` and
+        # overwrite on their first backward of a step (a second use in the same step accumulates through autograd as usual)
+        first_write = getattr(ctx.layer, "grad_inplace", False) and not ctx.layer._grad_written
+        sunk = ((sink is not None or first_write) and ctx.has_bias and weight.grad is not None
+                and ctx.layer.bias.grad is not None)
+        if sunk and sink is None:
+            ctx.layer._grad_written = True
         # the bias gradient (column sums of dOut) and the aggregation of dOut are independent and each fills only part of
         # the GPU: they run side by side, and so do the weight and the input gradient of an inner layer
         bias_job = None
@@ -43,21 +50,21 @@ class _GCNConvFn(torch.autograd.Function):
             into = ctx.layer.bias.grad if sunk else None
             bias_job = ops.Fork(lambda: ops.colsum(d_out, out=into), reads=(d_out, into))
         d_h = ops.spmm(g.rowptr_t, g.col_t, g.val_t, d_out, None, n=g.n, hub=g.hub_t)     # transposed CSR
-        if sunk and not x.is_floating_point():
+        if sunk and sink is not None and not x.is_floating_point():
             # data-parallel training (parallel.FlatGrads): dW and db go straight into the flat gradient buffer and their
             # all-reduces start here; autograd gets None for both and has nothing to accumulate
             bias_job.join()
             sink.write(ctx.layer, x, d_h)
             return None, None, None, None, None
+        w_into = weight.grad if sunk else None
         if ctx.x_needs_grad:
-            w_job = ops.Fork(lambda: ops.linear_bwd_w(x, d_h, p=weight.shape[1]), reads=(x, d_h), slot=1)
+            w_job = ops.Fork(lambda: ops.linear_bwd_w(x, d_h, p=weight.shape[1], out=w_into), reads=(x, d_h, w_into), slot=1)
             d_x = ops.linear_bwd_x(d_h, weight)
             d_w = w_job.join()
         else:
-            d_w, d_x = ops.linear_bwd_w(x, d_h, p=weight.shape[1]), None
+            d_w, d_x = ops.linear_bwd_w(x, d_h, p=weight.shape[1], out=w_into), None
         d_bias = bias_job.join() if bias_job is not None else None
-        if sunk:        # float features: same contract (the sink's slices are overwritten, not accumulated into), plain kernels
-            weight.grad.copy_(d_w)
+        if sunk:        # float features / inner layers: same contract (the slices are overwritten, not accumulated into)
             return d_x, None, None, None, None
         return d_x, d_w, d_bias, None, None
 
@@ -89,6 +96,7 @@ class GCNConv(torch.nn.Module):
         self.in_channels, self.out_channels = in_channels, out_channels
         self.add_self_loops = add_self_loops
         self.grad_sink = None           # set by parallel.FlatGrads: takes dW / db of this layer directly (see _GCNConvFn.backward)
+        self.grad_inplace, self._grad_written = False, False    # ditto, for the layers behind the first one
         self.lin = _Lin(in_channels, out_channels)
         if bias:
             self.bias = torch.nn.Parameter(torch.zeros(out_channels))

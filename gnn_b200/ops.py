@@ -748,8 +748,9 @@ def head_fwd(A, W, bias=None):
     return out
 
 
-def head_bwd(d_out, A, W, need_dA=True, need_db=True):
-    """(dA or None, dW, db or None) of ``head_fwd``."""
+def head_bwd(d_out, A, W, need_dA=True, need_db=True, out_w=None, out_b=None):
+    """(dA or None, dW, db or None) of ``head_fwd``; ``out_w`` [o, h] / ``out_b`` [o]: contiguous float32 tensors to write
+    dW / db into (e.g. the layer's slices of a flat gradient buffer)."""
     _need_cuda(d_out, A, W)
     A = A if (A.dtype == torch.float32 and A.stride(1) == 1) else A.float().contiguous()
     d_out = d_out.contiguous()
@@ -757,8 +758,11 @@ def head_bwd(d_out, A, W, need_dA=True, need_db=True):
     n, h = A.shape
     o = W.shape[0]
     dA = torch.empty((n, h), dtype=torch.float32, device=A.device) if need_dA else None
-    dW = torch.empty((o, h), dtype=torch.float32, device=A.device)
-    db = torch.empty(o, dtype=torch.float32, device=A.device) if need_db else None
+    for t, shape in ((out_w, (o, h)), (out_b, (o,))):
+        if t is not None and (tuple(t.shape) != shape or t.dtype != torch.float32 or not t.is_contiguous() or t.device != A.device):
+            raise _lib.GnnbError(f"head_bwd: an output tensor must be contiguous float32 {shape} on the inputs' device")
+    dW = out_w if out_w is not None else torch.empty((o, h), dtype=torch.float32, device=A.device)
+    db = (out_b if out_b is not None else torch.empty(o, dtype=torch.float32, device=A.device)) if need_db else None
     with torch.cuda.device(A.device):
         ws = _ws(_ws_bytes("gnnb_head_workspace_bytes", n, h, o), A.device)
         _call("gnnb_head_bwd", _p(d_out), d_out.stride(0), _p(A), A.stride(0), n, h, _p(W), W.stride(0), o,

@@ -54,12 +54,33 @@ class FlatGrads:
     the next range runs (``ops.linear_bwd_w_ranges``).  Everything else is the small tail.  Without a sink layer the
     buffer is zeroed and reduced in one piece."""
 
-    def __init__(self, params, sink_layer=None, world=1, group=None, averaging="auto"):
+    def __init__(self, params, sink_layer=None, world=1, group=None, averaging="auto", model=None):
         params = [p for p in params if p.requires_grad]
         head = []
         if sink_layer is not None and getattr(sink_layer, "bias", None) is not None:
             head = [sink_layer.lin.weight, sink_layer.bias]
-            params = head + [p for p in params if all(p is not q for q in head)]
+        # With ``model``: every other GCNConv and dense head of it (with a bias, all parameters trainable) also writes its
+        # gradients in place -- its backward hands autograd None, so a step has no zero-fill of and no accumulate pass over
+        # them either (seven small launches per step at C5).  The first backward of such a layer after zero() overwrites,
+        # later ones in the same step accumulate as usual; a marked layer that takes no part in a step would keep the
+        # previous step's gradient, so pass ``model`` only when every layer runs in every step (the GCN factories' do).
+        self.inplace_layers = []
+        owned = list(head)
+        if model is not None:
+            from . import ops
+            from .networks.gcn_conv import GCNConv
+            from .networks.head import Linear
+            for m in model.modules():
+                if m is sink_layer or not isinstance(m, (GCNConv, Linear)) or getattr(m, "bias", None) is None:
+                    continue
+                if isinstance(m, Linear) and not ops.head_supported(m.in_features, m.out_features):
+                    continue                                      # runs through torch's Linear: autograd accumulates
+                mine = [m.lin.weight if isinstance(m, GCNConv) else m.weight, m.bias]
+                if all(q.requires_grad and any(q is r for r in params) for q in mine) and \
+                        not any(q is r for q in mine for r in owned):
+                    self.inplace_layers.append(m)
+                    owned += mine
+        params = owned + [p for p in params if all(p is not q for q in owned)]
         self.params = params
         total = sum(p.numel() for p in self.params)
         dev = self.params[0].device
@@ -81,10 +102,12 @@ class FlatGrads:
         self.has_sink = bool(head)
         self.range_markers = None           # markers per wave of the weight-gradient kernel; None = ask the library
         self.cut = "last_wave"              # see _ranges
+        self.tail = self.flat[sum(q.numel() for q in owned):]          # what autograd still accumulates into
         if head:
             self.w_numel = head[0].numel()
-            self.tail = self.flat[self.w_numel + head[1].numel():]      # what autograd still accumulates into
             sink_layer.grad_sink = self
+        for m in self.inplace_layers:
+            m.grad_inplace, m._grad_written = True, False
 
     # ---- averaging through the NVSwitch -------------------------------------------------------------------------------
     def _try_symmetric(self, total, dev, world, group):
@@ -196,10 +219,10 @@ class FlatGrads:
 
     # ---- per step ----------------------------------------------------------------------------------------------------
     def zero(self):
-        if self.has_sink:
-            self.tail.zero_()                    # the sink layer's slices are overwritten, never accumulated into
-        else:
-            self.flat.zero_()
+        if self.tail.numel():
+            self.tail.zero_()                    # the slices of the sink / in-place layers are overwritten, not accumulated into
+        for m in self.inplace_layers:
+            m._grad_written = False
 
     def allreduce_mean(self, world, group=None):
         if world <= 1:

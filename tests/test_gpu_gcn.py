@@ -351,6 +351,47 @@ def test_gradient_sink_writes_the_first_layer_gradients_in_place(packed):
     assert rel_err(layer.lin.weight.grad, plain.nns[0].lin.weight.grad) < 1e-5
 
 
+@pytest.mark.parametrize("factory", ["create_network_two_no_conv_dropout", "create_network_test", "create_network_two_relu"])
+def test_flat_gradients_written_in_place_by_every_layer(factory):
+    """parallel.FlatGrads(model=...): the inner GCNConv layers and the dense head write dW / db into their slices of the flat
+    buffer too, so a step zero-fills nothing and autograd accumulates nothing; the bits are those of plain autograd over
+    two steps that start from stale buffer contents.  A layer applied twice in one step still accumulates."""
+    from gnn_b200 import parallel
+    n, p, h = 700, 512, 40
+    X = torch.from_numpy(synth.genotypes(n, p, seed=9)).to(DEV)
+    ei, ew = random_graph(n, 6000, 8)
+    ei, ew = ei.to(DEV), ew.to(DEV)
+    y = torch.randn(n, 1, device=DEV)
+    torch.manual_seed(1)
+    plain = getattr(nets, factory)(p, 1, internal_size=h, dropout=0.0).to(DEV)
+    mine = getattr(nets, factory)(p, 1, internal_size=h, dropout=0.0).to(DEV)
+    mine.load_state_dict(plain.state_dict())
+    flat = parallel.FlatGrads(mine.parameters(), sink_layer=parallel.first_genotype_layer(mine), model=mine)
+    marked = [m for m in mine.modules() if getattr(m, "grad_inplace", False)]
+    assert marked and flat.inplace_layers == marked
+    covered = sum(q.numel() for m in marked for q in m.parameters()) + (flat.w_numel + h if flat.has_sink else 0)
+    assert flat.tail.numel() == flat.flat.numel() - covered
+    flat.flat.fill_(-7.0)
+    flat.tail.zero_()                                        # (what zero() keeps clean; everything else is stale)
+    for step in range(2):
+        plain.zero_grad()
+        torch.nn.functional.mse_loss(plain(X, ei, ew), y).backward()
+        flat.zero()
+        torch.nn.functional.mse_loss(mine(X, ei, ew), y).backward()
+        flat.allreduce_mean(1)
+        for (k, a), (_, b) in zip(plain.named_parameters(), mine.named_parameters()):
+            assert torch.equal(a.grad, b.grad), (factory, step, k)
+    # the same model applied twice in one step: the second backward of every marked layer accumulates
+    plain.zero_grad()
+    (torch.nn.functional.mse_loss(plain(X, ei, ew), y) + torch.nn.functional.mse_loss(plain(X, ei, ew), -y)).backward()
+    flat.zero()
+    (torch.nn.functional.mse_loss(mine(X, ei, ew), y) + torch.nn.functional.mse_loss(mine(X, ei, ew), -y)).backward()
+    for (k, a), (_, b) in zip(plain.named_parameters(), mine.named_parameters()):
+        if flat.has_sink and any(b is q for q in flat.params[:2]):
+            continue                                         # the sink layer itself overwrites: one use per step
+        assert rel_err(b.grad, a.grad) < 1e-5, (factory, k)
+
+
 @pytest.mark.parametrize("n,h,o", [(15625, 100, 1), (1000, 100, 3), (77, 128, 4), (500, 300, 1), (64, 1024, 1), (10, 7, 2), (1, 100, 1)])
 def test_head_linear_kernels_against_torch(n, h, o):
     """networks.head.Linear (the dense head of every GCN factory): one kernel forward, one backward, against torch's own
