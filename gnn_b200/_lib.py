@@ -62,6 +62,9 @@ PROTOTYPES = {
     "gnnb_head_workspace_bytes": (_i32, [_i64, _i64, _i64, _psz]),
     "gnnb_head_fwd": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _vp]),
     "gnnb_head_bwd": (_i32, [_vp, _i64, _vp, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _sz, _vp]),
+    "gnnb_head_dropout_fwd": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _c.c_double, _vp, _vp, _vp]),
+    "gnnb_head_dropout_bwd": (_i32, [_vp, _i64, _vp, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _i64, _vp, _i64, _vp, _c.c_double, _vp,
+                                     _vp, _sz, _vp]),
     "gnnb_adam_step": (_i32, [_i32, _vp, _vp, _vp, _vp, _vp, _vp, _c.c_float, _c.c_float, _c.c_float, _c.c_float, _vp]),
     "gnnb_allreduce_mean_multimem": (_i32, [_vp, _i64, _i32, _i32, _i32, _vp]),
     "gnnb_allreduce_mean_p2p": (_i32, [_vp, _i64, _i32, _i32, _i32, _vp]),

@@ -14,11 +14,37 @@ namespace gnnb {
 
 constexpr int HEAD_WARPS = 8, HEAD_THREADS = HEAD_WARPS * 32;
 
-template <int O, int T>
+// Dropout in front of the head (torch.nn.Dropout -> Linear, gnn/networks/networks.py:272-274), applied on the fly: no mask and
+// no dropped copy of the activations is ever stored.  Counter-based: element (r, c) of call number `counter` keeps its value
+// (times 1 / (1 - p)) iff a 32-bit slice of splitmix64(key ^ position) is >= p * 2^32, key = f(seed, counter).  The counter
+// lives on the device (state[1]) and is advanced by the forward kernel itself, so a step replayed as a CUDA graph draws a
+// fresh mask on every replay without any host work; the forward pass hands (seed, counter) to its backward pass in `used`.
+struct DropArgs {
+    unsigned long long* state;      // forward: {seed, counter, ticket, -} (device);  backward: unused
+    unsigned long long* used;       // forward: writes {seed, counter};  backward: reads them
+    uint32_t thresh;                // p * 2^32
+    float scale;                    // 1 / (1 - p)
+};
+__device__ __forceinline__ unsigned long long drop_key(unsigned long long seed, unsigned long long counter) {
+    return splitmix64_dev(seed ^ splitmix64_dev(counter));
+}
+__device__ __forceinline__ float4 drop_mask4(unsigned long long key, int64_t r, int c, uint32_t thresh, float scale) {
+    const unsigned long long g = ((unsigned long long)r << 9) | ((unsigned long long)(c >> 2) << 1);     // c < 1024
+    const unsigned long long h0 = splitmix64_dev(key ^ g), h1 = splitmix64_dev(key ^ (g | 1ull));
+    return make_float4((uint32_t)h0 >= thresh ? scale : 0.f, (uint32_t)(h0 >> 32) >= thresh ? scale : 0.f,
+                       (uint32_t)h1 >= thresh ? scale : 0.f, (uint32_t)(h1 >> 32) >= thresh ? scale : 0.f);
+}
+
+template <int O, int T, bool DROP>
 __global__ void __launch_bounds__(HEAD_THREADS)
 head_fwd_kernel(const float* __restrict__ A, int64_t lda, int64_t n, int h, const float* __restrict__ W, int64_t ldw,
-                const float* __restrict__ bias, float* __restrict__ out, int64_t ldo) {
+                const float* __restrict__ bias, float* __restrict__ out, int64_t ldo, DropArgs drop) {
     __shared__ __align__(16) float w_s[O * T * 128];
+    unsigned long long key = 0, counter = 0;
+    if (DROP) {
+        counter = *reinterpret_cast<volatile unsigned long long*>(drop.state + 1);     // every CTA reads it before it takes its ticket
+        key = drop_key(drop.state[0], counter);
+    }
     for (int i = threadIdx.x; i < O * T * 128; i += HEAD_THREADS) {
         const int o = i / (T * 128), c = i % (T * 128);
         w_s[i] = c < h ? W[(int64_t)o * ldw + c] : 0.f;
@@ -48,6 +74,15 @@ head_fwd_kernel(const float* __restrict__ A, int64_t lda, int64_t n, int h, cons
                     }
                 }
             }
+        if (DROP) {
+#pragma unroll
+            for (int q = 0; q < R; ++q)
+#pragma unroll
+                for (int t = 0; t < T; ++t) {
+                    const float4 m = drop_mask4(key, r0 + q, t * 128 + lane * 4, drop.thresh, drop.scale);
+                    a[q][t].x *= m.x; a[q][t].y *= m.y; a[q][t].z *= m.z; a[q][t].w *= m.w;
+                }
+        }
 #pragma unroll
         for (int q = 0; q < R; ++q) {
             float acc[O];
@@ -69,14 +104,28 @@ head_fwd_kernel(const float* __restrict__ A, int64_t lda, int64_t n, int h, cons
             }
         }
     }
+    if (DROP) {
+        // the CTA that takes the last ticket knows every CTA has read the counter: it advances it for the next call
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            if (blockIdx.x == 0) { drop.used[0] = drop.state[0]; drop.used[1] = counter; }
+            unsigned* ticket = reinterpret_cast<unsigned*>(drop.state + 2);
+            if (atomicAdd(ticket, 1u) == gridDim.x - 1) {
+                *ticket = 0;
+                drop.state[1] = counter + 1;
+            }
+        }
+    }
 }
 
 // partial layout per CTA: [O][T * 128] weight-gradient columns, then [O] bias gradients
-template <int O, int T>
+template <int O, int T, bool DROP>
 __global__ void __launch_bounds__(HEAD_THREADS)
 head_bwd_kernel(const float* __restrict__ dOut, int64_t lddo, const float* __restrict__ A, int64_t lda, int64_t n, int h,
                 const float* __restrict__ W, int64_t ldw, float* __restrict__ dA, int64_t ldda,
-                float* __restrict__ dW, int64_t lddw, float* __restrict__ db, float* __restrict__ partial, unsigned* __restrict__ ticket) {
+                float* __restrict__ dW, int64_t lddw, float* __restrict__ db, float* __restrict__ partial, unsigned* __restrict__ ticket,
+                DropArgs drop) {
+    const unsigned long long key = DROP ? drop_key(drop.used[0], drop.used[1]) : 0ull;
     constexpr int PER = O * T * 128 + O;
     constexpr int PER_S = (PER + 3) / 4 * 4;                        // rows of `red` stay 16-byte aligned for the float4 stores
     __shared__ __align__(16) float w_s[O * T * 128];
@@ -131,6 +180,11 @@ head_bwd_kernel(const float* __restrict__ dOut, int64_t lddo, const float* __res
             for (int t = 0; t < T; ++t) {
                 const int c = t * 128 + lane * 4;
                 float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
+                float4 m = make_float4(1.f, 1.f, 1.f, 1.f);
+                if (DROP) {                                         // the forward pass saw A * m: so does dW, and dA is masked the same way
+                    m = drop_mask4(key, r, c, drop.thresh, drop.scale);
+                    a[q][t].x *= m.x; a[q][t].y *= m.y; a[q][t].z *= m.z; a[q][t].w *= m.w;
+                }
 #pragma unroll
                 for (int o = 0; o < O; ++o) {
                     const float4 w = *reinterpret_cast<const float4*>(w_s + (o * T + t) * 128 + lane * 4);
@@ -140,6 +194,7 @@ head_bwd_kernel(const float* __restrict__ dOut, int64_t lddo, const float* __res
                     acc.x = fmaf(go, a[q][t].x, acc.x); acc.y = fmaf(go, a[q][t].y, acc.y);
                     acc.z = fmaf(go, a[q][t].z, acc.z); acc.w = fmaf(go, a[q][t].w, acc.w);
                 }
+                if (DROP) { d.x *= m.x; d.y *= m.y; d.z *= m.z; d.w *= m.w; }
                 if (dA && r < n) {
                     float* drow = dA + r * ldda;
                     if (c + 3 < h && vec_d) *reinterpret_cast<float4*>(drow + c) = d;
@@ -232,16 +287,28 @@ int gnnb_head_workspace_bytes(int64_t n, int64_t h, int64_t out, size_t* bytes) 
     return GNNB_OK;
 }
 
-int gnnb_head_fwd(const float* A, int64_t lda, int64_t n, int64_t h, const float* W, int64_t ldw, int64_t out_features,
-                  const float* bias, float* out, int64_t ldo, void* stream) {
-    GNNB_ENTER();
+static int drop_args(double p, unsigned long long* state, unsigned long long* used, DropArgs* d, const char* who) {
+    GNNB_REQUIRE(p >= 0.0 && p < 1.0 && used && (((uintptr_t)used | (uintptr_t)state) & 7) == 0, GNNB_E_BADARG,
+                 "%s: 0 <= p < 1 and 8-byte aligned device pointers for the generator state", who);
+    d->state = state;
+    d->used = used;
+    d->thresh = (uint32_t)(p * 4294967296.0);
+    d->scale = (float)(1.0 / (1.0 - p));
+    return GNNB_OK;
+}
+
+static int head_fwd_impl(const float* A, int64_t lda, int64_t n, int64_t h, const float* W, int64_t ldw, int64_t out_features,
+                         const float* bias, float* out, int64_t ldo, const DropArgs* drop, void* stream) {
     GNNB_REQUIRE(A && W && out && n >= 0 && lda >= h && ldw >= h && ldo >= out_features, GNNB_E_BADARG, "head_fwd: bad argument");
     GNNB_REQUIRE(head_ok(h, out_features), GNNB_E_UNSUPPORTED, "head_fwd: out <= 4, h <= 1024 and out * ceil(h / 128) <= 8 (got h = %lld, out = %lld)",
                  (long long)h, (long long)out_features);
     if (n == 0) return GNNB_OK;
     const int o = (int)out_features, t = head_t(h), grid = head_grid(n);
     bool launched = false;
-#define CALL_FWD(O_, T_) head_fwd_kernel<O_, T_><<<grid, HEAD_THREADS, 0, (cudaStream_t)stream>>>(A, lda, n, (int)h, W, ldw, bias, out, ldo)
+    const DropArgs none = {nullptr, nullptr, 0u, 1.f};
+#define CALL_FWD(O_, T_)                                                                                                              \
+    if (drop) head_fwd_kernel<O_, T_, true><<<grid, HEAD_THREADS, 0, (cudaStream_t)stream>>>(A, lda, n, (int)h, W, ldw, bias, out, ldo, *drop); \
+    else head_fwd_kernel<O_, T_, false><<<grid, HEAD_THREADS, 0, (cudaStream_t)stream>>>(A, lda, n, (int)h, W, ldw, bias, out, ldo, none)
     HEAD_ALL(CALL_FWD)
 #undef CALL_FWD
     GNNB_REQUIRE(launched, GNNB_E_UNSUPPORTED, "head_fwd: shape not instantiated");
@@ -249,10 +316,9 @@ int gnnb_head_fwd(const float* A, int64_t lda, int64_t n, int64_t h, const float
     return GNNB_OK;
 }
 
-int gnnb_head_bwd(const float* dOut, int64_t lddo, const float* A, int64_t lda, int64_t n, int64_t h, const float* W, int64_t ldw,
-                  int64_t out_features, float* dA, int64_t ldda, float* dW, int64_t lddw, float* db,
-                  void* workspace, size_t workspace_bytes, void* stream) {
-    GNNB_ENTER();
+static int head_bwd_impl(const float* dOut, int64_t lddo, const float* A, int64_t lda, int64_t n, int64_t h, const float* W, int64_t ldw,
+                         int64_t out_features, float* dA, int64_t ldda, float* dW, int64_t lddw, float* db, const DropArgs* drop,
+                         void* workspace, size_t workspace_bytes, void* stream) {
     GNNB_REQUIRE(dOut && A && W && dW && n >= 0 && lda >= h && ldw >= h && lddw >= h && lddo >= out_features && (!dA || ldda >= h), GNNB_E_BADARG,
                  "head_bwd: bad argument");
     GNNB_REQUIRE(head_ok(h, out_features), GNNB_E_UNSUPPORTED, "head_bwd: out <= 4, h <= 1024 and out * ceil(h / 128) <= 8 (got h = %lld, out = %lld)",
@@ -266,12 +332,48 @@ int gnnb_head_bwd(const float* dOut, int64_t lddo, const float* A, int64_t lda, 
     GNNB_CUDA(cudaMemsetAsync(ticket, 0, sizeof(unsigned), (cudaStream_t)stream));
     const int o = (int)out_features, t = head_t(h), grid = n == 0 ? 1 : head_grid(n);
     bool launched = false;
-#define CALL_BWD(O_, T_) head_bwd_kernel<O_, T_><<<grid, HEAD_THREADS, 0, (cudaStream_t)stream>>>(dOut, lddo, A, lda, n, (int)h, W, ldw, dA, ldda, dW, lddw, db, partial, ticket)
+    const DropArgs none = {nullptr, nullptr, 0u, 1.f};
+#define CALL_BWD(O_, T_)                                                                                                     \
+    if (drop) head_bwd_kernel<O_, T_, true><<<grid, HEAD_THREADS, 0, (cudaStream_t)stream>>>(dOut, lddo, A, lda, n, (int)h, W, ldw, dA, ldda, dW, lddw, db, partial, ticket, *drop); \
+    else head_bwd_kernel<O_, T_, false><<<grid, HEAD_THREADS, 0, (cudaStream_t)stream>>>(dOut, lddo, A, lda, n, (int)h, W, ldw, dA, ldda, dW, lddw, db, partial, ticket, none)
     HEAD_ALL(CALL_BWD)
 #undef CALL_BWD
     GNNB_REQUIRE(launched, GNNB_E_UNSUPPORTED, "head_bwd: shape not instantiated");
     GNNB_LAUNCH_CHECK();
     return GNNB_OK;
+}
+
+int gnnb_head_fwd(const float* A, int64_t lda, int64_t n, int64_t h, const float* W, int64_t ldw, int64_t out_features,
+                  const float* bias, float* out, int64_t ldo, void* stream) {
+    GNNB_ENTER();
+    return head_fwd_impl(A, lda, n, h, W, ldw, out_features, bias, out, ldo, nullptr, stream);
+}
+
+int gnnb_head_bwd(const float* dOut, int64_t lddo, const float* A, int64_t lda, int64_t n, int64_t h, const float* W, int64_t ldw,
+                  int64_t out_features, float* dA, int64_t ldda, float* dW, int64_t lddw, float* db,
+                  void* workspace, size_t workspace_bytes, void* stream) {
+    GNNB_ENTER();
+    return head_bwd_impl(dOut, lddo, A, lda, n, h, W, ldw, out_features, dA, ldda, dW, lddw, db, nullptr, workspace, workspace_bytes, stream);
+}
+
+int gnnb_head_dropout_fwd(const float* A, int64_t lda, int64_t n, int64_t h, const float* W, int64_t ldw, int64_t out_features,
+                          const float* bias, float* out, int64_t ldo, double p, uint64_t* state, uint64_t* used, void* stream) {
+    GNNB_ENTER();
+    GNNB_REQUIRE(state, GNNB_E_BADARG, "head_dropout_fwd: generator state missing");
+    DropArgs d;
+    int rc = drop_args(p, (unsigned long long*)state, (unsigned long long*)used, &d, "head_dropout_fwd");
+    if (rc != GNNB_OK) return rc;
+    return head_fwd_impl(A, lda, n, h, W, ldw, out_features, bias, out, ldo, &d, stream);
+}
+
+int gnnb_head_dropout_bwd(const float* dOut, int64_t lddo, const float* A, int64_t lda, int64_t n, int64_t h, const float* W, int64_t ldw,
+                          int64_t out_features, float* dA, int64_t ldda, float* dW, int64_t lddw, float* db, double p,
+                          const uint64_t* used, void* workspace, size_t workspace_bytes, void* stream) {
+    GNNB_ENTER();
+    DropArgs d;
+    int rc = drop_args(p, nullptr, (unsigned long long*)used, &d, "head_dropout_bwd");
+    if (rc != GNNB_OK) return rc;
+    return head_bwd_impl(dOut, lddo, A, lda, n, h, W, ldw, out_features, dA, ldda, dW, lddw, db, &d, workspace, workspace_bytes, stream);
 }
 
 }  // extern "C"

@@ -53,9 +53,20 @@ class Sequential(torch.nn.Module):
         state = dict(zip(names, args))
         state["self"] = self
         out = None
-        for m, f, (ins, outs) in zip(self.nns, self.fns, self.descs):
+        fused_p = 0.0
+        for i, (m, f, (ins, outs)) in enumerate(zip(self.nns, self.fns, self.descs)):
             call = m if f is None else f
             vals = [state[k] for k in ins if k not in absent]
+            if self._dropout_feeds_head(i, vals):
+                # Dropout -> Linear head (networks.py:272-274): the head's kernels drop the activations as they read them
+                # (no mask, no dropped copy in memory); this module passes its input on untouched
+                fused_p = float(m.p)
+                continue
+            if fused_p > 0.0:
+                out = (m(vals[0], dropout_p=fused_p),)
+                fused_p = 0.0
+                state.update(zip(outs, out))
+                continue
             if isinstance(m, torch.nn.Linear) and vals and torch.is_tensor(vals[0]) and not vals[0].is_floating_point():
                 # the loaders keep genotypes as int8 codes where the reference has float32 (load.py:50); GCNConv reads the
                 # codes directly, a stock Linear in front of them (create_network_linear / _test) needs the float tensor
@@ -67,6 +78,20 @@ class Sequential(torch.nn.Module):
             assert len(out) == len(outs)
             state.update(zip(outs, out))
         return out[0] if len(out) == 1 else out
+
+    def _dropout_feeds_head(self, i, vals):
+        """Module i is a train-mode Dropout whose one float32 CUDA matrix goes, under the same name, to a dense head that runs
+        on our kernels (networks.head.Linear) as the next module."""
+        from .. import ops
+        from .head import Linear
+        m = self.nns[i]
+        if not (isinstance(m, torch.nn.Dropout) and m.training and 0.0 < m.p < 1.0 and not m.inplace
+                and ops.config["fused_dropout"] and i + 1 < len(self.nns) and len(vals) == 1):
+            return False
+        nxt = self.nns[i + 1]
+        (ins, outs), (nins, _) = self.descs[i], self.descs[i + 1]
+        return (isinstance(nxt, Linear) and nxt.runs_on_kernels(vals[0]) and len(ins) == 1 and list(outs) == list(ins)
+                and list(nins) == list(outs))
 
     def __repr__(self):
         rows = [f"  ({i}): {m if f is None else f.__name__}" for i, (m, f) in enumerate(zip(self.nns, self.fns))]

@@ -18,9 +18,12 @@ config = {
     "knn_fp4": os.environ.get("GNNB_KNN_FP4", "1") != "0",      # "pick" prefers the FP4 tiles where they apply
     "knn_query_block": 1 << 18,
     "fork": os.environ.get("GNNB_FORK", "1") != "0",    # independent pieces of a backward pass on side streams (ops.Fork)
+    # a train-mode torch.nn.Dropout directly in front of the dense head is applied inside the head's kernels (networks.Sequential)
+    "fused_dropout": os.environ.get("GNNB_FUSED_DROPOUT", "1") != "0",
 }
 
 _launches = 0                   # C-ABI calls that enqueue kernels (bench.py reports it)
+_dropout_states = 0
 
 
 def launches():
@@ -736,21 +739,42 @@ def head_supported(h, out):
     return bool(_lib.lib().gnnb_head_supported(int(h), int(out)))
 
 
-def head_fwd(A, W, bias=None):
-    """out = A . W^T + bias for a Linear(h -> out) with a handful of outputs (see include/gnnb.h)."""
+def dropout_state(device, seed=None):
+    """Generator state of the fused dropout (``head_fwd(..., drop=(p, state))``): int64 [4] = {seed, call counter, 0, 0} on
+    ``device``.  The seed defaults to a function of ``torch.initial_seed()`` and of how many states were made before, so
+    ``torch.manual_seed`` makes runs repeatable."""
+    global _dropout_states
+    if seed is None:                # torch's seed (not a draw: the caller's random stream stays where it is) + a per-state stride
+        _dropout_states += 1
+        seed = (int(torch.initial_seed()) + 0x9E3779B97F4A7C15 * _dropout_states) & (2 ** 62 - 1)
+    return torch.tensor([seed, 0, 0, 0], dtype=torch.int64, device=device)
+
+
+def head_fwd(A, W, bias=None, drop=None):
+    """out = A . W^T + bias for a Linear(h -> out) with a handful of outputs (see include/gnnb.h).
+    ``drop = (p, state)``: train-mode dropout with probability p applied to A on the fly (``state`` from ``dropout_state``,
+    advanced on the device); returns ``(out, used)`` then, ``used`` being what ``head_bwd(drop=(p, used))`` needs."""
     _need_cuda(A, W)
     A = A if (A.dtype == torch.float32 and A.stride(1) == 1) else A.float().contiguous()
     W = W.contiguous()
     n, h = A.shape
     out = torch.empty((n, W.shape[0]), dtype=torch.float32, device=A.device)
     with torch.cuda.device(A.device):
-        _call("gnnb_head_fwd", _p(A), A.stride(0), n, h, _p(W), W.stride(0), W.shape[0], _p(bias), _p(out), out.stride(0), _stream())
-    return out
+        if drop is None:
+            _call("gnnb_head_fwd", _p(A), A.stride(0), n, h, _p(W), W.stride(0), W.shape[0], _p(bias), _p(out), out.stride(0), _stream())
+            return out
+        p, state = drop
+        if state.dtype != torch.int64 or state.numel() != 4 or state.device != A.device or not state.is_contiguous():
+            raise _lib.GnnbError("head_fwd: the dropout state is an int64 [4] tensor on the inputs' device (ops.dropout_state)")
+        used = torch.empty(2, dtype=torch.int64, device=A.device)
+        _call("gnnb_head_dropout_fwd", _p(A), A.stride(0), n, h, _p(W), W.stride(0), W.shape[0], _p(bias), _p(out), out.stride(0),
+              float(p), _p(state), _p(used), _stream())
+    return out, used
 
 
-def head_bwd(d_out, A, W, need_dA=True, need_db=True, out_w=None, out_b=None):
+def head_bwd(d_out, A, W, need_dA=True, need_db=True, out_w=None, out_b=None, drop=None):
     """(dA or None, dW, db or None) of ``head_fwd``; ``out_w`` [o, h] / ``out_b`` [o]: contiguous float32 tensors to write
-    dW / db into (e.g. the layer's slices of a flat gradient buffer)."""
+    dW / db into (e.g. the layer's slices of a flat gradient buffer); ``drop = (p, used)`` from the dropout forward."""
     _need_cuda(d_out, A, W)
     A = A if (A.dtype == torch.float32 and A.stride(1) == 1) else A.float().contiguous()
     d_out = d_out.contiguous()
@@ -765,8 +789,12 @@ def head_bwd(d_out, A, W, need_dA=True, need_db=True, out_w=None, out_b=None):
     db = (out_b if out_b is not None else torch.empty(o, dtype=torch.float32, device=A.device)) if need_db else None
     with torch.cuda.device(A.device):
         ws = _ws(_ws_bytes("gnnb_head_workspace_bytes", n, h, o), A.device)
-        _call("gnnb_head_bwd", _p(d_out), d_out.stride(0), _p(A), A.stride(0), n, h, _p(W), W.stride(0), o,
-              _p(dA), h, _p(dW), h, _p(db), _p(ws), ws.numel(), _stream())
+        if drop is None:
+            _call("gnnb_head_bwd", _p(d_out), d_out.stride(0), _p(A), A.stride(0), n, h, _p(W), W.stride(0), o,
+                  _p(dA), h, _p(dW), h, _p(db), _p(ws), ws.numel(), _stream())
+        else:
+            _call("gnnb_head_dropout_bwd", _p(d_out), d_out.stride(0), _p(A), A.stride(0), n, h, _p(W), W.stride(0), o,
+                  _p(dA), h, _p(dW), h, _p(db), float(drop[0]), _p(drop[1]), _p(ws), ws.numel(), _stream())
     return dA, dW, db
 
 

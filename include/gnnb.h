@@ -252,6 +252,20 @@ int gnnb_head_fwd(const float* A, int64_t lda, int64_t n, int64_t h, const float
 int gnnb_head_bwd(const float* dOut, int64_t lddo, const float* A, int64_t lda, int64_t n, int64_t h, const float* W, int64_t ldw,
                   int64_t out_features, float* dA, int64_t ldda, float* dW, int64_t lddw, float* db,
                   void* workspace, size_t workspace_bytes, void* stream);
+/* The same head behind a train-mode torch.nn.Dropout(p) (gnn/networks/networks.py:272-274: Dropout -> Linear), the dropout
+ * applied on the fly -- neither a mask nor the dropped activations are stored:
+ *   fwd: out[r, o] = sum_c (A[r, c] m[r, c]) W[o, c] + bias[o],  m = 1 / (1 - p) with probability 1 - p, else 0
+ *   bwd: dA[r, c] = m[r, c] sum_o dOut[r, o] W[o, c];  dW[o, c] = sum_r dOut[r, o] A[r, c] m[r, c];  db as above
+ * m comes from a counter-based generator: `state` = four DEVICE uint64 {seed, call counter, 0, 0} owned by the caller (set
+ * once); the forward kernel draws the mask of call number `counter`, writes {seed, counter} to the two DEVICE uint64 `used`
+ * and advances the counter ON THE DEVICE, so a captured step draws a new mask on every replay.  The backward pass gets the
+ * `used` of its forward pass and regenerates the same mask.  The masks are NOT those torch's generator would draw (torch's
+ * CUDA and CPU generators do not agree with each other either); the distribution is the same.  0 <= p < 1. */
+int gnnb_head_dropout_fwd(const float* A, int64_t lda, int64_t n, int64_t h, const float* W, int64_t ldw, int64_t out_features,
+                          const float* bias, float* out, int64_t ldo, double p, uint64_t* state, uint64_t* used, void* stream);
+int gnnb_head_dropout_bwd(const float* dOut, int64_t lddo, const float* A, int64_t lda, int64_t n, int64_t h, const float* W, int64_t ldw,
+                          int64_t out_features, float* dA, int64_t ldda, float* dW, int64_t lddw, float* db, double p,
+                          const uint64_t* used, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Replaces torch.optim.Adam(lr).step() (gnn/main.py:318: no weight decay, no amsgrad) for up to 8 float32 tensors in one
  * launch: m = m + (g - m)(1 - b1); v = b2 v + (1 - b2) g^2; p -= (lr / (1 - b1^t)) m / (sqrt(v) / sqrt(1 - b2^t) + eps).

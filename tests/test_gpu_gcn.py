@@ -351,6 +351,88 @@ def test_gradient_sink_writes_the_first_layer_gradients_in_place(packed):
     assert rel_err(layer.lin.weight.grad, plain.nns[0].lin.weight.grad) < 1e-5
 
 
+@pytest.mark.parametrize("n,h,o,p", [(15625, 100, 1, 0.4012), (300, 128, 3, 0.5), (1000, 260, 2, 0.1)])
+def test_head_with_fused_dropout(n, h, o, p):
+    """gnnb_head_dropout_fwd / _bwd: the mask is never stored, so recover it from dA (W = 1, dOut = 1 gives dA = m) and check
+    that the forward pass, dW and db are those of the explicitly masked activations; keep rate, scaling, a new mask per call
+    (the counter advances on the device, also under CUDA-graph replay), the same mask again from the same (seed, counter)."""
+    torch.manual_seed(n)
+    A = torch.randn(n, h, device=DEV)
+    W = torch.randn(o, h, device=DEV)
+    b = torch.randn(o, device=DEV)
+    state = ops.dropout_state(DEV, seed=1234)
+    ones_w, ones_d = torch.ones(o, h, device=DEV), torch.ones(n, o, device=DEV)
+    out, used = ops.head_fwd(A, W, b, drop=(p, state))
+    assert used.tolist() == [1234, 0] and state.tolist() == [1234, 1, 0, 0]
+    mask = ops.head_bwd(ones_d, A, ones_w, drop=(p, used))[0] / o               # dA = m * sum_o 1 * 1
+    scale = 1.0 / (1.0 - p)
+    kept = mask != 0
+    assert torch.allclose(mask[kept], torch.full_like(mask[kept], scale), rtol=1e-6)
+    rate = float(kept.double().mean())
+    assert abs(rate - (1 - p)) < 5 * (p * (1 - p) / (n * h)) ** 0.5, rate
+    assert abs(float(kept.double().mean(0).std())) < 3 * (p * (1 - p) / n) ** 0.5          # no column is favoured
+    ref = (A * mask).double() @ W.double().t() + b.double()
+    assert rel_err(out, ref) < 1e-5
+    dO = torch.randn(n, o, device=DEV)
+    dA, dW, db = ops.head_bwd(dO, A, W, drop=(p, used))
+    assert rel_err(dA, (dO.double() @ W.double()) * mask.double()) < 1e-5
+    assert rel_err(dW, dO.double().t() @ (A * mask).double()) < 1e-5
+    assert rel_err(db, dO.double().sum(0)) < 1e-5
+    # the next call draws another mask; the same (seed, counter) the same one
+    out2, used2 = ops.head_fwd(A, W, b, drop=(p, state))
+    assert used2.tolist() == [1234, 1] and not torch.equal(out2, out)
+    again = ops.dropout_state(DEV, seed=1234)
+    assert torch.equal(ops.head_fwd(A, W, b, drop=(p, again))[0], out)
+    # replayed as a CUDA graph: every replay advances the counter on the device
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        ops.head_fwd(A, W, b, drop=(p, state))
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        got, _ = ops.head_fwd(A, W, b, drop=(p, state))
+    before = int(state[1])
+    g.replay(); first = got.clone()
+    g.replay(); second = got.clone()
+    assert int(state[1]) == before + 2 and not torch.equal(first, second)
+
+
+def test_sequential_fuses_train_mode_dropout_into_the_head():
+    """Dropout -> Linear at the end of the GCN factories: in train mode the head's kernels apply the dropout (no dropout kernel
+    of torch runs), in eval mode and with ``ops.config["fused_dropout"] = False`` nothing changes; the gradients reaching the
+    layers in front are those of the masked head."""
+    n, p, h = 500, 256, 64
+    X = torch.from_numpy(synth.genotypes(n, p, seed=2)).to(DEV)
+    ei, ew = random_graph(n, 4000, 3)
+    ei, ew = ei.to(DEV), ew.to(DEV)
+    torch.manual_seed(5)
+    net = nets.create_network_two_no_conv_dropout(p, 1, internal_size=h, dropout=0.5).to(DEV)
+    net.eval()
+    quiet = net(X, ei, ew)
+    net.train()
+    calls = []
+    real = torch.nn.functional.dropout
+    torch.nn.functional.dropout = lambda *a, **k: (calls.append(1), real(*a, **k))[1]
+    try:
+        noisy = net(X, ei, ew)
+        assert not calls and not torch.equal(noisy, quiet)
+        assert net.nns[-1]._drop_state is not None and int(net.nns[-1]._drop_state[1]) == 1
+        noisy.sum().backward()
+        assert all(q.grad is not None and bool(torch.isfinite(q.grad).all()) for q in net.parameters())
+        # E[dropout(x)] = x: the mean over many masks approaches the eval output
+        with torch.no_grad():
+            mean = torch.stack([net(X, ei, ew) for _ in range(200)]).mean(0)
+        assert rel_err(mean, quiet) < 0.1
+        ops.config["fused_dropout"] = False
+        net(X, ei, ew)
+        assert calls
+    finally:
+        torch.nn.functional.dropout = real
+        ops.config["fused_dropout"] = True
+    net.eval()
+    assert torch.equal(net(X, ei, ew), quiet)
+
+
 @pytest.mark.parametrize("factory", ["create_network_two_no_conv_dropout", "create_network_test", "create_network_two_relu"])
 def test_flat_gradients_written_in_place_by_every_layer(factory):
     """parallel.FlatGrads(model=...): the inner GCNConv layers and the dense head write dW / db into their slices of the flat
