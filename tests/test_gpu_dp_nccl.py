@@ -48,7 +48,7 @@ def _worker(rank, world, port, out):
     ref = nets.create_network_two_no_conv_dropout(p, 1, internal_size=h, dropout=0.0).to(dev)
     parallel.broadcast_parameters(model)
     ref.load_state_dict(model.state_dict())
-    flat = parallel.FlatGrads(model.parameters(), sink_layer=parallel.first_genotype_layer(model), world=world, averaging="nccl")
+    flat = parallel.FlatGrads(model.parameters(), sink_layer=parallel.first_genotype_layer(model), world=world, averaging="nccl", model=model)
     flat.range_markers, flat.cut = 512, "every_wave"                  # four ranges at p = 2048: staged, overlapped reduces
     opt = torch.optim.Adam(model.parameters(), lr=1e-2)
     opt_ref = torch.optim.Adam(ref.parameters(), lr=1e-2)
@@ -71,7 +71,7 @@ def _worker(rank, world, port, out):
     for mode in ("nvls", "p2p"):
         torch.manual_seed(1)
         m2 = nets.create_network_two_no_conv_dropout(p, 1, internal_size=h, dropout=0.0).to(dev)
-        f2 = parallel.FlatGrads(m2.parameters(), sink_layer=parallel.first_genotype_layer(m2), world=world, averaging=mode)
+        f2 = parallel.FlatGrads(m2.parameters(), sink_layer=parallel.first_genotype_layer(m2), world=world, averaging=mode, model=m2)
         assert f2.nvls is not None and f2.averaging == mode, f2.nvls_error
         for trial in range(3):
             vals = torch.randn(f2.flat.numel(), device=dev, generator=torch.Generator(device=dev).manual_seed(10 * trial + rank))
