@@ -236,3 +236,64 @@ def test_pack_2bit_host_layout():
             assert not (P[:, p // 4] >> (2 * (p % 4))).any()       # padding codes inside the last byte are zero
     with pytest.raises(ValueError):
         ops.pack_2bit_host(np.array([[0, 4]], dtype=np.int8))
+
+
+def test_flat_grads_marks_the_layers_that_write_in_place():
+    """parallel.FlatGrads(model=...): the sink layer's parameters come first, then those of the other GCNConv layers and of
+    a dense head our kernels take, then what autograd still accumulates into (here: nothing, or a wide Linear)."""
+    from gnn_b200 import parallel
+    from gnn_b200.networks.gcn_conv import GCNConv
+    net = nets.create_network_two_no_conv_dropout(300, 1, internal_size=20, dropout=0.5)
+    first = parallel.first_genotype_layer(net)
+    flat = parallel.FlatGrads(net.parameters(), sink_layer=first, model=net)
+    assert first.grad_sink is flat and not first.grad_inplace
+    assert flat.inplace_layers == [net.nns[1], net.nns[3]] and all(m.grad_inplace for m in flat.inplace_layers)
+    assert flat.params[0] is first.lin.weight and flat.params[1] is first.bias and flat.tail.numel() == 0
+    assert sum(p.numel() for p in flat.params) == flat.flat.numel() == sum(p.numel() for p in net.parameters())
+    for p in net.parameters():                                     # every gradient is a view into the flat buffer
+        assert flat.flat.data_ptr() <= p.grad.data_ptr() < flat.flat.data_ptr() + 4 * flat.flat.numel()
+    for m in flat.inplace_layers:
+        m._grad_written = True
+    flat.zero()
+    assert not any(m._grad_written for m in flat.inplace_layers)
+    # a wide first Linear (create_network_test) stays with autograd: its gradients form the zeroed tail
+    net = nets.create_network_test(300, 1, internal_size=20)
+    flat = parallel.FlatGrads(net.parameters(), sink_layer=parallel.first_genotype_layer(net), model=net)
+    assert not flat.has_sink and not net.nns[0].grad_inplace
+    assert [type(m) for m in flat.inplace_layers] == [GCNConv, GCNConv, type(net.nns[-1])]
+    assert flat.tail.numel() == net.nns[0].weight.numel() + net.nns[0].bias.numel()
+    flat.tail.fill_(3.0)
+    flat.zero()
+    assert float(flat.tail.abs().max()) == 0.0
+    # without `model` nothing is marked and everything is zeroed
+    net = nets.create_network_two_no_conv_dropout(300, 1, internal_size=20)
+    flat = parallel.FlatGrads(net.parameters())
+    assert flat.inplace_layers == [] and flat.tail.numel() == flat.flat.numel()
+
+
+def test_dropout_in_front_of_the_head_stays_with_torch_on_the_host():
+    """The fused Dropout -> head path needs CUDA float32 activations; CPU tensors (and eval mode) go through torch's modules
+    unchanged, and a head marked for in-place gradients clears its slices itself on that path."""
+    from gnn_b200 import parallel
+    from gnn_b200.networks.head import Linear
+    torch.manual_seed(0)
+    net = Sequential("x", [(Linear(12, 6), "x -> x"), torch.nn.Dropout(0.5), Linear(6, 1)])
+    x = torch.randn(40, 12)
+    assert not net._dropout_feeds_head(1, [x])
+    net.eval()
+    quiet = net(x)
+    assert torch.equal(quiet, net.nns[2](net.nns[0](x)))
+    net.train()
+    assert not torch.equal(net(x), quiet)                           # torch's dropout ran
+    flat = parallel.FlatGrads(net.parameters(), model=net)
+    assert flat.inplace_layers == [net.nns[2]]                       # 6 -> 1 is a head our kernels take; 12 -> 6 is not
+    flat.flat.fill_(5.0)
+    flat.zero()
+    net.eval()
+    net(x).sum().backward()
+    ref = Sequential("x", [(Linear(12, 6), "x -> x"), torch.nn.Dropout(0.5), Linear(6, 1)])
+    ref.load_state_dict(net.state_dict())
+    ref.eval()
+    ref(x).sum().backward()
+    for a, b in zip(net.parameters(), ref.parameters()):
+        assert torch.allclose(a.grad, b.grad)
