@@ -196,6 +196,69 @@ __global__ void quantize_rows_kernel(const float* __restrict__ W, int64_t ldw, i
     }
 }
 
+// The same result as row_absmax_kernel + quantize_rows_kernel in ONE launch, for rows that fit shared memory (4 * cols bytes;
+// 200 KB at p = 50 000): a CTA = one feature slot, the row goes through shared memory once (largest magnitude on the way in,
+// digits on the way out).  Between the optimiser step and the next projection these launches sit on the critical path of a
+// training step; this takes two kernels and a memset (~22 us) to one (~8 us).  Bit-identical digits and scales.
+template <int SHIFT>
+__global__ void __launch_bounds__(1024, 1)
+quantize_rows_fused_kernel(const float* __restrict__ W, int64_t ldw, int h, int64_t cols, int8_t* __restrict__ limbs, int64_t ldl,
+                           float* __restrict__ scale) {
+    extern __shared__ __align__(16) float q_row[];                 // [ldl] (ldl = cols rounded up to 16), zero beyond cols
+    __shared__ unsigned red[32];
+    const int f = blockIdx.x;
+    const int64_t groups = ldl / 16;
+    if (f >= h) {                                                  // padding slot of the MMA N dimension: zero digits
+        const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+        for (int64_t g = threadIdx.x; g < groups; g += blockDim.x) {
+            if (f < HP) {
+                *reinterpret_cast<uint4*>(limbs + (int64_t)f * ldl + g * 16) = z;
+                *reinterpret_cast<uint4*>(limbs + (int64_t)(HP + f) * ldl + g * 16) = z;
+            }
+            *reinterpret_cast<uint4*>(limbs + (int64_t)(D2_ROW + f) * ldl + g * 16) = z;
+        }
+        return;
+    }
+    const float* row = W + (int64_t)f * ldw;
+    unsigned m = 0;
+    if ((reinterpret_cast<uintptr_t>(row) & 15) == 0) {
+        const int64_t n4 = cols / 4;
+        for (int64_t i = threadIdx.x; i < n4; i += blockDim.x) {
+            const float4 v = reinterpret_cast<const float4*>(row)[i];
+            reinterpret_cast<float4*>(q_row)[i] = v;
+            m = max(max(m, __float_as_uint(v.x) & 0x7FFFFFFFu), max(max(__float_as_uint(v.y) & 0x7FFFFFFFu, __float_as_uint(v.z) & 0x7FFFFFFFu),
+                                                                    __float_as_uint(v.w) & 0x7FFFFFFFu));
+        }
+        for (int64_t c = 4 * n4 + threadIdx.x; c < cols; c += blockDim.x) { q_row[c] = row[c]; m = max(m, __float_as_uint(row[c]) & 0x7FFFFFFFu); }
+    } else {
+        for (int64_t c = threadIdx.x; c < cols; c += blockDim.x) { const float v = row[c]; q_row[c] = v; m = max(m, __float_as_uint(v) & 0x7FFFFFFFu); }
+    }
+    for (int64_t c = cols + threadIdx.x; c < ldl; c += blockDim.x) q_row[c] = 0.f;
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+    __syncthreads();
+    m = red[0];
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) m = max(m, red[w]);
+    float inv, sc;
+    feature_scale(m, SHIFT == 8 ? QMAX24 : QMAX21, inv, sc);
+    if (threadIdx.x == 0) scale[f] = sc;
+    // a thread takes four consecutive columns at a time: conflict-free 128-bit reads of the row, and a warp's three 32-bit
+    // stores cover 128 consecutive bytes of each digit row
+    for (int64_t g = threadIdx.x; g < ldl / 4; g += blockDim.x) {
+        const float4 v = reinterpret_cast<const float4*>(q_row)[g];
+        __align__(4) int8_t d[3][4];
+        digits3<SHIFT>(v.x, inv, d[0][0], d[1][0], d[2][0]);
+        digits3<SHIFT>(v.y, inv, d[0][1], d[1][1], d[2][1]);
+        digits3<SHIFT>(v.z, inv, d[0][2], d[1][2], d[2][2]);
+        digits3<SHIFT>(v.w, inv, d[0][3], d[1][3], d[2][3]);
+        if (f < HP) {
+            *reinterpret_cast<uint32_t*>(limbs + (int64_t)f * ldl + g * 4) = *reinterpret_cast<const uint32_t*>(d[0]);
+            *reinterpret_cast<uint32_t*>(limbs + (int64_t)(HP + f) * ldl + g * 4) = *reinterpret_cast<const uint32_t*>(d[1]);
+        }
+        *reinterpret_cast<uint32_t*>(limbs + (int64_t)(D2_ROW + f) * ldl + g * 4) = *reinterpret_cast<const uint32_t*>(d[2]);
+    }
+}
+
 // limbs[(digit rows), r] of dH[r, f]: transposed through shared memory.  CTA = 128 rows x a quarter of the 128 limb-row
 // triples; a thread packs 4 consecutive rows of one triple into 32-bit stores (a warp writes 128 consecutive bytes).
 template <int SHIFT>
@@ -669,6 +732,20 @@ int linear_i8_fwd(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p
     const int64_t ldl = (int64_t)align_up((size_t)p, 16);
     unsigned* amax_bits = reinterpret_cast<unsigned*>(wsb + limb_bytes(p));
     float* scale = reinterpret_cast<float*>(amax_bits + 512);
+    const size_t row_smem = (size_t)ldl * sizeof(float);
+    const char* fused_env = getenv("GNNB_QUANT_FUSED");                                     // "0": the two-kernel path (A/B, parity test)
+    const bool fused_off = fused_env && fused_env[0] == '0';
+    if (row_smem <= 220 * 1024 && !fused_off) {
+        // a weight row fits shared memory: maximum, scale and digits in one launch (see quantize_rows_fused_kernel)
+        if (shift == 8) {
+            GNNB_SET_DYN_SMEM(quantize_rows_fused_kernel<8>, row_smem);
+            quantize_rows_fused_kernel<8><<<F_ROWS, 1024, row_smem, stream>>>(W, ldw, (int)h, p, limbs, ldl, scale);
+        } else {
+            GNNB_SET_DYN_SMEM(quantize_rows_fused_kernel<7>, row_smem);
+            quantize_rows_fused_kernel<7><<<F_ROWS, 1024, row_smem, stream>>>(W, ldw, (int)h, p, limbs, ldl, scale);
+        }
+        GNNB_LAUNCH_CHECK();
+    } else {
     GNNB_CUDA(cudaMemsetAsync(amax_bits, 0, 512 * sizeof(unsigned), stream));
     row_absmax_kernel<<<dim3((unsigned)h, 16), 256, 0, stream>>>(W, ldw, p, amax_bits);
     GNNB_LAUNCH_CHECK();
@@ -678,6 +755,7 @@ int linear_i8_fwd(const void* X, int x_format, int64_t ldx, int64_t n, int64_t p
         if (shift == 8) quantize_rows_kernel<8><<<grid, 256, 0, stream>>>(W, ldw, (int)h, p, amax_bits, limbs, ldl, scale);
         else            quantize_rows_kernel<7><<<grid, 256, 0, stream>>>(W, ldw, (int)h, p, amax_bits, limbs, ldl, scale);
         GNNB_LAUNCH_CHECK();
+    }
     }
     CUtensorMap mx, mb0, mb1;
     int rc = x_format == 2 ? make_tensor_map_2d(&mx, X, 1, (uint64_t)((p + 3) / 4), (uint64_t)n, (uint64_t)ldx, BKB / 4, BM, /*swizzle*/ false)

@@ -351,6 +351,35 @@ def test_gradient_sink_writes_the_first_layer_gradients_in_place(packed):
     assert rel_err(layer.lin.weight.grad, plain.nns[0].lin.weight.grad) < 1e-5
 
 
+@pytest.mark.parametrize("p,h", [(50000, 100), (4096, 104), (1000, 7), (131, 33)])
+def test_one_launch_weight_quantiser_is_bit_identical(p, h):
+    """quantize_rows_fused_kernel (maximum, scale and digits of a weight row in one pass through shared memory) against the
+    two-kernel path it replaces (GNNB_QUANT_FUSED=0): the projection's output is the same bits, also with an outlier column,
+    an all-zero feature and a NaN."""
+    import os
+    n = 300
+    wide = torch.zeros((n, (p + 15) // 16 * 16), dtype=torch.int8, device=DEV)
+    wide[:, :p] = torch.from_numpy(synth.genotypes(n, p, seed=p)).to(DEV)
+    X = wide[:, :p]                                           # rows start on 16-byte boundaries whatever p is
+    torch.manual_seed(p + h)
+    W = torch.randn(h, p, device=DEV) * 0.02
+    W[0, p // 2] = 40.0                                       # outlier: the feature's scale is set by one element
+    W[h - 1] = 0.0                                            # all-zero feature
+    for nan in (False, True):
+        if nan:
+            W[1, 3] = float("nan")
+        got = {}
+        try:
+            for mode in ("1", "0"):
+                os.environ["GNNB_QUANT_FUSED"] = mode
+                got[mode] = ops.linear_fwd(X, W, precision=4)
+        finally:
+            os.environ.pop("GNNB_QUANT_FUSED", None)
+        assert torch.equal(got["1"].isnan(), got["0"].isnan()) and bool(got["1"][:, 1].isnan().all()) == nan
+        assert torch.equal(torch.nan_to_num(got["1"]), torch.nan_to_num(got["0"]))
+    assert rel_err(torch.nan_to_num(got["1"][:, 2:]), (X.double() @ W.double().t())[:, 2:]) < 1e-5
+
+
 @pytest.mark.parametrize("n,h,o,p", [(15625, 100, 1, 0.4012), (300, 128, 3, 0.5), (1000, 260, 2, 0.1)])
 def test_head_with_fused_dropout(n, h, o, p):
     """gnnb_head_dropout_fwd / _bwd: the mask is never stored, so recover it from dA (W = 1, dOut = 1 gives dA = m) and check
