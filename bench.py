@@ -630,6 +630,8 @@ def run_ours(a):
                                    f"takes {steps_per_epoch} optimiser steps here and {B} at dp1 / in the reference's train_batches"),
                    "linear_precision": ops.config["linear_precision"], "cuda_graphs": bool(graphs_ok), "dp_cut": a.dp_cut, "overlap_eval": overlap,
                    "optimizer": "gnn_b200.optim.Adam (csrc/adam.cu)" if a.optimizer == "own" else "torch.optim.Adam(fused=True, capturable=True)",
+                   "gradients": f"written in place into one flat buffer by {1 + len(flat.inplace_layers)} of the model's layers (FlatGrads(model=))",
+                   "dropout": "applied inside the head kernels (csrc/head.cu)" if ops.config["fused_dropout"] else "torch.nn.Dropout",
                    "gradient_averaging": (f"own {flat.averaging} kernel over a symmetric flat buffer (csrc/comm.cu)" if flat.nvls is not None else
                                           "NCCL all-reduce" + (f" (NVLS path unavailable: {flat.nvls_error})" if flat.nvls_error else "")) if world > 1 else "single GPU",
                    "cuda_graph_errors": graph_errors,
